@@ -1,0 +1,72 @@
+"""ctypes binding of libdpvo_b200.so (the C ABI declared in include/dpvo_b200.h).
+
+The product path has no CPU or eager fallback: if the shared library is missing
+the import fails loudly with the build instruction.
+"""
+import ctypes
+import os
+
+import torch
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "libdpvo_b200.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build the sm_100a extension first "
+        "(python -c 'import __graft_entry__ as g; g.build()' or "
+        "python deep-visual-odometry-slam_b200/build.py)")
+
+lib = ctypes.CDLL(LIB_PATH)
+lib.dpvo_last_error.restype = ctypes.c_char_p
+lib.dpvo_abi_version.restype = ctypes.c_int
+
+ABI_VERSION = 1
+if lib.dpvo_abi_version() != ABI_VERSION:
+    raise ImportError(f"libdpvo_b200.so ABI {lib.dpvo_abi_version()} != expected {ABI_VERSION}: rebuild")
+
+F16, F32, F64 = 0, 1, 2
+_DT = {torch.float16: F16, torch.float32: F32, torch.float64: F64}
+
+c_i32 = ctypes.c_int32
+c_i64 = ctypes.c_int64
+c_f32 = ctypes.c_float
+c_p = ctypes.c_void_p
+
+
+class CorrLevel(ctypes.Structure):
+    """Mirror of dpvo_corr_level."""
+    _fields_ = [("fmap", c_p),
+                ("sb", c_i64), ("sn", c_i64), ("sc", c_i64), ("sy", c_i64), ("sx", c_i64),
+                ("N2", c_i32), ("H2", c_i32), ("W2", c_i32),
+                ("coord_scale", c_f32),
+                ("out", c_p),
+                ("out_edge_stride", c_i64), ("out_elem_stride", c_i64)]
+
+
+def dtype_code(t):
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise RuntimeError(f"dpvo_b200: unsupported dtype {t.dtype} (expected float16/float32/float64)")
+
+
+def ptr(t):
+    return c_p(t.data_ptr()) if t is not None else c_p(0)
+
+
+def stream_of(t):
+    """Current torch stream of the tensor's device (the reference uses the legacy default stream)."""
+    return c_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def check(status, what):
+    if status != 0:
+        msg = lib.dpvo_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"{what}: {msg}")
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if not t.is_cuda:
+            raise RuntimeError("dpvo_b200: expected CUDA tensors (no CPU path is provided for this operator)")

@@ -1,0 +1,252 @@
+"""`cuda_corr` — host side of the correlation / patchify operators.
+
+Same function names, argument order and return conventions as the reference's
+pybind module (/root/reference/methods/dpvo/dpvo/altcorr/correlation.cpp:28-63):
+
+    forward(fmap1, fmap2, coords, ii, jj, radius)            -> [corr]
+    backward(fmap1, fmap2, coords, ii, jj, corr_grad, radius) -> [fmap1_grad, fmap2_grad]
+    patchify_forward(net, coords, radius)                    -> [patches]
+    patchify_backward(net, coords, gradient, radius)         -> [net_grad]
+
+plus the fused two-level lookup `pyramid_forward` used by the B200-native update
+loop (one launch for DPVO.corr, dpvo.py:200-207).
+
+Everything here is plumbing: shape/dtype validation, output allocation through
+torch's caching allocator and one ctypes call into libdpvo_b200.so on torch's
+current stream.
+"""
+import ctypes
+import weakref
+
+import torch
+
+from . import _lib
+from ._lib import lib, CorrLevel, ptr, stream_of, check, dtype_code, require_cuda, c_i32, c_i64, c_p
+
+# ------------------------------------------------------------------ layout cache
+# The reference DPVO keeps its feature ring NCHW (dpvo.py:72-73).  The sm_100a
+# gather wants channels-last.  A caller that allocates the ring channels-last
+# (e.g. torch.zeros(1,N,H,W,C).permute(0,1,4,2,3)) is used zero-copy; for an
+# NCHW ring a channels-last shadow is kept per tensor object and refreshed when
+# the tensor's version counter moves.
+_shadow = {}  # id(tensor) -> (weakref, version, data_ptr, shadow)
+_SHADOW_MAX = 8
+shadow_refreshes = 0  # instrumentation for tests / bench
+
+
+def _drop_shadow(key):
+    _shadow.pop(key, None)
+
+
+def _channels_last_view(fmap):
+    """Return a tensor with the same logical [B,N,C,H,W] shape whose channel stride is 1."""
+    global shadow_refreshes
+    if fmap.stride(2) == 1 or fmap.shape[2] == 1:
+        return fmap
+    key = id(fmap)
+    ent = _shadow.get(key)
+    if ent is not None:
+        ref, ver, dptr, shadow = ent
+        if ref() is fmap and dptr == fmap.data_ptr() and shadow.shape == fmap.shape:
+            if ver == fmap._version:
+                return shadow
+        else:
+            ent = None
+    B, N, C, H, W = fmap.shape
+    if ent is None:
+        if len(_shadow) >= _SHADOW_MAX:
+            _shadow.pop(next(iter(_shadow)))
+        store = torch.empty((B, N, H, W, C), dtype=fmap.dtype, device=fmap.device)
+        shadow = store.permute(0, 1, 4, 2, 3)
+        ref = weakref.ref(fmap, lambda _r, k=key: _drop_shadow(k))
+    else:
+        ref, _, _, shadow = ent
+    src = fmap if fmap.is_contiguous() else fmap.contiguous()
+    check(lib.dpvo_nchw_to_nhwc(dtype_code(fmap), ptr(src), ptr(shadow), c_i64(B * N), c_i32(C), c_i64(H * W),
+                                stream_of(fmap)), "nchw_to_nhwc")
+    shadow_refreshes += 1
+    _shadow[key] = (ref, fmap._version, fmap.data_ptr(), shadow)
+    return shadow
+
+
+def _check_corr_args(fmap1, fmap2, coords, ii, jj):
+    require_cuda(fmap1, fmap2, coords, ii, jj)
+    if fmap1.dim() != 5 or fmap2.dim() != 5 or coords.dim() != 5:
+        raise RuntimeError("cuda_corr: fmap1, fmap2 and coords must be 5-D ([B,N,C,H,W] / [B,M,2,H,W])")
+    if fmap1.dtype != fmap2.dtype:
+        raise RuntimeError("cuda_corr: fmap1 and fmap2 must have the same dtype")
+    if coords.dtype != torch.float32:
+        raise RuntimeError("cuda_corr: coords must be float32")
+    if coords.shape[2] != 2:
+        raise RuntimeError("cuda_corr: coords must be [B,M,2,H,W]")
+    if ii.dtype != torch.int64 or jj.dtype != torch.int64 or ii.dim() != 1 or jj.dim() != 1:
+        raise RuntimeError("cuda_corr: ii and jj must be 1-D int64")
+    if ii.numel() != coords.shape[1] or jj.numel() != coords.shape[1]:
+        raise RuntimeError("cuda_corr: ii/jj length must equal coords.shape[1]")
+    if fmap1.shape[0] != coords.shape[0] or fmap2.shape[0] != coords.shape[0]:
+        raise RuntimeError("cuda_corr: batch sizes differ")
+    if fmap1.shape[2] != fmap2.shape[2]:
+        raise RuntimeError("cuda_corr: channel counts differ")
+    if tuple(fmap1.shape[3:]) != tuple(coords.shape[3:]):
+        raise RuntimeError("cuda_corr: fmap1 spatial size must equal the patch size of coords")
+
+
+def _wants_fast(fmap1, radius):
+    return (fmap1.dtype == torch.float16 and fmap1.shape[2] == 128 and tuple(fmap1.shape[3:]) == (3, 3)
+            and radius == 3)
+
+
+def _level(fmap2, scale, out, out_edge_stride, out_elem_stride):
+    lv = CorrLevel()
+    lv.fmap = fmap2.data_ptr()
+    lv.sb, lv.sn, lv.sc, lv.sy, lv.sx = fmap2.stride()
+    lv.N2, lv.H2, lv.W2 = fmap2.shape[1], fmap2.shape[3], fmap2.shape[4]
+    lv.coord_scale = scale
+    lv.out = out
+    lv.out_edge_stride = out_edge_stride
+    lv.out_elem_stride = out_elem_stride
+    return lv
+
+
+def _launch(fmap1, coords, ii, jj, radius, levels):
+    B, M = coords.shape[0], coords.shape[1]
+    arr = (CorrLevel * len(levels))(*levels)
+    g = fmap1.stride()
+    check(lib.dpvo_corr_forward(
+        c_i32(dtype_code(fmap1)), ptr(fmap1), c_i64(g[0]), c_i64(g[1]), c_i64(g[2]), c_i64(g[3]), c_i64(g[4]),
+        c_i32(fmap1.shape[1]), c_i32(fmap1.shape[2]), c_i32(fmap1.shape[3]), c_i32(fmap1.shape[4]),
+        ptr(coords), ptr(ii), ptr(jj), c_i32(B), c_i32(M), c_i32(radius),
+        arr, c_i32(len(levels)), stream_of(fmap1)), "cuda_corr.forward")
+
+
+def forward(fmap1, fmap2, coords, ii, jj, radius):
+    """corr[B,M,7,7,P,P] (x-offset major, as the reference's permuted view) in a list."""
+    _check_corr_args(fmap1, fmap2, coords, ii, jj)
+    radius = int(radius)
+    coords = coords.contiguous()
+    ii = ii.contiguous()
+    jj = jj.contiguous()
+    B, M, _, PH, PW = coords.shape
+    DO = 2 * radius + 1
+    out = torch.empty((B, M, DO, DO, PH, PW), dtype=fmap1.dtype, device=fmap1.device)
+    if B * M == 0:
+        return [out]
+    if _wants_fast(fmap1, radius):
+        fmap2 = _channels_last_view(fmap2)
+        if not _dense_patch_blob(fmap1):
+            fmap1 = fmap1.contiguous()
+    lv = _level(fmap2, 1.0, out.data_ptr(), DO * DO * PH * PW, 1)
+    _launch(fmap1, coords, ii, jj, radius, [lv])
+    return [out]
+
+
+def _dense_patch_blob(fmap1):
+    _, _, C, PH, PW = fmap1.shape
+    s = fmap1.stride()
+    if min(s[2], s[3], s[4]) <= 0:
+        return False
+    span = (C - 1) * s[2] + (PH - 1) * s[3] + (PW - 1) * s[4] + 1
+    return span == C * PH * PW and s[1] % 8 == 0 and s[0] % 8 == 0 and fmap1.data_ptr() % 16 == 0
+
+
+def pyramid_forward(fmap1, pyramid, scales, coords, ii, jj, radius):
+    """Fused multi-level lookup: returns [B, M, 49*P*P*L] with the level index fastest,
+    i.e. torch.stack([corr_l ...], -1).view(B, M, -1) of the per-level results
+    (dpvo.py:203-207, net.py:165-169).  One launch for two levels."""
+    if len(pyramid) != len(scales) or len(pyramid) not in (1, 2):
+        raise RuntimeError("pyramid_forward: 1 or 2 levels supported")
+    for fm in pyramid:
+        _check_corr_args(fmap1, fm, coords, ii, jj)
+    radius = int(radius)
+    coords = coords.contiguous()
+    ii = ii.contiguous()
+    jj = jj.contiguous()
+    B, M, _, PH, PW = coords.shape
+    DO = 2 * radius + 1
+    L = len(pyramid)
+    per = DO * DO * PH * PW
+    out = torch.empty((B, M, per * L), dtype=fmap1.dtype, device=fmap1.device)
+    if B * M == 0:
+        return out
+    if _wants_fast(fmap1, radius):
+        pyramid = [_channels_last_view(fm) for fm in pyramid]
+        if not _dense_patch_blob(fmap1):
+            fmap1 = fmap1.contiguous()
+    esz = out.element_size()
+    levels = [_level(fm, float(sc), out.data_ptr() + l * esz, per * L, L)
+              for l, (fm, sc) in enumerate(zip(pyramid, scales))]
+    _launch(fmap1, coords, ii, jj, radius, levels)
+    return out
+
+
+def patchify_forward(net, coords, radius):
+    require_cuda(net, coords)
+    if net.dim() != 4 or coords.dim() != 3 or coords.shape[2] != 2:
+        raise RuntimeError("cuda_corr.patchify_forward: net must be [B,C,H,W] and coords [B,M,2]")
+    if coords.dtype != torch.float32:
+        raise RuntimeError("cuda_corr.patchify_forward: coords must be float32")
+    if coords.shape[0] != net.shape[0]:
+        raise RuntimeError("cuda_corr.patchify_forward: batch sizes differ")
+    radius = int(radius)
+    coords = coords.contiguous()
+    B, C, H, W = net.shape
+    M = coords.shape[1]
+    D = 2 * radius + 2
+    out = torch.empty((B, M, C, D, D), dtype=net.dtype, device=net.device)
+    s = net.stride()
+    check(lib.dpvo_patchify_forward(
+        c_i32(dtype_code(net)), ptr(net), c_i64(s[0]), c_i64(s[1]), c_i64(s[2]), c_i64(s[3]),
+        c_i32(B), c_i32(C), c_i32(H), c_i32(W), ptr(coords), c_i32(M), c_i32(radius), ptr(out),
+        stream_of(net)), "cuda_corr.patchify_forward")
+    return [out]
+
+
+def patchify_backward(net, coords, gradient, radius):
+    require_cuda(net, coords, gradient)
+    if net.dim() != 4 or coords.dim() != 3 or gradient.dim() != 5:
+        raise RuntimeError("cuda_corr.patchify_backward: bad ranks")
+    radius = int(radius)
+    coords = coords.float().contiguous()
+    gradient = gradient.to(net.dtype).contiguous()
+    B, C, H, W = net.shape
+    M = coords.shape[1]
+    D = 2 * radius + 2
+    if tuple(gradient.shape) != (B, M, C, D, D):
+        raise RuntimeError("cuda_corr.patchify_backward: gradient must be [B,M,C,D,D]")
+    grad = torch.zeros((B, C, H, W), dtype=net.dtype, device=net.device)
+    check(lib.dpvo_patchify_backward(
+        c_i32(dtype_code(net)), ptr(gradient), ptr(coords), c_i32(B), c_i32(M), c_i32(C), c_i32(H), c_i32(W),
+        c_i32(radius), ptr(grad), stream_of(net)), "cuda_corr.patchify_backward")
+    return [grad]
+
+
+def backward(fmap1, fmap2, coords, ii, jj, corr_grad, radius):
+    _check_corr_args(fmap1, fmap2, coords, ii, jj)
+    radius = int(radius)
+    coords = coords.contiguous()
+    ii = ii.contiguous()
+    jj = jj.contiguous()
+    B, M, _, PH, PW = coords.shape
+    DO = 2 * radius + 1
+    if tuple(corr_grad.shape) != (B, M, DO, DO, PH, PW):
+        raise RuntimeError("cuda_corr.backward: corr_grad must be [B,M,2r+1,2r+1,P,P]")
+    corr_grad = corr_grad.to(fmap1.dtype)
+    g1 = torch.zeros(fmap1.shape, dtype=fmap1.dtype, device=fmap1.device)
+    g2 = torch.zeros(fmap2.shape, dtype=fmap2.dtype, device=fmap2.device)
+    if B * M == 0:
+        return [g1, g2]
+    acc1 = acc2 = None
+    if fmap1.dtype == torch.float16:
+        acc1 = torch.zeros(fmap1.shape, dtype=torch.float32, device=fmap1.device)
+        acc2 = torch.zeros(fmap2.shape, dtype=torch.float32, device=fmap2.device)
+    s1, s2, cg = fmap1.stride(), fmap2.stride(), corr_grad.stride()
+    check(lib.dpvo_corr_backward(
+        c_i32(dtype_code(fmap1)),
+        ptr(fmap1), c_i64(s1[0]), c_i64(s1[1]), c_i64(s1[2]), c_i64(s1[3]), c_i64(s1[4]),
+        ptr(fmap2), c_i64(s2[0]), c_i64(s2[1]), c_i64(s2[2]), c_i64(s2[3]), c_i64(s2[4]),
+        c_i32(fmap1.shape[1]), c_i32(fmap2.shape[1]), c_i32(fmap1.shape[2]), c_i32(PH), c_i32(PW),
+        c_i32(fmap2.shape[3]), c_i32(fmap2.shape[4]),
+        ptr(coords), ptr(ii), ptr(jj), c_i32(B), c_i32(M), c_i32(radius),
+        ptr(corr_grad), c_i64(cg[0]), c_i64(cg[1]), c_i64(cg[2]), c_i64(cg[3]), c_i64(cg[4]), c_i64(cg[5]),
+        ptr(g1), ptr(g2), ptr(acc1), ptr(acc2), stream_of(fmap1)), "cuda_corr.backward")
+    return [g1, g2]

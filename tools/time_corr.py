@@ -1,0 +1,99 @@
+"""Kernel-level timing of the fused 2-level correlation lookup (development tool).
+
+    python tools/time_corr.py [--edges 45312] [--iters 20] [--ref]
+
+Prints one JSON line per configuration: CUDA-event time, algorithmic bytes (SURVEY §8d,
+computed exactly from the coords) and achieved GB/s.  --ref also times the reference's
+own extension (oracle/_ref/cuda_corr.so) on the same inputs.
+"""
+import argparse
+import importlib
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def algorithmic_bytes(coords, shapes, scales, R=3, C=128, P=3, esz=2):
+    """gmap patch + union of in-bounds window pixels per level + output + coords + indices."""
+    E = coords.shape[1]
+    D = 2 * R + 2
+    total = E * (C * P * P * esz + len(scales) * (D - 1) ** 2 * P * P * esz + 2 * P * P * 4 + 16)
+    off = np.arange(D) - R
+    for (H, W), s in zip(shapes, scales):
+        c = coords[0] * np.float32(s)
+        fx = np.floor(c[:, 0]).astype(np.int64).reshape(E, -1)
+        fy = np.floor(c[:, 1]).astype(np.int64).reshape(E, -1)
+        xs = fx[:, :, None] + off[None, None]  # [E,9,D]
+        ys = fy[:, :, None] + off[None, None]
+        # union size via a small bitmap per edge (bbox-relative)
+        x0 = xs.min((1, 2)); y0 = ys.min((1, 2))
+        bw = xs.max((1, 2)) - x0 + 1
+        n = 0
+        for e0 in range(0, E, 4096):
+            sl = slice(e0, min(E, e0 + 4096))
+            X = xs[sl][:, :, None, :]  # [e,9,1,D]
+            Y = ys[sl][:, :, :, None]  # [e,9,D,1]
+            ok = (X >= 0) & (X < W) & (Y >= 0) & (Y < H)
+            key = (Y - y0[sl, None, None, None]) * bw[sl, None, None, None] + (X - x0[sl, None, None, None])
+            key = np.where(ok, key, -1).reshape(key.shape[0], -1)
+            key.sort(axis=1)
+            uniq = (key[:, 1:] != key[:, :-1]).sum(1) + 1 - (key[:, 0] == -1)
+            n += int(uniq.sum())
+        total += n * C * esz
+    return total
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--edges", type=int, default=0, help="0 = DPVO steady-state graph (45,312)")
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--ref", action="store_true")
+    a = ap.parse_args()
+    pkg = importlib.import_module("deep-visual-odometry-slam_b200")
+    synth = importlib.import_module("deep-visual-odometry-slam_b200.synth")
+    edges = synth.dpvo_edges(40) if a.edges == 0 else None
+    d = synth.corr_inputs(a.edges, seed=1, edges=edges, oob_frac=0.02)
+    E = len(d["us"])
+    nbytes = algorithmic_bytes(d["coords"], [(120, 160), (30, 40)], [1.0, 0.25])
+    dev = lambda x: torch.from_numpy(x).cuda()
+    g = dev(d["gmap"]); f1n = dev(d["fmap1"]); f2n = dev(d["fmap2"])
+    f1 = f1n.permute(0, 1, 3, 4, 2).contiguous().permute(0, 1, 4, 2, 3)
+    f2 = f2n.permute(0, 1, 3, 4, 2).contiguous().permute(0, 1, 4, 2, 3)
+    c = dev(d["coords"]); us = dev(d["us"]); vs = dev(d["vs"])
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def timeit(fn, iters):
+        for _ in range(3):
+            fn()
+        ts = []
+        for _ in range(iters):
+            flush.zero_()
+            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        return float(np.median(ts)), float(np.min(ts))
+
+    med, mn = timeit(lambda: pkg.altcorr.corr_pyramid(g, (f1, f2), c, us, vs, 3), a.iters)
+    print(json.dumps({"impl": "b200 fused 2-level", "edges": E, "ms_median": med, "ms_min": mn,
+                      "alg_bytes": nbytes, "alg_GBs": nbytes / med / 1e6, "bytes_per_edge": nbytes / E}))
+    if a.ref:
+        from oracle.ref_ext import load_ref
+        ref = load_ref("cuda_corr")
+        if ref is not None:
+            def ref_fn():
+                c1, = ref.forward(g, f1n, c, us, vs, 3)
+                c2, = ref.forward(g, f2n, c / 4, us, vs, 3)
+                return torch.stack([c1, c2], -1).view(1, E, -1)
+            med, mn = timeit(ref_fn, max(3, a.iters // 4))
+            print(json.dumps({"impl": "reference ext (sm_100 rebuild)", "edges": E, "ms_median": med, "ms_min": mn,
+                              "alg_GBs": nbytes / med / 1e6}))
+
+
+if __name__ == "__main__":
+    main()
