@@ -12,3 +12,5 @@ reference Python code.
 from . import _lib          # noqa: F401  (fails loudly if libdpvo_b200.so is missing)
 from . import cuda_corr     # noqa: F401
 from . import altcorr       # noqa: F401
+from . import cuda_ba       # noqa: F401
+from . import fastba        # noqa: F401

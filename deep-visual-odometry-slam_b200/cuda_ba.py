@@ -1,0 +1,120 @@
+"""`cuda_ba` — host side of the bundle-adjustment operators.
+
+Same function names, argument order and conventions as the reference's pybind module
+(/root/reference/methods/dpvo/dpvo/fastba/ba.cpp:32-97,183-189):
+
+    forward(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk,
+            PPF, t0, t1, iterations, eff_impl) -> []      (poses / patches updated in place)
+    neighbors(ii, jj) -> [ix, jx]
+    reproject(poses, patches, intrinsics, ii, jj, kk) -> coords[1,E,2,P,P]
+
+Unlike the reference nothing here synchronises with the host: `neighbors` runs on the
+device, `forward` derives the sorted-unique patch list on the device, and all launches go
+to torch's current stream.
+"""
+import torch
+
+from ._lib import lib, ptr, stream_of, check, require_cuda, c_i32, c_i64
+
+lib.dpvo_ba_workspace_bytes.restype = c_i64
+lib.dpvo_neighbors_workspace_bytes.restype = c_i64
+lib.dpvo_unique_workspace_bytes.restype = c_i64
+
+_ws = {}  # device index -> grow-only uint8 workspace (reused on the same stream order)
+
+
+def _workspace(device, nbytes):
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    t = _ws.get(key)
+    if t is None or t.numel() < nbytes:
+        t = torch.empty(int(nbytes * 1.25) + 1024, dtype=torch.uint8, device=device)
+        _ws[key] = t
+    return t
+
+
+def _f32c(t, name):
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"cuda_ba: {name} must be float32")
+    if not t.is_contiguous():
+        raise RuntimeError(f"cuda_ba: {name} must be contiguous")
+    return t
+
+
+def _i64c(t, name):
+    if t.dtype != torch.int64 or t.dim() != 1:
+        raise RuntimeError(f"cuda_ba: {name} must be 1-D int64")
+    return t.contiguous()
+
+
+def forward(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, PPF, t0, t1, iterations, eff_impl):
+    require_cuda(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk)
+    _f32c(poses, "poses"); _f32c(patches, "patches")
+    intrinsics = _f32c(intrinsics, "intrinsics")
+    target = _f32c(target.contiguous(), "target")
+    weight = _f32c(weight.contiguous(), "weight")
+    lmbda = _f32c(lmbda.reshape(-1), "lmbda")
+    ii = _i64c(ii, "ii"); jj = _i64c(jj, "jj"); kk = _i64c(kk, "kk")
+    E = ii.numel()
+    if jj.numel() != E or kk.numel() != E or target.numel() != 2 * E or weight.numel() != 2 * E:
+        raise RuntimeError("cuda_ba.forward: ii/jj/kk/target/weight lengths differ")
+    P = patches.shape[-1]
+    if patches.shape[-2] != P or patches.shape[-3] != 3:
+        raise RuntimeError("cuda_ba.forward: patches must be [...,3,P,P]")
+    n_frames = poses.numel() // 7
+    n_patches = patches.numel() // (3 * P * P)
+    t0, t1, iterations, PPF = int(t0), int(t1), int(iterations), int(PPF)
+    nbytes = lib.dpvo_ba_workspace_bytes(c_i64(E), c_i64(n_patches), c_i32(max(t1 - t0, 0)), c_i32(bool(eff_impl)),
+                                         c_i32(PPF), c_i64(n_frames))
+    ws = _workspace(poses.device, nbytes)
+    check(lib.dpvo_ba_forward(ptr(poses), ptr(patches), ptr(intrinsics), ptr(target), ptr(weight), ptr(lmbda),
+                              ptr(ii), ptr(jj), ptr(kk), c_i64(E), c_i64(n_frames), c_i64(n_patches), c_i32(P),
+                              c_i32(PPF), c_i32(t0), c_i32(t1), c_i32(iterations), c_i32(bool(eff_impl)),
+                              ptr(ws), c_i64(ws.numel()), stream_of(poses)), "cuda_ba.forward")
+    return []
+
+
+def neighbors(ii, jj):
+    require_cuda(ii, jj)
+    ii = _i64c(ii, "ii"); jj = _i64c(jj, "jj")
+    n = ii.numel()
+    if jj.numel() != n:
+        raise RuntimeError("cuda_ba.neighbors: ii and jj lengths differ")
+    ix = torch.empty(n, dtype=torch.int64, device=ii.device)
+    jx = torch.empty(n, dtype=torch.int64, device=ii.device)
+    if n:
+        ws = _workspace(ii.device, lib.dpvo_neighbors_workspace_bytes(c_i64(n)))
+        check(lib.dpvo_neighbors(ptr(ii), ptr(jj), c_i64(n), ptr(ix), ptr(jx), ptr(ws), c_i64(ws.numel()),
+                                 stream_of(ii)), "cuda_ba.neighbors")
+    return [ix, jx]
+
+
+def reproject(poses, patches, intrinsics, ii, jj, kk):
+    require_cuda(poses, patches, intrinsics, ii, jj, kk)
+    _f32c(poses, "poses"); _f32c(patches, "patches"); _f32c(intrinsics, "intrinsics")
+    ii = _i64c(ii, "ii"); jj = _i64c(jj, "jj"); kk = _i64c(kk, "kk")
+    P = patches.shape[-1]
+    E = ii.numel()
+    coords = torch.empty((1, E, 2, P, P), dtype=torch.float32, device=poses.device)
+    check(lib.dpvo_reproject(ptr(poses), ptr(patches), ptr(intrinsics), ptr(ii), ptr(jj), ptr(kk), c_i64(E),
+                             c_i32(P), ptr(coords), stream_of(poses)), "cuda_ba.reproject")
+    return coords
+
+
+def unique_inverse(keys, key_bound):
+    """Sorted unique + inverse of bounded non-negative int64 keys, no host sync.
+    Returns (uniq[padded to len(keys)], inverse, n_uniq device int32 tensor)."""
+    require_cuda(keys)
+    keys = _i64c(keys, "keys")
+    n = keys.numel()
+    uniq = torch.empty(min(n, int(key_bound)), dtype=torch.int64, device=keys.device)
+    inv = torch.empty(n, dtype=torch.int64, device=keys.device)
+    cnt = torch.zeros(1, dtype=torch.int32, device=keys.device)
+    ws = _workspace(keys.device, lib.dpvo_unique_workspace_bytes(c_i64(int(key_bound))))
+    check(lib.dpvo_unique_inverse(ptr(keys), c_i64(n), c_i64(int(key_bound)), ptr(uniq), ptr(inv), ptr(cnt),
+                                  ptr(ws), c_i64(ws.numel()), stream_of(keys)), "cuda_ba.unique_inverse")
+    return uniq, inv, cnt
+
+
+def solve_system(*args, **kwargs):
+    raise RuntimeError("cuda_ba.solve_system (classic loop-closure PGO, fastba/ba.cpp:120-180) is outside the "
+                       "hot path of this build (SURVEY.md §8f N5)")

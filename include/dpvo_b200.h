@@ -94,6 +94,51 @@ int dpvo_patchify_backward(dpvo_dtype dtype, const void* patch_grad,
 int dpvo_nchw_to_nhwc(dpvo_dtype dtype, const void* src, void* dst,
                       int64_t N, int32_t C, int64_t HW, void* stream);
 
+/* ------------------------------------------------------------------- fastba */
+
+/* Bytes of device workspace dpvo_ba_forward needs for a problem of this size.
+ * n_patches_total = rows of the patch buffer (patches.numel()/(3*P*P)); it bounds kk. */
+int64_t dpvo_ba_workspace_bytes(int64_t n_edges, int64_t n_patches_total, int32_t n_poses_opt,
+                                int32_t eff_impl, int32_t ppf, int64_t n_frames_total);
+
+/* Bundle adjustment — replaces cuda_ba.forward (fastba/ba.cpp:32-45, ba_cuda.cu:433-582,
+ * block_e.cu).  `iterations` Gauss-Newton steps on poses[t0,t1) and the inverse depths of
+ * every patch referenced by kk; poses [n_frames_total,7] and patches [n_patches_total,3,P,P]
+ * are updated IN PLACE.  intrinsics: row 0 is used for every frame (ba_cuda.cu:255-258).
+ * target/weight: [E,2] float32.  lmbda: device pointer to one float.  ii/jj/kk: [E] int64.
+ * eff_impl selects the block-E ("efficient E") Schur path used for global BA; it assumes
+ * kk == ii*ppf + slot like the reference (block_e.cu:57-62).  workspace: >= the size
+ * returned by dpvo_ba_workspace_bytes, 256-byte aligned, contents irrelevant. */
+int dpvo_ba_forward(float* poses, float* patches, const float* intrinsics,
+                    const float* target, const float* weight, const float* lmbda,
+                    const int64_t* ii, const int64_t* jj, const int64_t* kk,
+                    int64_t n_edges, int64_t n_frames_total, int64_t n_patches_total, int32_t P,
+                    int32_t ppf, int32_t t0, int32_t t1, int32_t iterations, int32_t eff_impl,
+                    void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Temporal neighbours — replaces cuda_ba.neighbors (fastba/ba.cpp:59-97), entirely on the
+ * device (the reference round-trips through the host).  For edge e: ix[e] / jx[e] = index of
+ * the previous / next edge with the same ii value when that group is stably sorted by jj;
+ * -1 at the ends.  Bit-exact.  Keys may be any int64 except INT64_MIN-like 0x8080808080808080.
+ * workspace: dpvo_neighbors_workspace_bytes(n) bytes. */
+int64_t dpvo_neighbors_workspace_bytes(int64_t n);
+int dpvo_neighbors(const int64_t* ii, const int64_t* jj, int64_t n,
+                   int64_t* ix, int64_t* jx, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Sorted unique + inverse of a non-negative int64 key array bounded by key_bound
+ * (what torch::_unique(kk, true, true) yields at ba_cuda.cu:447-449): uniq[0..*n_uniq),
+ * inverse[n].  n_uniq is a device int32.  workspace: dpvo_unique_workspace_bytes(key_bound). */
+int64_t dpvo_unique_workspace_bytes(int64_t key_bound);
+int dpvo_unique_inverse(const int64_t* keys, int64_t n, int64_t key_bound,
+                        int64_t* uniq, int64_t* inverse, int32_t* n_uniq,
+                        void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Reprojection of all PxP pixels of patch kk[e] from frame ii[e] into frame jj[e] —
+ * replaces cuda_ba.reproject (ba_cuda.cu:379-429,585-617).  coords: [E,2,P,P] float32. */
+int dpvo_reproject(const float* poses, const float* patches, const float* intrinsics,
+                   const int64_t* ii, const int64_t* jj, const int64_t* kk,
+                   int64_t n_edges, int32_t P, float* coords, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,225 @@
+"""GPU parity tests for fastba (BA, neighbors, reproject, unique/inverse) through the Python
+operator surface -> ctypes -> C ABI -> sm_100a kernels.
+
+Oracles: oracle/fastba_oracle.py (float64 restatement) and, when oracle/_ref/cuda_ba.so is
+present, the reference's own CUDA extension on identical inputs.
+
+Tolerances (north star: BA pose/depth updates within 1e-5 relative in fp32): the updated
+poses and inverse depths must agree with the float64 restatement to 1e-5 norm-wise relative;
+the update vectors themselves (state_after - state_before) to 2e-3, which is what fp32
+normal equations allow — the reference's own fp32 CUDA path is held to the same bar against
+the restatement in test_ba_vs_reference_extension, and ours must be at least as close.
+Integer outputs (neighbors, unique/inverse) are bit-exact.
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_pkg
+from oracle import fastba_oracle as fo
+from oracle.ref_ext import load_ref
+
+pytestmark = pytest.mark.gpu
+
+STATE_TOL = 1e-5
+UPDATE_TOL = 2e-3
+
+
+def _rel(a, b):
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30)
+
+
+def _dev(x):
+    return torch.from_numpy(np.ascontiguousarray(x)).cuda()
+
+
+def _run_ours(pkg, d, t0, t1, iters=2, eff=False):
+    poses = _dev(d["poses"])[None].clone()
+    patches = _dev(d["patches"])[None].clone()
+    lm = torch.tensor([1e-4], device="cuda")
+    pkg.fastba.BA(poses, patches, _dev(d["intrinsics"])[None], _dev(d["target"])[None], _dev(d["weight"])[None], lm,
+                  _dev(d["ii"]), _dev(d["jj"]), _dev(d["kk"]), t0, t1, d["M"], iters, eff)
+    torch.cuda.synchronize()
+    return poses[0].cpu().numpy(), patches[0].cpu().numpy()
+
+
+def _run_oracle(d, t0, t1, iters=2):
+    return fo.ba(d["poses"], d["patches"], d["intrinsics"], d["target"], d["weight"], np.array([1e-4]),
+                 d["ii"], d["jj"], d["kk"], d["M"], t0, t1, iters)
+
+
+def _check_against(d, got, want, tol_state=STATE_TOL, tol_up=UPDATE_TOL):
+    gp, gz = got
+    wp, wz = want
+    p0 = d["poses"].astype(np.float64); z0 = d["patches"].astype(np.float64)
+    assert _rel(gp, wp) < tol_state
+    assert _rel(gz[:, 2], wz[:, 2]) < tol_state
+    assert _rel(gp - p0, wp - p0) < tol_up
+    assert _rel(gz[:, 2] - z0[:, 2], wz[:, 2] - z0[:, 2]) < tol_up
+    # x/y of the patches and frames outside the window are untouched
+    assert np.array_equal(gz[:, :2], d["patches"][:, :2])
+
+
+@pytest.mark.parametrize("n_frames,M", [(14, 96), (9, 32), (30, 24)])
+def test_ba_local_window_vs_oracle(n_frames, M):
+    pkg = load_pkg(); synth = load_pkg("synth")
+    d = synth.ba_inputs(n_frames, seed=n_frames, M=M)
+    t0, t1 = max(n_frames - 10, 1), n_frames
+    got = _run_ours(pkg, d, t0, t1)
+    want = _run_oracle(d, t0, t1)
+    _check_against(d, got, want)
+    assert np.array_equal(got[0][:t0], d["poses"][:t0]) and np.array_equal(got[0][t1:], d["poses"][t1:])
+
+
+def test_ba_wide_window_and_structure_only():
+    pkg = load_pkg(); synth = load_pkg("synth")
+    d = synth.ba_inputs(40, seed=7, M=16)
+    # 39 free poses: 234x234 system (Cholesky spills out of shared memory)
+    got = _run_ours(pkg, d, 1, 40)
+    want = _run_oracle(d, 1, 40)
+    _check_against(d, got, want)
+    # t1 == t0: structure-only branch (ba_cuda.cu:521-532): poses fixed, depths move
+    got = _run_ours(pkg, d, 5, 5)
+    want = _run_oracle(d, 5, 5)
+    assert np.array_equal(got[0], d["poses"])
+    assert _rel(got[1][:, 2], want[1][:, 2]) < STATE_TOL
+
+
+def test_ba_masked_and_degenerate_edges():
+    """Edges behind the camera / far out of bounds / zero weight contribute nothing; duplicate
+    (loop-closure style) edges and self edges are handled."""
+    pkg = load_pkg(); synth = load_pkg("synth")
+    d = synth.ba_inputs(14, seed=3, M=24)
+    rng = np.random.default_rng(0)
+    E = len(d["kk"])
+    d["target"][rng.choice(E, 200, replace=False)] += 1000.0   # residual > 128 -> masked
+    d["weight"][rng.choice(E, 200, replace=False)] = 0.0
+    dup = rng.choice(E, 300, replace=False)                      # duplicated edges
+    for k in ("ii", "jj", "kk"):
+        d[k] = np.concatenate([d[k], d[k][dup]])
+    d["target"] = np.concatenate([d["target"], d["target"][dup] + 0.3])
+    d["weight"] = np.concatenate([d["weight"], d["weight"][dup]])
+    got = _run_ours(pkg, d, 4, 14)
+    want = _run_oracle(d, 4, 14)
+    _check_against(d, got, want)
+
+
+def test_ba_vs_reference_extension():
+    ref = load_ref("cuda_ba")
+    if ref is None:
+        pytest.skip("oracle/_ref/cuda_ba.so not built")
+    pkg = load_pkg(); synth = load_pkg("synth")
+    d = synth.ba_inputs(14, seed=1)
+    t0, t1 = 4, 14
+    poses = _dev(d["poses"])[None].clone(); patches = _dev(d["patches"])[None].clone()
+    lm = torch.tensor([1e-4], device="cuda")
+    ref.forward(poses, patches, _dev(d["intrinsics"])[None], _dev(d["target"])[None], _dev(d["weight"])[None], lm,
+                _dev(d["ii"]), _dev(d["jj"]), _dev(d["kk"]), d["M"], t0, t1, 2, False)
+    torch.cuda.synchronize()
+    refp, refz = poses[0].cpu().numpy(), patches[0].cpu().numpy()
+    want = _run_oracle(d, t0, t1)
+    got = _run_ours(pkg, d, t0, t1)
+    # the restatement is pinned by the reference's own kernels ...
+    _check_against(d, (refp, refz), want)
+    # ... ours agrees with the reference's output directly ...
+    _check_against(d, got, (refp.astype(np.float64), refz.astype(np.float64)))
+    # ... and is at least as close to the float64 restatement as the reference is (x2 slack)
+    p0 = d["poses"].astype(np.float64)
+    err_ours = _rel(got[0] - p0, want[0] - p0)
+    err_ref = _rel(refp - p0, want[0] - p0)
+    assert err_ours <= max(2 * err_ref, 1e-5)
+
+
+def _random_edges(rng, n, nk, nj, dup=True):
+    kk = rng.integers(0, nk, n).astype(np.int64)
+    jj = rng.integers(0, nj, n).astype(np.int64)
+    if dup and n > 10:
+        kk[n // 2:n // 2 + 5] = kk[:5]; jj[n // 2:n // 2 + 5] = jj[:5]   # exact duplicate (kk,jj) pairs
+    return kk, jj
+
+
+@pytest.mark.parametrize("n", [0, 1, 7, 1000, 45312])
+def test_neighbors_bit_exact(n):
+    pkg = load_pkg(); synth = load_pkg("synth")
+    rng = np.random.default_rng(n)
+    if n == 45312:
+        _, jj, kk = synth.dpvo_edges(40)
+    else:
+        kk, jj = _random_edges(rng, n, max(n // 9, 1), 30)
+    if n == 0:
+        kk = np.zeros(0, np.int64); jj = np.zeros(0, np.int64)
+    ix, jx = pkg.fastba.neighbors(_dev(kk), _dev(jj))
+    wix, wjx = fo.neighbors(kk, jj)
+    assert ix.dtype == torch.int64 and ix.is_cuda
+    assert np.array_equal(ix.cpu().numpy(), wix) and np.array_equal(jx.cpu().numpy(), wjx)
+    ref = load_ref("cuda_ba")
+    if ref is not None and n > 0:
+        rix, rjx = ref.neighbors(_dev(kk), _dev(jj))
+        assert torch.equal(rix, ix) and torch.equal(rjx, jx)
+
+
+def test_neighbors_large_keys_and_properties():
+    """Keys far apart (no bound on the key range), then a chain property: jx[ix[e]] == e."""
+    pkg = load_pkg()
+    rng = np.random.default_rng(4)
+    kk = (rng.integers(0, 50, 5000) * 10_000_000_019 + 123).astype(np.int64)
+    jj = rng.integers(0, 40, 5000).astype(np.int64)
+    ix, jx = pkg.fastba.neighbors(_dev(kk), _dev(jj))
+    wix, wjx = fo.neighbors(kk, jj)
+    assert np.array_equal(ix.cpu().numpy(), wix) and np.array_equal(jx.cpu().numpy(), wjx)
+    has_prev = ix >= 0
+    assert torch.equal(jx[ix[has_prev]], torch.nonzero(has_prev).flatten())
+
+
+def test_unique_inverse_bit_exact():
+    pkg = load_pkg(); synth = load_pkg("synth")
+    _, _, kk = synth.dpvo_edges(40)
+    bound = 4096 * 96
+    uniq, inv, cnt = pkg.cuda_ba.unique_inverse(_dev(kk), bound)
+    wu, wi = fo.unique_inverse(kk)
+    m = int(cnt.item())
+    assert m == len(wu)
+    assert np.array_equal(uniq[:m].cpu().numpy(), wu) and np.array_equal(inv.cpu().numpy(), wi)
+    tu, ti = torch.unique(_dev(kk), sorted=True, return_inverse=True)
+    assert torch.equal(tu, uniq[:m]) and torch.equal(ti, inv)
+
+
+def test_reproject_vs_oracle_and_reference():
+    pkg = load_pkg(); synth = load_pkg("synth")
+    d = synth.ba_inputs(14, seed=5, M=48)
+    args = (_dev(d["poses"])[None], _dev(d["patches"])[None], _dev(d["intrinsics"])[None],
+            _dev(d["ii"]), _dev(d["jj"]), _dev(d["kk"]))
+    got = pkg.fastba.reproject(*args)
+    want = fo.reproject(d["poses"], d["patches"], d["intrinsics"], d["ii"], d["jj"], d["kk"])
+    assert got.shape == want.shape
+    assert _rel(got.cpu().numpy(), want) < 1e-5
+    ref = load_ref("cuda_ba")
+    if ref is not None:
+        w2 = ref.reproject(*args)
+        assert _rel(got.cpu().numpy(), w2.cpu().numpy()) < 1e-6
+
+
+def test_ba_full_size_properties():
+    """Steady-state DPVO graph (45,312 edges, 10-pose window): BA must lower the weighted
+    reprojection cost, leave fixed poses bit-identical, and be invariant to edge order."""
+    pkg = load_pkg(); synth = load_pkg("synth")
+    d = synth.ba_inputs(40, seed=2)
+    assert len(d["kk"]) == 45312
+    t0, t1 = 30, 40
+    got = _run_ours(pkg, d, t0, t1)
+
+    def cost(po, pa):
+        r, w, *_ = fo.edge_terms(po.astype(np.float64), pa.astype(np.float64), d["intrinsics"].astype(np.float64),
+                                 d["target"].astype(np.float64), d["weight"].astype(np.float64), d["ii"], d["jj"], d["kk"])
+        return float((w * r * r).sum())
+    assert cost(*got) < 0.5 * cost(d["poses"], d["patches"])
+    assert np.array_equal(got[0][:t0], d["poses"][:t0])
+    perm = np.random.default_rng(0).permutation(len(d["kk"]))
+    d2 = dict(d)
+    for k in ("ii", "jj", "kk", "target", "weight"):
+        d2[k] = d[k][perm]
+    got2 = _run_ours(pkg, d2, t0, t1)
+    assert _rel(got2[0], got[0]) < 1e-5 and _rel(got2[1], got[1]) < 1e-5
+    want = _run_oracle(d, t0, t1)
+    _check_against(d, got, want)

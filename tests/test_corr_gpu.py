@@ -203,7 +203,7 @@ def test_patchify_backward():
 
 def test_full_size_properties():
     """BASELINE.json full size (45,312 edges, 36-frame rings): size-independent properties.
-    (1) linearity in the patch features: corr(2*g) == 2*corr(g) exactly in fp16 (power of two);
+    (1) linearity in the patch features: corr(2*g) == 2*corr(g) in fp16 (power of two scaling);
     (2) an edge's result does not depend on its position in the edge list (permutation);
     (3) spot-check 128 random edges against the oracle."""
     pkg = load_pkg()
@@ -217,7 +217,8 @@ def test_full_size_properties():
     out = pkg.altcorr.corr_pyramid(g, (f1, f2), c, us, vs, 3)
     out2 = pkg.altcorr.corr_pyramid(g * 2, (f1, f2), c, us, vs, 3)
     fin = torch.isfinite(out2)
-    assert torch.equal((out * 2)[fin], out2[fin])
+    # exact up to fp16 subnormal rounding (spacing 2^-24) of tiny blend products
+    assert ((out.float() * 2)[fin] - out2.float()[fin]).abs().max().item() <= 1e-6
     perm = torch.randperm(E, device="cuda", generator=torch.Generator("cuda").manual_seed(0))
     outp = pkg.altcorr.corr_pyramid(g, (f1, f2), c[:, perm].contiguous(), us[perm], vs[perm], 3)
     assert torch.equal(outp, out[:, perm])
