@@ -515,6 +515,7 @@ extern "C" int dpvo_ba_forward(float* poses, float* patches, const float* intrin
     }
     ba_backsub_kernel<<<bgrid, 256, (size_t)(n + 1) * sizeof(float), st>>>(p);
   }
+  note_launches(2 + iterations * (N > 0 ? 5 : 3));
   return check_launch("ba_forward");
 }
 
@@ -525,6 +526,7 @@ extern "C" int dpvo_reproject(const float* poses, const float* patches, const fl
   if (n_edges == 0) return 0;
   DPVO_REQUIRE(poses && patches && intrinsics && ii && jj && kk && coords, "reproject: null pointer");
   const int grid = (int)(ceil_div64(n_edges, 256) < kNumSMs * 8 ? ceil_div64(n_edges, 256) : kNumSMs * 8);
+  note_launches(1);
   reproject_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(poses, patches, intrinsics, ii, jj, kk,
                                                                             n_edges, P, coords);
   return check_launch("reproject");

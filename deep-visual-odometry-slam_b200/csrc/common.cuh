@@ -15,6 +15,7 @@ namespace dpvo {
 constexpr int kNumSMs = 148;  // B200
 
 void set_error(const char* fmt, ...);
+void note_launches(int n);  // kernel launches issued by this library (dpvo_launch_count)
 
 inline int check_launch(const char* what) {
   cudaError_t e = cudaGetLastError();

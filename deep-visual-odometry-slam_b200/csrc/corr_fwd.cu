@@ -366,6 +366,7 @@ static int launch_generic(const CorrParams& prm, cudaStream_t st) {
     cudaFuncSetAttribute(corr_fwd_generic_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   int64_t nedge = (int64_t)prm.B * prm.M;
   int grid = (int)(nedge < (int64_t)kNumSMs * 64 ? nedge : (int64_t)kNumSMs * 64);
+  note_launches(1);
   corr_fwd_generic_kernel<T><<<grid, 128, smem, st>>>(prm);
   return check_launch("corr_fwd_generic");
 }
@@ -437,6 +438,7 @@ extern "C" int dpvo_corr_forward(dpvo_dtype dtype,
       corr_fwd_mma_f16_kernel<1, 3, 3><<<grid, kWarps * 32, 0, st>>>(prm);
     else
       corr_fwd_mma_f16_kernel<2, 3, 3><<<grid, kWarps * 32, 0, st>>>(prm);
+    note_launches(1);
     return check_launch("corr_fwd_mma_f16");
   }
   (void)D;

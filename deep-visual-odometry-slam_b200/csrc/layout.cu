@@ -43,6 +43,7 @@ static int launch(const void* src, void* dst, int64_t N, int C, int64_t HW, cuda
   const int64_t blocks = N * tiles_hw * tiles_c;
   if (blocks == 0) return 0;
   if (blocks > 0x7fffffffLL) { set_error("nchw_to_nhwc: too many tiles"); return 1; }
+  note_launches(1);
   nchw_to_nhwc_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(
       reinterpret_cast<const T*>(src), reinterpret_cast<T*>(dst), C, HW, tiles_hw, tiles_c);
   return check_launch("nchw_to_nhwc");

@@ -148,6 +148,7 @@ extern "C" int dpvo_neighbors(const int64_t* ii, const int64_t* jj, int64_t n,
   if (exclusive_scan_int(count, offset, T, sums, nullptr, st)) return 1;
   nb_fill_kernel<<<grid, 256, 0, st>>>(n, slot_of, offset, cursor, list);
   nb_predsucc_kernel<<<grid, 256, 0, st>>>(jj, n, slot_of, offset, count, list, ix, jx);
+  note_launches(6);
   return check_launch("neighbors");
 }
 
@@ -180,5 +181,6 @@ extern "C" int dpvo_unique_inverse(const int64_t* keys, int64_t n, int64_t key_b
   if (exclusive_scan_int(cnt, prefix, W, sums, n_uniq, st)) return 1;
   uq_emit_kernel<<<wgrid, 256, 0, st>>>(bitmap, W, prefix, uniq);
   uq_inverse_kernel<<<grid, 256, 0, st>>>(keys, n, bitmap, prefix, key_bound, inverse);
+  note_launches(7);
   return check_launch("unique_inverse");
 }

@@ -94,6 +94,7 @@ extern "C" int dpvo_patchify_forward(dpvo_dtype dtype, const void* net,
       set_error("patchify_forward: unknown dtype");
       return 1;
   }
+  note_launches(1);
   return check_launch("patchify_fwd");
 }
 
@@ -125,5 +126,6 @@ extern "C" int dpvo_patchify_backward(dpvo_dtype dtype, const void* patch_grad,
       set_error("patchify_backward: unknown dtype");
       return 1;
   }
+  note_launches(1);
   return check_launch("patchify_bwd");
 }

@@ -1,0 +1,151 @@
+"""One frame of DPVO's update hot path, driven through this package's operator surface.
+
+Mirrors what `DPVO.__call__` -> `DPVO.update` does per frame between the network calls
+(/root/reference/methods/dpvo/dpvo/dpvo.py:328-360,435-438, net.py:76,135-145):
+
+    ring write      new frame's fmaps into the feature rings           dpvo.py:437-438
+    patchify        gmap (r=1, C=128) and imap (r=0, C=384) gathers    net.py:135-145
+    reproject       coords of every active edge                        dpvo.py:209-213
+    corr            2-level correlation lookup -> [1,E,882] fp16       dpvo.py:200-207
+    neighbors       temporal neighbours of every edge                  net.py:76
+    BA              2 Gauss-Newton iterations, 10-pose window          dpvo.py:351-354
+
+The Update network and the encoders that sit between these operators are outside this
+build's scope; `target` and `weight` (the network's outputs) are inputs.
+Used by bench.py and the tests; all tensors live on one CUDA device, all launches go to
+torch's current stream, nothing synchronises with the host.
+"""
+import numpy as np
+import torch
+
+from . import altcorr, cuda_corr, fastba, synth, _lib
+
+
+class UpdateHotPath:
+    """Steady-state DPVO window (default config: 96 patches/frame, 45,312 active edges)."""
+
+    def __init__(self, device, n_frames=40, seed=0, opt_window=synth.OPT_WINDOW, M=synth.M_DEFAULT):
+        self.device = torch.device(device)
+        self.n = n_frames
+        self.M = M
+        d = synth.ba_inputs(n_frames, seed=seed, M=M)
+        c = synth.corr_inputs(0, seed=seed + 1, edges=(d["ii"], d["jj"], d["kk"]), M=M, oob_frac=0.0)
+        dev = lambda x: torch.from_numpy(np.ascontiguousarray(x)).to(self.device)
+        self.E = len(d["kk"])
+        self.poses0 = dev(d["poses"])[None]
+        self.patches0 = dev(d["patches"])[None]
+        self.poses = self.poses0.clone()
+        self.patches = self.patches0.clone()
+        self.intrinsics = dev(d["intrinsics"])[None]
+        self.target = dev(d["target"])[None]
+        self.weight = dev(d["weight"])[None]
+        self.ii, self.jj, self.kk = dev(d["ii"]), dev(d["jj"]), dev(d["kk"])
+        self.lmbda = torch.tensor([1e-4], device=self.device)
+        self.t0, self.t1 = max(n_frames - opt_window, 1), n_frames
+        # feature rings, channels-last storage behind the reference's logical [1,mem,C,H,W] shape
+        nhwc = lambda t: t.permute(0, 1, 3, 4, 2).contiguous().permute(0, 1, 4, 2, 3)
+        self.fmap1 = nhwc(dev(c["fmap1"]))
+        self.fmap2 = nhwc(dev(c["fmap2"]))
+        self.gmap = dev(c["gmap"])                        # [1, mem*M, 128, 3, 3]
+        self.mem = self.fmap1.shape[1]
+        self.n_patches = self.gmap.shape[1]
+        # per-frame inputs (what the encoders hand over): NCHW fmaps of the newest frame, an imap,
+        # and the patch centres
+        rng = np.random.default_rng(seed + 2)
+        self.new_f1 = dev(rng.standard_normal((1, synth.C, synth.H1, synth.W1), dtype=np.float32).astype(np.float16))
+        self.new_f2 = dev(rng.standard_normal((1, synth.C, synth.H2, synth.W2), dtype=np.float32).astype(np.float16))
+        self.new_imap = dev(rng.standard_normal((1, 384, synth.H1, synth.W1), dtype=np.float32).astype(np.float16))
+        xy = np.stack([rng.uniform(1, synth.W1 - 2, (1, M)), rng.uniform(1, synth.H1 - 2, (1, M))], -1)
+        self.centres = dev(xy.astype(np.float32))
+        self.host_coords = c["coords"]                    # for the CPU baseline / byte accounting
+        self.host = dict(d=d, c=c)
+        self.stage_events = None
+
+    # ------------------------------------------------------------------ stages
+    def ring_write(self):
+        slot = (self.n - 1) % self.mem
+        for src, ring in ((self.new_f1, self.fmap1), (self.new_f2, self.fmap2)):
+            C, H, W = src.shape[1:]
+            dst = ring[0, slot]                            # logical [C,H,W], memory [H,W,C]
+            _lib.check(_lib.lib.dpvo_nchw_to_nhwc(_lib.c_i32(_lib.dtype_code(src)), _lib.ptr(src),
+                                                  _lib.c_p(dst.data_ptr()), _lib.c_i64(1), _lib.c_i32(C),
+                                                  _lib.c_i64(H * W), _lib.stream_of(src)), "ring_write")
+
+    def patchify(self):
+        g, = cuda_corr.patchify_forward(self.new_f1, self.centres, 1)
+        i, = cuda_corr.patchify_forward(self.new_imap, self.centres, 0)
+        return g, i
+
+    def reproject(self):
+        return fastba.reproject(self.poses, self.patches, self.intrinsics, self.ii, self.jj, self.kk)
+
+    def corr(self, coords):
+        us = self.kk % self.n_patches
+        vs = self.jj % self.mem
+        return altcorr.corr_pyramid(self.gmap, (self.fmap1, self.fmap2), coords, us, vs, 3)
+
+    def neighbors(self):
+        return fastba.neighbors(self.kk, self.jj)
+
+    def ba(self):
+        fastba.BA(self.poses, self.patches, self.intrinsics, self.target, self.weight, self.lmbda,
+                  self.ii, self.jj, self.kk, self.t0, self.t1, self.M, 2, False)
+
+    # ------------------------------------------------------------------ one frame
+    def step(self, events=None):
+        """All hot-path operators of one frame.  `events`: optional dict name -> list of
+        (start, end) CUDA event pairs appended per stage (recorded on the current stream)."""
+        self.poses.copy_(self.poses0)
+        self.patches.copy_(self.patches0)
+
+        def timed(name, fn):
+            if events is None:
+                return fn()
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            r = fn()
+            e1.record()
+            events.setdefault(name, []).append((e0, e1))
+            return r
+
+        timed("ring_write", self.ring_write)
+        timed("patchify", self.patchify)
+        coords = timed("reproject", self.reproject)
+        corr = timed("corr", lambda: self.corr(coords))
+        timed("neighbors", self.neighbors)
+        timed("ba", self.ba)
+        return corr
+
+    # ------------------------------------------------------------------ host-buffer variant
+    def make_host_inputs(self):
+        """Pinned host copies of the per-frame inputs (encoder outputs + network outputs)."""
+        pin = lambda t: t.cpu().pin_memory()
+        return dict(f1=pin(self.new_f1), f2=pin(self.new_f2), imap=pin(self.new_imap), centres=pin(self.centres),
+                    target=pin(self.target), weight=pin(self.weight))
+
+    def step_host(self, hin, hout):
+        """Same frame with host<->device copies inside: inputs from pinned host memory, updated
+        window poses and patch inverse depths read back.  Returns (h2d_bytes, d2h_bytes)."""
+        h2d = 0
+        for name, dst in (("f1", self.new_f1), ("f2", self.new_f2), ("imap", self.new_imap),
+                          ("centres", self.centres), ("target", self.target), ("weight", self.weight)):
+            dst.copy_(hin[name], non_blocking=True)
+            h2d += hin[name].numel() * hin[name].element_size()
+        self.step()
+        pw = self.poses[0, self.t0:self.t1]
+        dz = self.patches[0, :, 2, 0, 0]
+        hout["poses"].copy_(pw, non_blocking=True)
+        hout["depths"].copy_(dz, non_blocking=True)
+        d2h = pw.numel() * 4 + dz.numel() * 4
+        return h2d, d2h
+
+    def make_host_outputs(self):
+        return dict(poses=torch.empty((self.t1 - self.t0, 7), dtype=torch.float32).pin_memory(),
+                    depths=torch.empty(self.patches.shape[1], dtype=torch.float32).pin_memory())
+
+    def corr_algorithmic_bytes(self):
+        """exact algorithmic bytes of one fused 2-level lookup over the edge list
+        at the coords produced by reproject() on the initial state."""
+        coords = self.reproject().cpu().numpy()
+        return synth.corr_algorithmic_bytes(coords, [(synth.H1, synth.W1), (synth.H2, synth.W2)], [1.0, 0.25])

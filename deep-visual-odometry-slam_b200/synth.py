@@ -159,3 +159,34 @@ def ba_inputs(n_frames, seed=0, M=M_DEFAULT, n_buf=None, pose_noise=0.01, px_noi
                 intrinsics=intrinsics.astype(np.float32), target=target.astype(np.float32),
                 weight=weight.astype(np.float32), ii=ii.astype(np.int64), jj=jj.astype(np.int64),
                 kk=kk.astype(np.int64), n=n_frames, M=M)
+
+
+# ------------------------------------------------------------------ roofline accounting
+def corr_algorithmic_bytes(coords, shapes, scales, R=3, C=128, P=3, esz=2):
+    """gmap patch + union of in-bounds window pixels per level + output + coords + indices."""
+    E = coords.shape[1]
+    D = 2 * R + 2
+    total = E * (C * P * P * esz + len(scales) * (D - 1) ** 2 * P * P * esz + 2 * P * P * 4 + 16)
+    off = np.arange(D) - R
+    for (H, W), s in zip(shapes, scales):
+        c = coords[0] * np.float32(s)
+        fx = np.floor(c[:, 0]).astype(np.int64).reshape(E, -1)
+        fy = np.floor(c[:, 1]).astype(np.int64).reshape(E, -1)
+        xs = fx[:, :, None] + off[None, None]  # [E,9,D]
+        ys = fy[:, :, None] + off[None, None]
+        # union size via a small bitmap per edge (bbox-relative)
+        x0 = xs.min((1, 2)); y0 = ys.min((1, 2))
+        bw = xs.max((1, 2)) - x0 + 1
+        n = 0
+        for e0 in range(0, E, 4096):
+            sl = slice(e0, min(E, e0 + 4096))
+            X = xs[sl][:, :, None, :]  # [e,9,1,D]
+            Y = ys[sl][:, :, :, None]  # [e,9,D,1]
+            ok = (X >= 0) & (X < W) & (Y >= 0) & (Y < H)
+            key = (Y - y0[sl, None, None, None]) * bw[sl, None, None, None] + (X - x0[sl, None, None, None])
+            key = np.where(ok, key, -1).reshape(key.shape[0], -1)
+            key.sort(axis=1)
+            uniq = (key[:, 1:] != key[:, :-1]).sum(1) + 1 - (key[:, 0] == -1)
+            n += int(uniq.sum())
+        total += n * C * esz
+    return total

@@ -28,6 +28,9 @@ typedef enum { DPVO_F16 = 0, DPVO_F32 = 1, DPVO_F64 = 2 } dpvo_dtype;
 
 int dpvo_abi_version(void);
 const char* dpvo_last_error(void);
+/* Number of CUDA kernels this library has launched so far in this process (for bench.py's
+ * gpu_launches; memsets are not counted). */
+uint64_t dpvo_launch_count(void);
 
 /* ------------------------------------------------------------------ altcorr */
 
