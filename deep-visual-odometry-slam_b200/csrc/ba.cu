@@ -24,27 +24,52 @@
 
 namespace dpvo {
 
-// ------------------------------------------------------------------ compaction
+// ------------------------------------------------- compaction + edge grouping
+// Pose-pair key of an edge for the dense path: (ix+1)*(N+1) + (jx+1) with out-of-window
+// (fixed) poses mapped to 0.  Edges with the same key add into the same Hessian blocks.
+__device__ __forceinline__ int pair_key(const BADev& p, int64_t fi, int64_t fj) {
+  const int64_t ix = fi - p.t0, jx = fj - p.t0;
+  const int a = (ix >= 0 && ix < p.N) ? (int)ix + 1 : 0;
+  const int b = (jx >= 0 && jx < p.N) ? (int)jx + 1 : 0;
+  return a * (p.N + 1) + b;
+}
+
+// Marks the patches referenced by kk (bitmap) and histograms the pose-pair keys
+// (one atomic per distinct key per warp).
 __global__ void __launch_bounds__(256)
-ba_mark_kernel(const int64_t* __restrict__ kk, int64_t E, uint32_t* __restrict__ bitmap, int64_t npatches) {
-  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < E; e += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t k = kk[e];
-    if (k >= 0 && k < npatches) atomicOr(&bitmap[k >> 5], 1u << (k & 31));
+ba_prep_kernel(const __grid_constant__ BADev p) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int lane = threadIdx.x & 31;
+  for (int64_t e0 = (int64_t)blockIdx.x * blockDim.x; e0 < p.E; e0 += stride) {
+    const int64_t e = e0 + threadIdx.x;
+    const bool act = e < p.E;
+    int key = -1;
+    if (act) {
+      const int64_t k = p.kk[e];
+      if (k >= 0 && k < p.npatches) atomicOr(&p.bitmap[k >> 5], 1u << (k & 31));
+      key = pair_key(p, p.ii[e], p.jj[e]);
+      p.ekey[e] = key;
+    }
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    if (act && lane == __ffs(peers) - 1) atomicAdd(&p.hist[key], __popc(peers));
   }
 }
 
-// One CTA: exclusive popcount prefix over the bitmap words, list of set bits (kx), total M.
+// One CTA: (1) exclusive popcount prefix over the bitmap words, list of set bits (kx), total M;
+// (2) exclusive scans of the key histogram: edge offsets `off` and warp-task offsets `toff`
+// (a task = up to 32 edges of one key).
 __global__ void __launch_bounds__(1024)
-ba_prefix_kernel(const uint32_t* __restrict__ bitmap, int64_t W, int* __restrict__ prefix,
-                 int64_t* __restrict__ kx, int* __restrict__ meta, int64_t Mmax) {
+ba_prefix_kernel(const __grid_constant__ BADev p) {
   __shared__ int s_warp[32];
-  __shared__ int s_carry;
+  __shared__ int s_warp2[32];
+  __shared__ int s_carry, s_carry2;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  if (tid == 0) s_carry = 0;
+  const uint32_t* bitmap = p.bitmap;
+  if (tid == 0) { s_carry = 0; s_carry2 = 0; }
   __syncthreads();
-  for (int64_t base = 0; base < W; base += 1024) {
+  for (int64_t base = 0; base < p.W; base += 1024) {
     const int64_t w = base + tid;
-    const uint32_t bits = (w < W) ? bitmap[w] : 0u;
+    const uint32_t bits = (w < p.W) ? bitmap[w] : 0u;
     const int c = __popc(bits);
     int inc = c;
 #pragma unroll
@@ -65,14 +90,14 @@ ba_prefix_kernel(const uint32_t* __restrict__ bitmap, int64_t W, int* __restrict
     }
     __syncthreads();
     const int excl = s_carry + (wid ? s_warp[wid - 1] : 0) + inc - c;
-    if (w < W) {
-      prefix[w] = excl;
+    if (w < p.W) {
+      p.prefix[w] = excl;
       uint32_t b = bits;
       int r = excl;
       while (b) {
         const int bit = __ffs(b) - 1;
         b &= b - 1;
-        if (r < Mmax) kx[r] = w * 32 + bit;
+        if (r < p.Mmax) p.kx[r] = w * 32 + bit;
         ++r;
       }
     }
@@ -80,7 +105,66 @@ ba_prefix_kernel(const uint32_t* __restrict__ bitmap, int64_t W, int* __restrict
     if (tid == 0) s_carry += s_warp[31];
     __syncthreads();
   }
-  if (tid == 0) meta[0] = (int)(s_carry < Mmax ? s_carry : Mmax);
+  if (tid == 0) p.meta[0] = (int)(s_carry < p.Mmax ? s_carry : p.Mmax);
+
+  // ---- key histogram scans
+  if (tid == 0) s_carry = 0;
+  __syncthreads();
+  for (int base = 0; base < p.K; base += 1024) {
+    const int k = base + tid;
+    const int c = (k < p.K) ? p.hist[k] : 0;
+    const int t = (c + 31) >> 5;
+    int inc = c, inc2 = t;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int a = __shfl_up_sync(0xffffffffu, inc, o);
+      const int b = __shfl_up_sync(0xffffffffu, inc2, o);
+      if (lane >= o) { inc += a; inc2 += b; }
+    }
+    if (lane == 31) { s_warp[wid] = inc; s_warp2[wid] = inc2; }
+    __syncthreads();
+    if (wid == 0) {
+      int x = s_warp[lane], y = s_warp2[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int a = __shfl_up_sync(0xffffffffu, x, o);
+        const int b = __shfl_up_sync(0xffffffffu, y, o);
+        if (lane >= o) { x += a; y += b; }
+      }
+      s_warp[lane] = x; s_warp2[lane] = y;
+    }
+    __syncthreads();
+    if (k < p.K) {
+      p.off[k] = s_carry + (wid ? s_warp[wid - 1] : 0) + inc - c;
+      p.toff[k] = s_carry2 + (wid ? s_warp2[wid - 1] : 0) + inc2 - t;
+    }
+    __syncthreads();
+    if (tid == 0) { s_carry += s_warp[31]; s_carry2 += s_warp2[31]; }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    p.off[p.K] = s_carry;
+    p.toff[p.K] = s_carry2;
+    p.meta[2] = s_carry2;  // number of warp tasks
+  }
+}
+
+// perm[off[key] + rank] = e  (rank from a per-key cursor; one atomic per distinct key per warp)
+__global__ void __launch_bounds__(256)
+ba_scatter_kernel(const __grid_constant__ BADev p) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int lane = threadIdx.x & 31;
+  for (int64_t e0 = (int64_t)blockIdx.x * blockDim.x; e0 < p.E; e0 += stride) {
+    const int64_t e = e0 + threadIdx.x;
+    const bool act = e < p.E;
+    const int key = act ? p.ekey[e] : -1;
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    const int leader = __ffs(peers) - 1;
+    int base = 0;
+    if (act && lane == leader) base = atomicAdd(&p.cursor[key], __popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (act) p.perm[p.off[key] + base + __popc(peers & ((1u << lane) - 1u))] = (int)e;
+  }
 }
 
 // --------------------------------------------------------------------- zeroing
@@ -99,34 +183,56 @@ ba_zero_kernel(const __grid_constant__ BADev p) {
 }
 
 // -------------------------------------------------------------------- assembly
-template <bool SMEM>
-__global__ void __launch_bounds__(256)
-ba_assemble_kernel(const __grid_constant__ BADev p) {
-  extern __shared__ float sm[];
-  const int n = p.n, N = p.N;
-  float* Us = SMEM ? sm : p.U;
-  float* vs = SMEM ? sm + n * n : p.v;
-  if (SMEM) {
-    for (int i = threadIdx.x; i < n * n + n; i += blockDim.x) sm[i] = 0.f;
-    __syncthreads();
+// One warp per task = up to 32 edges that share a pose-pair key.  Every lane evaluates one
+// edge (residual, Ji/Jj/Jz, validity), forms its contribution to the pair's Hessian blocks
+// (Hii, Hjj upper triangles, Hij, vi, vj: 90 values, both residual rows combined), and the
+// warp reduces them with a shuffle reduce-scatter (93 shuffles for 96 values instead of 5 per
+// value); each lane then adds 3 fully reduced values to U / v.  Patch-keyed terms (E^T rows,
+// C, u) go to memory directly: their addresses are spread over M patches.
+__constant__ unsigned char c_tri_a[21] = {0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 4, 4, 5};
+__constant__ unsigned char c_tri_b[21] = {0, 1, 2, 3, 4, 5, 1, 2, 3, 4, 5, 2, 3, 4, 5, 3, 4, 5, 4, 5, 5};
+
+template <int HALF>
+__device__ __forceinline__ void reduce_scatter_step(float (&v)[96], bool hi, int off) {
+#pragma unroll
+  for (int i = 0; i < HALF; ++i) {
+    const float keep = hi ? v[i + HALF] : v[i];
+    const float send = hi ? v[i] : v[i + HALF];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
   }
+}
+
+constexpr int kAsmWarps = 4;
+
+__global__ void __launch_bounds__(kAsmWarps * 32)
+ba_assemble_kernel(const __grid_constant__ BADev p) {
+  const int lane = threadIdx.x & 31;
+  const int task = blockIdx.x * kAsmWarps + (threadIdx.x >> 5);
+  if (task >= p.meta[2]) return;
+  // segment of this task: last key s with toff[s] <= task (empty keys have toff[s] == toff[s+1])
+  int lo = 0, hi = p.K;  // invariant: toff[lo] <= task < toff[hi]
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (p.toff[mid] <= task) lo = mid; else hi = mid;
+  }
+  const int key = lo;
+  const int chunk = task - p.toff[key];
+  const int pos = p.off[key] + chunk * 32 + lane;
+  const bool act = pos < p.off[key + 1];
+  const int n = p.n;
+  const int ix = key / (p.N + 1) - 1;   // -1: fixed pose
+  const int jx = key % (p.N + 1) - 1;
   const float fx = p.intr[0], fy = p.intr[1], cx = p.intr[2], cy = p.intr[3];
 
-  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < p.E; e += (int64_t)gridDim.x * blockDim.x) {
-    EdgeTerms T;
-    if (!edge_terms(p, e, fx, fy, cx, cy, T)) continue;
-    const int k = patch_rank(p, T.kf);
-    const bool iv = (T.ix >= 0) && (T.ix < N);
-    const bool jv = (T.jx >= 0) && (T.jx < N);
+  float v[96];
+#pragma unroll
+  for (int i = 0; i < 96; ++i) v[i] = 0.f;
 
+  EdgeTerms T;
+  if (act && edge_terms(p, p.perm[pos], fx, fy, cx, cy, T)) {
+    const int k = patch_rank(p, T.kf);
     float cc = 0.f, uu = 0.f;
-    float vi[6] = {0, 0, 0, 0, 0, 0}, vj[6] = {0, 0, 0, 0, 0, 0};
     float ei[6] = {0, 0, 0, 0, 0, 0}, ej[6] = {0, 0, 0, 0, 0, 0};
-    float Hii[21], Hjj[21], Hij[36];
-#pragma unroll
-    for (int i = 0; i < 21; ++i) { Hii[i] = 0.f; Hjj[i] = 0.f; }
-#pragma unroll
-    for (int i = 0; i < 36; ++i) Hij[i] = 0.f;
 #pragma unroll
     for (int row = 0; row < 2; ++row) {
       const float w = T.w[row], r = T.r[row], Jz = T.Jz[row];
@@ -135,71 +241,69 @@ ba_assemble_kernel(const __grid_constant__ BADev p) {
       int idx = 0;
 #pragma unroll
       for (int a = 0; a < 6; ++a) {
+        const float wi = w * Ji[a], wj = w * Jj[a];
 #pragma unroll
         for (int b = a; b < 6; ++b) {
-          Hii[idx] += w * Ji[a] * Ji[b];
-          Hjj[idx] += w * Jj[a] * Jj[b];
+          v[idx] += wi * Ji[b];
+          v[21 + idx] += wj * Jj[b];
           ++idx;
         }
 #pragma unroll
-        for (int b = 0; b < 6; ++b) Hij[a * 6 + b] += w * Ji[a] * Jj[b];
-        vi[a] += -w * r * Ji[a];
-        vj[a] += w * r * Jj[a];
-        ei[a] += -w * Jz * Ji[a];
-        ej[a] += w * Jz * Jj[a];
+        for (int b = 0; b < 6; ++b) v[42 + a * 6 + b] += wi * Jj[b];
+        v[78 + a] += -r * wi;
+        v[84 + a] += r * wj;
+        ei[a] += -Jz * wi;
+        ej[a] += Jz * wj;
       }
       cc += w * Jz * Jz;
       uu += w * r * Jz;
     }
-
-    if (iv) {
-      const int o = 6 * T.ix;
-      int idx = 0;
+    float* et = p.Et + (int64_t)k * n;
+    if (ix >= 0) {
 #pragma unroll
-      for (int a = 0; a < 6; ++a) {
-#pragma unroll
-        for (int b = a; b < 6; ++b) {
-          atomicAdd(&Us[(o + a) * n + o + b], (a == b ? 0.5f : 1.0f) * Hii[idx]);
-          ++idx;
-        }
-        atomicAdd(&vs[o + a], vi[a]);
-        atomicAdd(&p.Et[(int64_t)k * n + o + a], ei[a]);
-      }
+      for (int a = 0; a < 6; ++a) atomicAdd(&et[6 * ix + a], ei[a]);
     }
-    if (jv) {
-      const int o = 6 * T.jx;
-      int idx = 0;
+    if (jx >= 0) {
 #pragma unroll
-      for (int a = 0; a < 6; ++a) {
-#pragma unroll
-        for (int b = a; b < 6; ++b) {
-          atomicAdd(&Us[(o + a) * n + o + b], (a == b ? 0.5f : 1.0f) * Hjj[idx]);
-          ++idx;
-        }
-        atomicAdd(&vs[o + a], vj[a]);
-        atomicAdd(&p.Et[(int64_t)k * n + o + a], ej[a]);
-      }
-    }
-    if (iv && jv) {
-      const int oi = 6 * T.ix, oj = 6 * T.jx;
-#pragma unroll
-      for (int a = 0; a < 6; ++a)
-#pragma unroll
-        for (int b = 0; b < 6; ++b) atomicAdd(&Us[(oi + a) * n + oj + b], -Hij[a * 6 + b]);
+      for (int a = 0; a < 6; ++a) atomicAdd(&et[6 * jx + a], ej[a]);
     }
     atomicAdd(&p.C[k], cc);
     atomicAdd(&p.u[k], uu);
   }
+  if (ix < 0 && jx < 0) return;  // both poses fixed: no pose blocks (warp-uniform)
 
-  if (SMEM) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < n * n; i += blockDim.x) {
-      const float x = sm[i];
-      if (x != 0.f) atomicAdd(&p.U[i], x);
-    }
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      const float x = sm[n * n + i];
-      if (x != 0.f) atomicAdd(&p.v[i], x);
+  reduce_scatter_step<48>(v, lane & 16, 16);
+  reduce_scatter_step<24>(v, lane & 8, 8);
+  reduce_scatter_step<12>(v, lane & 4, 4);
+  reduce_scatter_step<6>(v, lane & 2, 2);
+  reduce_scatter_step<3>(v, lane & 1, 1);
+  const int base = ((lane >> 4) & 1) * 48 + ((lane >> 3) & 1) * 24 + ((lane >> 2) & 1) * 12 +
+                   ((lane >> 1) & 1) * 6 + (lane & 1) * 3;
+  const int oi = 6 * ix, oj = 6 * jx;
+#pragma unroll
+  for (int t = 0; t < 3; ++t) {
+    const int idx = base + t;
+    const float val = v[t];
+    if (val == 0.f) continue;
+    if (idx < 21) {
+      if (ix >= 0) {
+        const int a = c_tri_a[idx], b = c_tri_b[idx];
+        atomicAdd(&p.U[(oi + a) * n + oi + b], (a == b ? 0.5f : 1.0f) * val);
+      }
+    } else if (idx < 42) {
+      if (jx >= 0) {
+        const int a = c_tri_a[idx - 21], b = c_tri_b[idx - 21];
+        atomicAdd(&p.U[(oj + a) * n + oj + b], (a == b ? 0.5f : 1.0f) * val);
+      }
+    } else if (idx < 78) {
+      if (ix >= 0 && jx >= 0) {
+        const int a = (idx - 42) / 6, b = (idx - 42) % 6;
+        atomicAdd(&p.U[(oi + a) * n + oj + b], -val);
+      }
+    } else if (idx < 84) {
+      if (ix >= 0) atomicAdd(&p.v[oi + idx - 78], val);
+    } else if (idx < 90) {
+      if (jx >= 0) atomicAdd(&p.v[oj + idx - 84], val);
     }
   }
 }
@@ -271,11 +375,87 @@ ba_schur_kernel(const __grid_constant__ BADev p) {
   if (tb == 0 && threadIdx.x < 64 && a0 + threadIdx.x < n && gacc != 0.f) atomicAdd(&p.g[a0 + threadIdx.x], gacc);
 }
 
+// ----------------------------------------------------------------- solve (small)
+// One CTA, system resident in shared memory: A is (n+1) x ld, rows 0..n-1 hold the lower
+// triangle of S = B - E Q E^T (+ damping), row n holds y^T, so the forward substitution
+// L z = y falls out of the factorisation.  Right-looking Cholesky with ONE barrier per column:
+// the unscaled column j is read from the lower triangle while the scaled L(:,j) is written to
+// the (unused) upper triangle, A[j][i] = L[i][j].  Then L^T x = z by one warp, dX -> global,
+// pose retraction (ba_cuda.cu:178-206).  Also clears U, v, G, g for the next iteration.
+__global__ void __launch_bounds__(256)
+ba_solve_small_kernel(const __grid_constant__ BADev p) {
+  extern __shared__ float sm[];
+  const int n = p.n, N = p.N;
+  const int ld = (n + 2) | 1;
+  float* A = sm;                       // (n+1) * ld
+  float* dinv = sm + (n + 1) * ld;     // n
+  float* x = dinv + n;                 // n
+  __shared__ int s_fail;
+  const int T = blockDim.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = T >> 5;
+  if (tid == 0) s_fail = 0;
+  for (int a = wid; a < n; a += nw)
+    for (int b = lane; b <= a; b += 32) {
+      float s = p.U[a * n + b] + p.U[b * n + a] - 0.5f * (p.G[a * n + b] + p.G[b * n + a]);
+      if (a == b) s += 1e-4f * s + 1.0f;
+      A[a * ld + b] = s;
+    }
+  for (int i = tid; i < n; i += T) A[n * ld + i] = p.v[i] - p.g[i];
+  __syncthreads();
+  for (int i = tid; i < 2 * n * n + 2 * n; i += T) p.U[i] = 0.f;   // U, v, G, g contiguous
+
+  for (int j = 0; j < n; ++j) {
+    const float d = A[j * ld + j];
+    if (!(d > 0.f)) { if (tid == 0) s_fail = 1; break; }   // uniform: every thread reads the same d
+    const float r = 1.0f / sqrtf(d);
+    const float invd = 1.0f / d;
+    if (tid == 0) dinv[j] = r;
+    // rows i in (j, n]: scaled column to the upper triangle, trailing update of the lower one
+    for (int i = j + 1 + wid; i <= n; i += nw) {
+      const float aij = A[i * ld + j];
+      if (lane == 0) A[j * ld + i] = aij * r;
+      const float f = aij * invd;
+      const int kend = (i < n) ? i : n - 1;
+      for (int k = j + 1 + lane; k <= kend; k += 32) A[i * ld + k] -= f * A[k * ld + j];
+    }
+    __syncthreads();
+  }
+  __syncthreads();
+  if (s_fail) {
+    for (int i = tid; i < n; i += T) p.dX[i] = 0.f;
+    if (tid == 0) p.meta[1] = 1;  // tells backsub to skip the depth update too
+    return;
+  }
+  if (wid == 0) {
+    for (int j = n - 1; j >= 0; --j) {
+      float acc = 0.f;
+      for (int i = j + 1 + lane; i < n; i += 32) acc += A[j * ld + i] * x[i];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (lane == 0) x[j] = (A[j * ld + n] - acc) * dinv[j];
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < n; i += T) p.dX[i] = x[i];
+  if (tid == 0) p.meta[1] = 0;
+  for (int i = tid; i < N; i += T) {
+    float* ps = p.poses + (int64_t)(p.t0 + i) * 7;
+    const Vec3 t = {ps[0], ps[1], ps[2]};
+    const Quat q = {ps[3], ps[4], ps[5], ps[6]};
+    const float xi[6] = {x[6 * i + 0], x[6 * i + 1], x[6 * i + 2], x[6 * i + 3], x[6 * i + 4], x[6 * i + 5]};
+    Vec3 t1;
+    Quat q1;
+    retr_se3(xi, t, q, t1, q1);
+    ps[0] = t1.x; ps[1] = t1.y; ps[2] = t1.z;
+    ps[3] = q1.x; ps[4] = q1.y; ps[5] = q1.z; ps[6] = q1.w;
+  }
+}
+
 // ----------------------------------------------------------------------- solve
 // One CTA.  S = (U + U^T) - G, y = v - g, S_dd += 1e-4 S_dd + 1, Cholesky, solves,
 // dX -> global, pose retraction.  S lives in shared memory when it fits.
 __global__ void __launch_bounds__(512)
-ba_solve_kernel(const __grid_constant__ BADev p, int s_in_smem) {
+ba_solve_big_kernel(const __grid_constant__ BADev p, int s_in_smem) {
   extern __shared__ float sm[];
   const int n = p.n, N = p.N;
   const int T = blockDim.x, tid = threadIdx.x;
@@ -293,6 +473,7 @@ ba_solve_kernel(const __grid_constant__ BADev p, int s_in_smem) {
   }
   for (int i = tid; i < n; i += T) y[i] = p.v[i] - p.g[i];
   __syncthreads();
+  for (int i = tid; i < 2 * n * n + 2 * n; i += T) p.U[i] = 0.f;   // U, v, G, g contiguous: clear for the next iteration
 
   for (int j = 0; j < n; ++j) {
     if (tid == 0) {
@@ -358,7 +539,7 @@ ba_backsub_kernel(const __grid_constant__ BADev p) {
   extern __shared__ float dXs[];
   const int n = p.n;
   const int M = p.meta[0];
-  if (n > 0 && p.meta[1]) return;  // failed factorisation: leave the depths alone
+  const bool failed = n > 0 && p.meta[1];  // failed factorisation: leave the depths alone, still clear
   for (int i = threadIdx.x; i < n; i += blockDim.x) dXs[i] = p.dX[i];
   __syncthreads();
   const float lm = p.lmbda[0];
@@ -369,7 +550,12 @@ ba_backsub_kernel(const __grid_constant__ BADev p) {
     for (int a = 0; a < n; ++a) dot += er[a] * dXs[a];
     const float q = 1.0f / (p.C[k] + lm);
     const float dz = q * (p.u[k] - dot);
-    depth_retract(p.patches, p.kx[k], PP, dz);
+    if (!failed) depth_retract(p.patches, p.kx[k], PP, dz);
+    // clear this patch's accumulators for the next iteration
+    float* ew = p.Et + (int64_t)k * n;
+    for (int a = 0; a < n; ++a) ew[a] = 0.f;
+    p.C[k] = 0.f;
+    p.u[k] = 0.f;
   }
 }
 
@@ -413,9 +599,18 @@ int64_t ba_carve(BADev& p, char* base, int64_t E, int64_t npatches, int N, int e
   const int64_t Mmax = E < npatches ? E : npatches;
   int64_t off = 0;
   auto take = [&](int64_t bytes) { int64_t o = off; off += align256(bytes); return base ? base + o : (char*)nullptr; };
+  // bitmap, hist, cursor, meta are contiguous: cleared by one memset per call
+  const int64_t K = ((int64_t)N + 1) * (N + 1);
+  p.K = (int)K;
   p.bitmap = (uint32_t*)take(W * 4);
-  p.prefix = (int*)take(W * 4);
+  p.hist = (int*)take(K * 4);
+  p.cursor = (int*)take(K * 4);
   p.meta = (int*)take(64);
+  p.prefix = (int*)take(W * 4);
+  p.off = (int*)take((K + 1) * 4);
+  p.toff = (int*)take((K + 1) * 4);
+  p.perm = (int*)take(E * 4);
+  p.ekey = (int*)take(E * 4);
   p.kx = (int64_t*)take(Mmax * 8);
   // U, v, G, g contiguous (zeroed as one range)
   char* fixed = take((2 * n * n + 2 * n) * 4);
@@ -475,47 +670,47 @@ extern "C" int dpvo_ba_forward(float* poses, float* patches, const float* intrin
   p.ii = ii; p.jj = jj; p.kk = kk; p.E = n_edges; p.nframes = n_frames_total; p.npatches = n_patches_total;
   p.P = P; p.t0 = t0; p.N = N; p.n = 6 * N; p.ppf = ppf;
 
+  DPVO_REQUIRE(N <= 2048, "ba_forward: dense path supports at most 2048 free poses (use eff_impl)");
   const int egrid = (int)(ceil_div64(n_edges, 256) < kNumSMs * 8 ? ceil_div64(n_edges, 256) : kNumSMs * 8);
-  cudaMemsetAsync(p.bitmap, 0, p.W * 4, st);
-  cudaMemsetAsync(p.meta, 0, 64, st);
-  ba_mark_kernel<<<egrid, 256, 0, st>>>(kk, n_edges, p.bitmap, n_patches_total);
-  ba_prefix_kernel<<<1, 1024, 0, st>>>(p.bitmap, p.W, p.prefix, p.kx, p.meta, p.Mmax);
+  cudaMemsetAsync(p.bitmap, 0, reinterpret_cast<char*>(p.meta) + 64 - reinterpret_cast<char*>(p.bitmap), st);
+  ba_prep_kernel<<<egrid, 256, 0, st>>>(p);
+  ba_prefix_kernel<<<1, 1024, 0, st>>>(p);
   if (check_launch("ba_prefix")) return 1;
 
   if (eff_impl) return ba_eff_run(p, iterations, st);
 
+  ba_scatter_kernel<<<egrid, 256, 0, st>>>(p);
   const int n = p.n;
-  const size_t asm_smem = (size_t)(n * n + n) * sizeof(float);
-  const bool asm_in_smem = N > 0 && asm_smem <= 200 * 1024;
-  if (asm_in_smem && asm_smem > 48 * 1024)
-    cudaFuncSetAttribute(ba_assemble_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)asm_smem);
-  const size_t solve_full = (size_t)(n * (size_t)n + n) * sizeof(float);
-  const int s_in_smem = solve_full <= 200 * 1024;
-  const size_t solve_smem = s_in_smem ? solve_full : (size_t)n * sizeof(float);
-  if (solve_smem > 48 * 1024)
-    cudaFuncSetAttribute(ba_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)solve_smem);
+  const int ld = (n + 2) | 1;
+  const size_t small_smem = ((size_t)(n + 1) * ld + 2 * (size_t)n) * sizeof(float);
+  const bool small = N > 0 && small_smem <= 220 * 1024;
+  if (small && small_smem > 48 * 1024)
+    cudaFuncSetAttribute(ba_solve_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)small_smem);
+  const size_t solve_smem = (size_t)n * sizeof(float);
   const int64_t zero_total = 2 * (int64_t)n * n + 2 * n + 2 * p.Mmax + p.Mmax * n;
   const int zgrid = (int)(ceil_div64(zero_total, 256 * 8) < kNumSMs * 4 ? ceil_div64(zero_total, 256 * 8) : kNumSMs * 4);
-  const int agrid = asm_in_smem ? (int)(ceil_div64(n_edges, 256) < kNumSMs ? ceil_div64(n_edges, 256) : kNumSMs) : egrid;
-  const int tiles = (n + 63) / 64;
+  const int64_t max_tasks = n_edges / 32 + p.K + 1;
+  const int agrid = (int)ceil_div64(max_tasks, kAsmWarps);
+  const int tiles = n > 0 ? (n + 63) / 64 : 1;
   int ksplit = (int)ceil_div64(p.Mmax, kSchurKC);
   const int kcap = (2 * kNumSMs) / (tiles * tiles) > 1 ? (2 * kNumSMs) / (tiles * tiles) : 1;
   if (ksplit > kcap) ksplit = kcap;
   const int bgrid = (int)(ceil_div64(p.Mmax, 256) < kNumSMs * 4 ? ceil_div64(p.Mmax, 256) : kNumSMs * 4);
 
+  // accumulators are cleared once here; solve / backsub clear what they consumed for the next iteration
+  ba_zero_kernel<<<zgrid > 0 ? zgrid : 1, 256, 0, st>>>(p);
   for (int it = 0; it < iterations; ++it) {
-    ba_zero_kernel<<<zgrid > 0 ? zgrid : 1, 256, 0, st>>>(p);
-    if (asm_in_smem)
-      ba_assemble_kernel<true><<<agrid, 256, asm_smem, st>>>(p);
-    else
-      ba_assemble_kernel<false><<<agrid, 256, 0, st>>>(p);
+    ba_assemble_kernel<<<agrid, kAsmWarps * 32, 0, st>>>(p);
     if (N > 0) {
       ba_schur_kernel<<<dim3(ksplit, tiles * tiles), 256, 0, st>>>(p);
-      ba_solve_kernel<<<1, 512, solve_smem, st>>>(p, s_in_smem);
+      if (small)
+        ba_solve_small_kernel<<<1, n <= 96 ? 128 : 256, small_smem, st>>>(p);
+      else
+        ba_solve_big_kernel<<<1, 512, solve_smem, st>>>(p, 0);
     }
     ba_backsub_kernel<<<bgrid, 256, (size_t)(n + 1) * sizeof(float), st>>>(p);
   }
-  note_launches(2 + iterations * (N > 0 ? 5 : 3));
+  note_launches(4 + iterations * (N > 0 ? 4 : 2));
   return check_launch("ba_forward");
 }
 

@@ -14,6 +14,9 @@ struct BADev {
   // compaction
   uint32_t* bitmap; int* prefix; int* meta; int64_t* kx;
   int64_t Mmax, W;
+  // edge grouping by pose-pair key (counting sort): hist[K], cursor[K], off[K+1], toff[K+1], perm[E], ekey[E]
+  int K;
+  int *hist, *cursor, *off, *toff, *perm, *ekey;
   // normal equations (dense path)
   float *U, *v, *G, *g, *C, *u, *Et, *dX, *Sg;
   // block-E path (global BA)

@@ -217,8 +217,12 @@ def test_full_size_properties():
     out = pkg.altcorr.corr_pyramid(g, (f1, f2), c, us, vs, 3)
     out2 = pkg.altcorr.corr_pyramid(g * 2, (f1, f2), c, us, vs, 3)
     fin = torch.isfinite(out2)
-    # exact up to fp16 subnormal rounding (spacing 2^-24) of tiny blend products
-    assert ((out.float() * 2)[fin] - out2.float()[fin]).abs().max().item() <= 1e-6
+    # exact except where a blend product falls into fp16's subnormal range (spacing 2^-24): that
+    # perturbation can flip a round-to-nearest tie of the running blend sum, i.e. at most one fp16
+    # ulp of the result, and only on a vanishing fraction of outputs
+    a = (out.float() * 2)[fin]; b = out2.float()[fin]
+    assert ((a - b).abs() <= b.abs() * 2.0 ** -10 + 2.0 ** -23).all()
+    assert (a != b).float().mean().item() < 1e-3
     perm = torch.randperm(E, device="cuda", generator=torch.Generator("cuda").manual_seed(0))
     outp = pkg.altcorr.corr_pyramid(g, (f1, f2), c[:, perm].contiguous(), us[perm], vs[perm], 3)
     assert torch.equal(outp, out[:, perm])
