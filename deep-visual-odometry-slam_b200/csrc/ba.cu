@@ -36,22 +36,45 @@ __device__ __forceinline__ int pair_key(const BADev& p, int64_t fi, int64_t fj) 
 
 // Marks the patches referenced by kk (bitmap) and histograms the pose-pair keys
 // (one atomic per distinct key per warp).
+constexpr int kPrepSmemKeys = 2048;
+
 __global__ void __launch_bounds__(256)
 ba_prep_kernel(const __grid_constant__ BADev p) {
+  __shared__ int s_hist[kPrepSmemKeys];
+  const bool use_smem = p.K <= kPrepSmemKeys;
+  if (use_smem) {
+    for (int i = threadIdx.x; i < p.K; i += blockDim.x) s_hist[i] = 0;
+    __syncthreads();
+  }
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int lane = threadIdx.x & 31;
   for (int64_t e0 = (int64_t)blockIdx.x * blockDim.x; e0 < p.E; e0 += stride) {
     const int64_t e = e0 + threadIdx.x;
     const bool act = e < p.E;
     int key = -1;
+    int word = -1;
+    uint32_t bit = 0;
     if (act) {
       const int64_t k = p.kk[e];
-      if (k >= 0 && k < p.npatches) atomicOr(&p.bitmap[k >> 5], 1u << (k & 31));
+      if (k >= 0 && k < p.npatches) { word = (int)(k >> 5); bit = 1u << (k & 31); }
       key = pair_key(p, p.ii[e], p.jj[e]);
       p.ekey[e] = key;
     }
+    // one atomicOr per distinct bitmap word per warp, and only if it would change the word
+    // (bits only ever get set: a stale read can only cause a redundant atomic)
+    const unsigned wpeers = __match_any_sync(0xffffffffu, word);
+    const uint32_t bits = __reduce_or_sync(wpeers, bit);
+    if (word >= 0 && lane == __ffs(wpeers) - 1 && (__ldcg(&p.bitmap[word]) & bits) != bits)
+      atomicOr(&p.bitmap[word], bits);
     const unsigned peers = __match_any_sync(0xffffffffu, key);
-    if (act && lane == __ffs(peers) - 1) atomicAdd(&p.hist[key], __popc(peers));
+    if (act && lane == __ffs(peers) - 1) atomicAdd(use_smem ? &s_hist[key] : &p.hist[key], __popc(peers));
+  }
+  if (use_smem) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < p.K; i += blockDim.x) {
+      const int c = s_hist[i];
+      if (c) atomicAdd(&p.hist[i], c);
+    }
   }
 }
 
@@ -375,6 +398,121 @@ ba_schur_kernel(const __grid_constant__ BADev p) {
   if (tb == 0 && threadIdx.x < 64 && a0 + threadIdx.x < n && gacc != 0.f) atomicAdd(&p.g[a0 + threadIdx.x], gacc);
 }
 
+// ------------------------------------------------------------- solve (registers)
+// n + 1 <= 16*TS.  256 threads as a 16 x 16 grid; thread (ti, tk) keeps elements (i, k),
+// i = ti + 16 r, k = tk + 16 c, of the augmented system [S ; y^T] in registers (TS x TS tile,
+// cyclic distribution keeps the shrinking trailing matrix balanced).  Per column j its owners
+// publish the unscaled column through a double-buffered shared-memory vector — one barrier per
+// column — and every thread applies the rank-1 update to its tile.  The scaled columns
+// (L, with z = L^-1 y as row n) go to shared memory for the back substitution L^T x = z,
+// done column-oriented by one warp.  Then dX -> global, pose retraction (ba_cuda.cu:178-206);
+// U, v, G, g are cleared for the next iteration.
+template <int TS>
+__global__ void __launch_bounds__(256)
+ba_solve_reg_kernel(const __grid_constant__ BADev p) {
+  extern __shared__ float sm[];
+  const int n = p.n, N = p.N;
+  const int ldL = (n + 2) | 1;
+  float* Ls = sm;                    // n * ldL : Ls[j*ldL + i] = L[i][j], i in (j, n]
+  float* col = Ls + n * ldL;         // 2 * 16*TS
+  float* dinv = col + 2 * 16 * TS;   // n
+  float* x = dinv + n;               // n
+  __shared__ int s_fail;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int ti = tid >> 4, tk = tid & 15;
+  if (tid == 0) s_fail = 0;
+
+  float a[TS][TS];
+#pragma unroll
+  for (int r = 0; r < TS; ++r)
+#pragma unroll
+    for (int c = 0; c < TS; ++c) {
+      const int i = ti + 16 * r, k = tk + 16 * c;
+      float s = 0.f;
+      if (i < n && k <= i) {
+        s = p.U[i * n + k] + p.U[k * n + i] - 0.5f * (p.G[i * n + k] + p.G[k * n + i]);
+        if (i == k) s += 1e-4f * s + 1.0f;
+      } else if (i == n && k < n) {
+        s = p.v[k] - p.g[k];
+      }
+      a[r][c] = s;
+    }
+  __syncthreads();   // every element has been read: U, v, G, g (contiguous) can be cleared
+  for (int i = tid; i < 2 * n * n + 2 * n; i += 256) p.U[i] = 0.f;
+
+  bool fail = false;
+#pragma unroll
+  for (int jb = 0; jb < TS; ++jb) {
+    for (int jj = 0; jj < 16; ++jj) {
+      const int j = jb * 16 + jj;
+      if (j >= n || fail) break;
+      float* cb = col + (j & 1) * 16 * TS;
+      if (tk == jj) {
+#pragma unroll
+        for (int r = 0; r < TS; ++r) cb[ti + 16 * r] = a[r][jb];
+      }
+      __syncthreads();
+      const float d = cb[j];
+      if (!(d > 0.f)) { fail = true; break; }   // uniform
+      // 1/sqrt(d) by MUFU.RSQ + one Newton step (<= 1 ulp) instead of an IEEE sqrt and two divisions:
+      // this chain sits on the critical path of every column
+      float rs = rsqrtf(d);
+      rs = rs * (1.5f - 0.5f * d * rs * rs);
+      const float invd = rs * rs;
+      float li[TS];
+#pragma unroll
+      for (int r = 0; r < TS; ++r) li[r] = cb[ti + 16 * r];
+#pragma unroll
+      for (int c = jb; c < TS; ++c) {
+        const int k = tk + 16 * c;
+        const float lk = (k > j) ? cb[k < 16 * TS ? k : 0] * invd : 0.f;
+#pragma unroll
+        for (int r = 0; r < TS; ++r) a[r][c] -= li[r] * lk;
+      }
+      if (tk == jj) {
+#pragma unroll
+        for (int r = 0; r < TS; ++r) {
+          const int i = ti + 16 * r;
+          if (i > j && i <= n) Ls[j * ldL + i] = li[r] * rs;
+        }
+        if (ti == 0) dinv[j] = rs;
+      }
+    }
+  }
+  if (fail && tid == 0) s_fail = 1;
+  __syncthreads();
+  if (s_fail) {
+    for (int i = tid; i < n; i += 256) p.dX[i] = 0.f;
+    if (tid == 0) p.meta[1] = 1;  // tells backsub to skip the depth update too
+    return;
+  }
+  for (int i = tid; i < n; i += 256) x[i] = Ls[i * ldL + n];   // z
+  __syncthreads();
+  if (wid == 0) {
+    for (int j = n - 1; j >= 0; --j) {
+      const float xj = x[j] * dinv[j];
+      __syncwarp();
+      if (lane == 0) x[j] = xj;
+      for (int i = lane; i < j; i += 32) x[i] -= Ls[i * ldL + j] * xj;
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < n; i += 256) p.dX[i] = x[i];
+  if (tid == 0) p.meta[1] = 0;
+  for (int i = tid; i < N; i += 256) {
+    float* ps = p.poses + (int64_t)(p.t0 + i) * 7;
+    const Vec3 t = {ps[0], ps[1], ps[2]};
+    const Quat q = {ps[3], ps[4], ps[5], ps[6]};
+    const float xi[6] = {x[6 * i + 0], x[6 * i + 1], x[6 * i + 2], x[6 * i + 3], x[6 * i + 4], x[6 * i + 5]};
+    Vec3 t1;
+    Quat q1;
+    retr_se3(xi, t, q, t1, q1);
+    ps[0] = t1.x; ps[1] = t1.y; ps[2] = t1.z;
+    ps[3] = q1.x; ps[4] = q1.y; ps[5] = q1.z; ps[6] = q1.w;
+  }
+}
+
 // ----------------------------------------------------------------- solve (small)
 // One CTA, system resident in shared memory: A is (n+1) x ld, rows 0..n-1 hold the lower
 // triangle of S = B - E Q E^T (+ damping), row n holds y^T, so the forward substitution
@@ -403,19 +541,22 @@ ba_solve_small_kernel(const __grid_constant__ BADev p) {
   __syncthreads();
   for (int i = tid; i < 2 * n * n + 2 * n; i += T) p.U[i] = 0.f;   // U, v, G, g contiguous
 
+  // thread -> (row group rg, column lane cl): owns columns k == cl (mod 64) and rows i == rg (mod T/64)
+  const int cl = tid & 63, rg = tid >> 6, nrg = T >> 6;
   for (int j = 0; j < n; ++j) {
     const float d = A[j * ld + j];
     if (!(d > 0.f)) { if (tid == 0) s_fail = 1; break; }   // uniform: every thread reads the same d
     const float r = 1.0f / sqrtf(d);
     const float invd = 1.0f / d;
     if (tid == 0) dinv[j] = r;
-    // rows i in (j, n]: scaled column to the upper triangle, trailing update of the lower one
-    for (int i = j + 1 + wid; i <= n; i += nw) {
-      const float aij = A[i * ld + j];
-      if (lane == 0) A[j * ld + i] = aij * r;
-      const float f = aij * invd;
-      const int kend = (i < n) ? i : n - 1;
-      for (int k = j + 1 + lane; k <= kend; k += 32) A[i * ld + k] -= f * A[k * ld + j];
+    // scaled column j -> upper triangle (row j), rows (j, n]
+    for (int i = j + 1 + tid; i <= n; i += T) A[j * ld + i] = A[i * ld + j] * r;
+    // trailing update of the lower triangle: A[i][k] -= A[i][j] A[k][j] / d, j < k <= min(i, n-1), i <= n
+    for (int k = j + 1 + cl; k < n; k += 64) {
+      const float f = A[k * ld + j] * invd;
+      int i = k + ((rg - k) % nrg + nrg) % nrg;   // first row >= k in this thread's row class
+#pragma unroll 4
+      for (; i <= n; i += nrg) A[i * ld + k] -= A[i * ld + j] * f;
     }
     __syncthreads();
   }
@@ -425,13 +566,15 @@ ba_solve_small_kernel(const __grid_constant__ BADev p) {
     if (tid == 0) p.meta[1] = 1;  // tells backsub to skip the depth update too
     return;
   }
+  for (int i = tid; i < n; i += T) x[i] = A[i * ld + n];   // z
+  __syncthreads();
   if (wid == 0) {
+    // L^T x = z, column oriented: once x_j is known, z_i -= L[j][i] x_j for i < j (L[j][i] = A[i][j], upper)
     for (int j = n - 1; j >= 0; --j) {
-      float acc = 0.f;
-      for (int i = j + 1 + lane; i < n; i += 32) acc += A[j * ld + i] * x[i];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-      if (lane == 0) x[j] = (A[j * ld + n] - acc) * dinv[j];
+      const float xj = x[j] * dinv[j];
+      __syncwarp();
+      if (lane == 0) x[j] = xj;
+      for (int i = lane; i < j; i += 32) x[i] -= A[i * ld + j] * xj;
       __syncwarp();
     }
   }
@@ -544,18 +687,24 @@ ba_backsub_kernel(const __grid_constant__ BADev p) {
   __syncthreads();
   const float lm = p.lmbda[0];
   const int PP = p.P * p.P;
-  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < M; k += gridDim.x * blockDim.x) {
+  const int lane = threadIdx.x & 31;
+  const int nwarp = (gridDim.x * blockDim.x) >> 5;
+  for (int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; k < M; k += nwarp) {
+    float* er = p.Et + (int64_t)k * n;
     float dot = 0.f;
-    const float* er = p.Et + (int64_t)k * n;
-    for (int a = 0; a < n; ++a) dot += er[a] * dXs[a];
-    const float q = 1.0f / (p.C[k] + lm);
-    const float dz = q * (p.u[k] - dot);
-    if (!failed) depth_retract(p.patches, p.kx[k], PP, dz);
-    // clear this patch's accumulators for the next iteration
-    float* ew = p.Et + (int64_t)k * n;
-    for (int a = 0; a < n; ++a) ew[a] = 0.f;
-    p.C[k] = 0.f;
-    p.u[k] = 0.f;
+    for (int a = lane; a < n; a += 32) {
+      dot += er[a] * dXs[a];
+      er[a] = 0.f;                       // clear this patch's accumulators for the next iteration
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+    if (lane == 0) {
+      const float q = 1.0f / (p.C[k] + lm);
+      const float dz = q * (p.u[k] - dot);
+      p.C[k] = 0.f;
+      p.u[k] = 0.f;
+      if (!failed) depth_retract(p.patches, p.kx[k], PP, dz);
+    }
   }
 }
 
@@ -687,6 +836,9 @@ extern "C" int dpvo_ba_forward(float* poses, float* patches, const float* intrin
   if (small && small_smem > 48 * 1024)
     cudaFuncSetAttribute(ba_solve_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)small_smem);
   const size_t solve_smem = (size_t)n * sizeof(float);
+  const size_t reg_smem = ((size_t)n * ld + 2 * 16 * 8 + 2 * (size_t)n) * sizeof(float);
+  if (n + 1 <= 128 && reg_smem > 48 * 1024)
+    cudaFuncSetAttribute(ba_solve_reg_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)reg_smem);
   const int64_t zero_total = 2 * (int64_t)n * n + 2 * n + 2 * p.Mmax + p.Mmax * n;
   const int zgrid = (int)(ceil_div64(zero_total, 256 * 8) < kNumSMs * 4 ? ceil_div64(zero_total, 256 * 8) : kNumSMs * 4);
   const int64_t max_tasks = n_edges / 32 + p.K + 1;
@@ -695,7 +847,7 @@ extern "C" int dpvo_ba_forward(float* poses, float* patches, const float* intrin
   int ksplit = (int)ceil_div64(p.Mmax, kSchurKC);
   const int kcap = (2 * kNumSMs) / (tiles * tiles) > 1 ? (2 * kNumSMs) / (tiles * tiles) : 1;
   if (ksplit > kcap) ksplit = kcap;
-  const int bgrid = (int)(ceil_div64(p.Mmax, 256) < kNumSMs * 4 ? ceil_div64(p.Mmax, 256) : kNumSMs * 4);
+  const int bgrid = (int)(ceil_div64(p.Mmax, 8) < kNumSMs * 8 ? ceil_div64(p.Mmax, 8) : kNumSMs * 8);
 
   // accumulators are cleared once here; solve / backsub clear what they consumed for the next iteration
   ba_zero_kernel<<<zgrid > 0 ? zgrid : 1, 256, 0, st>>>(p);
@@ -703,8 +855,12 @@ extern "C" int dpvo_ba_forward(float* poses, float* patches, const float* intrin
     ba_assemble_kernel<<<agrid, kAsmWarps * 32, 0, st>>>(p);
     if (N > 0) {
       ba_schur_kernel<<<dim3(ksplit, tiles * tiles), 256, 0, st>>>(p);
-      if (small)
-        ba_solve_small_kernel<<<1, n <= 96 ? 128 : 256, small_smem, st>>>(p);
+      if (n + 1 <= 64)
+        ba_solve_reg_kernel<4><<<1, 256, reg_smem, st>>>(p);
+      else if (n + 1 <= 128)
+        ba_solve_reg_kernel<8><<<1, 256, reg_smem, st>>>(p);
+      else if (small)
+        ba_solve_small_kernel<<<1, 256, small_smem, st>>>(p);
       else
         ba_solve_big_kernel<<<1, 512, solve_smem, st>>>(p, 0);
     }
