@@ -71,9 +71,27 @@ constexpr int kWarps = 4;     // warps (edges in flight) per CTA
 constexpr int kUMax = 160;    // max pixels in a union bounding box
 constexpr int kRawStride = 168;  // halves; 84 words -> conflict-free fragment stores
 
-template <int NLEV, int R, int P>
+// Native fp16 multiply / add are bit-identical to ATen's "compute in fp32, round once"
+// for these two operations (the fp32 product of two halves is exact; for the sum, 24 bits
+// >= 2*11 + 2 makes the double rounding innocuous), so the blend can use packed HMUL2 / HADD2.
+// The _rn forms forbid contraction into HFMA2, which would drop a rounding.
+__device__ __forceinline__ __half2 h2_mul(__half2 a, __half2 b) { return __hmul2_rn(a, b); }
+__device__ __forceinline__ __half2 h2_add(__half2 a, __half2 b) { return __hadd2_rn(a, b); }
+__device__ __forceinline__ __half2 as_h2(uint32_t v) { return *reinterpret_cast<__half2*>(&v); }
+__device__ __forceinline__ uint32_t as_u32(__half2 v) { return *reinterpret_cast<uint32_t*>(&v); }
+
+// Warp-uniform description of one pyramid level of one edge.
+struct LevelBox {
+  int x0, y0;      // top-left fmap pixel of the union bounding box (window origin included)
+  int bw, nU;      // box width, number of box pixels
+  bool uni;        // the 9 windows fit one box of <= kUMax pixels
+  bool interior;   // ... and the box lies inside the feature map
+};
+
+template <int NLEV>
 __global__ void __launch_bounds__(kWarps * 32, 4)
 corr_fwd_mma_f16_kernel(const __grid_constant__ CorrParams prm) {
+  constexpr int R = 3, P = 3;
   constexpr int PP = P * P;
   constexpr int D = 2 * R + 2;
   constexpr int DO = D - 1;
@@ -83,8 +101,8 @@ corr_fwd_mma_f16_kernel(const __grid_constant__ CorrParams prm) {
   __shared__ __align__(16) __half s_patch[kWarps][PP * C];
   __shared__ __align__(16) __half s_raw[kWarps][NLEV][PP][kRawStride];
   __shared__ int s_bofs[kWarps][NLEV][PP];
-  __shared__ int s_bw[kWarps][NLEV][PP];
-  __shared__ __half s_w[kWarps][NLEV][PP][4];
+  __shared__ int s_fxy[kWarps][NLEV][PP][2];
+  __shared__ __align__(8) __half s_w[kWarps][NLEV][PP][4];
 
   const int lane = threadIdx.x & 31;
   const int wid = threadIdx.x >> 5;
@@ -99,47 +117,22 @@ corr_fwd_mma_f16_kernel(const __grid_constant__ CorrParams prm) {
     const int64_t u = prm.us[m];
     const int64_t v = prm.vs[m];
 
-    // ---- stage the gmap patch (dense blob of PP*C halves) and build A fragments
+    // ---- stage the gmap patch (dense blob of PP*C halves)
     {
       const bool u_ok = (u >= 0) && (u < prm.N1);
       const __half* gp = fmap1 + (int64_t)b * prm.g_sb + (u_ok ? u : 0) * prm.g_sn;
       uint4* dst = reinterpret_cast<uint4*>(&s_patch[wid][0]);
-      for (int i = lane; i < PP * C / 8; i += 32)
-        dst[i] = u_ok ? ldg128(gp + 8 * i) : make_uint4(0, 0, 0, 0);
-    }
-    __syncwarp();
-
-    uint32_t a[8][4];
-    {
-      const unsigned short* sp = reinterpret_cast<const unsigned short*>(&s_patch[wid][0]);
-      const int p_lo = g, p_hi = g + 8;
-      const int off_lo = (p_lo < PP) ? (int)((p_lo / P) * prm.g_sy + (p_lo % P) * prm.g_sx) : -1;
-      const int off_hi = (p_hi < PP) ? (int)((p_hi / P) * prm.g_sy + (p_hi % P) * prm.g_sx) : -1;
-      const int sc = (int)prm.g_sc;
 #pragma unroll
-      for (int s = 0; s < 8; ++s) {
-        const int c0 = 32 * (s >> 1) + 8 * t + 4 * (s & 1);
-        uint32_t lo01 = 0, lo23 = 0, hi01 = 0, hi23 = 0;
-        if (off_lo >= 0) {
-          lo01 = (uint32_t)sp[off_lo + (c0 + 0) * sc] | ((uint32_t)sp[off_lo + (c0 + 1) * sc] << 16);
-          lo23 = (uint32_t)sp[off_lo + (c0 + 2) * sc] | ((uint32_t)sp[off_lo + (c0 + 3) * sc] << 16);
-        }
-        if (off_hi >= 0) {
-          hi01 = (uint32_t)sp[off_hi + (c0 + 0) * sc] | ((uint32_t)sp[off_hi + (c0 + 1) * sc] << 16);
-          hi23 = (uint32_t)sp[off_hi + (c0 + 2) * sc] | ((uint32_t)sp[off_hi + (c0 + 3) * sc] << 16);
-        }
-        a[s][0] = lo01; a[s][1] = hi01; a[s][2] = lo23; a[s][3] = hi23;
-      }
+      for (int i = 0; i < (PP * C / 8 + 31) / 32; ++i)
+        if (lane + 32 * i < PP * C / 8)
+          dst[lane + 32 * i] = u_ok ? ldg128(gp + 8 * (lane + 32 * i)) : make_uint4(0, 0, 0, 0);
     }
 
+    // ---- per level: window origins, blend weights, union bounding box (overlaps the patch load)
+    LevelBox box[NLEV];
 #pragma unroll
     for (int l = 0; l < NLEV; ++l) {
       const CorrLevelDev& L = prm.lev[l];
-      const __half* fm = reinterpret_cast<const __half*>(L.fmap);
-      const bool v_ok = (v >= 0) && (v < L.N2);
-      const __half* fbase = fm + (int64_t)b * L.sb + (v_ok ? v : 0) * L.sn + 8 * t;
-
-      // ---- per patch pixel: window origin and blend weights (lanes 0..PP-1)
       float x = 0.f, y = 0.f;
       if (lane < PP) {
         const float* cp = prm.coords + e * (2 * PP) + lane;
@@ -164,30 +157,66 @@ corr_fwd_mma_f16_kernel(const __grid_constant__ CorrParams prm) {
         s_w[wid][l][lane][2] = h_mul(mdx, hdy);
         s_w[wid][l][lane][3] = h_mul(hdx, hdy);
         s_bofs[wid][l][lane] = uni ? (fy - mny) * ubw + (fx - mnx) : 0;
-        s_bw[wid][l][lane] = uni ? ubw : D;
+        s_fxy[wid][l][lane][0] = fx;
+        s_fxy[wid][l][lane][1] = fy;
       }
+      box[l].x0 = mnx - R;
+      box[l].y0 = mny - R;
+      box[l].bw = uni ? ubw : D;
+      box[l].nU = ubw * ubh;
+      box[l].uni = uni;
+      box[l].interior = uni && (mnx - R >= 0) && (mny - R >= 0) && (mnx - R + ubw <= L.W2) && (mny - R + ubh <= L.H2);
+    }
+    __syncwarp();
 
-      // ---- contraction over the window pixels, 8 pixels per mma tile
-      const int npass = uni ? 1 : PP;
-      for (int pass = 0; pass < npass; ++pass) {
-        int x0, y0, bw, nU;
-        if (uni) {
-          x0 = mnx - R; y0 = mny - R; bw = ubw; nU = ubw * ubh;
-        } else {
-          x0 = __shfl_sync(0xffffffffu, fx, pass) - R;
-          y0 = __shfl_sync(0xffffffffu, fy, pass) - R;
-          bw = D; nU = D * D;
+    // ---- A fragments: rows = patch pixels, contraction order permuted identically to the B loads
+    uint32_t a[8][4];
+    {
+      const unsigned short* sp = reinterpret_cast<const unsigned short*>(&s_patch[wid][0]);
+      const int p_lo = g, p_hi = g + 8;
+      const int off_lo = (p_lo < PP) ? (int)((p_lo / P) * prm.g_sy + (p_lo % P) * prm.g_sx) : -1;
+      const int off_hi = (p_hi < PP) ? (int)((p_hi / P) * prm.g_sy + (p_hi % P) * prm.g_sx) : -1;
+      const int sc = (int)prm.g_sc;
+#pragma unroll
+      for (int s = 0; s < 8; ++s) {
+        const int c0 = 32 * (s >> 1) + 8 * t + 4 * (s & 1);
+        uint32_t lo01 = 0, lo23 = 0, hi01 = 0, hi23 = 0;
+        if (off_lo >= 0) {
+          lo01 = (uint32_t)sp[off_lo + (c0 + 0) * sc] | ((uint32_t)sp[off_lo + (c0 + 1) * sc] << 16);
+          lo23 = (uint32_t)sp[off_lo + (c0 + 2) * sc] | ((uint32_t)sp[off_lo + (c0 + 3) * sc] << 16);
         }
+        if (off_hi >= 0) {
+          hi01 = (uint32_t)sp[off_hi + (c0 + 0) * sc] | ((uint32_t)sp[off_hi + (c0 + 1) * sc] << 16);
+          hi23 = (uint32_t)sp[off_hi + (c0 + 2) * sc] | ((uint32_t)sp[off_hi + (c0 + 3) * sc] << 16);
+        }
+        a[s][0] = lo01; a[s][1] = hi01; a[s][2] = lo23; a[s][3] = hi23;
+      }
+    }
+
+    // ---- contraction over the window pixels, 8 pixels per mma tile, loads two tiles ahead
+#pragma unroll
+    for (int l = 0; l < NLEV; ++l) {
+      const CorrLevelDev& L = prm.lev[l];
+      const __half* fm = reinterpret_cast<const __half*>(L.fmap);
+      const bool v_ok = (v >= 0) && (v < L.N2) && (u >= 0) && (u < prm.N1);
+      const __half* fmv = fm + (int64_t)b * L.sb + (v_ok ? v : 0) * L.sn;
+      if (box[l].uni) {
+        const int x0 = box[l].x0, y0 = box[l].y0, bw = box[l].bw, nU = box[l].nU;
+        const bool interior = box[l].interior;
         const int ntile = (nU + 7) >> 3;
-        int uidx = g;
-        int uy = g / bw;
-        int ux = g - uy * bw;
+        const int sx = (int)L.sx, sy = (int)L.sy;
+        // this lane's pixel walks the box row-major in steps of 8 (bw >= 8: at most one wrap per step)
+        int uidx = g, ux = g, py = y0;
+        const __half* ptr = fmv + (int64_t)y0 * sy + (int64_t)(x0 + g) * sx + 8 * t;
+        const int step = 8 * sx, wrap = sy - bw * sx;
 
         auto load_tile = [&](uint4 (&q)[4]) {
-          const int py = y0 + uy, px = x0 + ux;
-          const bool ok = v_ok && (uidx < nU) && (py >= 0) && (py < L.H2) && (px >= 0) && (px < L.W2);
+          bool ok = v_ok && (uidx < nU);
+          if (!interior) {
+            const int px = x0 + ux;
+            ok = ok && (py >= 0) && (py < L.H2) && (px >= 0) && (px < L.W2);
+          }
           if (ok) {
-            const __half* ptr = fbase + (int64_t)py * L.sy + (int64_t)px * L.sx;
 #pragma unroll
             for (int j = 0; j < 4; ++j) q[j] = ldg128(ptr + 32 * j);
           } else {
@@ -196,13 +225,10 @@ corr_fwd_mma_f16_kernel(const __grid_constant__ CorrParams prm) {
           }
           uidx += 8;
           ux += 8;
-          if (ux >= bw) { ux -= bw; ++uy; }
+          ptr += step;
+          if (ux >= bw) { ux -= bw; ++py; ptr += wrap; }
         };
-
-        uint4 q[4], qn[4];
-        load_tile(q);
-        for (int tile = 0; tile < ntile; ++tile) {
-          if (tile + 1 < ntile) load_tile(qn);
+        auto compute_tile = [&](const uint4 (&q)[4], int tile) {
           float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -210,51 +236,115 @@ corr_fwd_mma_f16_kernel(const __grid_constant__ CorrParams prm) {
             mma_16816(acc, a[2 * j + 1], q[j].z, q[j].w);
           }
           const int col = tile * 8 + 2 * t;
-          if (uni) {
-            if (g < PP)
-              *reinterpret_cast<__half2*>(&s_raw[wid][l][g][col]) = __floats2half2_rn(acc[0], acc[1]);
-            if (g + 8 < PP)
-              *reinterpret_cast<__half2*>(&s_raw[wid][l][g + 8][col]) = __floats2half2_rn(acc[2], acc[3]);
-          } else {
-            if (g == pass)
-              *reinterpret_cast<__half2*>(&s_raw[wid][l][pass][col]) = __floats2half2_rn(acc[0], acc[1]);
-            if (g + 8 == pass)
-              *reinterpret_cast<__half2*>(&s_raw[wid][l][pass][col]) = __floats2half2_rn(acc[2], acc[3]);
-          }
+          *reinterpret_cast<__half2*>(&s_raw[wid][l][g][col]) = __floats2half2_rn(acc[0], acc[1]);   // g < 8 < PP
+          if (g + 8 < PP)
+            *reinterpret_cast<__half2*>(&s_raw[wid][l][g + 8][col]) = __floats2half2_rn(acc[2], acc[3]);
+        };
+
+        uint4 q0[4], q1[4], q2[4];
+        load_tile(q0);
+        load_tile(q1);
+        for (int tile = 0; tile < ntile; tile += 3) {
+          load_tile(q2);
+          compute_tile(q0, tile);
+          if (tile + 1 < ntile) { load_tile(q0); compute_tile(q1, tile + 1); }
+          if (tile + 2 < ntile) { load_tile(q1); compute_tile(q2, tile + 2); }
+        }
+      } else {
+        // Patch pixels too far apart for one box (large scale change): plain per-window dot
+        // products.  Rare; correctness path.
+        const unsigned short* sp = reinterpret_cast<const unsigned short*>(&s_patch[wid][0]);
+        const int sc = (int)prm.g_sc;
+        for (int idx = lane; idx < PP * D * D; idx += 32) {
+          const int p = idx / (D * D);
+          const int w = idx - p * D * D;
+          const int py = s_fxy[wid][l][p][1] - R + w / D;
+          const int px = s_fxy[wid][l][p][0] - R + w % D;
+          float s = 0.f;
+          if (v_ok && py >= 0 && py < L.H2 && px >= 0 && px < L.W2) {
+            const __half* fp = fmv + (int64_t)py * L.sy + (int64_t)px * L.sx;
+            const int off = (int)((p / P) * prm.g_sy + (p % P) * prm.g_sx);
+            for (int c8 = 0; c8 < C / 8; ++c8) {
+              const uint4 q = ldg128(fp + 8 * c8);
+              const __half2* qh = reinterpret_cast<const __half2*>(&q);
 #pragma unroll
-          for (int j = 0; j < 4; ++j) q[j] = qn[j];
+              for (int i = 0; i < 4; ++i) {
+                const float2 f = __half22float2(qh[i]);
+                const __half_raw r0 = {sp[off + (8 * c8 + 2 * i) * sc]};
+                const __half_raw r1 = {sp[off + (8 * c8 + 2 * i + 1) * sc]};
+                s = fmaf(__half2float(__half(r0)), f.x, s);
+                s = fmaf(__half2float(__half(r1)), f.y, s);
+              }
+            }
+          }
+          s_raw[wid][l][p][w] = __float2half_rn(s);
         }
       }
     }
     __syncwarp();
 
-    // ---- bilinear blend (reference rounding points) + write in consumer order
-    for (int o = lane; o < DO * DO * PP; o += 32) {
-      const int p = o % PP;
-      const int r = o / PP;
-      const int yo = r % DO;
-      const int xo = r / DO;
-      __half res[NLEV];
+    // ---- bilinear blend (reference rounding points) + write in consumer order.
+    // lane <-> (window row yo, patch pixel p): 63 pairs in two passes; each lane produces the 7
+    // window columns of its row for all levels, as packed (level0, level1) half2 values.  For a
+    // fixed column the 63 lanes write 63 consecutive outputs -> coalesced stores.
 #pragma unroll
-      for (int l = 0; l < NLEV; ++l) {
-        const int bw = s_bw[wid][l][p];
-        const int bo = s_bofs[wid][l][p] + yo * bw + xo;
-        const __half* rw = &s_raw[wid][l][p][0];
-        const __half c00 = rw[bo], c01 = rw[bo + 1], c10 = rw[bo + bw], c11 = rw[bo + bw + 1];
-        __half acc = h_mul(s_w[wid][l][p][0], c00);
-        acc = h_add(acc, h_mul(s_w[wid][l][p][1], c01));
-        acc = h_add(acc, h_mul(s_w[wid][l][p][2], c10));
-        acc = h_add(acc, h_mul(s_w[wid][l][p][3], c11));
-        res[l] = acc;
-      }
-      if (NLEV == 2 && prm.pair) {
-        __half* op = reinterpret_cast<__half*>(prm.lev[0].out) + e * prm.lev[0].oes + 2 * (int64_t)o;
-        *reinterpret_cast<__half2*>(op) = __halves2half2(res[0], res[NLEV - 1]);
-      } else {
+    for (int pass = 0; pass < 2; ++pass) {
+      const int idx = pass * 32 + lane;
+      if (idx < DO * PP) {
+        const int yo = idx / PP;
+        const int p = idx - yo * PP;
+        uint32_t hv[NLEV][2][4];   // [level][row yo / yo+1][4 words = 8 window columns]
+        uint32_t wv[NLEV][2];      // blend weights (w00,w01),(w10,w11)
 #pragma unroll
         for (int l = 0; l < NLEV; ++l) {
-          __half* op = reinterpret_cast<__half*>(prm.lev[l].out) + e * prm.lev[l].oes + (int64_t)o * prm.lev[l].oel;
-          *op = res[l];
+          const uint32_t* rw = reinterpret_cast<const uint32_t*>(&s_raw[wid][l][0][0]);
+          const int bw = box[l].bw;
+          const int h0 = p * kRawStride + s_bofs[wid][l][p] + yo * bw;
+#pragma unroll
+          for (int r = 0; r < 2; ++r) {
+            const int h = h0 + r * bw;
+            const uint32_t* src = rw + (h >> 1);
+            uint32_t w5[5];
+#pragma unroll
+            for (int i = 0; i < 5; ++i) w5[i] = src[i];
+            const uint32_t sel = (h & 1) ? 0x5432u : 0x3210u;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) hv[l][r][i] = __byte_perm(w5[i], w5[i + 1], sel);
+          }
+          const uint2 wq = *reinterpret_cast<const uint2*>(&s_w[wid][l][p][0]);
+          wv[l][0] = wq.x;
+          wv[l][1] = wq.y;
+        }
+        constexpr int L1 = NLEV - 1;
+        const __half2 W00 = as_h2(__byte_perm(wv[0][0], wv[L1][0], 0x5410));
+        const __half2 W01 = as_h2(__byte_perm(wv[0][0], wv[L1][0], 0x7632));
+        const __half2 W10 = as_h2(__byte_perm(wv[0][1], wv[L1][1], 0x5410));
+        const __half2 W11 = as_h2(__byte_perm(wv[0][1], wv[L1][1], 0x7632));
+        __half2 c0[D], c1[D];      // (level0, level1) raw values of rows yo and yo+1
+#pragma unroll
+        for (int x = 0; x < D; ++x) {
+          const uint32_t sel = (x & 1) ? 0x7632u : 0x5410u;
+          c0[x] = as_h2(__byte_perm(hv[0][0][x >> 1], hv[L1][0][x >> 1], sel));
+          c1[x] = as_h2(__byte_perm(hv[0][1][x >> 1], hv[L1][1][x >> 1], sel));
+        }
+#pragma unroll
+        for (int xo = 0; xo < DO; ++xo) {
+          __half2 acc = h2_mul(W00, c0[xo]);
+          acc = h2_add(acc, h2_mul(W01, c0[xo + 1]));
+          acc = h2_add(acc, h2_mul(W10, c1[xo]));
+          acc = h2_add(acc, h2_mul(W11, c1[xo + 1]));
+          const int64_t o = (xo * DO + yo) * PP + p;
+          if (NLEV == 2 && prm.pair) {
+            __half* op = reinterpret_cast<__half*>(prm.lev[0].out) + e * prm.lev[0].oes + 2 * o;
+            *reinterpret_cast<__half2*>(op) = acc;
+          } else {
+            __half* op0 = reinterpret_cast<__half*>(prm.lev[0].out) + e * prm.lev[0].oes + o * prm.lev[0].oel;
+            *op0 = __low2half(acc);
+            if (NLEV == 2) {
+              __half* op1 = reinterpret_cast<__half*>(prm.lev[L1].out) + e * prm.lev[L1].oes + o * prm.lev[L1].oel;
+              *op1 = __high2half(acc);
+            }
+          }
         }
       }
     }
@@ -435,9 +525,9 @@ extern "C" int dpvo_corr_forward(dpvo_dtype dtype,
     int64_t want = ceil_div64(nedge, kWarps);
     int grid = (int)(want < (int64_t)kNumSMs * 64 ? want : (int64_t)kNumSMs * 64);
     if (nlev == 1)
-      corr_fwd_mma_f16_kernel<1, 3, 3><<<grid, kWarps * 32, 0, st>>>(prm);
+      corr_fwd_mma_f16_kernel<1><<<grid, kWarps * 32, 0, st>>>(prm);
     else
-      corr_fwd_mma_f16_kernel<2, 3, 3><<<grid, kWarps * 32, 0, st>>>(prm);
+      corr_fwd_mma_f16_kernel<2><<<grid, kWarps * 32, 0, st>>>(prm);
     note_launches(1);
     return check_launch("corr_fwd_mma_f16");
   }
