@@ -1,0 +1,97 @@
+"""CPU suite, part 2: the C-ABI library loads and exports every symbol include/dpvo_b200.h declares,
+argument validation fails loudly without touching a GPU, and the Python operator surface refuses
+CPU tensors (there is no CPU fallback in the product path)."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+from conftest import load_pkg, ROOT
+
+HEADER = os.path.join(ROOT, "include", "dpvo_b200.h")
+
+
+def _declared():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(dpvo_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    pkg = load_pkg()
+    names = _declared()
+    assert len(names) >= 14
+    for n in names:
+        assert hasattr(pkg._lib.lib, n), f"{n} declared in include/dpvo_b200.h but not exported"
+
+
+def test_abi_version_matches_header():
+    pkg = load_pkg()
+    ver = int(re.search(r"#define DPVO_B200_ABI_VERSION (\d+)", open(HEADER).read()).group(1))
+    assert pkg._lib.lib.dpvo_abi_version() == ver == pkg._lib.ABI_VERSION
+
+
+def test_workspace_queries_are_host_only_and_monotone():
+    lib = load_pkg()._lib.lib
+    lib.dpvo_ba_workspace_bytes.restype = ctypes.c_int64
+    lib.dpvo_neighbors_workspace_bytes.restype = ctypes.c_int64
+    f = lambda E, N: lib.dpvo_ba_workspace_bytes(ctypes.c_int64(E), ctypes.c_int64(4096 * 96), ctypes.c_int32(N),
+                                                 ctypes.c_int32(0), ctypes.c_int32(96), ctypes.c_int64(4096))
+    assert 0 < f(1000, 10) < f(45312, 10) < f(45312, 64)
+    g = lambda n: lib.dpvo_neighbors_workspace_bytes(ctypes.c_int64(n))
+    assert 0 < g(0) <= g(1000) < g(100000)
+
+
+def test_bad_arguments_return_errors_without_a_gpu():
+    lib = load_pkg()._lib.lib
+    lib.dpvo_last_error.restype = ctypes.c_char_p
+    null = ctypes.c_void_p(0)
+    # nlev = 3 is rejected before any CUDA call
+    rc = lib.dpvo_corr_forward(ctypes.c_int32(0), null, *[ctypes.c_int64(0)] * 5, ctypes.c_int32(1), ctypes.c_int32(128),
+                               ctypes.c_int32(3), ctypes.c_int32(3), null, null, null, ctypes.c_int32(1),
+                               ctypes.c_int32(1), ctypes.c_int32(3), null, ctypes.c_int32(3), null)
+    assert rc != 0 and b"nlev" in lib.dpvo_last_error()
+    # empty edge list is a successful no-op
+    rc = lib.dpvo_corr_forward(ctypes.c_int32(0), null, *[ctypes.c_int64(0)] * 5, ctypes.c_int32(1), ctypes.c_int32(128),
+                               ctypes.c_int32(3), ctypes.c_int32(3), null, null, null, ctypes.c_int32(1),
+                               ctypes.c_int32(0), ctypes.c_int32(3), null, ctypes.c_int32(1), null)
+    assert rc == 0
+    rc = lib.dpvo_ba_forward(null, null, null, null, null, null, null, null, null, ctypes.c_int64(10),
+                             ctypes.c_int64(8), ctypes.c_int64(8 * 96), ctypes.c_int32(3), ctypes.c_int32(96),
+                             ctypes.c_int32(5), ctypes.c_int32(2), ctypes.c_int32(2), ctypes.c_int32(0), null,
+                             ctypes.c_int64(0), null)
+    assert rc != 0 and b"t0" in lib.dpvo_last_error()
+    rc = lib.dpvo_neighbors(null, null, ctypes.c_int64(-1), null, null, null, ctypes.c_int64(0), null)
+    assert rc != 0
+
+
+def test_operator_surface_refuses_cpu_tensors():
+    pkg = load_pkg()
+    g = torch.zeros(1, 4, 128, 3, 3, dtype=torch.float16)
+    f = torch.zeros(1, 2, 128, 8, 8, dtype=torch.float16)
+    c = torch.zeros(1, 5, 2, 3, 3)
+    ii = torch.zeros(5, dtype=torch.int64)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        pkg.altcorr.corr(g, f, c, ii, ii, 3)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        pkg.fastba.neighbors(ii, ii)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        pkg.altcorr.patchify(torch.zeros(1, 8, 6, 6), torch.zeros(1, 3, 2), 1)
+
+
+def test_fastba_argument_order_follows_the_reference_wrapper():
+    """fastba.BA(..., ii, jj, kk, t0, t1, M, iterations, eff_impl) -> forward(..., ii, jj, kk, M, t0, t1, ...)
+    (fastba/ba.py:7-8)."""
+    pkg = load_pkg()
+    seen = {}
+    orig = pkg.cuda_ba.forward
+    try:
+        pkg.cuda_ba.forward = lambda *a: seen.setdefault("args", a) and []
+        p = torch.zeros(1, 4, 7)
+        pkg.fastba.BA(p, 1, 2, 3, 4, 5, "ii", "jj", "kk", 10, 20, 96, 2, True)
+    finally:
+        pkg.cuda_ba.forward = orig
+    a = seen["args"]
+    assert a[6:] == ("ii", "jj", "kk", 96, 10, 20, 2, True)
