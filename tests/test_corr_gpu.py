@@ -229,3 +229,44 @@ def test_full_size_properties():
     sel = np.random.default_rng(0).choice(E, 128, replace=False)
     want = oc.corr_pyramid(d["gmap"], [d["fmap1"], d["fmap2"]], [1.0, 0.25], d["coords"][:, sel], d["us"][sel], d["vs"][sel], 3)
     assert _rel(out[:, torch.from_numpy(sel).cuda()].cpu().numpy(), want) < REL_TOL_F16
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float16])
+def test_corr_backward_vs_oracle_and_reference(dtype):
+    """cuda_corr.backward (correlation_kernel.cu:140-191,237-287) and the autograd path of altcorr.corr.
+    fp32: 1e-5 norm-wise against the float64-accumulating restatement and the reference extension.
+    fp16: ours accumulates in fp32 and rounds once; the reference accumulates with fp16 atomics, so it
+    is compared at the looser fp16-accumulation level."""
+    pkg = load_pkg()
+    rng = np.random.default_rng(21)
+    B, N1, N2, C, P, H2, W2, M, R = 1, 12, 3, 128, 3, 30, 40, 96, 3
+    f1 = rng.standard_normal((B, N1, C, P, P)).astype(dtype)
+    f2 = rng.standard_normal((B, N2, C, H2, W2)).astype(dtype)
+    cx = rng.uniform(-2, W2 + 1, (B, M, 1, 1)); cy = rng.uniform(-2, H2 + 1, (B, M, 1, 1))
+    gy, gx = np.meshgrid(np.arange(P) - 1.0, np.arange(P) - 1.0, indexing="ij")
+    coords = np.stack([cx + gx + rng.normal(0, 0.2, (B, M, P, P)), cy + gy + rng.normal(0, 0.2, (B, M, P, P))], 2).astype(np.float32)
+    coords[0, :4] *= 7.0      # spread-out patches: no compact bounding box
+    us = rng.integers(0, N1, M).astype(np.int64); vs = rng.integers(0, N2, M).astype(np.int64)
+    grad = rng.standard_normal((B, M, 2 * R + 1, 2 * R + 1, P, P)).astype(dtype)
+    w1, w2 = oc.corr_backward(f1, f2, coords, us, vs, grad, R)
+    g1, g2 = pkg.cuda_corr.backward(_dev(f1), _dev(f2), _dev(coords), _dev(us), _dev(vs), _dev(grad), R)
+    assert g1.shape == f1.shape and g2.shape == f2.shape and g1.dtype == _dev(f1).dtype
+    tol = 1e-5 if dtype == np.float32 else 1e-3
+    assert _rel(g1.float().cpu().numpy(), w1) < tol
+    assert _rel(g2.float().cpu().numpy(), w2) < tol
+    # non-contiguous (permuted) upstream gradient, as autograd hands it over
+    gperm = _dev(np.ascontiguousarray(grad.transpose(0, 1, 3, 2, 4, 5))).permute(0, 1, 3, 2, 4, 5)
+    h1, h2 = pkg.cuda_corr.backward(_dev(f1), _dev(f2), _dev(coords), _dev(us), _dev(vs), gperm, R)
+    assert _rel(h1.float().cpu().numpy(), w1) < tol and _rel(h2.float().cpu().numpy(), w2) < tol
+    ref = load_ref("cuda_corr")
+    if ref is not None:
+        r1, r2 = ref.backward(_dev(f1), _dev(f2), _dev(coords), _dev(us), _dev(vs), _dev(grad), R)
+        rt = 1e-5 if dtype == np.float32 else 2e-2
+        assert _rel(g1.float().cpu().numpy(), r1.float().cpu().numpy()) < rt
+        assert _rel(g2.float().cpu().numpy(), r2.float().cpu().numpy()) < rt
+    # autograd: d/dfmap of sum(corr * grad)
+    if dtype == np.float32:
+        t1 = _dev(f1).requires_grad_(True); t2 = _dev(f2).requires_grad_(True)
+        out = pkg.altcorr.corr(t1, t2, _dev(coords), _dev(us), _dev(vs), R)
+        (out * _dev(grad)).sum().backward()
+        assert _rel(t1.grad.cpu().numpy(), w1) < tol and _rel(t2.grad.cpu().numpy(), w2) < tol
