@@ -739,6 +739,21 @@ reproject_kernel(const float* __restrict__ poses, const float* __restrict__ patc
   }
 }
 
+// S (lower triangle) and y row for the blocked solver; clears nothing (a memset follows).
+__global__ void __launch_bounds__(256)
+ba_build_s_kernel(const __grid_constant__ BADev p, float* __restrict__ A, int lda) {
+  const int n = p.n;
+  const int64_t total = (int64_t)(n + 1) * n;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int a = (int)(idx / n), b = (int)(idx - (int64_t)a * n);
+    if (a == n) { A[(int64_t)n * lda + b] = p.v[b] - p.g[b]; continue; }
+    if (b > a) continue;
+    float s = p.U[(int64_t)a * n + b] + p.U[(int64_t)b * n + a] - 0.5f * (p.G[(int64_t)a * n + b] + p.G[(int64_t)b * n + a]);
+    if (a == b) s += 1e-4f * s + 1.0f;
+    A[(int64_t)a * lda + b] = s;
+  }
+}
+
 static int64_t align256(int64_t x) { return (x + 255) & ~(int64_t)255; }
 
 // Carve the workspace; returns total bytes.  With base==nullptr only sizes are computed.
@@ -770,7 +785,7 @@ int64_t ba_carve(BADev& p, char* base, int64_t E, int64_t npatches, int N, int e
   p.C = (float*)take(Mmax * 4);
   p.u = (float*)take(Mmax * 4);
   p.dX = (float*)take((n + 8) * 4);
-  p.Sg = (float*)take(n * n * 4);
+  p.Sg = (float*)take(((n + 1) * (int64_t)chol_lda((int)n) + 2 * n + 64) * 4);
   p.Mmax = Mmax;
   p.W = W;
   if (!eff) {
@@ -859,10 +874,16 @@ extern "C" int dpvo_ba_forward(float* poses, float* patches, const float* intrin
         ba_solve_reg_kernel<4><<<1, 256, reg_smem, st>>>(p);
       else if (n + 1 <= 128)
         ba_solve_reg_kernel<8><<<1, 256, reg_smem, st>>>(p);
-      else if (small)
-        ba_solve_small_kernel<<<1, 256, small_smem, st>>>(p);
-      else
-        ba_solve_big_kernel<<<1, 512, solve_smem, st>>>(p, 0);
+      else {
+        // blocked multi-CTA Cholesky on a global copy of S; U, v, G, g are cleared for the next iteration
+        const int lda = chol_lda(n);
+        const int64_t tot = (int64_t)(n + 1) * n;
+        const int sgrid = (int)(ceil_div64(tot, 256) < kNumSMs * 8 ? ceil_div64(tot, 256) : kNumSMs * 8);
+        ba_build_s_kernel<<<sgrid, 256, 0, st>>>(p, p.Sg, lda);
+        cudaMemsetAsync(p.U, 0, (size_t)(2 * (int64_t)n * n + 2 * n) * sizeof(float), st);
+        note_launches(1);
+        if (ba_chol_solve(p, p.Sg, lda, p.Sg + (int64_t)(n + 1) * lda, st)) return 1;
+      }
     }
     ba_backsub_kernel<<<bgrid, 256, (size_t)(n + 1) * sizeof(float), st>>>(p);
   }

@@ -107,5 +107,7 @@ __device__ __forceinline__ void depth_retract(float* patches, int64_t kx, int PP
 
 int64_t ba_eff_carve(BADev& p, char* base, int64_t E, int64_t npatches, int N, int ppf, int64_t nframes);
 int ba_eff_run(BADev& p, int iterations, cudaStream_t st);
+int ba_chol_solve(const BADev& p, float* A, int lda, float* xbuf, cudaStream_t st);
+inline int chol_lda(int n) { return (n + 63) & ~63; }
 
 }  // namespace dpvo
