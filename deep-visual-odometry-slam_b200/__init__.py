@@ -14,3 +14,4 @@ from . import cuda_corr     # noqa: F401
 from . import altcorr       # noqa: F401
 from . import cuda_ba       # noqa: F401
 from . import fastba        # noqa: F401
+from . import lietorch_backends  # noqa: F401

@@ -142,6 +142,50 @@ int dpvo_reproject(const float* poses, const float* patches, const float* intrin
                    const int64_t* ii, const int64_t* jj, const int64_t* kk,
                    int64_t n_edges, int32_t P, float* coords, void* stream);
 
+/* ----------------------------------------------------------------- lietorch */
+
+/* Element-wise Lie-group operators — replace lietorch_backends (lietorch/src/lietorch.cpp:18-316,
+ * kernels lietorch/src/lietorch_gpu.cu:20-601).  `group` uses the reference's group ids
+ * (lietorch/groups.py:236,252,268,290); SO3 and SE3 are provided, the others return an error.
+ * All tensors are contiguous [n, width] rows of `dt` (DPVO_F32 / DPVO_F64) on the device:
+ * group element N = 4 (SO3: qx qy qz qw) / 7 (SE3: tx ty tz qx qy qz qw), tangent K = 3 / 6
+ * (SE3: tau, phi).  Quaternions are normalised on load like the reference (so3.h:35-37).
+ * Gradients follow lietorch_cpu.cpp: row vectors in the tangent space stored in the first K slots
+ * of an N-wide row (remaining slots written as zero).  Every output element is written. */
+typedef enum { DPVO_LIE_SO3 = 1, DPVO_LIE_RXSO3 = 2, DPVO_LIE_SE3 = 3, DPVO_LIE_SIM3 = 4 } dpvo_lie_group;
+
+int dpvo_lie_expm(int32_t group, dpvo_dtype dt, const void* a /*[n,K]*/, void* X /*[n,N]*/, int64_t n, void* stream);
+int dpvo_lie_expm_backward(int32_t group, dpvo_dtype dt, const void* grad /*[n,N]*/, const void* a /*[n,K]*/,
+                           void* da /*[n,K]*/, int64_t n, void* stream);
+int dpvo_lie_logm(int32_t group, dpvo_dtype dt, const void* X /*[n,N]*/, void* a /*[n,K]*/, int64_t n, void* stream);
+int dpvo_lie_logm_backward(int32_t group, dpvo_dtype dt, const void* grad /*[n,K]*/, const void* X /*[n,N]*/,
+                           void* dX /*[n,N]*/, int64_t n, void* stream);
+int dpvo_lie_inv(int32_t group, dpvo_dtype dt, const void* X, void* Y, int64_t n, void* stream);
+int dpvo_lie_inv_backward(int32_t group, dpvo_dtype dt, const void* grad /*[n,N]*/, const void* X, void* dX,
+                          int64_t n, void* stream);
+int dpvo_lie_mul(int32_t group, dpvo_dtype dt, const void* X, const void* Y, void* Z, int64_t n, void* stream);
+int dpvo_lie_mul_backward(int32_t group, dpvo_dtype dt, const void* grad /*[n,N]*/, const void* X, const void* Y,
+                          void* dX, void* dY, int64_t n, void* stream);
+int dpvo_lie_adj(int32_t group, dpvo_dtype dt, const void* X, const void* a /*[n,K]*/, void* b /*[n,K]*/, int64_t n,
+                 void* stream);
+int dpvo_lie_adj_backward(int32_t group, dpvo_dtype dt, const void* grad /*[n,K]*/, const void* X, const void* a,
+                          void* dX /*[n,N]*/, void* da /*[n,K]*/, int64_t n, void* stream);
+int dpvo_lie_adjT(int32_t group, dpvo_dtype dt, const void* X, const void* a, void* b, int64_t n, void* stream);
+int dpvo_lie_adjT_backward(int32_t group, dpvo_dtype dt, const void* grad /*[n,K]*/, const void* X, const void* a,
+                           void* dX, void* da, int64_t n, void* stream);
+int dpvo_lie_act(int32_t group, dpvo_dtype dt, const void* X, const void* p /*[n,3]*/, void* q /*[n,3]*/, int64_t n,
+                 void* stream);
+int dpvo_lie_act_backward(int32_t group, dpvo_dtype dt, const void* grad /*[n,3]*/, const void* X, const void* p,
+                          void* dX /*[n,N]*/, void* dp /*[n,3]*/, int64_t n, void* stream);
+int dpvo_lie_act4(int32_t group, dpvo_dtype dt, const void* X, const void* p /*[n,4]*/, void* q /*[n,4]*/, int64_t n,
+                  void* stream);
+int dpvo_lie_act4_backward(int32_t group, dpvo_dtype dt, const void* grad /*[n,4]*/, const void* X, const void* p,
+                           void* dX, void* dp /*[n,4]*/, int64_t n, void* stream);
+int dpvo_lie_as_matrix(int32_t group, dpvo_dtype dt, const void* X, void* T4x4 /*[n,4,4]*/, int64_t n, void* stream);
+int dpvo_lie_projector(int32_t group, dpvo_dtype dt, const void* X, void* P /*[n,N,N]*/, int64_t n, void* stream);
+int dpvo_lie_jinv(int32_t group, dpvo_dtype dt, const void* X, const void* a /*[n,K]*/, void* b /*[n,K]*/, int64_t n,
+                  void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -95,3 +95,38 @@ def test_fastba_argument_order_follows_the_reference_wrapper():
         pkg.cuda_ba.forward = orig
     a = seen["args"]
     assert a[6:] == ("ii", "jj", "kk", 96, 10, 20, 2, True)
+
+
+def test_dropin_modules_import_by_bare_name():
+    """The reference imports `cuda_corr`, `cuda_ba`, `lietorch_backends` by bare name
+    (altcorr/correlation.py:2, fastba/ba.py:2, lietorch/group_ops.py:1)."""
+    import subprocess
+    import sys
+    d = os.path.join(ROOT, "deep-visual-odometry-slam_b200", "dropin")
+    code = ("import cuda_corr, cuda_ba, lietorch_backends as lb\n"
+            "assert all(hasattr(cuda_corr, n) for n in ('forward','backward','patchify_forward','patchify_backward'))\n"
+            "assert all(hasattr(cuda_ba, n) for n in ('forward','neighbors','reproject','solve_system'))\n"
+            "names = ['expm','logm','inv','mul','adj','adjT','act','act4']\n"
+            "assert all(hasattr(lb, n) and hasattr(lb, n + '_backward') for n in names)\n"
+            "assert all(hasattr(lb, n) for n in ('as_matrix','projector','Jinv'))\n")
+    env = dict(os.environ, PYTHONPATH=d)
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, cwd="/")
+    assert r.returncode == 0, r.stderr[-2000:]
+
+
+def test_lietorch_refuses_cpu_and_bad_groups():
+    lb = load_pkg("lietorch_backends")
+    X = torch.zeros(3, 7)
+    with pytest.raises(RuntimeError):
+        lb.inv(3, X)
+    with pytest.raises(RuntimeError):
+        lb.inv(2, X)
+    lib = load_pkg()._lib.lib
+    lib.dpvo_last_error.restype = ctypes.c_char_p
+    null = ctypes.c_void_p(0)
+    one = ctypes.c_void_p(256)   # never dereferenced: the group check fails first
+    rc = lib.dpvo_lie_inv(ctypes.c_int32(4), ctypes.c_int32(1), one, one, ctypes.c_int64(5), null)
+    assert rc != 0 and b"group" in lib.dpvo_last_error()
+    rc = lib.dpvo_lie_inv(ctypes.c_int32(3), ctypes.c_int32(0), one, one, ctypes.c_int64(5), null)
+    assert rc != 0 and b"dtype" in lib.dpvo_last_error()
+    assert lib.dpvo_lie_inv(ctypes.c_int32(3), ctypes.c_int32(1), null, null, ctypes.c_int64(0), null) == 0

@@ -1,0 +1,166 @@
+"""GPU parity tests for the lietorch_backends replacement (Python surface -> ctypes -> C ABI ->
+csrc/lietorch.cu), checked against
+  (a) tests/golden/ref_cpu_se3.npz — outputs of the reference's own CPU backend (make_golden_cpu.py),
+  (b) the float64 numpy oracle on larger seeded batches (incl. the small-angle branches),
+  (c) the reference's CUDA extension (oracle/_ref/lietorch_backends.so) on identical inputs, when present.
+Tolerance: fp32 results within 1e-5 relative (norm-wise, plus 2e-5 of the row scale element-wise);
+fp64 within 1e-11.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_pkg
+from oracle import lietorch_oracle as lo
+from oracle.ref_ext import load_ref
+
+pytestmark = pytest.mark.gpu
+SE3 = 3
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_cpu_se3.npz")
+
+
+def _rel(a, b):
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30)
+
+
+def _close(got, want, tol):
+    got = got.detach().cpu().numpy() if torch.is_tensor(got) else got
+    want = np.asarray(want, np.float64)
+    assert got.shape == want.shape, (got.shape, want.shape)
+    assert _rel(got, want) < tol, _rel(got, want)
+    scale = np.abs(want).reshape(want.shape[0], -1).max(1).reshape((-1,) + (1,) * (want.ndim - 1)) + 1.0
+    assert np.all(np.abs(got - want) <= 4 * tol * scale)
+
+
+def _dev(x, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(x)).cuda()
+    return t if dtype is None else t.to(dtype)
+
+
+def _all_ops(lb, d):
+    """Every operator on one input set -> dict name -> tensor (names = golden file keys)."""
+    X, Y = d["X"], d["Y"]
+    out = dict(exp=lb.expm(SE3, d["xi"]), log=lb.logm(SE3, X), inv=lb.inv(SE3, X), mul=lb.mul(SE3, X, Y),
+               adj=lb.adj(SE3, X, d["a6"]), adjT=lb.adjT(SE3, X, d["a6"]), act=lb.act(SE3, X, d["p3"]),
+               act4=lb.act4(SE3, X, d["p4"]), matrix=lb.as_matrix(SE3, X), projector=lb.projector(SE3, X),
+               Jinv=lb.Jinv(SE3, X, d["a6"]))
+    out["expm_bwd"] = lb.expm_backward(SE3, d["gX"], d["xi"])[0]
+    out["logm_bwd"] = lb.logm_backward(SE3, d["g6"], X)[0]
+    out["inv_bwd"] = lb.inv_backward(SE3, d["gX"], X)[0]
+    out["mul_bwd_X"], out["mul_bwd_Y"] = lb.mul_backward(SE3, d["gX"], X, Y)
+    out["act_bwd_X"], out["act_bwd_p"] = lb.act_backward(SE3, d["g3"], X, d["p3"])
+    out["act4_bwd_X"], out["act4_bwd_p"] = lb.act4_backward(SE3, d["g4"], X, d["p4"])
+    out["adj_bwd_X"], out["adj_bwd_a"] = lb.adj_backward(SE3, d["g6"], X, d["a6"])
+    out["adjT_bwd_X"], out["adjT_bwd_a"] = lb.adjT_backward(SE3, d["g6"], X, d["a6"])
+    return out
+
+
+def _oracle_all(d):
+    X, Y = d["X"], d["Y"]
+    out = dict(exp=lo.exp(d["xi"]), log=lo.log(X), inv=lo.inv(X), mul=lo.mul(X, Y), adj=lo.adj(X, d["a6"]),
+               adjT=lo.adjT(X, d["a6"]), act=lo.act(X, d["p3"]), act4=lo.act4(X, d["p4"]), matrix=lo.matrix(X),
+               projector=lo.projector(X), Jinv=lo.jinv(X, d["a6"]))
+    out["expm_bwd"] = lo.exp_backward(d["gX"], d["xi"])
+    out["logm_bwd"] = lo.log_backward(d["g6"], X)
+    out["inv_bwd"] = lo.inv_backward(d["gX"], X)
+    out["mul_bwd_X"], out["mul_bwd_Y"] = lo.mul_backward(d["gX"], X, Y)
+    out["act_bwd_X"], out["act_bwd_p"] = lo.act_backward(d["g3"], X, d["p3"])
+    out["act4_bwd_X"], out["act4_bwd_p"] = lo.act4_backward(d["g4"], X, d["p4"])
+    out["adj_bwd_X"], out["adj_bwd_a"] = lo.adj_backward(d["g6"], X, d["a6"])
+    out["adjT_bwd_X"], out["adjT_bwd_a"] = lo.adjT_backward(d["g6"], X, d["a6"])
+    return out
+
+
+def _inputs(n, seed, dtype=np.float32):
+    r = np.random.default_rng(seed)
+    xi = r.standard_normal((n, 6)) * np.array([0.5, 0.5, 0.5, 0.9, 0.9, 0.9])
+    xi[: n // 16, 3:] *= 1e-7          # small-angle branches of Exp / Jacobians
+    xi[n // 16] = 0
+    X = lo.exp(xi)
+    X[:, 3:] *= r.uniform(0.5, 2.0, (n, 1))   # un-normalised quaternions: normalised on load
+    Y = lo.exp(r.standard_normal((n, 6)) * 0.3)
+    d = dict(xi=xi, X=X, Y=Y, p3=r.standard_normal((n, 3)),
+             p4=np.concatenate([r.standard_normal((n, 3)), r.uniform(0, 1, (n, 1))], 1),
+             a6=r.standard_normal((n, 6)), gX=r.standard_normal((n, 7)), g3=r.standard_normal((n, 3)),
+             g4=r.standard_normal((n, 4)), g6=r.standard_normal((n, 6)))
+    return {k: v.astype(dtype) for k, v in d.items()}
+
+
+def test_golden_reference_cpu_vectors():
+    lb = load_pkg("lietorch_backends")
+    g = dict(np.load(GOLD))
+    d = {k: _dev(g[k]) for k in ("xi", "X", "Y", "p3", "p4", "a6", "gX", "g3", "g4", "g6")}
+    got = _all_ops(lb, d)
+    _close(got["exp"], g["X"], 1e-5)
+    for k, v in got.items():
+        if k == "exp":
+            continue
+        _close(v, g[k], 2e-5)
+
+
+@pytest.mark.parametrize("n", [1, 127, 128, 129, 5000])
+def test_f32_vs_oracle(n):
+    lb = load_pkg("lietorch_backends")
+    d = _inputs(n, seed=n)
+    want = _oracle_all(d)
+    got = _all_ops(lb, {k: _dev(v) for k, v in d.items()})
+    for k in want:
+        assert got[k].dtype == torch.float32
+        _close(got[k], want[k], 2e-5)
+
+
+def test_f64_vs_oracle():
+    lb = load_pkg("lietorch_backends")
+    d = _inputs(777, seed=5, dtype=np.float64)
+    want = _oracle_all(d)
+    got = _all_ops(lb, {k: _dev(v) for k, v in d.items()})
+    for k in want:
+        assert got[k].dtype == torch.float64
+        _close(got[k], want[k], 1e-10)
+
+
+def test_vs_reference_cuda_extension():
+    ref = load_ref("lietorch_backends")
+    if ref is None:
+        pytest.skip("oracle/_ref/lietorch_backends.so not built")
+    lb = load_pkg("lietorch_backends")
+    d = {k: _dev(v) for k, v in _inputs(4096, seed=9).items()}
+    want = _all_ops(ref, d)
+    got = _all_ops(lb, d)
+    for k in want:
+        _close(got[k], want[k].cpu().numpy(), 2e-5)
+
+
+def test_empty_and_errors():
+    lb = load_pkg("lietorch_backends")
+    e = torch.empty(0, 7, device="cuda")
+    assert lb.inv(SE3, e).shape == (0, 7)
+    assert lb.logm(SE3, e).shape == (0, 6)
+    X = torch.zeros(4, 7, device="cuda")
+    X[:, 6] = 1
+    with pytest.raises(RuntimeError):
+        lb.inv(SE3, X.cpu())                      # no CPU path
+    with pytest.raises(RuntimeError):
+        lb.inv(SE3, X.t().contiguous().t())       # non-contiguous
+    with pytest.raises(RuntimeError):
+        lb.inv(4, X)                              # Sim3 not provided
+    with pytest.raises(RuntimeError):
+        lb.mul(SE3, X, X[:2])                     # batch mismatch
+
+
+def test_so3_roundtrip():
+    lb = load_pkg("lietorch_backends")
+    r = np.random.default_rng(0)
+    phi = _dev((r.standard_normal((300, 3)) * 0.9).astype(np.float32))
+    q = lb.expm(1, phi)
+    assert torch.allclose(q.norm(dim=1), torch.ones(300, device="cuda"), atol=1e-6)
+    assert torch.allclose(lb.logm(1, q), phi, atol=2e-6)
+    p = _dev(r.standard_normal((300, 3)).astype(np.float32))
+    back = lb.act(1, lb.inv(1, q), lb.act(1, q, p))
+    assert torch.allclose(back, p, atol=1e-5)
+    want = lo.quat_rot(lo.so3_exp(phi.cpu().numpy().astype(np.float64)), p.cpu().numpy().astype(np.float64))
+    _close(lb.act(1, q, p), want, 2e-5)
