@@ -198,7 +198,7 @@ ba_zero_kernel(const __grid_constant__ BADev p) {
   const int64_t nfix = 2 * n * n + 2 * n;  // U, v, G, g are contiguous
   const int64_t total = nfix + 2 * (int64_t)M + (int64_t)M * n;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    if (i < nfix) p.U[i] = 0.f;
+    if (i < nfix) p.U[i] = 0.0;
     else if (i < nfix + M) p.C[i - nfix] = 0.f;
     else if (i < nfix + 2 * (int64_t)M) p.u[i - nfix - M] = 0.f;
     else p.Et[i - nfix - 2 * (int64_t)M] = 0.f;
@@ -281,17 +281,28 @@ ba_assemble_kernel(const __grid_constant__ BADev p) {
       cc += w * Jz * Jz;
       uu += w * r * Jz;
     }
-    float* et = p.Et + (int64_t)k * n;
-    if (ix >= 0) {
+    if (p.Et) {
+      float* et = p.Et + (int64_t)k * n;
+      if (ix >= 0) {
 #pragma unroll
-      for (int a = 0; a < 6; ++a) atomicAdd(&et[6 * ix + a], ei[a]);
-    }
-    if (jx >= 0) {
+        for (int a = 0; a < 6; ++a) atomicAdd(&et[6 * ix + a], ei[a]);
+      }
+      if (jx >= 0) {
 #pragma unroll
-      for (int a = 0; a < 6; ++a) atomicAdd(&et[6 * jx + a], ej[a]);
+        for (int a = 0; a < 6; ++a) atomicAdd(&et[6 * jx + a], ej[a]);
+      }
+    } else {
+      // block-E path: the edge's two E entries (w.r.t. its source and target pose) stay per edge
+      float4* ee = reinterpret_cast<float4*>(p.Ee + (int64_t)p.perm[pos] * 12);
+      ee[0] = make_float4(ei[0], ei[1], ei[2], ei[3]);
+      ee[1] = make_float4(ei[4], ei[5], ej[0], ej[1]);
+      ee[2] = make_float4(ej[2], ej[3], ej[4], ej[5]);
     }
     atomicAdd(&p.C[k], cc);
     atomicAdd(&p.u[k], uu);
+  } else if (act && !p.Et) {
+    float4* ee = reinterpret_cast<float4*>(p.Ee + (int64_t)p.perm[pos] * 12);
+    ee[0] = ee[1] = ee[2] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   if (ix < 0 && jx < 0) return;  // both poses fixed: no pose blocks (warp-uniform)
 
@@ -311,22 +322,22 @@ ba_assemble_kernel(const __grid_constant__ BADev p) {
     if (idx < 21) {
       if (ix >= 0) {
         const int a = c_tri_a[idx], b = c_tri_b[idx];
-        atomicAdd(&p.U[(oi + a) * n + oi + b], (a == b ? 0.5f : 1.0f) * val);
+        atomicAdd(&p.U[(oi + a) * n + oi + b], (double)((a == b ? 0.5f : 1.0f) * val));
       }
     } else if (idx < 42) {
       if (jx >= 0) {
         const int a = c_tri_a[idx - 21], b = c_tri_b[idx - 21];
-        atomicAdd(&p.U[(oj + a) * n + oj + b], (a == b ? 0.5f : 1.0f) * val);
+        atomicAdd(&p.U[(oj + a) * n + oj + b], (double)((a == b ? 0.5f : 1.0f) * val));
       }
     } else if (idx < 78) {
       if (ix >= 0 && jx >= 0) {
         const int a = (idx - 42) / 6, b = (idx - 42) % 6;
-        atomicAdd(&p.U[(oi + a) * n + oj + b], -val);
+        atomicAdd(&p.U[(oi + a) * n + oj + b], (double)-val);
       }
     } else if (idx < 84) {
-      if (ix >= 0) atomicAdd(&p.v[oi + idx - 78], val);
+      if (ix >= 0) atomicAdd(&p.v[oi + idx - 78], (double)val);
     } else if (idx < 90) {
-      if (jx >= 0) atomicAdd(&p.v[oj + idx - 84], val);
+      if (jx >= 0) atomicAdd(&p.v[oj + idx - 84], (double)val);
     }
   }
 }
@@ -348,12 +359,12 @@ ba_schur_kernel(const __grid_constant__ BADev p) {
   const int a0 = ta * 64, b0 = tb * 64;
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
   const float lm = p.lmbda[0];
-  float acc[4][4];
+  double acc[4][4];
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-  float gacc = 0.f;
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+  double gacc = 0.0;
 
   for (int k0 = blockIdx.x * kSchurKC; k0 < M; k0 += gridDim.x * kSchurKC) {
     for (int i = threadIdx.x; i < kSchurKC * 64; i += blockDim.x) {
@@ -381,10 +392,10 @@ ba_schur_kernel(const __grid_constant__ BADev p) {
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] += av[i] * bv[j];
+        for (int j = 0; j < 4; ++j) acc[i][j] += (double)av[i] * (double)bv[j];
     }
     if (tb == 0 && threadIdx.x < 64) {
-      for (int kk_ = 0; kk_ < kSchurKC; ++kk_) gacc += As[kk_][threadIdx.x] * us[kk_];
+      for (int kk_ = 0; kk_ < kSchurKC; ++kk_) gacc += (double)As[kk_][threadIdx.x] * (double)us[kk_];
     }
     __syncthreads();
   }
@@ -393,9 +404,9 @@ ba_schur_kernel(const __grid_constant__ BADev p) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int a = a0 + ty * 4 + i, b = b0 + tx * 4 + j;
-      if (a < n && b < n && acc[i][j] != 0.f) atomicAdd(&p.G[(int64_t)a * n + b], acc[i][j]);
+      if (a < n && b < n && acc[i][j] != 0.0) atomicAdd(&p.G[(int64_t)a * n + b], acc[i][j]);
     }
-  if (tb == 0 && threadIdx.x < 64 && a0 + threadIdx.x < n && gacc != 0.f) atomicAdd(&p.g[a0 + threadIdx.x], gacc);
+  if (tb == 0 && threadIdx.x < 64 && a0 + threadIdx.x < n && gacc != 0.0) atomicAdd(&p.g[a0 + threadIdx.x], gacc);
 }
 
 // ------------------------------------------------------------- solve (registers)
@@ -430,15 +441,15 @@ ba_solve_reg_kernel(const __grid_constant__ BADev p) {
       const int i = ti + 16 * r, k = tk + 16 * c;
       float s = 0.f;
       if (i < n && k <= i) {
-        s = p.U[i * n + k] + p.U[k * n + i] - 0.5f * (p.G[i * n + k] + p.G[k * n + i]);
+        s = (float)(p.U[i * n + k] + p.U[k * n + i] - 0.5 * (p.G[i * n + k] + p.G[k * n + i]));
         if (i == k) s += 1e-4f * s + 1.0f;
       } else if (i == n && k < n) {
-        s = p.v[k] - p.g[k];
+        s = (float)(p.v[k] - p.g[k]);
       }
       a[r][c] = s;
     }
   __syncthreads();   // every element has been read: U, v, G, g (contiguous) can be cleared
-  for (int i = tid; i < 2 * n * n + 2 * n; i += 256) p.U[i] = 0.f;
+  for (int i = tid; i < 2 * n * n + 2 * n; i += 256) p.U[i] = 0.0;
 
   bool fail = false;
 #pragma unroll
@@ -533,13 +544,13 @@ ba_solve_small_kernel(const __grid_constant__ BADev p) {
   if (tid == 0) s_fail = 0;
   for (int a = wid; a < n; a += nw)
     for (int b = lane; b <= a; b += 32) {
-      float s = p.U[a * n + b] + p.U[b * n + a] - 0.5f * (p.G[a * n + b] + p.G[b * n + a]);
+      float s = (float)(p.U[a * n + b] + p.U[b * n + a] - 0.5 * (p.G[a * n + b] + p.G[b * n + a]));
       if (a == b) s += 1e-4f * s + 1.0f;
       A[a * ld + b] = s;
     }
-  for (int i = tid; i < n; i += T) A[n * ld + i] = p.v[i] - p.g[i];
+  for (int i = tid; i < n; i += T) A[n * ld + i] = (float)(p.v[i] - p.g[i]);
   __syncthreads();
-  for (int i = tid; i < 2 * n * n + 2 * n; i += T) p.U[i] = 0.f;   // U, v, G, g contiguous
+  for (int i = tid; i < 2 * n * n + 2 * n; i += T) p.U[i] = 0.0;   // U, v, G, g contiguous
 
   // thread -> (row group rg, column lane cl): owns columns k == cl (mod 64) and rows i == rg (mod T/64)
   const int cl = tid & 63, rg = tid >> 6, nrg = T >> 6;
@@ -609,14 +620,14 @@ ba_solve_big_kernel(const __grid_constant__ BADev p, int s_in_smem) {
   for (int i = tid; i < n * n; i += T) {
     const int a = i / n, b = i - a * n;
     if (b <= a) {
-      float s = p.U[(int64_t)a * n + b] + p.U[(int64_t)b * n + a] - 0.5f * (p.G[(int64_t)a * n + b] + p.G[(int64_t)b * n + a]);
+      float s = (float)(p.U[(int64_t)a * n + b] + p.U[(int64_t)b * n + a] - 0.5 * (p.G[(int64_t)a * n + b] + p.G[(int64_t)b * n + a]));
       if (a == b) s += 1e-4f * s + 1.0f;
       S[(int64_t)a * n + b] = s;
     }
   }
-  for (int i = tid; i < n; i += T) y[i] = p.v[i] - p.g[i];
+  for (int i = tid; i < n; i += T) y[i] = (float)(p.v[i] - p.g[i]);
   __syncthreads();
-  for (int i = tid; i < 2 * n * n + 2 * n; i += T) p.U[i] = 0.f;   // U, v, G, g contiguous: clear for the next iteration
+  for (int i = tid; i < 2 * n * n + 2 * n; i += T) p.U[i] = 0.0;   // U, v, G, g contiguous: clear for the next iteration
 
   for (int j = 0; j < n; ++j) {
     if (tid == 0) {
@@ -744,11 +755,12 @@ __global__ void __launch_bounds__(256)
 ba_build_s_kernel(const __grid_constant__ BADev p, float* __restrict__ A, int lda) {
   const int n = p.n;
   const int64_t total = (int64_t)(n + 1) * n;
+  if (blockIdx.x == 0 && threadIdx.x == 0) p.meta[1] = 0;   // failure flag of THIS iteration's factorisation
   for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
     const int a = (int)(idx / n), b = (int)(idx - (int64_t)a * n);
-    if (a == n) { A[(int64_t)n * lda + b] = p.v[b] - p.g[b]; continue; }
+    if (a == n) { A[(int64_t)n * lda + b] = (float)(p.v[b] - p.g[b]); continue; }
     if (b > a) continue;
-    float s = p.U[(int64_t)a * n + b] + p.U[(int64_t)b * n + a] - 0.5f * (p.G[(int64_t)a * n + b] + p.G[(int64_t)b * n + a]);
+    float s = (float)(p.U[(int64_t)a * n + b] + p.U[(int64_t)b * n + a] - 0.5 * (p.G[(int64_t)a * n + b] + p.G[(int64_t)b * n + a]));
     if (a == b) s += 1e-4f * s + 1.0f;
     A[(int64_t)a * lda + b] = s;
   }
@@ -777,8 +789,8 @@ int64_t ba_carve(BADev& p, char* base, int64_t E, int64_t npatches, int N, int e
   p.ekey = (int*)take(E * 4);
   p.kx = (int64_t*)take(Mmax * 8);
   // U, v, G, g contiguous (zeroed as one range)
-  char* fixed = take((2 * n * n + 2 * n) * 4);
-  p.U = (float*)fixed;
+  char* fixed = take((2 * n * n + 2 * n) * 8);
+  p.U = (double*)fixed;
   p.v = p.U + n * n;
   p.G = p.v + n;
   p.g = p.G + n * n;
@@ -795,6 +807,39 @@ int64_t ba_carve(BADev& p, char* base, int64_t E, int64_t npatches, int N, int e
     off += ba_eff_carve(p, base ? base + off : nullptr, E, npatches, N, ppf, nframes);
   }
   return off;
+}
+
+
+void ba_launch_assemble(const BADev& p, cudaStream_t st) {
+  const int64_t max_tasks = p.E / 32 + p.K + 1;
+  const int agrid = (int)ceil_div64(max_tasks, kAsmWarps);
+  ba_assemble_kernel<<<agrid, kAsmWarps * 32, 0, st>>>(p);
+  note_launches(1);
+}
+
+int ba_launch_solve(const BADev& p, cudaStream_t st) {
+  const int n = p.n;
+  const int ld = (n + 2) | 1;
+  const size_t reg_smem = ((size_t)n * ld + 2 * 16 * 8 + 2 * (size_t)n) * sizeof(float);
+  if (n + 1 <= 64) {
+    ba_solve_reg_kernel<4><<<1, 256, reg_smem, st>>>(p);
+    note_launches(1);
+  } else if (n + 1 <= 128) {
+    if (reg_smem > 48 * 1024)
+      cudaFuncSetAttribute(ba_solve_reg_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)reg_smem);
+    ba_solve_reg_kernel<8><<<1, 256, reg_smem, st>>>(p);
+    note_launches(1);
+  } else {
+    // blocked multi-CTA Cholesky on a global copy of S; U, v, G, g are cleared for the next iteration
+    const int lda = chol_lda(n);
+    const int64_t tot = (int64_t)(n + 1) * n;
+    const int sgrid = (int)(ceil_div64(tot, 256) < kNumSMs * 8 ? ceil_div64(tot, 256) : kNumSMs * 8);
+    ba_build_s_kernel<<<sgrid, 256, 0, st>>>(p, p.Sg, lda);
+    cudaMemsetAsync(p.U, 0, (size_t)(2 * (int64_t)n * n + 2 * n) * sizeof(double), st);
+    note_launches(1);
+    if (ba_chol_solve(p, p.Sg, lda, p.Sg + (int64_t)(n + 1) * lda, st)) return 1;
+  }
+  return check_launch("ba_solve");
 }
 
 }  // namespace dpvo
@@ -834,30 +879,22 @@ extern "C" int dpvo_ba_forward(float* poses, float* patches, const float* intrin
   p.ii = ii; p.jj = jj; p.kk = kk; p.E = n_edges; p.nframes = n_frames_total; p.npatches = n_patches_total;
   p.P = P; p.t0 = t0; p.N = N; p.n = 6 * N; p.ppf = ppf;
 
-  DPVO_REQUIRE(N <= 2048, "ba_forward: dense path supports at most 2048 free poses (use eff_impl)");
+  DPVO_REQUIRE(eff_impl || N <= 2048, "ba_forward: dense path supports at most 2048 free poses (use eff_impl)");
+  DPVO_REQUIRE(N <= 8192, "ba_forward: at most 8192 free poses");
   const int egrid = (int)(ceil_div64(n_edges, 256) < kNumSMs * 8 ? ceil_div64(n_edges, 256) : kNumSMs * 8);
   cudaMemsetAsync(p.bitmap, 0, reinterpret_cast<char*>(p.meta) + 64 - reinterpret_cast<char*>(p.bitmap), st);
   ba_prep_kernel<<<egrid, 256, 0, st>>>(p);
   ba_prefix_kernel<<<1, 1024, 0, st>>>(p);
   if (check_launch("ba_prefix")) return 1;
 
-  if (eff_impl) return ba_eff_run(p, iterations, st);
-
   ba_scatter_kernel<<<egrid, 256, 0, st>>>(p);
+  if (eff_impl) {
+    note_launches(3);
+    return ba_eff_run(p, iterations, st);
+  }
   const int n = p.n;
-  const int ld = (n + 2) | 1;
-  const size_t small_smem = ((size_t)(n + 1) * ld + 2 * (size_t)n) * sizeof(float);
-  const bool small = N > 0 && small_smem <= 220 * 1024;
-  if (small && small_smem > 48 * 1024)
-    cudaFuncSetAttribute(ba_solve_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)small_smem);
-  const size_t solve_smem = (size_t)n * sizeof(float);
-  const size_t reg_smem = ((size_t)n * ld + 2 * 16 * 8 + 2 * (size_t)n) * sizeof(float);
-  if (n + 1 <= 128 && reg_smem > 48 * 1024)
-    cudaFuncSetAttribute(ba_solve_reg_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)reg_smem);
   const int64_t zero_total = 2 * (int64_t)n * n + 2 * n + 2 * p.Mmax + p.Mmax * n;
   const int zgrid = (int)(ceil_div64(zero_total, 256 * 8) < kNumSMs * 4 ? ceil_div64(zero_total, 256 * 8) : kNumSMs * 4);
-  const int64_t max_tasks = n_edges / 32 + p.K + 1;
-  const int agrid = (int)ceil_div64(max_tasks, kAsmWarps);
   const int tiles = n > 0 ? (n + 63) / 64 : 1;
   int ksplit = (int)ceil_div64(p.Mmax, kSchurKC);
   const int kcap = (2 * kNumSMs) / (tiles * tiles) > 1 ? (2 * kNumSMs) / (tiles * tiles) : 1;
@@ -867,27 +904,15 @@ extern "C" int dpvo_ba_forward(float* poses, float* patches, const float* intrin
   // accumulators are cleared once here; solve / backsub clear what they consumed for the next iteration
   ba_zero_kernel<<<zgrid > 0 ? zgrid : 1, 256, 0, st>>>(p);
   for (int it = 0; it < iterations; ++it) {
-    ba_assemble_kernel<<<agrid, kAsmWarps * 32, 0, st>>>(p);
+    ba_launch_assemble(p, st);
     if (N > 0) {
       ba_schur_kernel<<<dim3(ksplit, tiles * tiles), 256, 0, st>>>(p);
-      if (n + 1 <= 64)
-        ba_solve_reg_kernel<4><<<1, 256, reg_smem, st>>>(p);
-      else if (n + 1 <= 128)
-        ba_solve_reg_kernel<8><<<1, 256, reg_smem, st>>>(p);
-      else {
-        // blocked multi-CTA Cholesky on a global copy of S; U, v, G, g are cleared for the next iteration
-        const int lda = chol_lda(n);
-        const int64_t tot = (int64_t)(n + 1) * n;
-        const int sgrid = (int)(ceil_div64(tot, 256) < kNumSMs * 8 ? ceil_div64(tot, 256) : kNumSMs * 8);
-        ba_build_s_kernel<<<sgrid, 256, 0, st>>>(p, p.Sg, lda);
-        cudaMemsetAsync(p.U, 0, (size_t)(2 * (int64_t)n * n + 2 * n) * sizeof(float), st);
-        note_launches(1);
-        if (ba_chol_solve(p, p.Sg, lda, p.Sg + (int64_t)(n + 1) * lda, st)) return 1;
-      }
+      note_launches(1);
+      if (ba_launch_solve(p, st)) return 1;
     }
     ba_backsub_kernel<<<bgrid, 256, (size_t)(n + 1) * sizeof(float), st>>>(p);
   }
-  note_launches(4 + iterations * (N > 0 ? 4 : 2));
+  note_launches(4 + iterations);
   return check_launch("ba_forward");
 }
 

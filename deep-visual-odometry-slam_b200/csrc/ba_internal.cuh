@@ -18,16 +18,15 @@ struct BADev {
   int K;
   int *hist, *cursor, *off, *toff, *perm, *ekey;
   // normal equations (dense path)
-  float *U, *v, *G, *g, *C, *u, *Et, *dX, *Sg;
-  // block-E path (global BA)
-  int* pair_id;      // [nframes*nframes] -> dense pair index or -1   (only when small) / hash otherwise
-  float* Eb;         // [npairs][ppf][6]
-  int* pair_i; int* pair_j;  // [npairs]
-  int* row_ptr;      // CSR over source frames -> pairs
-  int64_t npairs_max;
-  unsigned long long* pair_keys; int pair_cap;  // open-addressing table of (i,j) keys
-  int* pair_slot_of_edge;   // [E] slot of (i,j)
-  int* self_slot_of_edge;   // [E] slot of (i,i)
+  // U, v, G, g are float64 accumulators: S = B - E Q E^T cancels most of B, so the sums over
+  // ~10^3-10^4 edge / patch terms are kept exact to fp32 rounding and S, y are rounded once.
+  double *U, *v, *G, *g;
+  float *C, *u, *Et, *dX, *Sg;
+  // block-E path (global BA): E is kept as two 6-vectors per edge (entries w.r.t. the edge's
+  // source and target pose), edges are grouped by source frame for the Schur product
+  float* Ee;         // [E][12]  (ei[6], ej[6]); zero for masked edges
+  float* w;          // [Mmax]   E^T dX accumulator
+  int *fhist, *foff, *fcursor, *fperm;   // counting sort of the edges by source frame (nframes keys)
 };
 
 struct EdgeTerms {
@@ -107,6 +106,9 @@ __device__ __forceinline__ void depth_retract(float* patches, int64_t kx, int PP
 
 int64_t ba_eff_carve(BADev& p, char* base, int64_t E, int64_t npatches, int N, int ppf, int64_t nframes);
 int ba_eff_run(BADev& p, int iterations, cudaStream_t st);
+// shared with the block-E path (defined in ba.cu)
+void ba_launch_assemble(const BADev& p, cudaStream_t st);
+int ba_launch_solve(const BADev& p, cudaStream_t st);   // S = B - G (+damping), Cholesky, dX, pose retraction; clears U, v, G, g
 int ba_chol_solve(const BADev& p, float* A, int lda, float* xbuf, cudaStream_t st);
 inline int chol_lda(int n) { return (n + 63) & ~63; }
 

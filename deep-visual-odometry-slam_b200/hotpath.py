@@ -118,21 +118,43 @@ class UpdateHotPath:
         return corr
 
     # ------------------------------------------------------------------ host-buffer variant
+    _PER_FRAME = ("new_f1", "new_f2", "new_imap", "centres", "target", "weight")
+
     def make_host_inputs(self):
-        """Pinned host copies of the per-frame inputs (encoder outputs + network outputs)."""
+        """Pinned host copies of the per-frame inputs (encoder outputs + network outputs), plus the
+        double-buffered device staging sets and the copy stream of the streaming pipeline."""
         pin = lambda t: t.cpu().pin_memory()
-        return dict(f1=pin(self.new_f1), f2=pin(self.new_f2), imap=pin(self.new_imap), centres=pin(self.centres),
-                    target=pin(self.target), weight=pin(self.weight))
+        hin = {k: pin(getattr(self, k)) for k in self._PER_FRAME}
+        self._sets = [{k: getattr(self, k) for k in self._PER_FRAME},
+                      {k: torch.empty_like(getattr(self, k)) for k in self._PER_FRAME}]
+        self._copy_stream = torch.cuda.Stream(self.device)
+        self._copied = [torch.cuda.Event() for _ in range(2)]
+        self._consumed = [torch.cuda.Event() for _ in range(2)]
+        self._frame = 0
+        return hin
 
     def step_host(self, hin, hout):
-        """Same frame with host<->device copies inside: inputs from pinned host memory, updated
-        window poses and patch inverse depths read back.  Returns (h2d_bytes, d2h_bytes)."""
+        """Same frame with host<->device copies inside, as a streaming front end would run it: frame
+        k's inputs go from pinned host memory into staging set k%2 on a copy stream (overlapping frame
+        k-1's kernels on the compute stream), the compute stream waits for that copy, runs the frame
+        and reads the updated window poses and patch inverse depths back.  Every frame's bytes cross
+        PCIe inside the caller's timed region.  Returns (h2d_bytes, d2h_bytes)."""
+        b = self._frame & 1
+        self._frame += 1
+        compute = torch.cuda.current_stream(self.device)
+        dst = self._sets[b]
         h2d = 0
-        for name, dst in (("f1", self.new_f1), ("f2", self.new_f2), ("imap", self.new_imap),
-                          ("centres", self.centres), ("target", self.target), ("weight", self.weight)):
-            dst.copy_(hin[name], non_blocking=True)
-            h2d += hin[name].numel() * hin[name].element_size()
+        with torch.cuda.stream(self._copy_stream):
+            self._copy_stream.wait_event(self._consumed[b])       # set b's previous frame is done with it
+            for k in self._PER_FRAME:
+                dst[k].copy_(hin[k], non_blocking=True)
+                h2d += hin[k].numel() * hin[k].element_size()
+            self._copied[b].record(self._copy_stream)
+        compute.wait_event(self._copied[b])
+        for k in self._PER_FRAME:
+            setattr(self, k, dst[k])
         self.step()
+        self._consumed[b].record(compute)
         pw = self.poses[0, self.t0:self.t1]
         dz = self.patches[0, :, 2, 0, 0]
         hout["poses"].copy_(pw, non_blocking=True)

@@ -135,6 +135,69 @@ def test_ba_masked_and_degenerate_edges():
     _check_against(d, got, want)
 
 
+def _with_loop_edges(synth, n_frames, M, seed, hub=None, n_pairs=12):
+    """DPVO-rule edges plus loop-closure style edges (all M patches of frame i -> far frame j,
+    patchgraph.py:56-82 shape) and optionally a hub frame whose patches see every later frame."""
+    rng = np.random.default_rng(seed)
+    ii, jj, kk = synth.dpvo_edges(n_frames, M)
+    extra = []
+    for _ in range(n_pairs):
+        i = int(rng.integers(0, n_frames)); j = int(rng.integers(0, n_frames))
+        if abs(i - j) > 14:
+            extra.append((i, j))
+    if hub is not None:
+        extra += [(hub, j) for j in range(n_frames) if abs(j - hub) > 13]
+    for i, j in extra:
+        k = i * M + np.arange(M)
+        ii = np.concatenate([ii, np.full(M, i)]); jj = np.concatenate([jj, np.full(M, j)]); kk = np.concatenate([kk, k])
+    return synth.ba_inputs(n_frames, seed=seed, M=M, edges=(ii.astype(np.int64), jj.astype(np.int64), kk.astype(np.int64)))
+
+
+@pytest.mark.parametrize("case", ["local_window", "gauge_free_blocked", "loop_closure_hub", "structure_only"])
+def test_ba_eff_impl(case):
+    """eff_impl=True (block-E Schur path, block_e.cu): same mathematics as the dense path, so it must
+    agree with the float64 restatement, with our dense path and with the reference's eff_impl run."""
+    pkg = load_pkg(); synth = load_pkg("synth")
+    if case == "local_window":
+        d = synth.ba_inputs(14, seed=21, M=96); t0, t1 = 4, 14
+    elif case == "gauge_free_blocked":
+        d = synth.ba_inputs(40, seed=22, M=16); t0, t1 = 1, 40            # n = 234: blocked Cholesky
+    elif case == "loop_closure_hub":
+        d = _with_loop_edges(synth, 64, 24, seed=23, hub=3); t0, t1 = 2, 64  # frame 3 sees ~50 frames: 2 conn tiles
+    else:
+        d = synth.ba_inputs(14, seed=24, M=32); t0, t1 = 6, 6
+    got = _run_ours(pkg, d, t0, t1, eff=True)
+    dense = _run_ours(pkg, d, t0, t1, eff=False)
+    want = _run_oracle(d, t0, t1)
+    ts, tu = _tolerances(d, t0, t1, want, eff=True)
+    print(f"tolerances used: state {ts:.2e} update {tu:.2e}")
+    _check_against(d, got, want, ts, tu)
+    _check_against(d, got, (dense[0].astype(np.float64), dense[1].astype(np.float64)), ts, tu)
+    assert np.array_equal(got[0][:t0], d["poses"][:t0]) and np.array_equal(got[0][t1:], d["poses"][t1:])
+
+
+def test_ba_eff_impl_global_300_keyframes():
+    """DPV-SLAM-style global BA (BASELINE config 5, scaled to what the numpy restatement finishes in
+    seconds): 300 keyframes, every sequential edge kept (no removal-window cull), 40 loop-closure
+    frame pairs, all poses but the first free (n = 1794), eff_impl=True, 2 iterations."""
+    pkg = load_pkg(); synth = load_pkg("synth")
+    M, nf = 32, 300
+    rng = np.random.default_rng(5)
+    ii, jj, kk = synth.dpvo_edges(nf, M, removal=10 ** 9)
+    for _ in range(40):
+        i, j = int(rng.integers(0, nf)), int(rng.integers(0, nf))
+        if abs(i - j) >= 30:
+            ii = np.concatenate([ii, np.full(M, i)]); jj = np.concatenate([jj, np.full(M, j)])
+            kk = np.concatenate([kk, i * M + np.arange(M)])
+    d = synth.ba_inputs(nf, seed=31, M=M, edges=(ii.astype(np.int64), jj.astype(np.int64), kk.astype(np.int64)))
+    t0, t1 = 1, nf
+    got = _run_ours(pkg, d, t0, t1, eff=True)
+    want = _run_oracle(d, t0, t1)
+    ts, tu = _tolerances(d, t0, t1, want, eff=True)
+    print(f"E={len(kk)} tolerances used: state {ts:.2e} update {tu:.2e}")
+    _check_against(d, got, want, ts, tu)
+
+
 def test_ba_vs_reference_extension():
     ref = load_ref("cuda_ba")
     if ref is None:
