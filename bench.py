@@ -182,29 +182,24 @@ def main():
         raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
 
     pkg = importlib.import_module(PKG)
     hotpath = importlib.import_module(PKG + ".hotpath")
+    par = importlib.import_module(PKG + ".parallel")
+    par.init(backend="nccl", device=dev)
     lib = pkg._lib.lib
     lib.dpvo_launch_count.restype = __import__("ctypes").c_uint64
 
-    hp = hotpath.UpdateHotPath(dev, n_frames=40, seed=rank)
+    # inference shards by independent sequence: rank r owns sequence r (seeded differently), no collective
+    seq, = par.shard_sequences(world, rank, world)
+    hp = hotpath.UpdateHotPath(dev, n_frames=40, seed=seq)
     alg_bytes = hp.corr_algorithmic_bytes()
 
     def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+        par.barrier(dev)
 
     def max_over_ranks(ms):
-        if world > 1:
-            t = torch.tensor([ms], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            return float(t.item())
-        return ms
+        return par.max_over_ranks(ms, device=dev)
 
     # ---------------------------------------------------------------- device-resident run
     for _ in range(args.warmup):
