@@ -121,38 +121,44 @@ class UpdateHotPath:
     _PER_FRAME = ("new_f1", "new_f2", "new_imap", "centres", "target", "weight")
 
     def make_host_inputs(self):
-        """Pinned host copies of the per-frame inputs (encoder outputs + network outputs), plus the
-        double-buffered device staging sets and the copy stream of the streaming pipeline."""
-        pin = lambda t: t.cpu().pin_memory()
-        hin = {k: pin(getattr(self, k)) for k in self._PER_FRAME}
-        self._sets = [{k: getattr(self, k) for k in self._PER_FRAME},
-                      {k: torch.empty_like(getattr(self, k)) for k in self._PER_FRAME}]
+        """One pinned host buffer holding the per-frame inputs (encoder outputs + network outputs)
+        back to back, two device staging buffers of the same layout (double buffering) and the
+        copy stream of the streaming pipeline.  One frame = ONE host->device copy."""
+        offs, total = {}, 0
+        for k in self._PER_FRAME:
+            t = getattr(self, k)
+            offs[k] = total
+            total += (t.numel() * t.element_size() + 255) & ~255
+        view = lambda buf, k: buf[offs[k]:offs[k] + getattr(self, k).numel() * getattr(self, k).element_size()] \
+            .view(getattr(self, k).dtype).view(getattr(self, k).shape)
+        host = torch.empty(total, dtype=torch.uint8).pin_memory()
+        for k in self._PER_FRAME:
+            view(host, k).copy_(getattr(self, k).cpu())
+        self._stage = [torch.empty(total, dtype=torch.uint8, device=self.device) for _ in range(2)]
+        self._sets = [{k: view(buf, k) for k in self._PER_FRAME} for buf in self._stage]
+        self._h2d_bytes = sum(getattr(self, k).numel() * getattr(self, k).element_size() for k in self._PER_FRAME)
         self._copy_stream = torch.cuda.Stream(self.device)
         self._copied = [torch.cuda.Event() for _ in range(2)]
         self._consumed = [torch.cuda.Event() for _ in range(2)]
         self._frame = 0
-        return hin
+        return host
 
     def step_host(self, hin, hout):
         """Same frame with host<->device copies inside, as a streaming front end would run it: frame
-        k's inputs go from pinned host memory into staging set k%2 on a copy stream (overlapping frame
-        k-1's kernels on the compute stream), the compute stream waits for that copy, runs the frame
-        and reads the updated window poses and patch inverse depths back.  Every frame's bytes cross
-        PCIe inside the caller's timed region.  Returns (h2d_bytes, d2h_bytes)."""
+        k's inputs go from pinned host memory into staging buffer k%2 on a copy stream (overlapping
+        frame k-1's kernels on the compute stream), the compute stream waits for that copy, runs the
+        frame and reads the updated window poses and patch inverse depths back.  Every frame's bytes
+        cross PCIe inside the caller's timed region.  Returns (h2d_bytes, d2h_bytes)."""
         b = self._frame & 1
         self._frame += 1
         compute = torch.cuda.current_stream(self.device)
-        dst = self._sets[b]
-        h2d = 0
         with torch.cuda.stream(self._copy_stream):
-            self._copy_stream.wait_event(self._consumed[b])       # set b's previous frame is done with it
-            for k in self._PER_FRAME:
-                dst[k].copy_(hin[k], non_blocking=True)
-                h2d += hin[k].numel() * hin[k].element_size()
+            self._copy_stream.wait_event(self._consumed[b])       # buffer b's previous frame is done with it
+            self._stage[b].copy_(hin, non_blocking=True)
             self._copied[b].record(self._copy_stream)
         compute.wait_event(self._copied[b])
         for k in self._PER_FRAME:
-            setattr(self, k, dst[k])
+            setattr(self, k, self._sets[b][k])
         self.step()
         self._consumed[b].record(compute)
         pw = self.poses[0, self.t0:self.t1]
@@ -160,7 +166,7 @@ class UpdateHotPath:
         hout["poses"].copy_(pw, non_blocking=True)
         hout["depths"].copy_(dz, non_blocking=True)
         d2h = pw.numel() * 4 + dz.numel() * 4
-        return h2d, d2h
+        return self._h2d_bytes, d2h
 
     def make_host_outputs(self):
         return dict(poses=torch.empty((self.t1 - self.t0, 7), dtype=torch.float32).pin_memory(),

@@ -47,8 +47,9 @@ def _blend_weights(coords_scaled, dtype):
     return w00, w01, w10, w11  # each [B,M,P,P]
 
 
-def corr_raw(fmap1, fmap2, coords, ii, jj, radius, chunk=256):
-    """Raw window volume [B,M,D,D,P,P] (rows=y offset, cols=x offset) in fmap dtype."""
+def corr_raw(fmap1, fmap2, coords, ii, jj, radius, chunk=256, _f64=None):
+    """Raw window volume [B,M,D,D,P,P] (rows=y offset, cols=x offset) in fmap dtype.
+    `_f64`: optional (fmap1, fmap2) already converted to float64 (callers that loop over edge chunks)."""
     B, N1, C, PH, PW = fmap1.shape
     _, N2, _, H2, W2 = fmap2.shape
     M = coords.shape[1]
@@ -56,8 +57,7 @@ def corr_raw(fmap1, fmap2, coords, ii, jj, radius, chunk=256):
     D = 2 * R + 2
     dtype = fmap1.dtype.type
     out = np.zeros((B, M, D, D, PH, PW), dtype=dtype)
-    f1 = fmap1.astype(np.float64)
-    f2 = fmap2.astype(np.float64)
+    f1, f2 = _f64 if _f64 is not None else (fmap1.astype(np.float64), fmap2.astype(np.float64))
     off = np.arange(D) - R
     for b in range(B):
         for m0 in range(0, M, chunk):
@@ -80,10 +80,10 @@ def corr_raw(fmap1, fmap2, coords, ii, jj, radius, chunk=256):
     return out
 
 
-def corr_forward(fmap1, fmap2, coords, ii, jj, radius):
+def corr_forward(fmap1, fmap2, coords, ii, jj, radius, _f64=None):
     """cuda_corr.forward: returns [B,M,2r+1(x),2r+1(y),P,P] in fmap dtype."""
     dtype = fmap1.dtype.type
-    raw = corr_raw(fmap1, fmap2, coords, ii, jj, radius)
+    raw = corr_raw(fmap1, fmap2, coords, ii, jj, radius, _f64=_f64)
     D = 2 * radius + 2
     w00, w01, w10, w11 = _blend_weights(coords, dtype)
     e = lambda w: w[:, :, None, None]
@@ -101,6 +101,29 @@ def corr_pyramid(fmap1, pyramid, scales, coords, ii, jj, radius):
             for fm, s in zip(pyramid, scales)]
     st = np.stack(outs, -1)
     return st.reshape(st.shape[0], st.shape[1], -1)
+
+
+def corr_pyramid_threads(fmap1, pyramid, scales, coords, ii, jj, radius, threads):
+    """corr_pyramid over `threads` host threads (edge chunks are independent; numpy's gathers and
+    einsum release the GIL).  Same result as corr_pyramid; used by bench.py's CPU baseline legs."""
+    from concurrent.futures import ThreadPoolExecutor
+    M = coords.shape[1]
+    threads = max(1, min(int(threads), M)) if M else 1
+    f1 = fmap1.astype(np.float64)
+    f2s = [fm.astype(np.float64) for fm in pyramid]
+    bounds = np.linspace(0, M, threads + 1).astype(np.int64)
+
+    def work(t):
+        a, b = int(bounds[t]), int(bounds[t + 1])
+        outs = [corr_forward(fmap1, fm, (coords[:, a:b].astype(np.float32) * np.float32(s)).astype(np.float32),
+                             ii[a:b], jj[a:b], radius, _f64=(f1, f2))
+                for fm, f2, s in zip(pyramid, f2s, scales)]
+        st = np.stack(outs, -1)
+        return st.reshape(st.shape[0], st.shape[1], -1)
+
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        parts = list(ex.map(work, range(threads)))
+    return np.concatenate(parts, 1)
 
 
 def corr_backward(fmap1, fmap2, coords, ii, jj, grad, radius, acc_dtype=np.float64):

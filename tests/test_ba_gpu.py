@@ -169,7 +169,8 @@ def test_ba_eff_impl(case):
     got = _run_ours(pkg, d, t0, t1, eff=True)
     dense = _run_ours(pkg, d, t0, t1, eff=False)
     want = _run_oracle(d, t0, t1)
-    ts, tu = _tolerances(d, t0, t1, want, eff=True)
+    # the reference's eff_impl run faults (illegal address) when t1 == t0, so it is not used there
+    ts, tu = (STATE_TOL, UPDATE_TOL) if case == "structure_only" else _tolerances(d, t0, t1, want, eff=True)
     print(f"tolerances used: state {ts:.2e} update {tu:.2e}")
     _check_against(d, got, want, ts, tu)
     _check_against(d, got, (dense[0].astype(np.float64), dense[1].astype(np.float64)), ts, tu)

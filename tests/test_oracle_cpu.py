@@ -222,3 +222,16 @@ def test_synthetic_graph_matches_survey_sizes():
     assert len(kk) == 45312 and len(np.unique(kk)) == 22 * 96
     assert np.array_equal(ii, kk // 96)
     assert (np.abs(ii - jj) <= 13).all()
+
+
+def test_torch_cpu_correlation_matches_numpy_restatement(synth):
+    """oracle/altcorr_torch.py (the multi-threaded CPU baseline bench.py times) against the numpy
+    restatement: fp32 vs float64 accumulation differ by at most a final-rounding flip."""
+    from oracle import altcorr_oracle as oc, altcorr_torch as ot
+    d = synth.corr_inputs(300, seed=11, mem=3, n_patches=32, oob_frac=0.1)
+    want = oc.corr_pyramid(d["gmap"], [d["fmap1"], d["fmap2"]], [1.0, 0.25], d["coords"], d["us"], d["vs"], 3)
+    got = ot.corr_pyramid(ot.prepare(d["gmap"], [d["fmap1"], d["fmap2"]]), [1.0, 0.25], d["coords"], d["us"], d["vs"], 3).numpy()
+    assert got.shape == want.shape and got.dtype == want.dtype
+    a, b = got.astype(np.float64), want.astype(np.float64)
+    assert np.linalg.norm(a - b) / np.linalg.norm(b) < 1e-4
+    assert (a == b).mean() > 0.99
