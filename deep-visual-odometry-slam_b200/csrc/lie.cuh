@@ -12,6 +12,12 @@ namespace dpvo {
 namespace lie {
 
 template <typename T> struct Eps { static __device__ __forceinline__ T v() { return T(1e-6); } };
+// Deliberate deviation: the reference switches the Jacobian coefficients ((1-cos t)/t^2, (t-sin t)/t^3, the
+// Q coefficients of se3.h:155-165, ...) from their Taylor series to the closed forms at t = EPS = 1e-6.
+// Just above that the closed forms cancel catastrophically (in float32 the reference's own values are
+// noise for t in ~[1e-6, 1e-2]); here the series (three terms, truncation error < 1e-14) is used below
+// t = 1e-2, so results follow the exact value instead of the rounding noise.
+template <typename T> struct SeriesTh { static __device__ __forceinline__ T v() { return T(1e-2); } };
 
 template <typename T> struct V3 { T x, y, z; };
 template <typename T> struct M3 { T a[3][3]; };
@@ -198,8 +204,9 @@ template <typename T> struct SO3 {
     const M3<T> Phi = hat(phi);
     const T th2 = dot(phi, phi);
     const T th = sqrt(th2);
-    const T c1 = (th < Eps<T>::v()) ? T(0.5) - T(1.0 / 24.0) * th2 : (T(1) - cos(th)) / th2;
-    const T c2 = (th < Eps<T>::v()) ? T(1.0 / 6.0) - T(1.0 / 120.0) * th2 : (th - sin(th)) / (th2 * th);
+    const bool small = th < SeriesTh<T>::v();
+    const T c1 = small ? T(0.5) - T(1.0 / 24.0) * th2 + T(1.0 / 720.0) * th2 * th2 : (T(1) - cos(th)) / th2;
+    const T c2 = small ? T(1.0 / 6.0) - T(1.0 / 120.0) * th2 + T(1.0 / 5040.0) * th2 * th2 : (th - sin(th)) / (th2 * th);
     return eye3<T>() + c1 * Phi + c2 * (Phi * Phi);
   }
   static __device__ __forceinline__ M3<T> left_jac_inv3(V3<T> phi) {
@@ -207,7 +214,8 @@ template <typename T> struct SO3 {
     const T th2 = dot(phi, phi);
     const T th = sqrt(th2);
     const T h = T(0.5) * th;
-    const T c2 = (th < Eps<T>::v()) ? T(1.0 / 12.0) : (T(1) - th * cos(h) / (T(2) * sin(h))) / (th * th);
+    const T c2 = (th < SeriesTh<T>::v()) ? T(1.0 / 12.0) + T(1.0 / 720.0) * th2 + T(1.0 / 30240.0) * th2 * th2
+                                         : (T(1) - th * cos(h) / (T(2) * sin(h))) / (th * th);
     return eye3<T>() + T(-0.5) * Phi + c2 * (Phi * Phi);
   }
   static __device__ __forceinline__ void left_jacobian(const T* a, T (&J)[K][K]) {
@@ -326,10 +334,11 @@ template <typename T> struct SE3 {
     const M3<T> Tau = hat(tau), Phi = hat(phi);
     const T th = sqrt(dot(phi, phi));
     const T th2 = th * th, th4 = th2 * th2;
-    const bool small = th < Eps<T>::v();
-    const T c1 = small ? T(1.0 / 6.0) - T(1.0 / 120.0) * th2 : (th - sin(th)) / (th2 * th);
-    const T c2 = small ? T(1.0 / 24.0) - T(1.0 / 720.0) * th2 : (th2 + T(2) * cos(th) - T(2)) / (T(2) * th4);
-    const T c3 = small ? T(1.0 / 120.0) - T(1.0 / 2520.0) * th2
+    const bool small = th < SeriesTh<T>::v();
+    const T c1 = small ? T(1.0 / 6.0) - T(1.0 / 120.0) * th2 + T(1.0 / 5040.0) * th4 : (th - sin(th)) / (th2 * th);
+    const T c2 = small ? T(1.0 / 24.0) - T(1.0 / 720.0) * th2 + T(1.0 / 40320.0) * th4
+                       : (th2 + T(2) * cos(th) - T(2)) / (T(2) * th4);
+    const T c3 = small ? T(1.0 / 120.0) - T(1.0 / 2520.0) * th2 + T(1.0 / 120960.0) * th4
                        : (T(2) * th - T(3) * sin(th) + th * cos(th)) / (T(2) * th4 * th);
     const M3<T> PT = Phi * Tau, TP = Tau * Phi, PTP = PT * Phi, PP = Phi * Phi;
     return T(0.5) * Tau + c1 * (PT + TP + PTP) + c2 * (PP * Tau + TP * Phi - T(3) * PTP) + c3 * (PTP * Phi + Phi * PTP);

