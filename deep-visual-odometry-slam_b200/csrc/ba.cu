@@ -797,7 +797,7 @@ int64_t ba_carve(BADev& p, char* base, int64_t E, int64_t npatches, int N, int e
   p.C = (float*)take(Mmax * 4);
   p.u = (float*)take(Mmax * 4);
   p.dX = (float*)take((n + 8) * 4);
-  p.Sg = (float*)take(((n + 1) * (int64_t)chol_lda((int)n) + 2 * n + 64) * 4);
+  p.Sg = (float*)take(((n + 1) * (int64_t)chol_lda((int)n) + chol_scratch_floats((int)n) + 128) * 4);
   p.Mmax = Mmax;
   p.W = W;
   if (!eff) {

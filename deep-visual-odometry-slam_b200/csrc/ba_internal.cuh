@@ -111,5 +111,6 @@ void ba_launch_assemble(const BADev& p, cudaStream_t st);
 int ba_launch_solve(const BADev& p, cudaStream_t st);   // S = B - G (+damping), Cholesky, dX, pose retraction; clears U, v, G, g
 int ba_chol_solve(const BADev& p, float* A, int lda, float* xbuf, cudaStream_t st);
 inline int chol_lda(int n) { return (n + 63) & ~63; }
+int64_t chol_scratch_floats(int n);
 
 }  // namespace dpvo

@@ -117,6 +117,23 @@ class UpdateHotPath:
         timed("ba", self.ba)
         return corr
 
+    # ------------------------------------------------------------------ CUDA-graph replay
+    def capture(self):
+        """Capture one frame (all ~24 launches of step()) into a CUDA graph; `replay()` then issues
+        the frame with a single launch.  Every buffer the frame touches is persistent (state,
+        rings, per-frame inputs, the BA / neighbours workspaces sized during the warm-up call), the
+        outputs of the captured frame live in the graph's private pool."""
+        self.step()                                   # sizes the workspaces outside the capture
+        torch.cuda.synchronize(self.device)
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            self._graph_out = self.step()
+        return self._graph
+
+    def replay(self):
+        self._graph.replay()
+        return self._graph_out
+
     # ------------------------------------------------------------------ host-buffer variant
     _PER_FRAME = ("new_f1", "new_f2", "new_imap", "centres", "target", "weight")
 
@@ -157,9 +174,12 @@ class UpdateHotPath:
             self._stage[b].copy_(hin, non_blocking=True)
             self._copied[b].record(self._copy_stream)
         compute.wait_event(self._copied[b])
-        for k in self._PER_FRAME:
-            setattr(self, k, self._sets[b][k])
-        self.step()
+        if getattr(self, "_host_graphs", None):
+            self._host_graphs[b].replay()
+        else:
+            for k in self._PER_FRAME:
+                setattr(self, k, self._sets[b][k])
+            self.step()
         self._consumed[b].record(compute)
         pw = self.poses[0, self.t0:self.t1]
         dz = self.patches[0, :, 2, 0, 0]
@@ -167,6 +187,20 @@ class UpdateHotPath:
         hout["depths"].copy_(dz, non_blocking=True)
         d2h = pw.numel() * 4 + dz.numel() * 4
         return self._h2d_bytes, d2h
+
+    def capture_host(self):
+        """One CUDA graph per staging buffer for step_host()."""
+        graphs = []
+        for b in range(2):
+            for k in self._PER_FRAME:
+                setattr(self, k, self._sets[b][k])
+            self.step()
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.step()
+            graphs.append(g)
+        self._host_graphs = graphs
 
     def make_host_outputs(self):
         return dict(poses=torch.empty((self.t1 - self.t0, 7), dtype=torch.float32).pin_memory(),
