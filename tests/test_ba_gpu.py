@@ -84,6 +84,10 @@ def _tolerances(d, t0, t1, want, iters=2, eff=False, loose=3e-4):
         return (loose, 10 * UPDATE_TOL) if t0 <= 1 else (STATE_TOL, UPDATE_TOL)
     es = max(_rel(rr[0], want[0]), _rel(rr[1][:, 2], want[1][:, 2]))
     eu = max(_rel(rr[0] - p0, want[0] - p0), _rel(rr[1][:, 2] - z0[:, 2], want[1][:, 2] - z0[:, 2]))
+    if t0 <= 1:
+        # gauge-free: both fp32 paths land anywhere in 1e-5 .. 3e-4 of float64 depending on the seed and
+        # on the atomics' order (profiles/r01_ba_accuracy.jsonl), so a bare "2x the reference" is a coin flip
+        return max(loose, 2 * es), max(10 * UPDATE_TOL, 2 * eu)
     return max(STATE_TOL, 2 * es), max(UPDATE_TOL, 2 * eu)
 
 
