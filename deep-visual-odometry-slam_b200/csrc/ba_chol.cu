@@ -6,14 +6,13 @@
 //
 // A is (n+1) x lda row-major in global memory: rows 0..n-1 hold the lower triangle of
 // S = B - E Q E^T (+ damping), row n holds y^T, so the forward substitution L z = y is part of
-// the factorisation (row n of L is z^T).  Panels of 64 columns, TWO launches per panel:
+// the factorisation (row n of L is z^T).  Panels of 64 columns, three launches per panel:
+//   diag   one CTA factors the 64x64 diagonal block AND inverts the factor (blocked 4 x 16 inside the
+//          tile, 16x16 blocks in one warp's registers with shuffles: ~22 barriers, not 64 + a serial solve)
 //   trsm   one CTA per 64-row tile below the panel: L21 = A21 * inv(L11)^T as a 64x64x64 product
 //          (inv(L11) was left behind by the CTA that factored the diagonal block), no sequential loop
 //   syrk   one CTA per 64x64 lower tile of the trailing matrix: A22 -= L21 L21^T (fp32 SIMT; the
-//          update is K=64 deep per panel — not worth a tensor-core pipeline at these sizes).  The CTA
-//          that owns tile (0,0) — the NEXT panel's diagonal block, touched by nobody else — goes on to
-//          factor it in shared memory (one barrier per column) and to invert the factor, so the
-//          serial 64-column factorisation hides behind the other tiles' updates.
+//          update is K=64 deep per panel — not worth a tensor-core pipeline at these sizes).
 // Back substitution L^T x = z from the bottom, ONE launch per panel: every CTA forms
 // x_p = inv(L11)^T (z_p - acc_p) (a 64x64 mat-vec), CTA q then adds L[p, q]^T x_p to acc_q for its
 // 64-column tile q < p (each acc segment has exactly one writer per launch: no atomics).
@@ -21,76 +20,153 @@
 // A non-positive pivot sets meta[1]; every later kernel returns early and dX is zeroed.
 #include "se3.cuh"
 #include "ba_internal.cuh"
+#include <stdlib.h>
 
 namespace dpvo {
 
 constexpr int NB = 64;
 
-// Factor the nb x nb SPD block held in L (lower triangle, row-major, leading dimension NB+1) and
-// invert the factor: on return the caller writes L11 = {strictly lower: L[c][r] (scaled copies in the
-// upper triangle), diagonal: dg[r]} and X = inv(L11) (lower).  256 threads.  Returns false on a
-// non-positive pivot (uniform across the CTA).
-__device__ __forceinline__ bool chol_factor_invert(float (*L)[NB + 1], float (*X)[NB + 1], float* dg, int nb) {
-  const int tid = threadIdx.x;
-  const int cl = tid & 63, rg = tid >> 6;
-  bool fail = false;
-  for (int j = 0; j < nb; ++j) {
-    const float d = L[j][j];
-    if (!(d > 0.f)) { fail = true; break; }   // uniform
-    float rs = rsqrtf(d);
-    rs = rs * (1.5f - 0.5f * d * rs * rs);
-    const float invd = rs * rs;
-    // trailing update reads the unscaled column j; scaled values go to the upper triangle
-    for (int i = j + 1 + tid; i < nb; i += 256) L[j][i] = L[i][j] * rs;
-    if (tid == 0) dg[j] = d * rs;             // sqrt(d); L[j][j] itself is still being read as d by slower warps
-    for (int k = j + 1 + cl; k < nb; k += 64) {
-      const float f = L[k][j] * invd;
-      for (int i = k + ((rg - k) & 3); i < nb; i += 4) L[i][k] -= L[i][j] * f;
+// Factor the nb x nb SPD block held in L (lower triangle, row-major, leading dimension NB+1) in place
+// and invert the factor into X (lower).  Blocked 4 x 16 inside the tile so that the serial chain is
+// short: each 16x16 diagonal block is factored AND inverted by one warp in registers (row l in lane l,
+// pivots / multipliers broadcast with shuffles: no barriers), the panel below is a product with that
+// inverse, the trailing update and the assembly of inv(L) from the block inverses use all 256 threads.
+// ~22 barriers instead of 64 + a 2,000-step serial substitution.  Returns false on a non-positive pivot.
+__device__ __forceinline__ bool chol_factor_invert(float (*L)[NB + 1], float (*X)[NB + 1], int nb) {
+  constexpr int SB = 16;
+  __shared__ float Tm[3][SB][SB + 1];
+  __shared__ int s_fail;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) s_fail = 0;
+  for (int i = tid; i < NB * NB; i += 256) {
+    const int r = i / NB, c = i % NB;
+    X[r][c] = 0.f;
+    if (r >= nb || c > r) L[r][c] = (r == c) ? 1.f : 0.f;     // identity padding, clean upper triangle
+  }
+  __syncthreads();
+  for (int b = 0; b < NB / SB; ++b) {
+    const int o = b * SB;
+    if (wid == 0) {
+      // ---- 16x16 diagonal block: lane l < 16 owns row l
+      const int l = lane & 15;
+      float a[SB];
+#pragma unroll
+      for (int k = 0; k < SB; ++k) a[k] = (k <= l) ? L[o + l][o + k] : 0.f;
+      bool bad = false;
+#pragma unroll
+      for (int j = 0; j < SB; ++j) {
+        const float d = __shfl_sync(0xffffffffu, a[j], j);
+        if (!(d > 0.f)) bad = true;
+        float rs = rsqrtf(d);
+        rs = rs * (1.5f - 0.5f * d * rs * rs);
+        a[j] = (l == j) ? d * rs : a[j] * rs;                    // L[l][j], l >= j (rows above hold 0)
+#pragma unroll
+        for (int k = j + 1; k < SB; ++k) {
+          const float lkj = __shfl_sync(0xffffffffu, a[j], k);   // L[k][j]
+          if (l >= k) a[k] -= a[j] * lkj;
+        }
+      }
+      // ---- inverse: lane c < 16 owns column c of Xd; L[i][k] comes from lane i
+      float x[SB];
+#pragma unroll
+      for (int i = 0; i < SB; ++i) {
+        float sacc = (i == l) ? 1.f : 0.f;
+#pragma unroll
+        for (int k = 0; k < i; ++k) sacc -= __shfl_sync(0xffffffffu, a[k], i) * x[k];
+        x[i] = sacc / __shfl_sync(0xffffffffu, a[i], i);
+      }
+      if (lane < SB) {
+#pragma unroll
+        for (int k = 0; k < SB; ++k) {
+          if (k <= l) L[o + l][o + k] = a[k];
+          if (k >= l) X[o + k][o + l] = x[k];
+        }
+        if (bad) s_fail = 1;
+      }
+    }
+    __syncthreads();
+    if (s_fail) return false;
+    const int below = NB - o - SB;           // rows under the diagonal block
+    if (below > 0) {
+      // ---- panel: L21 = A21 * Xd^T  (below x 16 outputs, <= 3 per thread)
+      float outv[3];
+#pragma unroll
+      for (int q = 0; q < 3; ++q) {
+        const int idx = tid + 256 * q;
+        float sacc = 0.f;
+        if (idx < below * SB) {
+          const int r = o + SB + idx / SB, c = idx % SB;
+          for (int k = 0; k <= c; ++k) sacc += L[r][o + k] * X[o + c][o + k];
+        }
+        outv[q] = sacc;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int q = 0; q < 3; ++q) {
+        const int idx = tid + 256 * q;
+        if (idx < below * SB) L[o + SB + idx / SB][o + idx % SB] = outv[q];
+      }
+      __syncthreads();
+      // ---- trailing update of the lower triangle: A22[r][c] -= L21[r][:] . L21[c][:]
+      for (int idx = tid; idx < below * below; idx += 256) {
+        const int r = idx / below, c = idx - r * below;
+        if (c > r) continue;
+        float sacc = 0.f;
+#pragma unroll
+        for (int k = 0; k < SB; ++k) sacc += L[o + SB + r][o + k] * L[o + SB + c][o + k];
+        L[o + SB + r][o + SB + c] -= sacc;
+      }
+      __syncthreads();
+    }
+  }
+  // ---- inv(L): X_ij = -X_ii * sum_{k=j}^{i-1} L_ik X_kj for block distance 1, 2, 3
+  for (int dist = 1; dist < NB / SB; ++dist) {
+    const int nblk = NB / SB - dist;
+    const int r = tid / SB, c = tid % SB;
+    for (int q = 0; q < nblk; ++q) {         // block (i = q + dist, j = q): one output per thread
+      const int i = q + dist, j = q;
+      float sacc = 0.f;
+      for (int k = j; k < i; ++k)
+#pragma unroll
+        for (int t = 0; t < SB; ++t) sacc += L[i * SB + r][k * SB + t] * X[k * SB + t][j * SB + c];
+      Tm[q][r][c] = sacc;
+    }
+    __syncthreads();
+    for (int q = 0; q < nblk; ++q) {
+      const int i = q + dist, j = q;
+      float sacc = 0.f;
+      for (int t = 0; t <= r; ++t) sacc += X[i * SB + r][i * SB + t] * Tm[q][t][c];
+      X[i * SB + r][j * SB + c] = -sacc;
     }
     __syncthreads();
   }
-  if (fail) return false;
-  // X = inv(L11): thread c solves L11 X[:,c] = e_c by forward substitution (L[i][k], i>k, is at L[k][i])
-  for (int i = tid; i < NB * NB; i += 256) X[i / NB][i % NB] = 0.f;
-  __syncthreads();
-  if (tid < nb) {
-    const int c = tid;
-    X[c][c] = 1.0f / dg[c];
-    for (int i = c + 1; i < nb; ++i) {
-      float s = 0.f;
-      for (int k = c; k < i; ++k) s += L[k][i] * X[k][c];
-      X[i][c] = -s / dg[i];
-    }
-  }
-  __syncthreads();
   return true;
 }
 
 // write L11 (lower incl. diagonal) into A and inv(L11) into Linv (dense NB x NB, zero upper)
 __device__ __forceinline__ void chol_store_diag(float* __restrict__ A, int lda, int p0, int nb, float (*L)[NB + 1],
-                                                float (*X)[NB + 1], const float* dg, float* __restrict__ Linv) {
+                                                float (*X)[NB + 1], float* __restrict__ Linv) {
   for (int i = threadIdx.x; i < NB * NB; i += 256) {
     const int r = i / NB, c = i % NB;
-    if (r < nb && c <= r) A[(int64_t)(p0 + r) * lda + p0 + c] = (c == r) ? dg[r] : L[c][r];
+    if (r < nb && c <= r) A[(int64_t)(p0 + r) * lda + p0 + c] = L[r][c];
     Linv[i] = X[r][c];
   }
 }
 
-// panel 0 only: the first diagonal block
+// diagonal block of panel p0: factor + invert (one CTA)
 __global__ void __launch_bounds__(256)
-chol_diag0_kernel(float* __restrict__ A, int lda, int n, float* __restrict__ Linv, int* __restrict__ meta) {
+chol_diag_kernel(float* __restrict__ A, int lda, int n, int p0, float* __restrict__ Linv, int* __restrict__ meta) {
   __shared__ float L[NB][NB + 1];
   __shared__ float X[NB][NB + 1];
-  __shared__ float dg[NB];
   if (meta[1]) return;
-  const int nb = min(NB, n);
+  const int nb = min(NB, n - p0);
   for (int i = threadIdx.x; i < NB * NB; i += 256) {
     const int r = i / NB, c = i % NB;
-    L[r][c] = (r < nb && c <= r) ? A[(int64_t)r * lda + c] : 0.f;
+    L[r][c] = (r < nb && c <= r) ? A[(int64_t)(p0 + r) * lda + p0 + c] : 0.f;
   }
   __syncthreads();
-  if (!chol_factor_invert(L, X, dg, nb)) { if (threadIdx.x == 0) meta[1] = 1; return; }
-  chol_store_diag(A, lda, 0, nb, L, X, dg, Linv);
+  if (!chol_factor_invert(L, X, nb)) { if (threadIdx.x == 0) meta[1] = 1; return; }
+  chol_store_diag(A, lda, p0, nb, L, X, Linv);
 }
 
 // rows [p0+nb, n] (incl. the y row) in tiles of 64: L21 = A21 * inv(L11)^T
@@ -136,14 +212,11 @@ chol_trsm_kernel(float* __restrict__ A, int lda, int n, int p0, const float* __r
     }
 }
 
-// trailing update: tile (ti, tj), tj <= ti, of rows/cols starting at q0 = p0 + nb; the CTA of tile
-// (0,0) then factors + inverts that tile (the next panel's diagonal block).
+// trailing update: tile (ti, tj), tj <= ti, of rows/cols starting at q0 = p0 + nb.
 __global__ void __launch_bounds__(256)
-chol_syrk_kernel(float* __restrict__ A, int lda, int n, int p0, float* __restrict__ Linv_next,
-                 int* __restrict__ meta) {
+chol_syrk_kernel(float* __restrict__ A, int lda, int n, int p0, const int* __restrict__ meta) {
   __shared__ float As[NB][NB + 1];
   __shared__ float Bs[NB][NB + 1];
-  __shared__ float dg[NB];
   if (meta[1]) return;
   // linear tile index -> (ti, tj) with tj <= ti
   const int t = blockIdx.x;
@@ -180,26 +253,13 @@ chol_syrk_kernel(float* __restrict__ A, int lda, int n, int p0, float* __restric
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[i][j] += av[i] * bv[j];
   }
-  const bool next_diag = (t == 0);
-  if (next_diag) __syncthreads();             // As / Bs are about to be reused
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int r = ty + 16 * i, c = tx + 16 * j;
-      const bool in = r < nri && c < nrj && (rj + c) <= (ri + r);
-      float v = 0.f;
-      if (in) {
-        v = A[(int64_t)(ri + r) * lda + rj + c] - acc[i][j];
-        if (!next_diag || r >= nrj) A[(int64_t)(ri + r) * lda + rj + c] = v;   // the y row (r == nrj) if present
-      }
-      if (next_diag) As[r][c] = (in && r < nrj) ? v : 0.f;
+      if (r < nri && c < nrj && (rj + c) <= (ri + r)) A[(int64_t)(ri + r) * lda + rj + c] -= acc[i][j];
     }
-  if (!next_diag) return;
-  __syncthreads();
-  const int nbn = nrj;                        // size of the next diagonal block
-  if (!chol_factor_invert(As, Bs, dg, nbn)) { if (tid == 0) meta[1] = 1; return; }
-  chol_store_diag(A, lda, q0, nbn, As, Bs, dg, Linv_next);
 }
 
 // Back substitution, panel p0: x_p = inv(L11)^T (z_p - acc_p); CTA 0 stores it, CTA q+1 folds it into
@@ -264,39 +324,105 @@ chol_finish_kernel(const __grid_constant__ BADev p, const float* __restrict__ x)
 int64_t chol_scratch_floats(int n) { return 3 * (int64_t)n + 64 + (int64_t)((n + NB - 1) / NB) * NB * NB; }
 
 // A: (n+1) x lda, lower triangle + y row already in place.  xbuf: chol_scratch_floats(n) floats.
+// DPVO_DEBUG_SYNC=1: synchronise after every launch and name the kernel that faulted
+#define CHOL_DBG(what)                                                                              \
+  do {                                                                                              \
+    if (dbg) {                                                                                      \
+      cudaError_t e_ = cudaStreamSynchronize(st);                                                   \
+      if (e_ == cudaSuccess) e_ = cudaGetLastError();                                               \
+      if (e_ != cudaSuccess) { set_error("ba_chol_solve: %s (p0=%d): %s", what, p0, cudaGetErrorString(e_)); return 1; } \
+    }                                                                                               \
+  } while (0)
+
 int ba_chol_solve(const BADev& p, float* A, int lda, float* xbuf, cudaStream_t st) {
   const int n = p.n;
   int launches = 0;
+  static const bool dbg = getenv("DPVO_DEBUG_SYNC") != nullptr;
+  int p0 = -1;
   float* z = xbuf;
   float* acc = z + n;
   float* sol = acc + n;
   float* Linv = sol + n + (64 - (3 * n) % 64) % 64;     // 256-byte aligned panels
-  chol_diag0_kernel<<<1, 256, 0, st>>>(A, lda, n, Linv, p.meta);
-  ++launches;
-  for (int p0 = 0; p0 < n; p0 += NB) {
+  for (p0 = 0; p0 < n; p0 += NB) {
     const int nb = n - p0 < NB ? n - p0 : NB;
     const int rows = n + 1 - p0 - nb;            // rows below the panel, incl. the y row
     const int T = (rows + NB - 1) / NB;
-    const float* Li = Linv + (int64_t)(p0 / NB) * NB * NB;
+    float* Li = Linv + (int64_t)(p0 / NB) * NB * NB;
+    chol_diag_kernel<<<1, 256, 0, st>>>(A, lda, n, p0, Li, p.meta);
+    ++launches;
+    CHOL_DBG("diag");
     chol_trsm_kernel<<<T, 256, 0, st>>>(A, lda, n, p0, Li, p.meta);
     ++launches;
+    CHOL_DBG("trsm");
     const int Tc = (n - p0 - nb + NB - 1) / NB;  // column tiles of the trailing matrix
     if (Tc > 0) {
-      chol_syrk_kernel<<<T * (T + 1) / 2, 256, 0, st>>>(A, lda, n, p0, Linv + (int64_t)(p0 / NB + 1) * NB * NB, p.meta);
+      chol_syrk_kernel<<<T * (T + 1) / 2, 256, 0, st>>>(A, lda, n, p0, p.meta);
       ++launches;
+      CHOL_DBG("syrk");
     }
   }
   chol_init_x_kernel<<<(n + 255) / 256, 256, 0, st>>>(A, lda, n, z, acc, p.meta);
   ++launches;
+  CHOL_DBG("init_x");
   const int last = ((n - 1) / NB) * NB;
-  for (int p0 = last; p0 >= 0; p0 -= NB) {
+  for (p0 = last; p0 >= 0; p0 -= NB) {
     chol_bs_kernel<<<1 + p0 / NB, 256, 0, st>>>(A, lda, n, p0, Linv + (int64_t)(p0 / NB) * NB * NB, z, acc, sol, p.meta);
     ++launches;
+    CHOL_DBG("bs");
   }
   const int m = n > p.N ? n : p.N;
   chol_finish_kernel<<<(m + 255) / 256, 256, 0, st>>>(p, sol);
+  CHOL_DBG("finish");
   note_launches(launches + 1);
   return check_launch("ba_chol_solve");
 }
 
 }  // namespace dpvo
+
+// ------------------------------------------------------------------ stand-alone entry (tests, tools)
+namespace dpvo {
+__global__ void __launch_bounds__(256)
+chol_pack_kernel(const float* __restrict__ S, const float* __restrict__ y, int n, float* __restrict__ A, int lda,
+                 int* __restrict__ meta) {
+  const int64_t total = (int64_t)(n + 1) * n;
+  if (blockIdx.x == 0 && threadIdx.x == 0) meta[1] = 0;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int a = (int)(idx / n), b = (int)(idx - (int64_t)a * n);
+    if (a == n) A[(int64_t)n * lda + b] = y[b];
+    else if (b <= a) A[(int64_t)a * lda + b] = S[(int64_t)a * n + b];
+  }
+}
+}  // namespace dpvo
+
+extern "C" int64_t dpvo_chol_workspace_bytes(int32_t n) {
+  if (n < 0) n = 0;
+  return 256 + ((int64_t)(n + 1) * dpvo::chol_lda(n) + dpvo::chol_scratch_floats(n) + 128) * 4;
+}
+
+extern "C" int dpvo_chol_solve(const float* S, const float* y, int32_t n, float* x, int32_t* info,
+                               void* workspace, int64_t workspace_bytes, void* stream) {
+  using namespace dpvo;
+  DPVO_REQUIRE(n >= 0, "chol_solve: negative size");
+  if (n == 0) return 0;
+  DPVO_REQUIRE(S && y && x && info && workspace, "chol_solve: null pointer");
+  DPVO_REQUIRE(workspace_bytes >= dpvo_chol_workspace_bytes(n), "chol_solve: workspace too small");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  char* base = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~(uintptr_t)255);
+  BADev p;
+  memset(&p, 0, sizeof(p));
+  p.n = n; p.N = 0; p.dX = x;
+  p.meta = reinterpret_cast<int*>(base);          // 64 ints
+  float* A = reinterpret_cast<float*>(base + 256);
+  const int lda = chol_lda(n);
+  const int64_t tot = (int64_t)(n + 1) * n;
+  const int grid = (int)(ceil_div64(tot, 256) < kNumSMs * 8 ? ceil_div64(tot, 256) : kNumSMs * 8);
+  chol_pack_kernel<<<grid, 256, 0, st>>>(S, y, n, A, lda, p.meta);
+  note_launches(1);
+  if (getenv("DPVO_DEBUG_SYNC")) {
+    cudaError_t e_ = cudaStreamSynchronize(st);
+    if (e_ != cudaSuccess) { set_error("chol_solve: pack: %s", cudaGetErrorString(e_)); return 1; }
+  }
+  if (ba_chol_solve(p, A, lda, A + (int64_t)(n + 1) * lda, st)) return 1;
+  cudaMemcpyAsync(info, p.meta + 1, sizeof(int), cudaMemcpyDeviceToDevice, st);
+  return check_launch("chol_solve");
+}

@@ -115,6 +115,23 @@ def unique_inverse(keys, key_bound):
     return uniq, inv, cnt
 
 
+def cholesky_solve(S, y):
+    """x = S^-1 y for a dense SPD float32 system with the BA's blocked Cholesky.  Returns (x, info);
+    info is a device int32 tensor (0 = ok, 1 = non-positive pivot, x zeroed).  No host sync."""
+    require_cuda(S, y)
+    S = _f32c(S, "S"); y = _f32c(y.reshape(-1), "y")
+    n = y.numel()
+    if S.dim() != 2 or S.shape[0] != n or S.shape[1] != n:
+        raise RuntimeError("cuda_ba.cholesky_solve: S must be [n,n] and y [n]")
+    x = torch.zeros(n, dtype=torch.float32, device=S.device)
+    info = torch.zeros(1, dtype=torch.int32, device=S.device)
+    lib.dpvo_chol_workspace_bytes.restype = c_i64
+    ws = _workspace(S.device, lib.dpvo_chol_workspace_bytes(c_i32(n)))
+    check(lib.dpvo_chol_solve(ptr(S), ptr(y), c_i32(n), ptr(x), ptr(info), ptr(ws), c_i64(ws.numel()), stream_of(S)),
+          "cuda_ba.cholesky_solve")
+    return x, info
+
+
 def solve_system(*args, **kwargs):
     raise RuntimeError("cuda_ba.solve_system (classic loop-closure PGO, fastba/ba.cpp:120-180) is outside the "
                        "hot path of this build (SURVEY.md §8f N5)")

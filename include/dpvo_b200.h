@@ -136,6 +136,14 @@ int dpvo_unique_inverse(const int64_t* keys, int64_t n, int64_t key_bound,
                         int64_t* uniq, int64_t* inverse, int32_t* n_uniq,
                         void* workspace, int64_t workspace_bytes, void* stream);
 
+/* Dense SPD solve S x = y with the blocked Cholesky the BA uses for 6N > 127 (csrc/ba_chol.cu) —
+ * what at::linalg_cholesky_ex + torch::cholesky_solve do at ba_cuda.cu:547-548,561-562.  S: [n,n]
+ * row-major float32 (lower triangle read), y: [n], x: [n] out, info: device int32, 0 = ok, 1 = a
+ * pivot was not positive (x is then zero).  workspace: dpvo_chol_workspace_bytes(n). */
+int64_t dpvo_chol_workspace_bytes(int32_t n);
+int dpvo_chol_solve(const float* S, const float* y, int32_t n, float* x, int32_t* info,
+                    void* workspace, int64_t workspace_bytes, void* stream);
+
 /* Reprojection of all PxP pixels of patch kk[e] from frame ii[e] into frame jj[e] —
  * replaces cuda_ba.reproject (ba_cuda.cu:379-429,585-617).  coords: [E,2,P,P] float32. */
 int dpvo_reproject(const float* poses, const float* patches, const float* intrinsics,

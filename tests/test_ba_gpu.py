@@ -321,3 +321,21 @@ def test_ba_full_size_properties():
     assert _rel(got2[0], got[0]) < 1e-5 and _rel(got2[1], got[1]) < 1e-5
     want = _run_oracle(d, t0, t1)
     _check_against(d, got, want)
+
+
+@pytest.mark.parametrize("n", [1, 17, 64, 65, 128, 200, 234, 384, 1000, 1794])
+def test_blocked_cholesky_solve(n):
+    """The blocked Cholesky of csrc/ba_chol.cu on its own: random SPD systems against numpy float64."""
+    pkg = load_pkg()
+    rng = np.random.default_rng(n)
+    M = rng.standard_normal((n, n + 8))
+    S = (M @ M.T / (n + 8) + 0.5 * np.eye(n)).astype(np.float32)
+    y = rng.standard_normal(n).astype(np.float32)
+    x, info = pkg.cuda_ba.cholesky_solve(_dev(S), _dev(y))
+    assert int(info.item()) == 0
+    want = np.linalg.solve(S.astype(np.float64), y.astype(np.float64))
+    assert _rel(x.cpu().numpy(), want) < 2e-5
+    # a matrix that is not positive definite is reported, not silently factored
+    S2 = S.copy(); S2[n // 2, n // 2] = -1.0
+    x2, info2 = pkg.cuda_ba.cholesky_solve(_dev(S2), _dev(y))
+    assert int(info2.item()) == 1 and float(x2.abs().max()) == 0.0
