@@ -15,3 +15,4 @@ from . import altcorr       # noqa: F401
 from . import cuda_ba       # noqa: F401
 from . import fastba        # noqa: F401
 from . import lietorch_backends  # noqa: F401
+from . import projective_ops     # noqa: F401

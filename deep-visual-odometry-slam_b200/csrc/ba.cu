@@ -384,6 +384,12 @@ ba_schur_kernel(const __grid_constant__ BADev p) {
       us[threadIdx.x] = (k < M) ? p.u[k] : 0.f;
     }
     __syncthreads();
+    // fp32 inside a chunk of kSchurKC patches, fp64 across chunks (and across CTAs, in the atomics)
+    float part[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) part[i][j] = 0.f;
 #pragma unroll 8
     for (int kk_ = 0; kk_ < kSchurKC; ++kk_) {
       float av[4], bv[4];
@@ -392,10 +398,16 @@ ba_schur_kernel(const __grid_constant__ BADev p) {
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] += (double)av[i] * (double)bv[j];
+        for (int j = 0; j < 4; ++j) part[i][j] += av[i] * bv[j];
     }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] += (double)part[i][j];
     if (tb == 0 && threadIdx.x < 64) {
-      for (int kk_ = 0; kk_ < kSchurKC; ++kk_) gacc += (double)As[kk_][threadIdx.x] * (double)us[kk_];
+      float gp = 0.f;
+      for (int kk_ = 0; kk_ < kSchurKC; ++kk_) gp += As[kk_][threadIdx.x] * us[kk_];
+      gacc += (double)gp;
     }
     __syncthreads();
   }

@@ -44,6 +44,7 @@ __device__ __forceinline__ bool chol_factor_invert(float (*L)[NB + 1], float (*X
     if (r >= nb || c > r) L[r][c] = (r == c) ? 1.f : 0.f;     // identity padding, clean upper triangle
   }
   __syncthreads();
+#pragma unroll 1
   for (int b = 0; b < NB / SB; ++b) {
     const int o = b * SB;
     if (wid == 0) {
@@ -51,7 +52,7 @@ __device__ __forceinline__ bool chol_factor_invert(float (*L)[NB + 1], float (*X
       const int l = lane & 15;
       float a[SB];
 #pragma unroll
-      for (int k = 0; k < SB; ++k) a[k] = (k <= l) ? L[o + l][o + k] : 0.f;
+      for (int k = 0; k < SB; ++k) a[k] = L[o + l][o + k];      // upper triangle is zero (kept so below)
       bool bad = false;
 #pragma unroll
       for (int j = 0; j < SB; ++j) {
@@ -59,11 +60,12 @@ __device__ __forceinline__ bool chol_factor_invert(float (*L)[NB + 1], float (*X
         if (!(d > 0.f)) bad = true;
         float rs = rsqrtf(d);
         rs = rs * (1.5f - 0.5f * d * rs * rs);
-        a[j] = (l == j) ? d * rs : a[j] * rs;                    // L[l][j], l >= j (rows above hold 0)
+        a[j] = (l == j) ? d * rs : a[j] * rs;                    // L[l][j] for l >= j
 #pragma unroll
         for (int k = j + 1; k < SB; ++k) {
           const float lkj = __shfl_sync(0xffffffffu, a[j], k);   // L[k][j]
-          if (l >= k) a[k] -= a[j] * lkj;
+          a[k] -= a[j] * lkj;      // unconditional: entries above the diagonal (l < k) become don't-care values
+                                  // (never read by another lane, masked at the store) and a[] stays in registers
         }
       }
       // ---- inverse: lane c < 16 owns column c of Xd; L[i][k] comes from lane i
@@ -77,9 +79,9 @@ __device__ __forceinline__ bool chol_factor_invert(float (*L)[NB + 1], float (*X
       }
       if (lane < SB) {
 #pragma unroll
-        for (int k = 0; k < SB; ++k) {
-          if (k <= l) L[o + l][o + k] = a[k];
-          if (k >= l) X[o + k][o + l] = x[k];
+        for (int k = 0; k < SB; ++k) {                           // unconditional stores: selects, not branches,
+          L[o + l][o + k] = (k <= l) ? a[k] : 0.f;               // so the arrays stay in registers
+          X[o + k][o + l] = (k >= l) ? x[k] : 0.f;
         }
         if (bad) s_fail = 1;
       }
@@ -108,6 +110,7 @@ __device__ __forceinline__ bool chol_factor_invert(float (*L)[NB + 1], float (*X
       }
       __syncthreads();
       // ---- trailing update of the lower triangle: A22[r][c] -= L21[r][:] . L21[c][:]
+#pragma unroll 1
       for (int idx = tid; idx < below * below; idx += 256) {
         const int r = idx / below, c = idx - r * below;
         if (c > r) continue;
@@ -120,21 +123,26 @@ __device__ __forceinline__ bool chol_factor_invert(float (*L)[NB + 1], float (*X
     }
   }
   // ---- inv(L): X_ij = -X_ii * sum_{k=j}^{i-1} L_ik X_kj for block distance 1, 2, 3
+#pragma unroll 1
   for (int dist = 1; dist < NB / SB; ++dist) {
     const int nblk = NB / SB - dist;
     const int r = tid / SB, c = tid % SB;
+#pragma unroll 1
     for (int q = 0; q < nblk; ++q) {         // block (i = q + dist, j = q): one output per thread
       const int i = q + dist, j = q;
       float sacc = 0.f;
+#pragma unroll 1
       for (int k = j; k < i; ++k)
 #pragma unroll
         for (int t = 0; t < SB; ++t) sacc += L[i * SB + r][k * SB + t] * X[k * SB + t][j * SB + c];
       Tm[q][r][c] = sacc;
     }
     __syncthreads();
+#pragma unroll 1
     for (int q = 0; q < nblk; ++q) {
       const int i = q + dist, j = q;
       float sacc = 0.f;
+#pragma unroll 4
       for (int t = 0; t <= r; ++t) sacc += X[i * SB + r][i * SB + t] * Tm[q][t][c];
       X[i * SB + r][j * SB + c] = -sacc;
     }

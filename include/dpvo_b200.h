@@ -150,6 +150,31 @@ int dpvo_reproject(const float* poses, const float* patches, const float* intrin
                    const int64_t* ii, const int64_t* jj, const int64_t* kk,
                    int64_t n_edges, int32_t P, float* coords, void* stream);
 
+/* --------------------------------------------------------- projective_ops */
+
+/* Fused projective transform — replaces the inference path of projective_ops.transform
+ * (projective_ops.py:53-108): coords of every pixel of patch kk[e] (source frame ii[e]) in frame jj[e],
+ * per-frame intrinsics, quaternions normalised on load, depth clamp 1 / max(Z, 0.1).
+ * coords: [E,P,P,2] (or [E,P,P,3] with the inverse depth when depth != 0).  valid (optional):
+ * [E,P,P] float, 1 where Z > 0.2.  tonly != 0 drops the rotation of G_ij.  Ji/Jj: [E,2,6],
+ * Jz: [E,2], jvalid: [E] (all four or none): centre-pixel Jacobians as at :71-106.  No autograd. */
+int dpvo_transform(const float* poses, const float* patches, const float* intrinsics,
+                   const int64_t* ii, const int64_t* jj, const int64_t* kk,
+                   int64_t n_edges, int64_t n_frames, int64_t n_patches, int32_t P,
+                   int32_t depth, int32_t tonly, float* coords, float* valid,
+                   float* Ji, float* Jj, float* Jz, float* jvalid, void* stream);
+
+/* projective_ops.flow_mag (:116-126): flow [E,P,P] = beta |x_ij - x_ii| + (1-beta) |x_ij(t only) - x_ii|,
+ * valid [E,P,P] uint8 = (Z_ij > 0.2). */
+int dpvo_flow_mag(const float* poses, const float* patches, const float* intrinsics,
+                  const int64_t* ii, const int64_t* jj, const int64_t* kk,
+                  int64_t n_edges, int64_t n_frames, int64_t n_patches, int32_t P, float beta,
+                  float* flow, uint8_t* valid, void* stream);
+
+/* projective_ops.point_cloud (:111-113): points [n,P,P,4] = G_{ix[n]}^-1 * iproj(patches[n], intrinsics[ix[n]]). */
+int dpvo_point_cloud(const float* poses, const float* patches, const float* intrinsics, const int64_t* ix,
+                     int64_t n, int64_t n_frames, int32_t P, float* points, void* stream);
+
 /* ----------------------------------------------------------------- lietorch */
 
 /* Element-wise Lie-group operators — replace lietorch_backends (lietorch/src/lietorch.cpp:18-316,

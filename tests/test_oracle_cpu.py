@@ -235,3 +235,28 @@ def test_torch_cpu_correlation_matches_numpy_restatement(synth):
     a, b = got.astype(np.float64), want.astype(np.float64)
     assert np.linalg.norm(a - b) / np.linalg.norm(b) < 1e-4
     assert (a == b).mean() > 0.99
+
+
+# ------------------------------------------------------------------ projective_ops vs reference CPU
+def test_projective_ops_restatement_matches_reference_cpu():
+    from oracle import pops_oracle as po
+    g = np.load(os.path.join(GOLD, "ref_cpu_pops.npz"))
+    a = (g["poses"], g["patches"], g["intrinsics"], g["ii"], g["jj"], g["kk"])
+    tol = 5e-6
+    rel = lambda x, y: np.linalg.norm(np.asarray(x, np.float64) - y) / max(np.linalg.norm(y), 1e-30)
+    assert rel(po.transform(*a), g["coords"]) < tol
+    assert rel(po.transform(*a, depth=True), g["coords_depth"]) < tol
+    c, v = po.transform(*a, valid=True)
+    assert np.array_equal(v, g["valid"])
+    assert rel(po.transform(*a, tonly=True), g["coords_tonly"]) < tol
+    c, jv, (Ji, Jj, Jz) = po.transform(*a, jacobian=True)
+    assert np.array_equal(jv, g["jvalid"])
+    assert rel(Ji, g["Ji"]) < tol and rel(Jj, g["Jj"]) < tol and rel(Jz, g["Jz"]) < tol
+    f, fv = po.flow_mag(*a, beta=0.5)
+    assert rel(f, g["flow"]) < 2e-4          # differences of nearly equal float32 coordinates
+    assert np.array_equal(fv, g["flow_valid"])
+    assert rel(po.point_cloud(g["poses"], g["patches"], g["intrinsics"], g["ix"]), g["points"]) < tol
+    # the older fixture (uniform intrinsics, jacobian=True) too
+    t = np.load(os.path.join(GOLD, "ref_cpu_transform.npz"))
+    c, jv, (Ji, Jj, Jz) = po.transform(t["poses"], t["patches"], t["intrinsics"], t["ii"], t["jj"], t["kk"], jacobian=True)
+    assert rel(c, t["coords"]) < tol and rel(Ji, t["Ji"]) < tol and rel(Jj, t["Jj"]) < tol and rel(Jz, t["Jz"]) < tol
