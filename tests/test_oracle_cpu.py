@@ -260,3 +260,17 @@ def test_projective_ops_restatement_matches_reference_cpu():
     t = np.load(os.path.join(GOLD, "ref_cpu_transform.npz"))
     c, jv, (Ji, Jj, Jz) = po.transform(t["poses"], t["patches"], t["intrinsics"], t["ii"], t["jj"], t["kk"], jacobian=True)
     assert rel(c, t["coords"]) < tol and rel(Ji, t["Ji"]) < tol and rel(Jj, t["Jj"]) < tol and rel(Jz, t["Jz"]) < tol
+
+
+def test_pure_torch_ba_restatement_matches_reference_cpu():
+    """oracle/ba_torch_oracle.py (dpvo/ba.py::BA, the CPU baseline bench.py times) against the reference's
+    own ba.BA output (ref_cpu_ba.npz).  Both are float32: state to 1e-4, update to 5e-3."""
+    from oracle import ba_torch_oracle as bt
+    t = np.load(os.path.join(GOLD, "ref_cpu_transform.npz")); g = np.load(os.path.join(GOLD, "ref_cpu_ba.npz"))
+    P, Z = bt.BA(t["poses"], t["patches"], t["intrinsics"], t["target"], t["weight"], 1e-4, t["ii"], t["jj"], t["kk"],
+                 list(g["bounds"]), ep=float(g["ep"]), fixedp=int(g["fixedp"]))
+    rel = lambda a, b: np.linalg.norm(a.astype(np.float64) - b) / np.linalg.norm(b)
+    wantP = g["poses_out"].reshape(-1, 7); wantZ = g["patches_out"].reshape(-1, 3, 3, 3)
+    assert rel(P, wantP) < 1e-4 and rel(Z[:, 2], wantZ[:, 2]) < 3e-4
+    assert rel(P - t["poses"], wantP - t["poses"]) < 5e-3
+    assert np.array_equal(P[:1], t["poses"][:1]) and np.array_equal(Z[:, :2], t["patches"][:, :2])
