@@ -204,6 +204,10 @@ def main():
     # inference shards by independent sequence: rank r owns sequence r (seeded differently), no collective
     seq, = par.shard_sequences(world, rank, world)
     hp = hotpath.UpdateHotPath(dev, n_frames=40, seed=seq)
+    if os.environ.get("DPVO_BENCH_NO_OVERLAP"):
+        hp.overlap_neighbors = False
+    if os.environ.get("DPVO_BENCH_STREAM"):
+        torch.cuda.set_stream(torch.cuda.Stream(dev))     # everything below runs on a non-default stream
     alg_bytes = hp.corr_algorithmic_bytes()
 
     def barrier():

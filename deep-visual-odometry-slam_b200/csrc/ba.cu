@@ -714,6 +714,11 @@ ba_backsub_kernel(const __grid_constant__ BADev p) {
   const int nwarp = (gridDim.x * blockDim.x) >> 5;
   for (int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; k < M; k += nwarp) {
     float* er = p.Et + (int64_t)k * n;
+    // everything the retraction needs is requested before the dot product, so the row of E^T, the
+    // diagonal terms and the patch depth are in flight together instead of one after the other
+    const float ck = p.C[k], uk = p.u[k];
+    float* dp = p.patches + p.kx[k] * 3 * PP + 2 * PP;
+    const float d0 = dp[0];
     float dot = 0.f;
     for (int a = lane; a < n; a += 32) {
       dot += er[a] * dXs[a];
@@ -722,11 +727,15 @@ ba_backsub_kernel(const __grid_constant__ BADev p) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
     if (lane == 0) {
-      const float q = 1.0f / (p.C[k] + lm);
-      const float dz = q * (p.u[k] - dot);
       p.C[k] = 0.f;
       p.u[k] = 0.f;
-      if (!failed) depth_retract(p.patches, p.kx[k], PP, dz);
+    }
+    if (!failed) {
+      // d <- d + dz; d > 20 -> 1; d <- max(d, 1e-4); broadcast over the patch (depth_retract, one pixel per lane)
+      float d = d0 + (uk - dot) * (1.0f / (ck + lm));
+      d = (d > 20.f) ? 1.0f : d;
+      d = fmaxf(d, 1e-4f);
+      for (int i = lane; i < PP; i += 32) dp[i] = d;
     }
   }
 }

@@ -60,6 +60,9 @@ class UpdateHotPath:
         self.host_coords = c["coords"]                    # for the CPU baseline / byte accounting
         self.host = dict(d=d, c=c)
         self.stage_events = None
+        self.overlap_neighbors = True
+        self._side = None
+        self._nb = None
 
     # ------------------------------------------------------------------ stages
     def ring_write(self):
@@ -109,6 +112,25 @@ class UpdateHotPath:
             events.setdefault(name, []).append((e0, e1))
             return r
 
+        if events is None and self.overlap_neighbors:
+            # `neighbors` only depends on the edge list (net.py:76): fork it onto a side stream so its six
+            # small launches run under the correlation kernel; join before BA.  Inside a CUDA-graph
+            # capture the fork / join become graph edges.
+            main = torch.cuda.current_stream(self.device)
+            if self._side is None:
+                self._side = torch.cuda.Stream(self.device)
+            fork, join = torch.cuda.Event(), torch.cuda.Event()
+            fork.record(main)
+            self._side.wait_event(fork)
+            with torch.cuda.stream(self._side):
+                self._nb = self.neighbors()
+                join.record(self._side)
+            self.ring_write()
+            self.patchify()
+            corr = self.corr(self.reproject())
+            main.wait_event(join)
+            self.ba()
+            return corr
         timed("ring_write", self.ring_write)
         timed("patchify", self.patchify)
         coords = timed("reproject", self.reproject)

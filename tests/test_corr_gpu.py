@@ -270,3 +270,21 @@ def test_corr_backward_vs_oracle_and_reference(dtype):
         out = pkg.altcorr.corr(t1, t2, _dev(coords), _dev(us), _dev(vs), R)
         (out * _dev(grad)).sum().backward()
         assert _rel(t1.grad.cpu().numpy(), w1) < tol and _rel(t2.grad.cpu().numpy(), w2) < tol
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.float32])
+@pytest.mark.parametrize("shape", [(3, 128, 30, 40), (2, 128, 7, 9), (1, 130, 6, 10), (2, 96, 5, 13), (1, 2, 1, 2)])
+def test_nchw_to_nhwc_bit_exact(dtype, shape):
+    """Layout kernel (ring write / channels-last shadow): a pure permutation, so bit-exact against
+    torch's permute for 16- and 32-bit elements, even and odd plane sizes, channel tails."""
+    pkg = load_pkg()
+    lib = pkg._lib
+    N, C, H, W = shape
+    g = torch.Generator(device="cpu").manual_seed(N * 1000 + C)
+    src = torch.randn(shape, generator=g).to(dtype).cuda()
+    dst = torch.full((N, H, W, C), float("nan"), dtype=dtype, device="cuda")
+    lib.check(lib.lib.dpvo_nchw_to_nhwc(lib.c_i32(lib.dtype_code(src)), lib.ptr(src), lib.ptr(dst), lib.c_i64(N),
+                                        lib.c_i32(C), lib.c_i64(H * W), lib.stream_of(src)), "nchw_to_nhwc")
+    want = src.permute(0, 2, 3, 1).contiguous()
+    iv = {2: torch.int16, 4: torch.int32}[src.element_size()]
+    assert torch.equal(dst.view(iv), want.view(iv))
