@@ -144,6 +144,31 @@ int64_t dpvo_chol_workspace_bytes(int32_t n);
 int dpvo_chol_solve(const float* S, const float* y, int32_t n, float* x, int32_t* info,
                     void* workspace, int64_t workspace_bytes, void* stream);
 
+/* ---- Update operator (net.py:23-88, blocks.py:15-48): edge-MLP layers on the tensor cores -------
+ * One nn.Linear(K, 384) over E edge rows with the row-local work that follows it in the reference
+ * fused into the epilogue:
+ *     v = A W^T + bias;  v *= gate;  v += res1;  v += res2[res2_index ? res2_index[row] : row];
+ *     v = LayerNorm(v; ln_gamma, ln_beta, ln_eps) when ln_gamma != NULL;  v = act(v);  Y = fp16(v)
+ * A: fp16 [M, K], row stride lda elements; W: fp16 [384, K] (nn.Linear weight layout), row stride
+ * ldw; strides are multiples of 8 elements and pointers 16-byte aligned (TMA); K is arbitrary (the
+ * tail is zero-filled).  gate / res1 / Y: fp16 [M, 384] contiguous; res2: fp16 [*, 384] rows
+ * gathered through the int64 index.  bias / ln_gamma / ln_beta: float32 [384].  fp32 accumulation.
+ * act: 0 none, 1 ReLU, 2 sigmoid.  Replaces the nn.Linear / nn.LayerNorm / ReLU / Sigmoid / add
+ * sequences of Update.forward (net.py:69-88) and GatedResidual.forward (blocks.py:30-31). */
+typedef struct dpvo_linear_params {
+  const void* A; int64_t lda;
+  const void* W; int64_t ldw;
+  const float* bias;
+  const void* gate;
+  const void* res1;
+  const void* res2; const int64_t* res2_index;
+  const float* ln_gamma; const float* ln_beta; float ln_eps;
+  int32_t act;
+  void* Y;
+  int64_t M; int32_t K;
+} dpvo_linear_params;
+int dpvo_linear384_f16(const dpvo_linear_params* p, void* stream);
+
 /* Reprojection of all PxP pixels of patch kk[e] from frame ii[e] into frame jj[e] —
  * replaces cuda_ba.reproject (ba_cuda.cu:379-429,585-617).  coords: [E,2,P,P] float32. */
 int dpvo_reproject(const float* poses, const float* patches, const float* intrinsics,
