@@ -149,10 +149,12 @@ def _dense_patch_blob(fmap1):
     return span == C * PH * PW and s[1] % 8 == 0 and s[0] % 8 == 0 and fmap1.data_ptr() % 16 == 0
 
 
-def pyramid_forward(fmap1, pyramid, scales, coords, ii, jj, radius):
+def pyramid_forward(fmap1, pyramid, scales, coords, ii, jj, radius, row_stride=None):
     """Fused multi-level lookup: returns [B, M, 49*P*P*L] with the level index fastest,
     i.e. torch.stack([corr_l ...], -1).view(B, M, -1) of the per-level results
-    (dpvo.py:203-207, net.py:165-169).  One launch for two levels."""
+    (dpvo.py:203-207, net.py:165-169).  One launch for two levels.  `row_stride` (elements, even,
+    >= the row length) makes the result a view of a [B, M, row_stride] buffer — 896 gives the
+    16-byte-aligned rows the Update operator's first layer loads with TMA (update.py)."""
     if len(pyramid) != len(scales) or len(pyramid) not in (1, 2):
         raise RuntimeError("pyramid_forward: 1 or 2 levels supported")
     for fm in pyramid:
@@ -165,7 +167,10 @@ def pyramid_forward(fmap1, pyramid, scales, coords, ii, jj, radius):
     DO = 2 * radius + 1
     L = len(pyramid)
     per = DO * DO * PH * PW
-    out = torch.empty((B, M, per * L), dtype=fmap1.dtype, device=fmap1.device)
+    stride = per * L if row_stride is None else int(row_stride)
+    if stride < per * L or stride % 2:
+        raise RuntimeError(f"pyramid_forward: row_stride must be even and >= {per * L}")
+    out = torch.empty((B, M, stride), dtype=fmap1.dtype, device=fmap1.device)[:, :, :per * L]
     if B * M == 0:
         return out
     if _wants_fast(fmap1, radius):
@@ -173,7 +178,7 @@ def pyramid_forward(fmap1, pyramid, scales, coords, ii, jj, radius):
         if not _dense_patch_blob(fmap1):
             fmap1 = fmap1.contiguous()
     esz = out.element_size()
-    levels = [_level(fm, float(sc), out.data_ptr() + l * esz, per * L, L)
+    levels = [_level(fm, float(sc), out.data_ptr() + l * esz, stride, L)
               for l, (fm, sc) in enumerate(zip(pyramid, scales))]
     _launch(fmap1, coords, ii, jj, radius, levels)
     return out

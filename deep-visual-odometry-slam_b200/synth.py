@@ -190,3 +190,51 @@ def corr_algorithmic_bytes(coords, shapes, scales, R=3, C=128, P=3, esz=2):
             n += int(uniq.sum())
         total += n * C * esz
     return total
+
+
+# ----------------------------------------------------------------------------- Update operator
+UPDATE_DIM = 384
+
+
+def update_state_dict(seed=0, P=3, dim=UPDATE_DIM):
+    """Random-initialised parameters of the reference's Update module (net.py:23-66), keyed like its
+    state_dict, as float32 numpy arrays from a seeded numpy generator (weights ~ U(-1,1)/sqrt(fan_in)
+    like nn.Linear's default scale; LayerNorm gains near 1 and small biases so every term matters)."""
+    rng = np.random.default_rng(seed)
+    sd = {}
+
+    def linear(name, fin, fout):
+        k = 1.0 / np.sqrt(fin)
+        sd[name + ".weight"] = rng.uniform(-k, k, (fout, fin)).astype(np.float32)
+        sd[name + ".bias"] = rng.uniform(-k, k, (fout,)).astype(np.float32)
+
+    def lnorm(name):
+        sd[name + ".weight"] = rng.uniform(0.8, 1.2, (dim,)).astype(np.float32)
+        sd[name + ".bias"] = rng.uniform(-0.1, 0.1, (dim,)).astype(np.float32)
+
+    linear("c1.0", dim, dim); linear("c1.2", dim, dim)
+    linear("c2.0", dim, dim); linear("c2.2", dim, dim)
+    lnorm("norm")
+    for a in ("agg_kk", "agg_ij"):
+        for l in "fgh":
+            linear(f"{a}.{l}", dim, dim)
+    lnorm("gru.0")
+    linear("gru.1.gate.0", dim, dim); linear("gru.1.res.0", dim, dim); linear("gru.1.res.2", dim, dim)
+    lnorm("gru.2")
+    linear("gru.3.gate.0", dim, dim); linear("gru.3.res.0", dim, dim); linear("gru.3.res.2", dim, dim)
+    linear("corr.0", 2 * 49 * P * P, dim); linear("corr.2", dim, dim); lnorm("corr.3"); linear("corr.5", dim, dim)
+    linear("d.1", dim, 2); linear("w.1", dim, 2)
+    return sd
+
+
+def update_inputs(n_frames=12, M=8, seed=0, P=3, dim=UPDATE_DIM, n_ctx=None):
+    """Edge list of a DPVO patch graph with the operator's per-edge inputs: hidden state `net`,
+    correlation features `corr` and the context table `imap` gathered through kk % len(imap)."""
+    rng = np.random.default_rng(seed + 1000)
+    ii, jj, kk = dpvo_edges(n_frames, M=M)
+    E = len(ii)
+    n_ctx = n_ctx or n_frames * M
+    return dict(ii=ii.astype(np.int64), jj=jj.astype(np.int64), kk=kk.astype(np.int64),
+                net=(0.5 * rng.standard_normal((E, dim))).astype(np.float32),
+                corr=rng.standard_normal((E, 2 * 49 * P * P)).astype(np.float32),
+                imap=rng.standard_normal((n_ctx, dim)).astype(np.float32))

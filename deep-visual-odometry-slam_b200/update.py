@@ -1,0 +1,198 @@
+"""DPVO's Update operator (net.py:23-88) on the B200 kernels — inference forward.
+
+Same call as the reference module:
+
+    net, (delta, weight, _) = update(net, inp, corr, flow, ii, jj, kk)
+
+with net / inp [1, E, 384], corr [1, E, 882], ii / jj / kk int64 [E]; built from a reference
+state_dict (`Update.from_state_dict`) or module (`Update.from_reference(network.update)`), so a
+maintainer swaps it in with one line after the checkpoint is loaded.
+
+What runs (19 tensor-core layer launches + 10 row kernels, no host synchronisation):
+  * every nn.Linear(·, 384) over the E edge rows is `update_ops.linear384` (tcgen05 + TMEM + TMA,
+    csrc/update_gemm.cu) with the row-local work that follows it in the reference fused into its
+    epilogue: bias, ReLU / sigmoid, LayerNorm, residual adds, the GatedResidual product and the
+    `imap[kk % n]` context gather;
+  * the neighbour gathers, SoftAgg's grouped softmax / sum and its expand, and the two 384->2 heads
+    are the row kernels of csrc/update_agg.cu; group labels come from `cuda_ba.unique_inverse`
+    (sorted unique, like torch.unique in blocks.py:43) without the host sync torch.unique has.
+
+Numerics: activations are stored as float16 between launches, every layer accumulates in float32 and
+LayerNorm / softmax statistics are float32.  The reference under autocast (dpvo.py:332) keeps the
+residual stream in float32 between its float16 GEMMs; the difference is bounded in
+tests/test_update_gpu.py against the float32 oracle next to the autocast graph's own error.
+CUDA only — there is no CPU fallback.
+"""
+import torch
+
+from . import _lib, cuda_ba, update_ops
+
+DIM = update_ops.DIM
+LN_EPS = 1e-3   # net.py:37,42,44,53
+_L = _lib.lib
+_L.dpvo_softagg_workspace_bytes.restype = _lib.c_i64
+
+_LINEAR = ("c1.0", "c1.2", "c2.0", "c2.2", "agg_kk.f", "agg_kk.g", "agg_kk.h", "agg_ij.f", "agg_ij.g", "agg_ij.h",
+           "gru.1.gate.0", "gru.1.res.0", "gru.1.res.2", "gru.3.gate.0", "gru.3.res.0", "gru.3.res.2",
+           "corr.0", "corr.2", "corr.5")
+_NORMS = ("norm", "gru.0", "gru.2", "corr.3")
+_HEADS = ("d.1", "w.1")
+
+
+def _rows(t, name, width):
+    """[1, E, width] or [E, width] -> [E, width] view."""
+    if t.dim() == 3:
+        if t.shape[0] != 1:
+            raise RuntimeError(f"Update: {name} must have batch size 1, got {tuple(t.shape)}")
+        t = t[0]
+    if t.dim() != 2 or t.shape[1] != width:
+        raise RuntimeError(f"Update: {name} must be [1, E, {width}], got {tuple(t.shape)}")
+    return t
+
+
+class Update:
+    def __init__(self, state_dict, device=None):
+        dev = torch.device(device if device is not None else "cuda")
+        if dev.type != "cuda":
+            raise RuntimeError("Update: CUDA device required (no CPU fallback)")
+        missing = [k + s for k in _LINEAR + _NORMS + _HEADS for s in (".weight", ".bias") if k + s not in state_dict]
+        if missing:
+            raise RuntimeError(f"Update: state_dict is missing {missing[:4]}{'...' if len(missing) > 4 else ''}")
+        self.device = dev
+        self.W, self.b, self.ln, self.head = {}, {}, {}, {}
+        for k in _LINEAR:
+            w = torch.as_tensor(state_dict[k + ".weight"]).detach().to(dev, torch.float32)
+            if w.shape[0] != DIM:
+                raise RuntimeError(f"Update: {k}.weight must have {DIM} output rows, got {tuple(w.shape)}")
+            K = w.shape[1]
+            ld = (K + 7) // 8 * 8                              # 16-byte rows for TMA
+            buf = torch.zeros((DIM, ld), dtype=torch.float16, device=dev)
+            buf[:, :K] = w.half()
+            self.W[k] = buf[:, :K]
+            self.b[k] = torch.as_tensor(state_dict[k + ".bias"]).detach().to(dev, torch.float32).contiguous()
+        for k in _NORMS:
+            self.ln[k] = (torch.as_tensor(state_dict[k + ".weight"]).detach().to(dev, torch.float32).contiguous(),
+                          torch.as_tensor(state_dict[k + ".bias"]).detach().to(dev, torch.float32).contiguous(), LN_EPS)
+        for k in _HEADS:
+            self.head[k] = (torch.as_tensor(state_dict[k + ".weight"]).detach().to(dev, torch.float32).contiguous(),
+                            torch.as_tensor(state_dict[k + ".bias"]).detach().to(dev, torch.float32).contiguous())
+        self.corr_features = self.W["corr.0"].shape[1]
+        self._ws = None
+
+    # ------------------------------------------------------------------ construction helpers
+    @classmethod
+    def from_state_dict(cls, state_dict, device=None, prefix=""):
+        if prefix:
+            state_dict = {k[len(prefix):]: v for k, v in state_dict.items() if k.startswith(prefix)}
+        return cls(state_dict, device)
+
+    @classmethod
+    def from_reference(cls, module, device=None):
+        """`module`: the reference's dpvo.net.Update instance (any nn.Module with its state_dict keys)."""
+        sd = module.state_dict()
+        if device is None:
+            device = next(iter(sd.values())).device
+        return cls(sd, device)
+
+    def eval(self):
+        return self
+
+    def cuda(self):
+        return self
+
+    # ------------------------------------------------------------------ pieces
+    def _lin(self, name, A, **kw):
+        return update_ops.linear384(A, self.W[name], self.b[name], **kw)
+
+    def _workspace(self, nbytes):
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def _gather(self, x, index):
+        out = torch.empty_like(x)
+        _lib.check(_L.dpvo_gather_rows_f16(_lib.ptr(x), _lib.ptr(index), _lib.c_i64(x.shape[0]), _lib.c_i32(DIM),
+                                           _lib.ptr(out), _lib.stream_of(x)), "gather_rows")
+        return out
+
+    def _soft_agg(self, name, x, keys, key_bound, ln=None):
+        """x + h(softagg(f(x), g(x)))[group], optionally followed by LayerNorm `ln`."""
+        E = x.shape[0]
+        _, ids, _ = cuda_ba.unique_inverse(keys, key_bound)
+        G = int(min(E, key_bound))
+        f = self._lin(name + ".f", x)
+        g = self._lin(name + ".g", x)
+        y = torch.zeros((G, DIM), dtype=torch.float16, device=x.device)
+        ws = self._workspace(_L.dpvo_softagg_workspace_bytes(_lib.c_i64(E), _lib.c_i64(G)))
+        _lib.check(_L.dpvo_softagg_f16(_lib.ptr(f), _lib.ptr(g), _lib.ptr(ids), _lib.c_i64(E), _lib.c_i64(G),
+                                       _lib.ptr(y), _lib.ptr(ws), _lib.c_i64(ws.numel()), _lib.stream_of(x)), "softagg")
+        hy = self._lin(name + ".h", y)
+        out = torch.empty_like(x)
+        gam, bet, eps = ln if ln is not None else (None, None, 0.0)
+        _lib.check(_L.dpvo_expand_add_f16(_lib.ptr(x), _lib.ptr(hy), _lib.ptr(ids), _lib.c_i64(E), _lib.ptr(gam),
+                                          _lib.ptr(bet), _lib.c_f32(eps), _lib.ptr(out), _lib.stream_of(x)),
+                   "expand_add")
+        return out
+
+    def _gated_residual(self, name, x, ln=None):
+        gate = self._lin(name + ".gate.0", x, act=2)
+        r = self._lin(name + ".res.0", x, act=1)
+        return self._lin(name + ".res.2", r, gate=gate, res1=x, ln=ln)
+
+    # ------------------------------------------------------------------ forward
+    def __call__(self, net, inp, corr, flow, ii, jj, kk, n_frames=None, n_patches=None):
+        """inp: [1, E, 384] tensor, or a (table [n, 384], index int64 [E]) pair — the context gather
+        `imap[:, kk % n]` of dpvo.py:333 then happens inside the layer that consumes it.
+        n_frames / n_patches: exclusive upper bounds of jj / ii and kk (size the group tables);
+        read from the index tensors (one host sync) when not given."""
+        _lib.require_cuda(net, corr, ii, jj, kk)
+        net = _rows(net, "net", DIM)
+        corr = _rows(corr, "corr", self.corr_features)
+        E = net.shape[0]
+        if corr.shape[0] != E or ii.numel() != E or jj.numel() != E or kk.numel() != E:
+            raise RuntimeError("Update: net, corr, ii, jj, kk disagree on the number of edges")
+        if isinstance(inp, (tuple, list)):
+            table, tidx = inp
+            table = _rows(table, "inp table", DIM)
+        else:
+            table, tidx = _rows(inp, "inp", DIM), None
+            if table.shape[0] != E:
+                raise RuntimeError("Update: inp must have one row per edge")
+        if E == 0:
+            z = net.new_zeros((1, 0, 2), dtype=torch.float32)
+            return net.half()[None], (z, z.clone(), None)
+        if n_frames is None:
+            n_frames = int(torch.maximum(ii.max(), jj.max()).item()) + 1
+        if n_patches is None:
+            n_patches = int(kk.max().item()) + 1
+        with torch.cuda.device(net.device):
+            net = net.half().contiguous()
+            table = table.half().contiguous()
+            if corr.dtype != torch.float16 or corr.stride(1) != 1 or corr.stride(0) % 8 or corr.data_ptr() % 16:
+                buf = torch.empty((E, (self.corr_features + 7) // 8 * 8), dtype=torch.float16, device=corr.device)
+                buf[:, :self.corr_features].copy_(corr)
+                corr = buf[:, :self.corr_features]
+            ii = ii.contiguous(); jj = jj.contiguous(); kk = kk.contiguous()
+            # correlation encoder + input injection + norm (net.py:71-72)
+            c = self._lin("corr.0", corr, act=1)
+            c = self._lin("corr.2", c, ln=self.ln["corr.3"], act=1)
+            net = self._lin("corr.5", c, res1=net, res2=table, idx=tidx, ln=self.ln["norm"])
+            # temporal neighbours along each patch track (net.py:74-80)
+            ix, jx = cuda_ba.neighbors(kk, jj)
+            t = self._lin("c1.0", self._gather(net, ix), act=1)
+            net = self._lin("c1.2", t, res1=net)
+            t = self._lin("c2.0", self._gather(net, jx), act=1)
+            net = self._lin("c2.2", t, res1=net)
+            # soft aggregation over patches and over frame pairs (net.py:82-83); gru.0's LayerNorm rides on the second
+            net = self._soft_agg("agg_kk", net, kk, n_patches)
+            net = self._soft_agg("agg_ij", net, ii * n_frames + jj, n_frames * n_frames, ln=self.ln["gru.0"])
+            # gated residual blocks (net.py:41-46,85)
+            net = self._gated_residual("gru.1", net, ln=self.ln["gru.2"])
+            net = self._gated_residual("gru.3", net)
+            delta = torch.empty((E, 2), dtype=torch.float32, device=net.device)
+            weight = torch.empty((E, 2), dtype=torch.float32, device=net.device)
+            (wd, bd), (ww, bw) = self.head["d.1"], self.head["w.1"]
+            _lib.check(_L.dpvo_update_heads_f16(_lib.ptr(net), _lib.ptr(wd), _lib.ptr(bd), _lib.ptr(ww), _lib.ptr(bw),
+                                                _lib.c_i64(E), _lib.ptr(delta), _lib.ptr(weight),
+                                                _lib.stream_of(net)), "update_heads")
+        return net[None], (delta[None], weight[None], None)

@@ -169,6 +169,31 @@ typedef struct dpvo_linear_params {
 } dpvo_linear_params;
 int dpvo_linear384_f16(const dpvo_linear_params* p, void* stream);
 
+/* out[r] = index[r] >= 0 ? src[index[r]] : 0 for fp16 rows of `dim` elements (dim % 8 == 0) —
+ * `mask * net[:, ix]` of Update.forward (net.py:76-80; ix from fastba.neighbors, -1 = no neighbour). */
+int dpvo_gather_rows_f16(const void* src, const int64_t* index, int64_t n_rows, int32_t dim, void* out,
+                         void* stream);
+
+/* SoftAgg's scatter_softmax + scatter_sum (blocks.py:42-50, torch_scatter.py:17-132) over fp16
+ * [E,384] rows f and g grouped by ids[e] in [0, group_bound) (any dense labelling of the groups, e.g.
+ * the inverse of dpvo_unique_inverse):  y[grp] = sum_e f_e softmax_grp(g)_e.  y: fp16
+ * [group_bound,384]; rows of empty groups are left untouched.  fp32 arithmetic, running maximum.
+ * workspace: dpvo_softagg_workspace_bytes(E, group_bound). */
+int64_t dpvo_softagg_workspace_bytes(int64_t n_edges, int64_t group_bound);
+int dpvo_softagg_f16(const void* f, const void* g, const int64_t* ids, int64_t n_edges, int64_t group_bound,
+                     void* y, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* out[e] = net[e] + hy[ids[e]] (SoftAgg's expand `h(y)[:, jx]` + the residual add, net.py:82-83),
+ * followed by LayerNorm(ln_gamma, ln_beta, ln_eps) when ln_gamma != NULL (gru.0, net.py:42).
+ * fp16 [*,384] rows, float32 gamma/beta. */
+int dpvo_expand_add_f16(const void* net, const void* hy, const int64_t* ids, int64_t n_edges,
+                        const float* ln_gamma, const float* ln_beta, float ln_eps, void* out, void* stream);
+
+/* delta = Linear(ReLU(net)), weight = sigmoid(Linear(ReLU(net))) (net.py:57-66,88): net fp16 [E,384],
+ * wd / ww float32 [2,384], bd / bw float32 [2]; delta, weight: float32 [E,2]. */
+int dpvo_update_heads_f16(const void* net, const float* wd, const float* bd, const float* ww, const float* bw,
+                          int64_t n_edges, float* delta, float* weight, void* stream);
+
 /* Reprojection of all PxP pixels of patch kk[e] from frame ii[e] into frame jj[e] —
  * replaces cuda_ba.reproject (ba_cuda.cu:379-429,585-617).  coords: [E,2,P,P] float32. */
 int dpvo_reproject(const float* poses, const float* patches, const float* intrinsics,

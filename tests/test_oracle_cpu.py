@@ -274,3 +274,23 @@ def test_pure_torch_ba_restatement_matches_reference_cpu():
     assert rel(P, wantP) < 1e-4 and rel(Z[:, 2], wantZ[:, 2]) < 3e-4
     assert rel(P - t["poses"], wantP - t["poses"]) < 5e-3
     assert np.array_equal(P[:1], t["poses"][:1]) and np.array_equal(Z[:, :2], t["patches"][:, :2])
+
+
+def test_update_oracle_vs_reference():
+    """Update operator (N1): the functional restatement against the reference nn.Module's own float32
+    output (tests/golden/make_golden_update.py).  Parameters come from the same seeded generator."""
+    import importlib
+    import torch
+    from oracle import update_oracle as uo
+    synth = importlib.import_module("deep-visual-odometry-slam_b200.synth")
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_cpu_update.npz"))
+    sd = uo.state_dict_tensors(synth.update_state_dict(int(g["seed_w"])))
+    d = synth.update_inputs(n_frames=int(g["n_frames"]), M=int(g["M"]), seed=int(g["seed_x"]))
+    ii, jj, kk = (torch.from_numpy(d[k]) for k in ("ii", "jj", "kk"))
+    imap = torch.from_numpy(d["imap"])
+    net, delta, weight = uo.forward(sd, torch.from_numpy(d["net"]), imap[kk % imap.shape[0]],
+                                    torch.from_numpy(d["corr"]), ii, jj, kk)
+    assert net.shape == g["net"].shape
+    np.testing.assert_allclose(net.numpy(), g["net"], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(delta.numpy(), g["delta"], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(weight.numpy(), g["weight"], rtol=1e-4, atol=1e-5)

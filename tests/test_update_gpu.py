@@ -1,0 +1,178 @@
+"""GPU parity tests for the Update operator (N1): tensor-core edge-MLP layers (csrc/update_gemm.cu),
+row kernels (csrc/update_agg.cu) and the whole operator (update.py), through the C ABI.
+
+Oracle: oracle/update_oracle.py (float32 restatement of net.py:69-88, pinned on CPU against the
+reference module's own output in tests/golden/ref_cpu_update.npz).
+
+Tolerances.  The reference runs this operator under torch.autocast(fp16) (dpvo.py:332): fp16 GEMM
+inputs / outputs, fp32 LayerNorm and residual stream.  The fused path stores fp16 activations with
+fp32 accumulation and statistics, so both sit at fp16 rounding distance from the float32 oracle:
+  * single layer: |err| <= 2e-3 * max|want| + 1e-3 (one fp16 rounding of the output);
+  * whole operator: norm-wise relative error of net / delta / weight <= 1e-2 AND not more than
+    3x the error of the autocast graph itself on the same inputs.
+"""
+import importlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_pkg
+from oracle import update_oracle as uo
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    a = a.double(); b = b.double()
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def _ref_layer(A, W, b, gate=None, res1=None, res2=None, idx=None, ln=None, act=0):
+    v = A.float() @ W.float().t() + b
+    if gate is not None: v = v * gate.float()
+    if res1 is not None: v = v + res1.float()
+    if res2 is not None: v = v + (res2[idx] if idx is not None else res2).float()
+    if ln is not None: v = torch.nn.functional.layer_norm(v, (384,), ln[0], ln[1], ln[2])
+    if act == 1: v = v.relu()
+    if act == 2: v = v.sigmoid()
+    return v
+
+
+@pytest.mark.parametrize("M,K,ld", [(1, 384, 384), (128, 64, 64), (300, 384, 384), (5000, 384, 392),
+                                    (1000, 882, 896), (20000, 882, 888)])
+def test_linear384_vs_torch(M, K, ld):
+    pkg = load_pkg()
+    ops = importlib.import_module(pkg.__name__ + ".update_ops")
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(M + K)
+    r = lambda *s: torch.randn(*s, device=dev, generator=g)
+    Abuf = torch.full((M, ld), float("nan"), dtype=torch.float16, device=dev)   # padding must never be read
+    Abuf[:, :K] = r(M, K).half()
+    A = Abuf[:, :K]
+    Wp = torch.full((384, ld), float("nan"), dtype=torch.float16, device=dev)
+    Wp[:, :K] = (r(384, K) / K ** 0.5).half()
+    W = Wp[:, :K]
+    b = r(384)
+    gate = torch.rand(M, 384, device=dev, generator=g).half()
+    res1 = r(M, 384).half()
+    table = r(77, 384).half()
+    idx = torch.randint(0, 77, (M,), device=dev, generator=g)
+    gam, bet = r(384), r(384)
+    cases = [dict(), dict(act=1), dict(act=2), dict(res1=res1), dict(gate=gate, res1=res1),
+             dict(res1=res1, res2=table, idx=idx, ln=(gam, bet, 1e-3)), dict(ln=(gam, bet, 1e-3), act=1),
+             dict(gate=gate, res1=res1, ln=(gam, bet, 1e-3))]
+    for kw in cases:
+        want = _ref_layer(A, W, b, **kw)
+        got = ops.linear384(A, W, b, **kw).float()
+        err = (got - want).abs().max().item()
+        assert err <= 2e-3 * want.abs().max().item() + 1e-3, (sorted(kw), err)
+
+
+def test_linear384_argument_errors():
+    pkg = load_pkg()
+    ops = importlib.import_module(pkg.__name__ + ".update_ops")
+    A = torch.zeros(4, 384, dtype=torch.float16, device="cuda")
+    W = torch.zeros(384, 384, dtype=torch.float16, device="cuda")
+    with pytest.raises(RuntimeError):
+        ops.linear384(A.float(), W)
+    with pytest.raises(RuntimeError):
+        ops.linear384(A, W[:100])
+    with pytest.raises(RuntimeError):
+        ops.linear384(A.cpu(), W.cpu())
+    with pytest.raises(RuntimeError):
+        ops.linear384(torch.zeros(4, 882, dtype=torch.float16, device="cuda"),
+                      torch.zeros(384, 882, dtype=torch.float16, device="cuda"))      # 1764-byte rows: not TMA-able
+    assert ops.linear384(A[:0], W).shape == (0, 384)
+
+
+def _operator_case(pkg, n_frames, M, seed_w, seed_x):
+    synth = importlib.import_module(pkg.__name__ + ".synth")
+    sd_np = synth.update_state_dict(seed_w)
+    d = synth.update_inputs(n_frames=n_frames, M=M, seed=seed_x)
+    return sd_np, d
+
+
+def _run_ours(pkg, sd_np, d, fused_ctx):
+    upd_mod = importlib.import_module(pkg.__name__ + ".update")
+    op = upd_mod.Update.from_state_dict({k: torch.from_numpy(v) for k, v in sd_np.items()}, device="cuda")
+    ii, jj, kk = (torch.from_numpy(d[k]).cuda() for k in ("ii", "jj", "kk"))
+    net = torch.from_numpy(d["net"]).cuda().half()[None]
+    corr = torch.from_numpy(d["corr"]).cuda().half()[None]
+    imap = torch.from_numpy(d["imap"]).cuda().half()
+    tidx = kk % imap.shape[0]
+    inp = (imap, tidx) if fused_ctx else imap[tidx][None]
+    out, (delta, weight, none) = op(net, inp, corr, None, ii, jj, kk)
+    assert none is None and out.shape == (1, len(d["ii"]), 384) and out.dtype == torch.float16
+    assert delta.shape == weight.shape == (1, len(d["ii"]), 2)
+    return out[0].float(), delta[0], weight[0]
+
+
+def _run_oracle(sd_np, d, autocast):
+    sd = uo.state_dict_tensors(sd_np, device="cuda")
+    ii, jj, kk = (torch.from_numpy(d[k]).cuda() for k in ("ii", "jj", "kk"))
+    # same fp16-rounded inputs as the fused path
+    net = torch.from_numpy(d["net"]).cuda().half().float()
+    corr = torch.from_numpy(d["corr"]).cuda().half().float()
+    imap = torch.from_numpy(d["imap"]).cuda().half().float()
+    with torch.no_grad():
+        o = uo.forward(sd, net, imap[kk % imap.shape[0]], corr, ii, jj, kk, autocast=autocast)
+    return tuple(t.float() for t in o)
+
+
+@pytest.mark.parametrize("fused_ctx", [False, True])
+def test_update_vs_reference_golden(fused_ctx):
+    """Small graph: the reference nn.Module's own float32 output (CPU golden)."""
+    pkg = load_pkg()
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_cpu_update.npz"))
+    sd_np, d = _operator_case(pkg, int(g["n_frames"]), int(g["M"]), int(g["seed_w"]), int(g["seed_x"]))
+    net, delta, weight = _run_ours(pkg, sd_np, d, fused_ctx)
+    a_net, a_delta, a_weight = _run_oracle(sd_np, d, autocast=True)
+    for name, got, auto in (("net", net, a_net), ("delta", delta, a_delta), ("weight", weight, a_weight)):
+        want = torch.from_numpy(g[name]).cuda()
+        e_ours, e_auto = _rel(got, want), _rel(auto, want)
+        assert e_ours <= 1e-2, (name, e_ours, e_auto)
+        assert e_ours <= 3 * e_auto + 1e-4, (name, e_ours, e_auto)
+
+
+@pytest.mark.parametrize("n_frames,M", [(3, 4), (14, 16), (22, 96)])
+def test_update_vs_oracle_sizes(n_frames, M):
+    """Up to the default sliding window (22 frames x 96 patches): float32 oracle on the same device."""
+    pkg = load_pkg()
+    sd_np, d = _operator_case(pkg, n_frames, M, seed_w=11, seed_x=n_frames)
+    net, delta, weight = _run_ours(pkg, sd_np, d, True)
+    w_net, w_delta, w_weight = _run_oracle(sd_np, d, autocast=False)
+    a_net, a_delta, a_weight = _run_oracle(sd_np, d, autocast=True)
+    for name, got, want, auto in (("net", net, w_net, a_net), ("delta", delta, w_delta, a_delta),
+                                  ("weight", weight, w_weight, a_weight)):
+        e_ours, e_auto = _rel(got, want), _rel(auto, want)
+        assert torch.isfinite(got).all()
+        assert e_ours <= 1e-2, (name, e_ours, e_auto)
+        assert e_ours <= 3 * e_auto + 1e-4, (name, e_ours, e_auto)
+
+
+def test_softagg_groups_match_torch():
+    """Grouped softmax / sum alone, ragged groups including singletons, large logits (running max)."""
+    pkg = load_pkg()
+    lib = pkg._lib
+    L = lib.lib
+    L.dpvo_softagg_workspace_bytes.restype = lib.c_i64
+    g = torch.Generator(device="cuda").manual_seed(5)
+    E, G = 5000, 700
+    ids = torch.randint(0, G - 50, (E,), device="cuda", generator=g)           # ids >= G-50 stay empty
+    ids[:3] = torch.tensor([G - 1, G - 1, G - 7], device="cuda")               # plus a pair and a singleton
+    f = torch.randn(E, 384, device="cuda", generator=g).half()
+    gm = (20 * torch.randn(E, 384, device="cuda", generator=g)).half()
+    y = torch.zeros(G, 384, dtype=torch.float16, device="cuda")
+    ws = torch.empty(int(L.dpvo_softagg_workspace_bytes(lib.c_i64(E), lib.c_i64(G))), dtype=torch.uint8, device="cuda")
+    lib.check(L.dpvo_softagg_f16(lib.ptr(f), lib.ptr(gm), lib.ptr(ids), lib.c_i64(E), lib.c_i64(G), lib.ptr(y),
+                                 lib.ptr(ws), lib.c_i64(ws.numel()), lib.stream_of(f)), "softagg")
+    idx = ids.view(-1, 1).expand(E, 384)
+    gmax = torch.full((G, 384), float("-inf"), device="cuda").scatter_reduce(0, idx, gm.float(), "amax", include_self=False)
+    ex = torch.exp(gm.float() - gmax[ids])
+    den = torch.zeros(G, 384, device="cuda").scatter_add_(0, idx, ex)
+    want = torch.zeros(G, 384, device="cuda").scatter_add_(0, idx, f.float() * ex / (den[ids] + 1e-12))
+    assert (y.float() - want).abs().max().item() <= 2e-3 * want.abs().max().item() + 1e-3
+    empty = torch.ones(G, dtype=torch.bool, device="cuda"); empty[ids] = False
+    assert empty.any() and (y[empty] == 0).all()
