@@ -3,11 +3,16 @@
 // tensor memory.
 //
 //   * one persistent CTA per SM walks 128-edge row tiles; the full 384-wide output row of a tile
-//     lives in TMEM (384 of 512 columns), so LayerNorm / gating / residuals are row-local in the
-//     epilogue: one thread owns one edge row;
-//   * warp 0 streams K-chunks of 64 (A: 128x64, W: 384x64 as two 192-row boxes) through a 3-stage
+//     lives in TMEM (384 of 512 columns), so LayerNorm / gating / residuals are row-local;
+//   * warp 0 streams K-chunks of 64 (A: 128x64, W: 384x64 as two 192-row boxes) through a 2-stage
 //     shared-memory ring with TMA (128-byte swizzle), warp 1's lane 0 issues tcgen05.mma
-//     (M128 x N192 x K16, two per K step), warps 2-5 are the epilogue;
+//     (M128 x N192 x K16, two per K step);
+//   * warps 2-13 are the epilogue: TMEM lanes are only reachable from warp (id % 4), so each lane
+//     quarter gets three warps that split the 384 columns; one thread = one row x 128 columns.
+//     LayerNorm statistics of the three thirds meet in spare TMEM columns, the pre-normalisation
+//     row is parked in TMEM between the two passes;
+//   * the fp16 output tile is assembled in shared memory in the swizzled 128x64 box layout and
+//     written with six TMA stores (coalesced, row tails clipped by the tensor map);
 //   * K tails (882 = 13.78 chunks) and row tails are zero-filled by TMA's out-of-bounds handling.
 #include "common.cuh"
 #include "sm100.cuh"
@@ -19,13 +24,16 @@ using namespace sm100;
 constexpr int kDim = 384;
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int kStages = 3;
+constexpr int kStages = 2;
 constexpr int kABytes = BM * BK * 2;             // 16 KB
 constexpr int kWBytes = kDim * BK * 2;           // 48 KB
 constexpr int kStageBytes = kABytes + kWBytes;   // 64 KB
-constexpr int kThreads = 192;
+constexpr int kOutBytes = BM * kDim * 2;         // 96 KB: six 128x64 boxes of 16 KB
+constexpr int kEpiWarps = 12;
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kThreads = 64 + kEpiThreads;       // 448
 constexpr uint32_t kTmemCols = 512;
-constexpr int kSmemBytes = kStages * kStageBytes + 1024;
+constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + 1024;
 
 struct LinearDev {
   const float* bias;
@@ -37,7 +45,6 @@ struct LinearDev {
   const float* ln_beta;
   float ln_eps;
   int act;
-  __half* Y;
   int64_t M;
   int kblocks;
 };
@@ -52,11 +59,16 @@ __device__ __forceinline__ void unpack8(const uint4& u, float* f) {
   }
 }
 
-// x[j] = acc[j] + bias, * gate, + res1, + res2 for 32 consecutive columns starting at n0 of one row
-__device__ __forceinline__ void apply_pre(float (&x)[32], const float* s_bias, int n0, const __half* gate,
+// x[j] = (acc[j] + bias) * gate + res1 + res2 for 32 consecutive columns starting at n0 of one row
+__device__ __forceinline__ void apply_pre(float (&x)[32], const float* bias, int n0, const __half* gate,
                                           const __half* res1, const __half* res2) {
+  if (bias) {
 #pragma unroll
-  for (int j = 0; j < 32; ++j) x[j] += s_bias[n0 + j];
+    for (int q = 0; q < 8; ++q) {
+      const float4 b = __ldg(reinterpret_cast<const float4*>(bias + n0) + q);
+      x[4 * q] += b.x; x[4 * q + 1] += b.y; x[4 * q + 2] += b.z; x[4 * q + 3] += b.w;
+    }
+  }
   if (gate) {
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
@@ -88,25 +100,21 @@ __device__ __forceinline__ void apply_pre(float (&x)[32], const float* s_bias, i
 
 __global__ void __launch_bounds__(kThreads, 1)
 linear384_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-                 const LinearDev p) {
+                 const __grid_constant__ CUtensorMap tmY, const LinearDev p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* out_tile = smem + kStages * kStageBytes;
   __shared__ uint64_t full[kStages], empty[kStages], tmem_full, tmem_empty;
   __shared__ uint32_t tmem_base_s;
-  __shared__ float s_bias[kDim], s_gamma[kDim], s_beta[kDim];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t tiles = (p.M + BM - 1) / BM;
   const bool ln = p.ln_gamma != nullptr;
 
-  for (int i = threadIdx.x; i < kDim; i += kThreads) {
-    s_bias[i] = p.bias ? p.bias[i] : 0.f;
-    s_gamma[i] = ln ? p.ln_gamma[i] : 1.f;
-    s_beta[i] = (ln && p.ln_beta) ? p.ln_beta[i] : 0.f;
-  }
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&tmY);
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -115,7 +123,7 @@ linear384_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         mbar_init(&empty[s], 1);
       }
       mbar_init(&tmem_full, 1);
-      mbar_init(&tmem_empty, 128);
+      mbar_init(&tmem_empty, kEpiThreads);
       mbar_fence_init();
     }
     __syncwarp();
@@ -175,75 +183,109 @@ linear384_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else {
     // ---------------------------------------------------------------- epilogue
     const int q = warp & 3;                           // TMEM lane quarter this warp may access
+    const int t = (warp - 2) >> 2;                    // column third: [128 t, 128 t + 128)
+    const int r_tile = q * 32 + lane;                 // row within the tile
+    const bool issuer = (warp == 2 && lane == 0);
     uint32_t tcount = 0;
     for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++tcount) {
       mbar_wait(&tmem_full, tcount & 1);
       tc_fence_after();
-      const int64_t row = tile * BM + q * 32 + lane;
+      const int64_t row = tile * BM + r_tile;
       const bool ok = row < p.M;
       const int64_t r = ok ? row : 0;
-      const uint32_t trow = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+      const uint32_t trow = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + t * 128;
       const __half* gate = p.gate ? p.gate + r * kDim : nullptr;
       const __half* res1 = p.res1 ? p.res1 + r * kDim : nullptr;
       const __half* res2 = p.res2 ? p.res2 + (p.res2_index ? p.res2_index[r] : r) * kDim : nullptr;
       float mean = 0.f, rstd = 1.f;
       if (ln) {
         float sum = 0.f, sq = 0.f;
-        for (int c = 0; c < kDim / 32; ++c) {
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
           uint32_t v[32];
           float x[32];
           tmem_ld32(trow + c * 32, v);
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]);
-          apply_pre(x, s_bias, c * 32, gate, res1, res2);
+          apply_pre(x, p.bias, t * 128 + c * 32, gate, res1, res2);
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             sum += x[j];
             sq += x[j] * x[j];
             v[j] = __float_as_uint(x[j]);
           }
-          tmem_st32(trow + c * 32, v);                // keep the pre-normalisation row in TMEM
+          tmem_st32(trow + c * 32, v);                // park the pre-normalisation row in TMEM
         }
+        // partial statistics of the three column thirds meet in spare TMEM columns 384..389 of the row
+        tmem_st2(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + kDim + 2 * t, __float_as_uint(sum),
+                 __float_as_uint(sq));
         tmem_st_wait();
+        tc_fence_before();
+        named_barrier(2, kEpiThreads);
+        tc_fence_after();
+        uint32_t ps[8];
+        tmem_ld8(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + kDim, ps);
+        tmem_ld_wait();
+        sum = __uint_as_float(ps[0]) + __uint_as_float(ps[2]) + __uint_as_float(ps[4]);
+        sq = __uint_as_float(ps[1]) + __uint_as_float(ps[3]) + __uint_as_float(ps[5]);
         mean = sum * (1.0f / kDim);
         const float var = fmaxf(sq * (1.0f / kDim) - mean * mean, 0.f);
         rstd = rsqrtf(var + p.ln_eps);
       }
-      for (int c = 0; c < kDim / 32; ++c) {
+      named_barrier(1, kEpiThreads);                  // previous tile's TMA stores have read out_tile (issuer waited)
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
         uint32_t v[32];
         float x[32];
         tmem_ld32(trow + c * 32, v);
         tmem_ld_wait();
+        const int n0 = t * 128 + c * 32;
 #pragma unroll
         for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]);
         if (ln) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) x[j] = (x[j] - mean) * rstd * s_gamma[c * 32 + j] + s_beta[c * 32 + j];
+          for (int qd = 0; qd < 8; ++qd) {
+            const float4 g4 = __ldg(reinterpret_cast<const float4*>(p.ln_gamma + n0) + qd);
+            const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.ln_beta + n0) + qd);
+            x[4 * qd] = (x[4 * qd] - mean) * rstd * g4.x + b4.x;
+            x[4 * qd + 1] = (x[4 * qd + 1] - mean) * rstd * g4.y + b4.y;
+            x[4 * qd + 2] = (x[4 * qd + 2] - mean) * rstd * g4.z + b4.z;
+            x[4 * qd + 3] = (x[4 * qd + 3] - mean) * rstd * g4.w + b4.w;
+          }
         } else {
-          apply_pre(x, s_bias, c * 32, gate, res1, res2);
+          apply_pre(x, p.bias, n0, gate, res1, res2);
         }
         if (p.act == 1) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
         } else if (p.act == 2) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) x[j] = 1.0f / (1.0f + __expf(-x[j]));
+          for (int j = 0; j < 32; ++j) x[j] = __fdividef(1.0f, 1.0f + __expf(-x[j]));
         }
-        if (ok) {
-          uint4* dst = reinterpret_cast<uint4*>(p.Y + row * kDim + c * 32);
+        // 32 columns = four 16-byte units of this row in box n0 / 64, XOR-swizzled like the TMA layout
+        uint8_t* box = out_tile + (n0 >> 6) * (BM * 128) + r_tile * 128;
+        const int u0 = (n0 & 63) >> 3;
 #pragma unroll
-          for (int qd = 0; qd < 4; ++qd) {
-            uint4 o;
-            __half2* h = reinterpret_cast<__half2*>(&o);
+        for (int qd = 0; qd < 4; ++qd) {
+          uint4 o;
+          __half2* h = reinterpret_cast<__half2*>(&o);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) h[j] = __floats2half2_rn(x[8 * qd + 2 * j], x[8 * qd + 2 * j + 1]);
-            dst[qd] = o;
-          }
+          for (int j = 0; j < 4; ++j) h[j] = __floats2half2_rn(x[8 * qd + 2 * j], x[8 * qd + 2 * j + 1]);
+          *reinterpret_cast<uint4*>(box + (((u0 + qd) ^ (r_tile & 7)) << 4)) = o;
         }
       }
       tc_fence_before();
-      mbar_arrive(&tmem_empty);
+      mbar_arrive(&tmem_empty);                       // TMEM drained: the next tile's MMAs may start
+      fence_proxy_async_smem();
+      named_barrier(3, kEpiThreads);                  // whole tile is in out_tile
+      if (issuer) {
+#pragma unroll
+        for (int b = 0; b < kDim / 64; ++b)
+          tma_store_2d(&tmY, out_tile + b * (BM * 128), b * 64, static_cast<int32_t>(tile * BM));
+        tma_store_commit();
+        tma_store_wait_read();
+      }
     }
   }
   tc_fence_before();
@@ -302,9 +344,10 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
                "linear384: A, W and Y must be 16-byte aligned");
   DPVO_REQUIRE(lp->act >= 0 && lp->act <= 2, "linear384: act must be 0 (none), 1 (relu) or 2 (sigmoid)");
   DPVO_REQUIRE(lp->M < (int64_t(1) << 31) - BM, "linear384: too many rows");
-  CUtensorMap tmA, tmW;
+  CUtensorMap tmA, tmW, tmY;
   if (make_map(&tmA, lp->A, lp->K, lp->M, lp->lda, BM)) return 1;
   if (make_map(&tmW, lp->W, lp->K, kDim, lp->ldw, kDim / 2)) return 1;
+  if (make_map(&tmY, lp->Y, kDim, lp->M, kDim, BM)) return 1;
   LinearDev p;
   p.bias = lp->bias;
   p.gate = static_cast<const __half*>(lp->gate);
@@ -315,7 +358,6 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
   p.ln_beta = lp->ln_beta;
   p.ln_eps = lp->ln_eps;
   p.act = lp->act;
-  p.Y = static_cast<__half*>(lp->Y);
   p.M = lp->M;
   p.kblocks = (lp->K + BK - 1) / BK;
   {
@@ -326,6 +368,6 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
   const int64_t tiles = (lp->M + BM - 1) / BM;
   const int grid = static_cast<int>(tiles < kNumSMs ? tiles : kNumSMs);
   note_launches(1);
-  linear384_kernel<<<grid, kThreads, kSmemBytes, reinterpret_cast<cudaStream_t>(stream)>>>(tmA, tmW, p);
+  linear384_kernel<<<grid, kThreads, kSmemBytes, reinterpret_cast<cudaStream_t>(stream)>>>(tmA, tmW, tmY, p);
   return check_launch("linear384");
 }

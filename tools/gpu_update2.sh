@@ -1,0 +1,3 @@
+mkdir -p gpurun_out
+timeout 600 python tools/time_update.py > gpurun_out/time_update.json 2>gpurun_out/time_update.err; echo rc=$?; cat gpurun_out/time_update.json; tail -5 gpurun_out/time_update.err
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/update_launches.csv python tools/time_update.py --profile > gpurun_out/ncu_update.log 2>&1; echo ncu rc=$?
