@@ -16,6 +16,7 @@
 //   * K tails (882 = 13.78 chunks) and row tails are zero-filled by TMA's out-of-bounds handling.
 #include "common.cuh"
 #include "sm100.cuh"
+#include <stdlib.h>
 
 namespace dpvo {
 namespace {
@@ -65,7 +66,7 @@ __device__ __forceinline__ void apply_pre(float (&x)[32], const float* bias, int
   if (bias) {
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
-      const float4 b = __ldg(reinterpret_cast<const float4*>(bias + n0) + q);
+      const float4 b = *(reinterpret_cast<const float4*>(bias + n0) + q);
       x[4 * q] += b.x; x[4 * q + 1] += b.y; x[4 * q + 2] += b.z; x[4 * q + 3] += b.w;
     }
   }
@@ -98,6 +99,10 @@ __device__ __forceinline__ void apply_pre(float (&x)[32], const float* bias, int
   }
 }
 
+// CL = CTAs per cluster.  The CL CTAs of a cluster work on CL consecutive row tiles in lock step and
+// share every W chunk: each loads 384/CL of its rows and multicasts them into all CL shared memories,
+// so W crosses the L2 -> SM fabric once per cluster instead of once per tile.
+template <int CL>
 __global__ void __launch_bounds__(kThreads, 1)
 linear384_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ CUtensorMap tmY, const LinearDev p) {
@@ -109,6 +114,11 @@ linear384_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t tiles = (p.M + BM - 1) / BM;
+  const int64_t groups = (tiles + CL - 1) / CL;       // groups of CL consecutive row tiles, one per cluster pass
+  const uint32_t crank = CL > 1 ? cluster_ctarank() : 0u;
+  const uint32_t cid = CL > 1 ? cluster_id_x() : blockIdx.x;
+  const uint32_t ncl = CL > 1 ? cluster_count_x() : gridDim.x;
+  constexpr uint16_t kMask = static_cast<uint16_t>((1u << CL) - 1u);
   const bool ln = p.ln_gamma != nullptr;
 
   if (warp == 0 && lane == 0) {
@@ -120,7 +130,7 @@ linear384_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (lane == 0) {
       for (int s = 0; s < kStages; ++s) {
         mbar_init(&full[s], 1);
-        mbar_init(&empty[s], 1);
+        mbar_init(&empty[s], CL);                     // one arrival per CTA of the cluster
       }
       mbar_init(&tmem_full, 1);
       mbar_init(&tmem_empty, kEpiThreads);
@@ -130,7 +140,7 @@ linear384_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tmem_alloc(&tmem_base_s, kTmemCols);
   }
   tc_fence_before();
-  __syncthreads();
+  if (CL > 1) cluster_sync_all(); else __syncthreads();   // barriers initialised cluster-wide before any multicast
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
 
@@ -138,16 +148,21 @@ linear384_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
       uint32_t it = 0;
-      for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+      for (int64_t grp = cid; grp < groups; grp += ncl) {
+        const int64_t tile = grp * CL + crank;        // may lie past the last tile: loads are zero-filled
         for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
           const int s = it % kStages;
           const uint32_t ph = (it / kStages) & 1;
-          mbar_wait(&empty[s], ph ^ 1);
+          mbar_wait(&empty[s], ph ^ 1);               // every CTA of the cluster has released stage s
           mbar_arrive_expect_tx(&full[s], kStageBytes);
           uint8_t* st = smem + s * kStageBytes;
           tma_load_2d(st, &tmA, &full[s], kb * BK, static_cast<int32_t>(tile * BM));
-          tma_load_2d(st + kABytes, &tmW, &full[s], kb * BK, 0);
-          tma_load_2d(st + kABytes + kWBytes / 2, &tmW, &full[s], kb * BK, kDim / 2);
+          if (CL == 1) {
+            tma_load_2d(st + kABytes, &tmW, &full[s], kb * BK, 0);
+            tma_load_2d(st + kABytes + kWBytes / 2, &tmW, &full[s], kb * BK, kDim / 2);
+          } else {
+            tma_load_2d_mc(st + kABytes + crank * (kWBytes / CL), &tmW, &full[s], kb * BK, crank * (kDim / CL), kMask);
+          }
         }
       }
     }
@@ -156,7 +171,7 @@ linear384_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (lane == 0) {
       constexpr uint32_t idesc = instr_desc_f16(BM, kDim / 2);
       uint32_t it = 0, tcount = 0;
-      for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++tcount) {
+      for (int64_t grp = cid; grp < groups; grp += ncl, ++tcount) {
         mbar_wait(&tmem_empty, (tcount & 1) ^ 1);     // epilogue has drained the previous tile
         tc_fence_after();
         for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
@@ -175,7 +190,8 @@ linear384_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mma_f16_ss(tmem_base, ad, b0, idesc, acc);
             mma_f16_ss(tmem_base + kDim / 2, ad, b1, idesc, acc);
           }
-          mma_commit(&empty[s]);                      // stage s is free once these MMAs have read it
+          // stage s is free once these MMAs have read it — tell every producer of the cluster
+          if (CL == 1) mma_commit(&empty[s]); else mma_commit_mc(&empty[s], kMask);
         }
         mma_commit(&tmem_full);                       // accumulator complete
       }
@@ -187,7 +203,8 @@ linear384_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int r_tile = q * 32 + lane;                 // row within the tile
     const bool issuer = (warp == 2 && lane == 0);
     uint32_t tcount = 0;
-    for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++tcount) {
+    for (int64_t grp = cid; grp < groups; grp += ncl, ++tcount) {
+      const int64_t tile = grp * CL + crank;
       mbar_wait(&tmem_full, tcount & 1);
       tc_fence_after();
       const int64_t row = tile * BM + r_tile;
@@ -279,13 +296,245 @@ linear384_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_arrive(&tmem_empty);                       // TMEM drained: the next tile's MMAs may start
       fence_proxy_async_smem();
       named_barrier(3, kEpiThreads);                  // whole tile is in out_tile
-      if (issuer) {
+      if (issuer && tile < tiles) {
 #pragma unroll
         for (int b = 0; b < kDim / 64; ++b)
           tma_store_2d(&tmY, out_tile + b * (BM * 128), b * 64, static_cast<int32_t>(tile * BM));
         tma_store_commit();
         tma_store_wait_read();
       }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (CL > 1) cluster_sync_all();                     // no CTA leaves while peers may still signal its barriers
+  if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ------------------------------------------------------ resident-W variant (K = 384, no LayerNorm)
+// The streaming kernel above is bound by what one SM can pull in from L2 / HBM (measured ~30 bytes per
+// clock per SM, whatever the ring depth or multicast):
+// every 128-row tile re-reads all of W (288 KB) next to its 96 KB of A.  Here the output columns are
+// split between the two CTAs of a pair: each keeps ITS half of W (192 x 384 fp16 = 144 KB) in shared
+// memory for the whole kernel and streams only A tiles through a 3-stage ring, so a tile costs 96 KB
+// of ingest per SM instead of 384 KB.  The half-width accumulator (192 TMEM columns) is double
+// buffered: the epilogue of tile i overlaps the MMAs of tile i+1.  Output chunks are transposed through
+// a 2 KB per-warp buffer so that every global store instruction writes whole 64-byte row segments.
+constexpr int kHalf = kDim / 2;                      // 192 output columns per CTA
+constexpr int kRwStages = 3;
+constexpr int kRwWBytes = kHalf * kDim * 2;          // 144 KB: six 192x64 chunks of 24 KB
+constexpr int kRwWChunk = kHalf * BK * 2;            // 24 KB
+constexpr int kRwStageOut = kEpiWarps * 2048;       // 2 KB transposition buffer per epilogue warp
+constexpr int kRwSmemBytes = kRwWBytes + kRwStages * kABytes + kRwStageOut + 1024;
+
+// Per-role wait-time counters of CTA 0 (DPVO_LINEAR_PROFILE=1; read with dpvo_linear_profile_read):
+// [0] producer: cycles waiting for a free ring stage   [1] producer: total
+// [2] MMA: waiting for A stages   [3] MMA: waiting for a drained accumulator   [4] MMA: waiting for W   [5] MMA: total
+// [6] epilogue: waiting for an accumulator   [7] epilogue: total   [8] tiles of this CTA
+// [9] epilogue: pack + transpose + global stores   [10] epilogue: TMEM loads
+__device__ long long g_linear_profile[16];
+
+struct LinearRwDev {
+  int profile;
+  const float* bias;
+  const __half* gate;
+  const __half* res1;
+  const __half* res2;
+  const int64_t* res2_index;
+  int act;
+  __half* Y;
+  int64_t M;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                    const LinearRwDev p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* w_res = smem;                              // [6][192 rows][128 B]
+  uint8_t* ring = smem + kRwWBytes;                   // [stages][128 rows][128 B]
+  uint8_t* stage_out = ring + kRwStages * kABytes;    // [epilogue warp][32 rows][64 B]
+  __shared__ uint64_t wfull, full[kRwStages], empty[kRwStages], tmem_full[2], tmem_empty[2];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float s_bias[kHalf];       // this CTA's half of the bias (L1 is tiny next to 220 KB of smem)
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t tiles = (p.M + BM - 1) / BM;
+  const int h = blockIdx.x & 1;                       // which half of the output columns
+  const int64_t first = blockIdx.x >> 1, step = gridDim.x >> 1;
+  constexpr int kKb = kDim / BK;                      // 6 K chunks
+
+  for (int i = threadIdx.x; i < kHalf; i += kThreads) s_bias[i] = p.bias ? p.bias[(blockIdx.x & 1) * kHalf + i] : 0.f;
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmW);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(&wfull, 1);
+      for (int s = 0; s < kRwStages; ++s) {
+        mbar_init(&full[s], 1);
+        mbar_init(&empty[s], 1);
+      }
+      for (int b = 0; b < 2; ++b) {
+        mbar_init(&tmem_full[b], 1);
+        mbar_init(&tmem_empty[b], kEpiThreads);
+      }
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc(&tmem_base_s, kTmemCols);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      const bool prof = p.profile && blockIdx.x == 0;
+      long long t_wait = 0;
+      const long long t_begin = clock64();
+      mbar_arrive_expect_tx(&wfull, kRwWBytes);
+      for (int kb = 0; kb < kKb; ++kb) tma_load_2d(w_res + kb * kRwWChunk, &tmW, &wfull, kb * BK, h * kHalf);
+      uint32_t it = 0;
+      for (int64_t tile = first; tile < tiles; tile += step) {
+        for (int kb = 0; kb < kKb; ++kb, ++it) {
+          const int s = it % kRwStages;
+          const uint32_t ph = (it / kRwStages) & 1;
+          const long long t0 = clock64();
+          mbar_wait(&empty[s], ph ^ 1);
+          t_wait += clock64() - t0;
+          mbar_arrive_expect_tx(&full[s], kABytes);
+          tma_load_2d(ring + s * kABytes, &tmA, &full[s], kb * BK, static_cast<int32_t>(tile * BM));
+        }
+      }
+      if (prof) {
+        g_linear_profile[0] = t_wait;
+        g_linear_profile[1] = clock64() - t_begin;
+      }
+    }
+  } else if (warp == 1) {
+    // -------------------------------------------------------------- MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = instr_desc_f16(BM, kHalf);
+      const bool prof = p.profile && blockIdx.x == 0;
+      long long t_full = 0, t_acc = 0;
+      const long long t_begin = clock64();
+      mbar_wait(&wfull, 0);
+      const long long t_w = clock64() - t_begin;
+      tc_fence_after();
+      const uint32_t w0 = smem_u32(w_res);
+      uint32_t it = 0, tcount = 0;
+      for (int64_t tile = first; tile < tiles; tile += step, ++tcount) {
+        const uint32_t buf = tcount & 1;
+        long long t0 = clock64();
+        mbar_wait(&tmem_empty[buf], ((tcount >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
+        t_acc += clock64() - t0;
+        tc_fence_after();
+        const uint32_t d = tmem_base + buf * kHalf;
+        for (int kb = 0; kb < kKb; ++kb, ++it) {
+          const int s = it % kRwStages;
+          const uint32_t ph = (it / kRwStages) & 1;
+          t0 = clock64();
+          mbar_wait(&full[s], ph);
+          t_full += clock64() - t0;
+          tc_fence_after();
+          const uint32_t a0 = smem_u32(ring + s * kABytes);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            mma_f16_ss(d, smem_desc_sw128(a0 + k * 32), smem_desc_sw128(w0 + kb * kRwWChunk + k * 32), idesc,
+                       (kb | k) != 0 ? 1u : 0u);
+          mma_commit(&empty[s]);
+        }
+        mma_commit(&tmem_full[buf]);
+      }
+      if (prof) {
+        g_linear_profile[2] = t_full;
+        g_linear_profile[3] = t_acc;
+        g_linear_profile[4] = t_w;
+        g_linear_profile[5] = clock64() - t_begin;
+        g_linear_profile[8] = tcount;
+      }
+    }
+  } else {
+    // ---------------------------------------------------------------- epilogue
+    const int q = warp & 3;                           // TMEM lane quarter
+    const int t = (warp - 2) >> 2;                    // column third of the half: [64 t, 64 t + 64)
+    const bool prof = p.profile && blockIdx.x == 0 && threadIdx.x == 64;
+    long long t_accw = 0, t_store = 0, t_ld = 0;
+    const long long t_begin = clock64();
+    const int r_tile = q * 32 + lane;
+    uint32_t tcount = 0;
+    for (int64_t tile = first; tile < tiles; tile += step, ++tcount) {
+      const uint32_t buf = tcount & 1;
+      const long long t0 = clock64();
+      mbar_wait(&tmem_full[buf], (tcount >> 1) & 1);
+      t_accw += clock64() - t0;
+      tc_fence_after();
+      const int64_t row = tile * BM + r_tile;
+      const bool ok = row < p.M;
+      const int64_t r = ok ? row : 0;
+      const uint32_t trow = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * kHalf + t * 64;
+      const __half* gate = p.gate ? p.gate + r * kDim + h * kHalf : nullptr;
+      const __half* res1 = p.res1 ? p.res1 + r * kDim + h * kHalf : nullptr;
+      const __half* res2 = p.res2 ? p.res2 + (p.res2_index ? p.res2_index[r] : r) * kDim + h * kHalf : nullptr;
+#pragma unroll 1
+      for (int c = 0; c < 2; ++c) {
+        uint32_t v[32];
+        float x[32];
+        const long long tl0 = clock64();
+        tmem_ld32(trow + c * 32, v);
+        tmem_ld_wait();
+        t_ld += clock64() - tl0;
+        const int n0 = t * 64 + c * 32;               // column within this CTA's half
+#pragma unroll
+        for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]);
+        apply_pre(x, s_bias, n0, gate, res1, res2);
+        if (p.act == 1) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
+        } else if (p.act == 2) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) x[j] = __fdividef(1.0f, 1.0f + __expf(-x[j]));
+        }
+        // transpose through shared memory so that global stores are whole 64-byte row segments:
+        // thread r parks its four 16-byte units (XOR-swizzled by row pair: conflict-free both ways) ...
+        const long long ts0 = clock64();
+        uint8_t* sw = stage_out + (warp - 2) * 2048;
+        __syncwarp();                                 // previous chunk has been read out
+#pragma unroll
+        for (int qd = 0; qd < 4; ++qd) {
+          uint4 o;
+          __half2* hh = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) hh[j] = __floats2half2_rn(x[8 * qd + 2 * j], x[8 * qd + 2 * j + 1]);
+          *reinterpret_cast<uint4*>(sw + lane * 64 + ((qd ^ ((lane >> 1) & 3)) << 4)) = o;
+        }
+        __syncwarp();
+        // ... then four lanes write one row: a warp store covers 8 rows x 64 contiguous bytes
+        if (p.Y) {
+          const int64_t row0 = tile * BM + q * 32;
+#pragma unroll
+          for (int ps = 0; ps < 4; ++ps) {
+            const int rr = ps * 8 + (lane >> 2);
+            const int u = lane & 3;
+            const uint4 o = *reinterpret_cast<const uint4*>(sw + rr * 64 + ((u ^ ((rr >> 1) & 3)) << 4));
+            if (row0 + rr < p.M)
+              *reinterpret_cast<uint4*>(p.Y + (row0 + rr) * kDim + h * kHalf + n0 + u * 8) = o;
+          }
+        }
+        t_store += clock64() - ts0;
+      }
+      tc_fence_before();
+      mbar_arrive(&tmem_empty[buf]);
+    }
+    if (prof) {
+      g_linear_profile[6] = t_accw;
+      g_linear_profile[7] = clock64() - t_begin;
+      g_linear_profile[9] = t_store;
+      g_linear_profile[10] = t_ld;
     }
   }
   tc_fence_before();
@@ -326,6 +575,70 @@ int make_map(CUtensorMap* m, const void* base, int64_t K, int64_t rows, int64_t 
   return 0;
 }
 
+// DPVO_LINEAR_RW=0 routes every layer through the streaming kernel (A/B measurements)
+bool use_resident_w() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DPVO_LINEAR_RW");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
+// CTAs per cluster: DPVO_LINEAR_CLUSTER = 1 | 2 | 4 overrides the default
+int cluster_size() {
+  static int cl = 0;
+  if (!cl) {
+    const char* e = getenv("DPVO_LINEAR_CLUSTER");
+    const int v = e ? atoi(e) : 0;
+    cl = (v == 1 || v == 2 || v == 4) ? v : 1;
+  }
+  return cl;
+}
+
+template <int CL>
+int launch_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmY, const LinearDev& p,
+                  cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(linear384_kernel<CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  DPVO_REQUIRE(e == cudaSuccess, "linear384: cannot reserve %d bytes of shared memory: %s", kSmemBytes,
+               cudaGetErrorString(e));
+  const int64_t tiles = (p.M + BM - 1) / BM;
+  const int64_t groups = (tiles + CL - 1) / CL;
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CL;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int max_clusters = kNumSMs / CL;
+  if (CL > 1) {
+    static int cached[5] = {0, 0, 0, 0, 0};
+    if (!cached[CL]) {
+      cfg.gridDim = dim3(kNumSMs / CL * CL);
+      int n = 0;
+      e = cudaOccupancyMaxActiveClusters(&n, linear384_kernel<CL>, &cfg);
+      DPVO_REQUIRE(e == cudaSuccess && n > 0, "linear384: no cluster of %d CTAs fits on this device: %s", CL,
+                   cudaGetErrorString(e));
+      cached[CL] = n;
+    }
+    if (cached[CL] < max_clusters) max_clusters = cached[CL];
+  }
+  const int64_t clusters = groups < max_clusters ? groups : max_clusters;
+  cfg.gridDim = dim3(static_cast<unsigned>(clusters * CL));
+  note_launches(1);
+  e = cudaLaunchKernelEx(&cfg, linear384_kernel<CL>, tmA, tmW, tmY, p);
+  if (e != cudaSuccess) {
+    set_error("linear384: launch failed: %s", cudaGetErrorString(e));
+    return 1;
+  }
+  return check_launch("linear384");
+}
+
 }  // namespace
 }  // namespace dpvo
 
@@ -346,7 +659,30 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
   DPVO_REQUIRE(lp->M < (int64_t(1) << 31) - BM, "linear384: too many rows");
   CUtensorMap tmA, tmW, tmY;
   if (make_map(&tmA, lp->A, lp->K, lp->M, lp->lda, BM)) return 1;
-  if (make_map(&tmW, lp->W, lp->K, kDim, lp->ldw, kDim / 2)) return 1;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (lp->K == kDim && lp->ln_gamma == nullptr && use_resident_w()) {
+    if (make_map(&tmW, lp->W, lp->K, kDim, lp->ldw, kHalf)) return 1;
+    LinearRwDev q;
+    q.profile = getenv("DPVO_LINEAR_PROFILE") ? 1 : 0;
+    q.bias = lp->bias;
+    q.gate = static_cast<const __half*>(lp->gate);
+    q.res1 = static_cast<const __half*>(lp->res1);
+    q.res2 = static_cast<const __half*>(lp->res2);
+    q.res2_index = lp->res2_index;
+    q.act = lp->act;
+    q.Y = getenv("DPVO_LINEAR_DEBUG_NOSTORE") ? nullptr : static_cast<__half*>(lp->Y);
+    q.M = lp->M;
+    cudaError_t e = cudaFuncSetAttribute(linear384_rw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRwSmemBytes);
+    DPVO_REQUIRE(e == cudaSuccess, "linear384: cannot reserve %d bytes of shared memory: %s", kRwSmemBytes,
+                 cudaGetErrorString(e));
+    const int64_t tiles = (lp->M + BM - 1) / BM;
+    const int pairs = static_cast<int>(tiles < kNumSMs / 2 ? tiles : kNumSMs / 2);
+    note_launches(1);
+    linear384_rw_kernel<<<2 * pairs, kThreads, kRwSmemBytes, st>>>(tmA, tmW, q);
+    return check_launch("linear384");
+  }
+  const int cl = cluster_size();
+  if (make_map(&tmW, lp->W, lp->K, kDim, lp->ldw, cl == 1 ? kDim / 2 : kDim / cl)) return 1;
   if (make_map(&tmY, lp->Y, kDim, lp->M, kDim, BM)) return 1;
   LinearDev p;
   p.bias = lp->bias;
@@ -360,14 +696,16 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
   p.act = lp->act;
   p.M = lp->M;
   p.kblocks = (lp->K + BK - 1) / BK;
-  {
-    cudaError_t e = cudaFuncSetAttribute(linear384_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-    DPVO_REQUIRE(e == cudaSuccess, "linear384: cannot reserve %d bytes of shared memory: %s", kSmemBytes,
-                 cudaGetErrorString(e));
-  }
-  const int64_t tiles = (lp->M + BM - 1) / BM;
-  const int grid = static_cast<int>(tiles < kNumSMs ? tiles : kNumSMs);
-  note_launches(1);
-  linear384_kernel<<<grid, kThreads, kSmemBytes, reinterpret_cast<cudaStream_t>(stream)>>>(tmA, tmW, tmY, p);
-  return check_launch("linear384");
+  if (cl == 4) return launch_linear<4>(tmA, tmW, tmY, p, st);
+  if (cl == 2) return launch_linear<2>(tmA, tmW, tmY, p, st);
+  return launch_linear<1>(tmA, tmW, tmY, p, st);
+}
+
+/* Diagnostics: per-role cycle counters of CTA 0 of the last resident-W launch made with
+ * DPVO_LINEAR_PROFILE=1 (see g_linear_profile in this file).  Synchronises the device. */
+extern "C" int dpvo_linear_profile_read(long long* out16) {
+  DPVO_REQUIRE(out16 != nullptr, "linear_profile_read: null pointer");
+  cudaError_t e = cudaMemcpyFromSymbol(out16, g_linear_profile, sizeof(long long) * 16);
+  DPVO_REQUIRE(e == cudaSuccess, "linear_profile_read: %s", cudaGetErrorString(e));
+  return 0;
 }

@@ -23,7 +23,8 @@ def main():
     torch.manual_seed(0)
     dev = "cuda"
     bad = 0
-    for (M, K, ld) in [(128, 64, 64), (128, 384, 384), (300, 384, 384), (45312, 384, 384), (1000, 882, 896), (45312, 882, 896)]:
+    prof = "--profile" in sys.argv
+    for (M, K, ld) in [] if prof else [(128, 64, 64), (128, 384, 384), (300, 384, 384), (45312, 384, 384), (1000, 882, 896), (45312, 882, 896)]:
         Abuf = torch.full((M, ld), float("nan"), dtype=torch.float16, device=dev)
         Abuf[:, :K] = torch.randn(M, K, device=dev).half()
         A = Abuf[:, :K]
@@ -55,11 +56,26 @@ def main():
         b = torch.randn(384, device=dev)
         for _ in range(3): upd.linear384(A, W, b, act=1)
         torch.cuda.synchronize()
+        if prof:
+            continue
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(20): upd.linear384(A, W, b, act=1)
         e1.record(); torch.cuda.synchronize()
+        ms_stream = e0.elapsed_time(e1) / 20
+        g = torch.cuda.CUDAGraph()                      # host launch cost (tensor-map encode + ctypes) out of the picture
+        with torch.cuda.graph(g):
+            for _ in range(20): upd.linear384(A, W, b, act=1)
+        g.replay(); torch.cuda.synchronize()
+        e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / 20
+        print(f"  stream-launched {ms_stream*1e3:.1f} us/launch, graph {ms*1e3:.1f} us/launch")
+        if os.environ.get("DPVO_LINEAR_PROFILE") and K == 384:
+            buf = (ctypes.c_longlong * 16)()
+            pkg._lib.lib.dpvo_linear_profile_read(buf)
+            names = ["prod_wait_empty", "prod_total", "mma_wait_A", "mma_wait_acc", "mma_wait_W", "mma_total",
+                     "epi_wait_acc", "epi_total", "tiles", "epi_store", "epi_tmem_ld"]
+            print("profile (cycles, CTA 0):", {n: int(buf[i]) for i, n in enumerate(names)})
         Ac = A.contiguous(); Wc = W.contiguous()
         for _ in range(3): torch.relu(torch.nn.functional.linear(Ac, Wc, b.half()))
         e0.record()
