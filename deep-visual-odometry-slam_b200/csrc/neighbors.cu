@@ -78,11 +78,21 @@ static uint32_t table_size(int64_t n) {
 static int64_t a256(int64_t x) { return (x + 255) & ~(int64_t)255; }
 
 // ------------------------------------------------------------ unique / inverse
+// Edge lists are runs of equal / neighbouring keys, so tens of lanes of a warp (and hundreds of edges in
+// total) hit the same bitmap word: lanes that share a word combine their bits, one lane per word issues
+// the atomic, and only when the word does not already hold those bits.
 __global__ void __launch_bounds__(256)
 uq_mark_kernel(const int64_t* __restrict__ keys, int64_t n, uint32_t* __restrict__ bitmap, int64_t bound) {
-  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t k = keys[e];
-    if (k >= 0 && k < bound) atomicOr(&bitmap[k >> 5], 1u << (k & 31));
+  const int lane = threadIdx.x & 31;
+  for (int64_t base = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) - lane; base < n;
+       base += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t e = base + lane;
+    const int64_t k = e < n ? keys[e] : -1;
+    const bool valid = k >= 0 && k < bound;
+    const int w = valid ? (int)(k >> 5) : -1;
+    const unsigned peers = __match_any_sync(0xffffffffu, w);
+    const unsigned bits = __reduce_or_sync(peers, valid ? (1u << (k & 31)) : 0u);
+    if (valid && lane == __ffs(peers) - 1 && (__ldcg(bitmap + w) & bits) != bits) atomicOr(bitmap + w, bits);
   }
 }
 __global__ void __launch_bounds__(256)

@@ -94,17 +94,21 @@ __device__ __forceinline__ void store4(__half* p, const float (&f)[4]) {
   *reinterpret_cast<uint2*>(p) = u;
 }
 
-__global__ void __launch_bounds__(96)
+constexpr int kAggSlices = 4;
+
+__global__ void __launch_bounds__(96 * kAggSlices)
 softagg_kernel(const __half* __restrict__ F, const __half* __restrict__ Gm, const int* __restrict__ offs,
                const int* __restrict__ perm, __half* __restrict__ Y) {
+  __shared__ float part[kAggSlices - 1][3][kDim];     // (max, numerator, denominator) of slices 1..
   const int grp = blockIdx.x;
   const int beg = offs[grp], end = offs[grp + 1];
   if (beg == end) return;
-  const int ch = threadIdx.x * 4;
+  const int slice = threadIdx.x / 96;                 // the group's edges are dealt round-robin to the slices
+  const int ch = (threadIdx.x % 96) * 4;
   float m[4], num[4], den[4];
 #pragma unroll
   for (int c = 0; c < 4; ++c) { m[c] = -INFINITY; num[c] = 0.f; den[c] = 0.f; }
-  for (int t = beg; t < end; ++t) {
+  for (int t = beg + slice; t < end; t += kAggSlices) {
     const int64_t e = perm[t];
     float fv[4], gv[4];
     load4(F + e * kDim + ch, fv);
@@ -119,10 +123,33 @@ softagg_kernel(const __half* __restrict__ F, const __half* __restrict__ Gm, cons
       m[c] = mn;
     }
   }
-  float y[4];
+  if (slice > 0) {
 #pragma unroll
-  for (int c = 0; c < 4; ++c) y[c] = num[c] / (den[c] + 1e-12f);
-  store4(Y + (int64_t)grp * kDim + ch, y);
+    for (int c = 0; c < 4; ++c) {
+      part[slice - 1][0][ch + c] = m[c];
+      part[slice - 1][1][ch + c] = num[c];
+      part[slice - 1][2][ch + c] = den[c];
+    }
+  }
+  __syncthreads();
+  if (slice == 0) {                                   // slice 0 always holds the group's first edge: m is finite
+    float y[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      float mx = m[c];
+#pragma unroll
+      for (int s = 0; s < kAggSlices - 1; ++s) mx = fmaxf(mx, part[s][0][ch + c]);
+      float nu = num[c] * __expf(m[c] - mx), de = den[c] * __expf(m[c] - mx);
+#pragma unroll
+      for (int s = 0; s < kAggSlices - 1; ++s) {
+        const float sc = __expf(part[s][0][ch + c] - mx);   // empty slice: exp(-inf) = 0
+        nu += part[s][1][ch + c] * sc;
+        de += part[s][2][ch + c] * sc;
+      }
+      y[c] = nu / (de + 1e-12f);
+    }
+    store4(Y + (int64_t)grp * kDim + ch, y);
+  }
 }
 
 // ------------------------------------------------------------------ expand_add
@@ -160,12 +187,14 @@ expand_add_kernel(const __half* __restrict__ net, const __half* __restrict__ hy,
       const float mean = sum * (1.0f / kDim);
       const float rstd = rsqrtf(fmaxf(sq * (1.0f / kDim) - mean * mean, 0.f) + eps);
 #pragma unroll
-      for (int c = 0; c < 3; ++c)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int n = 128 * c + 4 * lane + j;
-          x[c][j] = (x[c][j] - mean) * rstd * gamma[n] + beta[n];
-        }
+      for (int c = 0; c < 3; ++c) {
+        const float4 g4 = __ldg(reinterpret_cast<const float4*>(gamma + 128 * c + 4 * lane));
+        const float4 b4 = __ldg(reinterpret_cast<const float4*>(beta + 128 * c + 4 * lane));
+        x[c][0] = (x[c][0] - mean) * rstd * g4.x + b4.x;
+        x[c][1] = (x[c][1] - mean) * rstd * g4.y + b4.y;
+        x[c][2] = (x[c][2] - mean) * rstd * g4.z + b4.z;
+        x[c][3] = (x[c][3] - mean) * rstd * g4.w + b4.w;
+      }
     }
 #pragma unroll
     for (int c = 0; c < 3; ++c) store4(out + e * kDim + 128 * c + 4 * lane, x[c]);
@@ -178,7 +207,7 @@ __global__ void __launch_bounds__(256)
 heads_kernel(const __half* __restrict__ net, const float* __restrict__ wd, const float* __restrict__ bd,
              const float* __restrict__ ww, const float* __restrict__ bw, int64_t E, float* __restrict__ delta,
              float* __restrict__ weight) {
-  __shared__ float w_s[4][kDim];
+  __shared__ __align__(16) float w_s[4][kDim];
   for (int i = threadIdx.x; i < 2 * kDim; i += blockDim.x) {
     w_s[i / kDim][i % kDim] = wd[i];
     w_s[2 + i / kDim][i % kDim] = ww[i];
@@ -193,11 +222,9 @@ heads_kernel(const __half* __restrict__ net, const float* __restrict__ wd, const
       float u[4];
       load4(net + e * kDim + 128 * c + 4 * lane, u);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float r = fmaxf(u[j], 0.f);
-        const int n = 128 * c + 4 * lane + j;
-#pragma unroll
-        for (int h = 0; h < 4; ++h) acc[h] += r * w_s[h][n];
+      for (int h = 0; h < 4; ++h) {                   // 16-byte shared loads: consecutive lanes, consecutive banks
+        const float4 w4 = *reinterpret_cast<const float4*>(&w_s[h][128 * c + 4 * lane]);
+        acc[h] += fmaxf(u[0], 0.f) * w4.x + fmaxf(u[1], 0.f) * w4.y + fmaxf(u[2], 0.f) * w4.z + fmaxf(u[3], 0.f) * w4.w;
       }
     }
 #pragma unroll
@@ -260,7 +287,7 @@ extern "C" int dpvo_softagg_f16(const void* f, const void* g, const int64_t* ids
   agg_hist_kernel<<<grid_for(n_edges, 256, 8), 256, 0, st>>>(ids, n_edges, count);
   agg_scan_kernel<<<1, 1024, 0, st>>>(count, G, offs, cursor);
   agg_fill_kernel<<<grid_for(n_edges, 256, 8), 256, 0, st>>>(ids, n_edges, cursor, perm);
-  softagg_kernel<<<G, 96, 0, st>>>(static_cast<const __half*>(f), static_cast<const __half*>(g), offs, perm,
+  softagg_kernel<<<G, 96 * kAggSlices, 0, st>>>(static_cast<const __half*>(f), static_cast<const __half*>(g), offs, perm,
                                   static_cast<__half*>(y));
   note_launches(4);
   return check_launch("softagg");

@@ -341,11 +341,17 @@ struct LinearRwDev {
   const __half* res1;
   const __half* res2;
   const int64_t* res2_index;
+  const float* ln_gamma;
+  const float* ln_beta;
+  float ln_eps;
   int act;
   __half* Y;
   int64_t M;
 };
 
+// LN: LayerNorm over the full 384-wide row.  The two CTAs of a pair then run as a cluster and swap the
+// per-row (sum, sum of squares) of their halves through each other's shared memory once per tile.
+template <bool LN>
 __global__ void __launch_bounds__(kThreads, 1)
 linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                     const LinearRwDev p) {
@@ -357,6 +363,9 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __shared__ uint64_t wfull, full[kRwStages], empty[kRwStages], tmem_full[2], tmem_empty[2];
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float s_bias[kHalf];       // this CTA's half of the bias (L1 is tiny next to 220 KB of smem)
+  __shared__ __align__(16) float s_gamma[LN ? kHalf : 4], s_beta[LN ? kHalf : 4];
+  __shared__ __align__(8) float2 peer_part[2][LN ? BM : 1];   // written by the other CTA of the pair
+  __shared__ uint64_t ln_bar[2];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t tiles = (p.M + BM - 1) / BM;
@@ -364,7 +373,13 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int64_t first = blockIdx.x >> 1, step = gridDim.x >> 1;
   constexpr int kKb = kDim / BK;                      // 6 K chunks
 
-  for (int i = threadIdx.x; i < kHalf; i += kThreads) s_bias[i] = p.bias ? p.bias[(blockIdx.x & 1) * kHalf + i] : 0.f;
+  for (int i = threadIdx.x; i < kHalf; i += kThreads) {
+    s_bias[i] = p.bias ? p.bias[(blockIdx.x & 1) * kHalf + i] : 0.f;
+    if (LN) {
+      s_gamma[i] = p.ln_gamma[(blockIdx.x & 1) * kHalf + i];
+      s_beta[i] = p.ln_beta[(blockIdx.x & 1) * kHalf + i];
+    }
+  }
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmW);
@@ -379,6 +394,7 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       for (int b = 0; b < 2; ++b) {
         mbar_init(&tmem_full[b], 1);
         mbar_init(&tmem_empty[b], kEpiThreads);
+        mbar_init(&ln_bar[b], BM);                    // one arrival per row from the peer CTA
       }
       mbar_fence_init();
     }
@@ -386,7 +402,7 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tmem_alloc(&tmem_base_s, kTmemCols);
   }
   tc_fence_before();
-  __syncthreads();
+  if (LN) cluster_sync_all(); else __syncthreads();   // the peer's ln_bar must exist before the first remote arrive
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
 
@@ -480,6 +496,51 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const __half* gate = p.gate ? p.gate + r * kDim + h * kHalf : nullptr;
       const __half* res1 = p.res1 ? p.res1 + r * kDim + h * kHalf : nullptr;
       const __half* res2 = p.res2 ? p.res2 + (p.res2_index ? p.res2_index[r] : r) * kDim + h * kHalf : nullptr;
+      float mean = 0.f, rstd = 1.f;
+      if (LN) {
+        float sum = 0.f, sq = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+          uint32_t v[32];
+          float x[32];
+          tmem_ld32(trow + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]);
+          apply_pre(x, s_bias, t * 64 + c * 32, gate, res1, res2);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            sum += x[j];
+            sq += x[j] * x[j];
+            v[j] = __float_as_uint(x[j]);
+          }
+          tmem_st32(trow + c * 32, v);                // park the pre-normalisation row in TMEM
+        }
+        // the three column thirds of this half meet in spare TMEM columns 384 + 8 buf ..
+        const uint32_t tstat = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + kDim + 8 * buf;
+        tmem_st2(tstat + 2 * t, __float_as_uint(sum), __float_as_uint(sq));
+        tmem_st_wait();
+        tc_fence_before();
+        named_barrier(2, kEpiThreads);
+        tc_fence_after();
+        uint32_t ps[8];
+        tmem_ld8(tstat, ps);
+        tmem_ld_wait();
+        sum = __uint_as_float(ps[0]) + __uint_as_float(ps[2]) + __uint_as_float(ps[4]);
+        sq = __uint_as_float(ps[1]) + __uint_as_float(ps[3]) + __uint_as_float(ps[5]);
+        // .. and the two halves meet through the peer CTA's shared memory
+        const uint32_t par = (tcount >> 1) & 1;
+        if (t == 0) {
+          st_remote_f32x2(map_to_cta(&peer_part[buf][r_tile], h ^ 1), sum, sq);
+          mbar_arrive_remote(map_to_cta(&ln_bar[buf], h ^ 1));
+        }
+        mbar_wait_cluster(&ln_bar[buf], par);
+        const float2 other = peer_part[buf][r_tile];
+        sum += other.x;
+        sq += other.y;
+        mean = sum * (1.0f / kDim);
+        rstd = rsqrtf(fmaxf(sq * (1.0f / kDim) - mean * mean, 0.f) + p.ln_eps);
+      }
 #pragma unroll 1
       for (int c = 0; c < 2; ++c) {
         uint32_t v[32];
@@ -491,7 +552,12 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int n0 = t * 64 + c * 32;               // column within this CTA's half
 #pragma unroll
         for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]);
-        apply_pre(x, s_bias, n0, gate, res1, res2);
+        if (LN) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) x[j] = (x[j] - mean) * rstd * s_gamma[n0 + j] + s_beta[n0 + j];
+        } else {
+          apply_pre(x, s_bias, n0, gate, res1, res2);
+        }
         if (p.act == 1) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
@@ -539,6 +605,7 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
   tc_fence_before();
   __syncthreads();
+  if (LN) cluster_sync_all();                         // the peer may still be signalling this CTA's barriers
   if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
 }
 
@@ -660,7 +727,7 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
   CUtensorMap tmA, tmW, tmY;
   if (make_map(&tmA, lp->A, lp->K, lp->M, lp->lda, BM)) return 1;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (lp->K == kDim && lp->ln_gamma == nullptr && use_resident_w()) {
+  if (lp->K == kDim && use_resident_w()) {
     if (make_map(&tmW, lp->W, lp->K, kDim, lp->ldw, kHalf)) return 1;
     LinearRwDev q;
     q.profile = getenv("DPVO_LINEAR_PROFILE") ? 1 : 0;
@@ -669,16 +736,39 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
     q.res1 = static_cast<const __half*>(lp->res1);
     q.res2 = static_cast<const __half*>(lp->res2);
     q.res2_index = lp->res2_index;
+    q.ln_gamma = lp->ln_gamma;
+    q.ln_beta = lp->ln_beta;
+    q.ln_eps = lp->ln_eps;
     q.act = lp->act;
     q.Y = getenv("DPVO_LINEAR_DEBUG_NOSTORE") ? nullptr : static_cast<__half*>(lp->Y);
     q.M = lp->M;
-    cudaError_t e = cudaFuncSetAttribute(linear384_rw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRwSmemBytes);
-    DPVO_REQUIRE(e == cudaSuccess, "linear384: cannot reserve %d bytes of shared memory: %s", kRwSmemBytes,
-                 cudaGetErrorString(e));
     const int64_t tiles = (lp->M + BM - 1) / BM;
     const int pairs = static_cast<int>(tiles < kNumSMs / 2 ? tiles : kNumSMs / 2);
+    const bool ln = lp->ln_gamma != nullptr;
+    if (ln) DPVO_REQUIRE(lp->ln_beta != nullptr, "linear384: LayerNorm needs both gamma and beta");
+    cudaError_t e = ln ? cudaFuncSetAttribute(linear384_rw_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kRwSmemBytes)
+                       : cudaFuncSetAttribute(linear384_rw_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kRwSmemBytes);
+    DPVO_REQUIRE(e == cudaSuccess, "linear384: cannot reserve %d bytes of shared memory: %s", kRwSmemBytes,
+                 cudaGetErrorString(e));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * pairs);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = kRwSmemBytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = ln ? 2 : 1;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
     note_launches(1);
-    linear384_rw_kernel<<<2 * pairs, kThreads, kRwSmemBytes, st>>>(tmA, tmW, q);
+    e = ln ? cudaLaunchKernelEx(&cfg, linear384_rw_kernel<true>, tmA, tmW, q)
+           : cudaLaunchKernelEx(&cfg, linear384_rw_kernel<false>, tmA, tmW, q);
+    if (e != cudaSuccess) {
+      set_error("linear384: launch failed: %s", cudaGetErrorString(e));
+      return 1;
+    }
     return check_launch("linear384");
   }
   const int cl = cluster_size();
