@@ -108,19 +108,28 @@ softagg_kernel(const __half* __restrict__ F, const __half* __restrict__ Gm, cons
   float m[4], num[4], den[4];
 #pragma unroll
   for (int c = 0; c < 4; ++c) { m[c] = -INFINITY; num[c] = 0.f; den[c] = 0.f; }
-  for (int t = beg + slice; t < end; t += kAggSlices) {
-    const int64_t e = perm[t];
-    float fv[4], gv[4];
-    load4(F + e * kDim + ch, fv);
-    load4(Gm + e * kDim + ch, gv);
+  for (int t = beg + slice; t < end; t += 2 * kAggSlices) {
+    // two edges per trip: both rows are requested before either is folded in
+    const bool two = t + kAggSlices < end;
+    const int64_t e0 = perm[t];
+    const int64_t e1 = two ? perm[t + kAggSlices] : e0;
+    float fv[2][4], gv[2][4];
+    load4(F + e0 * kDim + ch, fv[0]);
+    load4(Gm + e0 * kDim + ch, gv[0]);
+    load4(F + e1 * kDim + ch, fv[1]);
+    load4(Gm + e1 * kDim + ch, gv[1]);
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      const float mn = fmaxf(m[c], gv[c]);
-      const float sc = __expf(m[c] - mn);         // exp(-inf) = 0 on the first edge
-      const float pe = __expf(gv[c] - mn);
-      num[c] = num[c] * sc + fv[c] * pe;
-      den[c] = den[c] * sc + pe;
-      m[c] = mn;
+    for (int k = 0; k < 2; ++k) {
+      if (k == 1 && !two) break;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const float mn = fmaxf(m[c], gv[k][c]);
+        const float sc = __expf(m[c] - mn);       // exp(-inf) = 0 on the first edge
+        const float pe = __expf(gv[k][c] - mn);
+        num[c] = num[c] * sc + fv[k][c] * pe;
+        den[c] = den[c] * sc + pe;
+        m[c] = mn;
+      }
     }
   }
   if (slice > 0) {
@@ -270,26 +279,50 @@ extern "C" int64_t dpvo_softagg_workspace_bytes(int64_t n_edges, int64_t group_b
   return (3 * group_bound + 1 + n_edges) * (int64_t)sizeof(int) + 64;
 }
 
+namespace {
+struct AggWs { int* count; int* offs; int* cursor; int* perm; };
+AggWs carve_agg(void* workspace, int G) {
+  AggWs w;
+  w.count = static_cast<int*>(workspace);
+  w.offs = w.count + G;
+  w.cursor = w.offs + G + 1;
+  w.perm = w.cursor + G;
+  return w;
+}
+}  // namespace
+
+extern "C" int dpvo_softagg_prepare(const int64_t* ids, int64_t n_edges, int64_t group_bound, void* workspace,
+                                    int64_t workspace_bytes, void* stream) {
+  DPVO_REQUIRE(n_edges >= 0 && group_bound >= 0 && group_bound < (int64_t(1) << 30) && n_edges < (int64_t(1) << 31),
+               "softagg_prepare: bad sizes");
+  if (n_edges == 0 || group_bound == 0) return 0;
+  DPVO_REQUIRE(ids && workspace, "softagg_prepare: null pointer");
+  DPVO_REQUIRE(workspace_bytes >= dpvo_softagg_workspace_bytes(n_edges, group_bound),
+               "softagg_prepare: workspace too small");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int G = (int)group_bound;
+  const AggWs w = carve_agg(workspace, G);
+  cudaMemsetAsync(w.count, 0, sizeof(int) * G, st);
+  agg_hist_kernel<<<grid_for(n_edges, 256, 8), 256, 0, st>>>(ids, n_edges, w.count);
+  agg_scan_kernel<<<1, 1024, 0, st>>>(w.count, G, w.offs, w.cursor);
+  agg_fill_kernel<<<grid_for(n_edges, 256, 8), 256, 0, st>>>(ids, n_edges, w.cursor, w.perm);
+  note_launches(3);
+  return check_launch("softagg_prepare");
+}
+
 extern "C" int dpvo_softagg_f16(const void* f, const void* g, const int64_t* ids, int64_t n_edges, int64_t group_bound,
-                                void* y, void* workspace, int64_t workspace_bytes, void* stream) {
+                                void* y, int32_t prepared, void* workspace, int64_t workspace_bytes, void* stream) {
   DPVO_REQUIRE(n_edges >= 0 && group_bound >= 0 && group_bound < (int64_t(1) << 30) && n_edges < (int64_t(1) << 31),
                "softagg: bad sizes");
   if (n_edges == 0 || group_bound == 0) return 0;
-  DPVO_REQUIRE(f && g && ids && y && workspace, "softagg: null pointer");
+  DPVO_REQUIRE(f && g && y && workspace, "softagg: null pointer");
   DPVO_REQUIRE(workspace_bytes >= dpvo_softagg_workspace_bytes(n_edges, group_bound), "softagg: workspace too small");
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!prepared && dpvo_softagg_prepare(ids, n_edges, group_bound, workspace, workspace_bytes, stream)) return 1;
   const int G = (int)group_bound;
-  int* count = static_cast<int*>(workspace);
-  int* offs = count + G;
-  int* cursor = offs + G + 1;
-  int* perm = cursor + G;
-  cudaMemsetAsync(count, 0, sizeof(int) * G, st);
-  agg_hist_kernel<<<grid_for(n_edges, 256, 8), 256, 0, st>>>(ids, n_edges, count);
-  agg_scan_kernel<<<1, 1024, 0, st>>>(count, G, offs, cursor);
-  agg_fill_kernel<<<grid_for(n_edges, 256, 8), 256, 0, st>>>(ids, n_edges, cursor, perm);
-  softagg_kernel<<<G, 96 * kAggSlices, 0, st>>>(static_cast<const __half*>(f), static_cast<const __half*>(g), offs, perm,
-                                  static_cast<__half*>(y));
-  note_launches(4);
+  const AggWs w = carve_agg(workspace, G);
+  softagg_kernel<<<G, 96 * kAggSlices, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __half*>(f), static_cast<const __half*>(g), w.offs, w.perm, static_cast<__half*>(y));
+  note_launches(1);
   return check_launch("softagg");
 }
 
@@ -312,7 +345,7 @@ extern "C" int dpvo_update_heads_f16(const void* net, const float* wd, const flo
   if (n_edges == 0) return 0;
   DPVO_REQUIRE(net && wd && bd && ww && bw && delta && weight, "update_heads: null pointer");
   note_launches(1);
-  heads_kernel<<<grid_for(n_edges, 8, 8), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  heads_kernel<<<grid_for(n_edges, 8, 64), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       static_cast<const __half*>(net), wd, bd, ww, bw, n_edges, delta, weight);
   return check_launch("update_heads");
 }

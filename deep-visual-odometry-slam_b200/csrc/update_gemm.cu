@@ -311,6 +311,52 @@ linear384_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
 }
 
+// Row operands (gate / residuals) for a 32-row x 32-column chunk, fetched the coalesced way round: four
+// lanes read one row's 64 bytes (a warp load covers 8 whole row segments instead of 32 scattered
+// 16-byte pieces); the pieces are parked in the warp's 2 KB buffer and every thread picks up its own
+// row.  (Issuing these loads a chunk ahead was tried: no gain — the kernel is bound by L2 throughput,
+// not by load latency — and the extra registers spilled.)
+// `myrow`: this lane's row (already offset to the CTA's first column); rows may be gathered.
+__device__ __forceinline__ void rows_issue(const __half* myrow, int n0, int lane, uint4 (&pc)[4]) {
+  const unsigned long long mine = reinterpret_cast<unsigned long long>(myrow + n0);
+#pragma unroll
+  for (int ps = 0; ps < 4; ++ps) {
+    const unsigned long long rp = __shfl_sync(0xffffffffu, mine, ps * 8 + (lane >> 2));
+    pc[ps] = ldg128(reinterpret_cast<const __half*>(rp) + (lane & 3) * 8);
+  }
+}
+template <bool MUL>
+__device__ __forceinline__ void rows_apply(uint8_t* sw, const uint4 (&pc)[4], int lane, float (&x)[32]) {
+  __syncwarp();                                       // the buffer's previous contents have been consumed
+#pragma unroll
+  for (int ps = 0; ps < 4; ++ps) {
+    const int rr = ps * 8 + (lane >> 2), u = lane & 3;
+    *reinterpret_cast<uint4*>(sw + rr * 64 + ((u ^ ((rr >> 1) & 3)) << 4)) = pc[ps];
+  }
+  __syncwarp();
+#pragma unroll
+  for (int qd = 0; qd < 4; ++qd) {
+    const uint4 o = *reinterpret_cast<const uint4*>(sw + lane * 64 + ((qd ^ ((lane >> 1) & 3)) << 4));
+    float f[8];
+    unpack8(o, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) x[8 * qd + j] = MUL ? x[8 * qd + j] * f[j] : x[8 * qd + j] + f[j];
+  }
+}
+template <bool MUL>
+__device__ __forceinline__ void rows_fetch_apply(uint8_t* sw, const __half* myrow, int n0, int lane, float (&x)[32]) {
+  uint4 pc[4];
+  rows_issue(myrow, n0, lane, pc);
+  rows_apply<MUL>(sw, pc, lane, x);
+}
+__device__ __forceinline__ void add_bias32(float (&x)[32], const float* bias) {
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const float4 b = *(reinterpret_cast<const float4*>(bias) + q);
+    x[4 * q] += b.x; x[4 * q + 1] += b.y; x[4 * q + 2] += b.z; x[4 * q + 3] += b.w;
+  }
+}
+
 // ------------------------------------------------------ resident-W variant (K = 384, no LayerNorm)
 // The streaming kernel above is bound by what one SM can pull in from L2 / HBM (measured ~30 bytes per
 // clock per SM, whatever the ring depth or multicast):
@@ -331,7 +377,6 @@ constexpr int kRwSmemBytes = kRwWBytes + kRwStages * kABytes + kRwStageOut + 102
 // [0] producer: cycles waiting for a free ring stage   [1] producer: total
 // [2] MMA: waiting for A stages   [3] MMA: waiting for a drained accumulator   [4] MMA: waiting for W   [5] MMA: total
 // [6] epilogue: waiting for an accumulator   [7] epilogue: total   [8] tiles of this CTA
-// [9] epilogue: pack + transpose + global stores   [10] epilogue: TMEM loads
 __device__ long long g_linear_profile[16];
 
 struct LinearRwDev {
@@ -479,16 +524,12 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int q = warp & 3;                           // TMEM lane quarter
     const int t = (warp - 2) >> 2;                    // column third of the half: [64 t, 64 t + 64)
     const bool prof = p.profile && blockIdx.x == 0 && threadIdx.x == 64;
-    long long t_accw = 0, t_store = 0, t_ld = 0;
+    long long t_accw = 0;
     const long long t_begin = clock64();
     const int r_tile = q * 32 + lane;
     uint32_t tcount = 0;
     for (int64_t tile = first; tile < tiles; tile += step, ++tcount) {
       const uint32_t buf = tcount & 1;
-      const long long t0 = clock64();
-      mbar_wait(&tmem_full[buf], (tcount >> 1) & 1);
-      t_accw += clock64() - t0;
-      tc_fence_after();
       const int64_t row = tile * BM + r_tile;
       const bool ok = row < p.M;
       const int64_t r = ok ? row : 0;
@@ -496,6 +537,11 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const __half* gate = p.gate ? p.gate + r * kDim + h * kHalf : nullptr;
       const __half* res1 = p.res1 ? p.res1 + r * kDim + h * kHalf : nullptr;
       const __half* res2 = p.res2 ? p.res2 + (p.res2_index ? p.res2_index[r] : r) * kDim + h * kHalf : nullptr;
+      uint8_t* sw = stage_out + (warp - 2) * 2048;
+      const long long t0 = clock64();
+      mbar_wait(&tmem_full[buf], (tcount >> 1) & 1);
+      t_accw += clock64() - t0;
+      tc_fence_after();
       float mean = 0.f, rstd = 1.f;
       if (LN) {
         float sum = 0.f, sq = 0.f;
@@ -507,7 +553,10 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]);
-          apply_pre(x, s_bias, t * 64 + c * 32, gate, res1, res2);
+          add_bias32(x, s_bias + t * 64 + c * 32);
+          if (gate) rows_fetch_apply<true>(sw, gate, t * 64 + c * 32, lane, x);
+          if (res1) rows_fetch_apply<false>(sw, res1, t * 64 + c * 32, lane, x);
+          if (res2) rows_fetch_apply<false>(sw, res2, t * 64 + c * 32, lane, x);
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             sum += x[j];
@@ -545,10 +594,8 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       for (int c = 0; c < 2; ++c) {
         uint32_t v[32];
         float x[32];
-        const long long tl0 = clock64();
         tmem_ld32(trow + c * 32, v);
         tmem_ld_wait();
-        t_ld += clock64() - tl0;
         const int n0 = t * 64 + c * 32;               // column within this CTA's half
 #pragma unroll
         for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]);
@@ -556,7 +603,10 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 32; ++j) x[j] = (x[j] - mean) * rstd * s_gamma[n0 + j] + s_beta[n0 + j];
         } else {
-          apply_pre(x, s_bias, n0, gate, res1, res2);
+          add_bias32(x, s_bias + n0);
+          if (gate) rows_fetch_apply<true>(sw, gate, t * 64 + c * 32, lane, x);
+          if (res1) rows_fetch_apply<false>(sw, res1, t * 64 + c * 32, lane, x);
+          if (res2) rows_fetch_apply<false>(sw, res2, t * 64 + c * 32, lane, x);
         }
         if (p.act == 1) {
 #pragma unroll
@@ -567,8 +617,6 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
         // transpose through shared memory so that global stores are whole 64-byte row segments:
         // thread r parks its four 16-byte units (XOR-swizzled by row pair: conflict-free both ways) ...
-        const long long ts0 = clock64();
-        uint8_t* sw = stage_out + (warp - 2) * 2048;
         __syncwarp();                                 // previous chunk has been read out
 #pragma unroll
         for (int qd = 0; qd < 4; ++qd) {
@@ -591,7 +639,6 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               *reinterpret_cast<uint4*>(p.Y + (row0 + rr) * kDim + h * kHalf + n0 + u * 8) = o;
           }
         }
-        t_store += clock64() - ts0;
       }
       tc_fence_before();
       mbar_arrive(&tmem_empty[buf]);
@@ -599,8 +646,6 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (prof) {
       g_linear_profile[6] = t_accw;
       g_linear_profile[7] = clock64() - t_begin;
-      g_linear_profile[9] = t_store;
-      g_linear_profile[10] = t_ld;
     }
   }
   tc_fence_before();
@@ -652,13 +697,13 @@ bool use_resident_w() {
   return v == 1;
 }
 
-// CTAs per cluster: DPVO_LINEAR_CLUSTER = 1 | 2 | 4 overrides the default
+// CTAs per cluster: DPVO_LINEAR_CLUSTER = 1 | 2 | 4 | 8 overrides the default
 int cluster_size() {
   static int cl = 0;
   if (!cl) {
     const char* e = getenv("DPVO_LINEAR_CLUSTER");
     const int v = e ? atoi(e) : 0;
-    cl = (v == 1 || v == 2 || v == 4) ? v : 1;
+    cl = (v == 1 || v == 2 || v == 4 || v == 8) ? v : 1;
   }
   return cl;
 }
@@ -684,7 +729,7 @@ int launch_linear(const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensor
   cfg.numAttrs = 1;
   int max_clusters = kNumSMs / CL;
   if (CL > 1) {
-    static int cached[5] = {0, 0, 0, 0, 0};
+    static int cached[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     if (!cached[CL]) {
       cfg.gridDim = dim3(kNumSMs / CL * CL);
       int n = 0;
@@ -786,6 +831,7 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
   p.act = lp->act;
   p.M = lp->M;
   p.kblocks = (lp->K + BK - 1) / BK;
+  if (cl == 8) return launch_linear<8>(tmA, tmW, tmY, p, st);
   if (cl == 4) return launch_linear<4>(tmA, tmW, tmY, p, st);
   if (cl == 2) return launch_linear<2>(tmA, tmW, tmY, p, st);
   return launch_linear<1>(tmA, tmW, tmY, p, st);

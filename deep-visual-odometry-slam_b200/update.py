@@ -8,7 +8,8 @@ with net / inp [1, E, 384], corr [1, E, 882], ii / jj / kk int64 [E]; built from
 state_dict (`Update.from_state_dict`) or module (`Update.from_reference(network.update)`), so a
 maintainer swaps it in with one line after the checkpoint is loaded.
 
-What runs (19 tensor-core layer launches + 10 row kernels, no host synchronisation):
+What runs (19 tensor-core layer launches + row kernels, no host synchronisation; the index-only work —
+neighbours, group labels, bucket sorts — is forked onto a side stream under the first three layers):
   * every nn.Linear(·, 384) over the E edge rows is `update_ops.linear384` (tcgen05 + TMEM + TMA,
     csrc/update_gemm.cu) with the row-local work that follows it in the reference fused into its
     epilogue: bias, ReLU / sigmoid, LayerNorm, residual adds, the GatedResidual product and the
@@ -77,7 +78,7 @@ class Update:
             self.head[k] = (torch.as_tensor(state_dict[k + ".weight"]).detach().to(dev, torch.float32).contiguous(),
                             torch.as_tensor(state_dict[k + ".bias"]).detach().to(dev, torch.float32).contiguous())
         self.corr_features = self.W["corr.0"].shape[1]
-        self._ws = None
+        self._side = None
 
     # ------------------------------------------------------------------ construction helpers
     @classmethod
@@ -104,28 +105,41 @@ class Update:
     def _lin(self, name, A, **kw):
         return update_ops.linear384(A, self.W[name], self.b[name], **kw)
 
-    def _workspace(self, nbytes):
-        if self._ws is None or self._ws.numel() < nbytes:
-            self._ws = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
-        return self._ws
-
     def _gather(self, x, index):
         out = torch.empty_like(x)
         _lib.check(_L.dpvo_gather_rows_f16(_lib.ptr(x), _lib.ptr(index), _lib.c_i64(x.shape[0]), _lib.c_i32(DIM),
                                            _lib.ptr(out), _lib.stream_of(x)), "gather_rows")
         return out
 
-    def _soft_agg(self, name, x, keys, key_bound, ln=None):
-        """x + h(softagg(f(x), g(x)))[group], optionally followed by LayerNorm `ln`."""
-        E = x.shape[0]
+    def _group(self, keys, key_bound, E):
+        """Edge groups of one SoftAgg: dense labels (cuda_ba.unique_inverse — torch.unique's inverse,
+        blocks.py:43, without its host sync) and the bucket sort of the edges by label."""
         _, ids, _ = cuda_ba.unique_inverse(keys, key_bound)
         G = int(min(E, key_bound))
+        ws = torch.empty(int(_L.dpvo_softagg_workspace_bytes(_lib.c_i64(E), _lib.c_i64(G))), dtype=torch.uint8,
+                         device=keys.device)
+        _lib.check(_L.dpvo_softagg_prepare(_lib.ptr(ids), _lib.c_i64(E), _lib.c_i64(G), _lib.ptr(ws),
+                                           _lib.c_i64(ws.numel()), _lib.stream_of(keys)), "softagg_prepare")
+        return ids, G, ws
+
+    def _index_work(self, ii, jj, kk, n_frames, n_patches):
+        """Everything that depends on the edge list only (not on the activations): neighbours along the
+        patch tracks (fastba.neighbors, net.py:74) and the two SoftAgg groupings (net.py:82-83)."""
+        E = kk.numel()
+        ix, jx = cuda_ba.neighbors(kk, jj)
+        return dict(ix=ix, jx=jx, kk=self._group(kk, n_patches, E),
+                    ij=self._group(ii * n_frames + jj, n_frames * n_frames, E))
+
+    def _soft_agg(self, name, x, group, ln=None):
+        """x + h(softagg(f(x), g(x)))[group], optionally followed by LayerNorm `ln`."""
+        E = x.shape[0]
+        ids, G, ws = group
         f = self._lin(name + ".f", x)
         g = self._lin(name + ".g", x)
         y = torch.zeros((G, DIM), dtype=torch.float16, device=x.device)
-        ws = self._workspace(_L.dpvo_softagg_workspace_bytes(_lib.c_i64(E), _lib.c_i64(G)))
         _lib.check(_L.dpvo_softagg_f16(_lib.ptr(f), _lib.ptr(g), _lib.ptr(ids), _lib.c_i64(E), _lib.c_i64(G),
-                                       _lib.ptr(y), _lib.ptr(ws), _lib.c_i64(ws.numel()), _lib.stream_of(x)), "softagg")
+                                       _lib.ptr(y), _lib.c_i32(1), _lib.ptr(ws), _lib.c_i64(ws.numel()),
+                                       _lib.stream_of(x)), "softagg")
         hy = self._lin(name + ".h", y)
         out = torch.empty_like(x)
         gam, bet, eps = ln if ln is not None else (None, None, 0.0)
@@ -173,19 +187,31 @@ class Update:
                 buf[:, :self.corr_features].copy_(corr)
                 corr = buf[:, :self.corr_features]
             ii = ii.contiguous(); jj = jj.contiguous(); kk = kk.contiguous()
+            # the index-only work runs on a side stream underneath the correlation encoder
+            main = torch.cuda.current_stream(net.device)
+            if self._side is None:
+                self._side = torch.cuda.Stream(net.device)
+                self._fork, self._join = torch.cuda.Event(), torch.cuda.Event()
+            self._fork.record(main)
+            with torch.cuda.stream(self._side):
+                self._side.wait_event(self._fork)
+                idx = self._index_work(ii, jj, kk, n_frames, n_patches)
+                self._join.record(self._side)
             # correlation encoder + input injection + norm (net.py:71-72)
             c = self._lin("corr.0", corr, act=1)
             c = self._lin("corr.2", c, ln=self.ln["corr.3"], act=1)
             net = self._lin("corr.5", c, res1=net, res2=table, idx=tidx, ln=self.ln["norm"])
+            main.wait_event(self._join)
+            for v in (idx["ix"], idx["jx"], *idx["kk"][::2], *idx["ij"][::2]):
+                v.record_stream(main)
             # temporal neighbours along each patch track (net.py:74-80)
-            ix, jx = cuda_ba.neighbors(kk, jj)
-            t = self._lin("c1.0", self._gather(net, ix), act=1)
+            t = self._lin("c1.0", self._gather(net, idx["ix"]), act=1)
             net = self._lin("c1.2", t, res1=net)
-            t = self._lin("c2.0", self._gather(net, jx), act=1)
+            t = self._lin("c2.0", self._gather(net, idx["jx"]), act=1)
             net = self._lin("c2.2", t, res1=net)
             # soft aggregation over patches and over frame pairs (net.py:82-83); gru.0's LayerNorm rides on the second
-            net = self._soft_agg("agg_kk", net, kk, n_patches)
-            net = self._soft_agg("agg_ij", net, ii * n_frames + jj, n_frames * n_frames, ln=self.ln["gru.0"])
+            net = self._soft_agg("agg_kk", net, idx["kk"])
+            net = self._soft_agg("agg_ij", net, idx["ij"], ln=self.ln["gru.0"])
             # gated residual blocks (net.py:41-46,85)
             net = self._gated_residual("gru.1", net, ln=self.ln["gru.2"])
             net = self._gated_residual("gru.3", net)

@@ -181,10 +181,15 @@ int dpvo_gather_rows_f16(const void* src, const int64_t* index, int64_t n_rows, 
  * [E,384] rows f and g grouped by ids[e] in [0, group_bound) (any dense labelling of the groups, e.g.
  * the inverse of dpvo_unique_inverse):  y[grp] = sum_e f_e softmax_grp(g)_e.  y: fp16
  * [group_bound,384]; rows of empty groups are left untouched.  fp32 arithmetic, running maximum.
- * workspace: dpvo_softagg_workspace_bytes(E, group_bound). */
+ * workspace: dpvo_softagg_workspace_bytes(E, group_bound).  The bucket sort of the edges by group
+ * depends on ids only: dpvo_softagg_prepare does it ahead of time (e.g. on another stream while the
+ * layers that produce f and g run) and dpvo_softagg_f16(prepared = 1) then reuses the workspace;
+ * with prepared = 0 the sort happens inside the call (ids required). */
 int64_t dpvo_softagg_workspace_bytes(int64_t n_edges, int64_t group_bound);
+int dpvo_softagg_prepare(const int64_t* ids, int64_t n_edges, int64_t group_bound, void* workspace,
+                         int64_t workspace_bytes, void* stream);
 int dpvo_softagg_f16(const void* f, const void* g, const int64_t* ids, int64_t n_edges, int64_t group_bound,
-                     void* y, void* workspace, int64_t workspace_bytes, void* stream);
+                     void* y, int32_t prepared, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* out[e] = net[e] + hy[ids[e]] (SoftAgg's expand `h(y)[:, jx]` + the residual add, net.py:82-83),
  * followed by LayerNorm(ln_gamma, ln_beta, ln_eps) when ln_gamma != NULL (gru.0, net.py:42).

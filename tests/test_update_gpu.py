@@ -167,7 +167,7 @@ def test_softagg_groups_match_torch():
     y = torch.zeros(G, 384, dtype=torch.float16, device="cuda")
     ws = torch.empty(int(L.dpvo_softagg_workspace_bytes(lib.c_i64(E), lib.c_i64(G))), dtype=torch.uint8, device="cuda")
     lib.check(L.dpvo_softagg_f16(lib.ptr(f), lib.ptr(gm), lib.ptr(ids), lib.c_i64(E), lib.c_i64(G), lib.ptr(y),
-                                 lib.ptr(ws), lib.c_i64(ws.numel()), lib.stream_of(f)), "softagg")
+                                 lib.c_i32(0), lib.ptr(ws), lib.c_i64(ws.numel()), lib.stream_of(f)), "softagg")
     idx = ids.view(-1, 1).expand(E, 384)
     gmax = torch.full((G, 384), float("-inf"), device="cuda").scatter_reduce(0, idx, gm.float(), "amax", include_self=False)
     ex = torch.exp(gm.float() - gmax[ids])

@@ -74,7 +74,7 @@ def main():
             buf = (ctypes.c_longlong * 16)()
             pkg._lib.lib.dpvo_linear_profile_read(buf)
             names = ["prod_wait_empty", "prod_total", "mma_wait_A", "mma_wait_acc", "mma_wait_W", "mma_total",
-                     "epi_wait_acc", "epi_total", "tiles", "epi_store", "epi_tmem_ld"]
+                     "epi_wait_acc", "epi_total", "tiles"]
             print("profile (cycles, CTA 0):", {n: int(buf[i]) for i, n in enumerate(names)})
         Ac = A.contiguous(); Wc = W.contiguous()
         for _ in range(3): torch.relu(torch.nn.functional.linear(Ac, Wc, b.half()))
