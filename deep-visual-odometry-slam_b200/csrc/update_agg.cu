@@ -249,6 +249,18 @@ heads_kernel(const __half* __restrict__ net, const float* __restrict__ wd, const
   }
 }
 
+// finish of the heads accumulated by the last layer's epilogue: acc [E,4] = (d0, d1, w0, w1) dot products
+__global__ void __launch_bounds__(256)
+heads_finish_kernel(const float4* __restrict__ acc, const float* __restrict__ bd, const float* __restrict__ bw,
+                    int64_t E, float2* __restrict__ delta, float2* __restrict__ weight) {
+  const float b0 = bd[0], b1 = bd[1], c0 = bw[0], c1 = bw[1];
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < E; e += (int64_t)gridDim.x * blockDim.x) {
+    const float4 a = acc[e];
+    delta[e] = make_float2(a.x + b0, a.y + b1);
+    weight[e] = make_float2(1.0f / (1.0f + __expf(-(a.z + c0))), 1.0f / (1.0f + __expf(-(a.w + c1))));
+  }
+}
+
 inline int grid_for(int64_t items, int per_block, int cap_mult) {
   const int64_t b = ceil_div64(items, per_block);
   const int64_t cap = (int64_t)kNumSMs * cap_mult;
@@ -348,4 +360,16 @@ extern "C" int dpvo_update_heads_f16(const void* net, const float* wd, const flo
   heads_kernel<<<grid_for(n_edges, 8, 64), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       static_cast<const __half*>(net), wd, bd, ww, bw, n_edges, delta, weight);
   return check_launch("update_heads");
+}
+
+extern "C" int dpvo_update_heads_finish(const float* acc, const float* bd, const float* bw, int64_t n_edges,
+                                        float* delta, float* weight, void* stream) {
+  DPVO_REQUIRE(n_edges >= 0, "update_heads_finish: bad sizes");
+  if (n_edges == 0) return 0;
+  DPVO_REQUIRE(acc && bd && bw && delta && weight, "update_heads_finish: null pointer");
+  note_launches(1);
+  heads_finish_kernel<<<grid_for(n_edges, 256, 8), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const float4*>(acc), bd, bw, n_edges, reinterpret_cast<float2*>(delta),
+      reinterpret_cast<float2*>(weight));
+  return check_launch("update_heads_finish");
 }

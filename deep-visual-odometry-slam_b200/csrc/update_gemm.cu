@@ -392,11 +392,13 @@ struct LinearRwDev {
   int act;
   __half* Y;
   int64_t M;
+  const float* head_w;   // [4][384]: rows of the two 384->2 heads, applied to ReLU(output)
+  float* head_acc;       // [M][4], accumulated with atomics (both column halves contribute)
 };
 
 // LN: LayerNorm over the full 384-wide row.  The two CTAs of a pair then run as a cluster and swap the
 // per-row (sum, sum of squares) of their halves through each other's shared memory once per tile.
-template <bool LN>
+template <bool LN, bool HEADS>
 __global__ void __launch_bounds__(kThreads, 1)
 linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                     const LinearRwDev p) {
@@ -411,6 +413,7 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __shared__ __align__(16) float s_gamma[LN ? kHalf : 4], s_beta[LN ? kHalf : 4];
   __shared__ __align__(8) float2 peer_part[2][LN ? BM : 1];   // written by the other CTA of the pair
   __shared__ uint64_t ln_bar[2];
+  __shared__ __align__(16) float s_head[HEADS ? 4 : 1][HEADS ? kHalf : 4];   // this half's slice of the head weights
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t tiles = (p.M + BM - 1) / BM;
@@ -420,6 +423,10 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   for (int i = threadIdx.x; i < kHalf; i += kThreads) {
     s_bias[i] = p.bias ? p.bias[(blockIdx.x & 1) * kHalf + i] : 0.f;
+    if (HEADS) {
+#pragma unroll
+      for (int hd = 0; hd < 4; ++hd) s_head[HEADS ? hd : 0][i] = p.head_w[hd * kDim + (blockIdx.x & 1) * kHalf + i];
+    }
     if (LN) {
       s_gamma[i] = p.ln_gamma[(blockIdx.x & 1) * kHalf + i];
       s_beta[i] = p.ln_beta[(blockIdx.x & 1) * kHalf + i];
@@ -590,6 +597,7 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         mean = sum * (1.0f / kDim);
         rstd = rsqrtf(fmaxf(sq * (1.0f / kDim) - mean * mean, 0.f) + p.ln_eps);
       }
+      float hacc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 1
       for (int c = 0; c < 2; ++c) {
         uint32_t v[32];
@@ -614,6 +622,17 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         } else if (p.act == 2) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) x[j] = __fdividef(1.0f, 1.0f + __expf(-x[j]));
+        }
+        if (HEADS) {                                  // the two 384->2 heads ride on the last layer (net.py:88)
+#pragma unroll
+          for (int hd = 0; hd < 4; ++hd) {
+#pragma unroll
+            for (int qd = 0; qd < 8; ++qd) {
+              const float4 w4 = *reinterpret_cast<const float4*>(&s_head[HEADS ? hd : 0][n0 + 4 * qd]);
+              hacc[hd] += fmaxf(x[4 * qd], 0.f) * w4.x + fmaxf(x[4 * qd + 1], 0.f) * w4.y +
+                          fmaxf(x[4 * qd + 2], 0.f) * w4.z + fmaxf(x[4 * qd + 3], 0.f) * w4.w;
+            }
+          }
         }
         // transpose through shared memory so that global stores are whole 64-byte row segments:
         // thread r parks its four 16-byte units (XOR-swizzled by row pair: conflict-free both ways) ...
@@ -642,6 +661,10 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       tc_fence_before();
       mbar_arrive(&tmem_empty[buf]);
+      if (HEADS && ok) {
+#pragma unroll
+        for (int hd = 0; hd < 4; ++hd) atomicAdd(p.head_acc + row * 4 + hd, hacc[hd]);
+      }
     }
     if (prof) {
       g_linear_profile[6] = t_accw;
@@ -768,6 +791,9 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
                    (reinterpret_cast<uintptr_t>(lp->Y) & 15) == 0,
                "linear384: A, W and Y must be 16-byte aligned");
   DPVO_REQUIRE(lp->act >= 0 && lp->act <= 2, "linear384: act must be 0 (none), 1 (relu) or 2 (sigmoid)");
+  DPVO_REQUIRE((lp->head_w == nullptr) == (lp->head_acc == nullptr), "linear384: head_w and head_acc go together");
+  DPVO_REQUIRE(lp->head_w == nullptr || (lp->K == kDim && lp->ln_gamma == nullptr && use_resident_w()),
+               "linear384: fused heads need K = 384 and no LayerNorm");
   DPVO_REQUIRE(lp->M < (int64_t(1) << 31) - BM, "linear384: too many rows");
   CUtensorMap tmA, tmW, tmY;
   if (make_map(&tmA, lp->A, lp->K, lp->M, lp->lda, BM)) return 1;
@@ -787,12 +813,17 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
     q.act = lp->act;
     q.Y = getenv("DPVO_LINEAR_DEBUG_NOSTORE") ? nullptr : static_cast<__half*>(lp->Y);
     q.M = lp->M;
+    q.head_w = lp->head_w;
+    q.head_acc = lp->head_acc;
     const int64_t tiles = (lp->M + BM - 1) / BM;
     const int pairs = static_cast<int>(tiles < kNumSMs / 2 ? tiles : kNumSMs / 2);
     const bool ln = lp->ln_gamma != nullptr;
     if (ln) DPVO_REQUIRE(lp->ln_beta != nullptr, "linear384: LayerNorm needs both gamma and beta");
-    cudaError_t e = ln ? cudaFuncSetAttribute(linear384_rw_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kRwSmemBytes)
-                       : cudaFuncSetAttribute(linear384_rw_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kRwSmemBytes);
+    const bool heads = lp->head_w != nullptr;
+    const void* fn = ln ? reinterpret_cast<const void*>(linear384_rw_kernel<true, false>)
+                        : heads ? reinterpret_cast<const void*>(linear384_rw_kernel<false, true>)
+                                : reinterpret_cast<const void*>(linear384_rw_kernel<false, false>);
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kRwSmemBytes);
     DPVO_REQUIRE(e == cudaSuccess, "linear384: cannot reserve %d bytes of shared memory: %s", kRwSmemBytes,
                  cudaGetErrorString(e));
     cudaLaunchConfig_t cfg = {};
@@ -808,8 +839,8 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     note_launches(1);
-    e = ln ? cudaLaunchKernelEx(&cfg, linear384_rw_kernel<true>, tmA, tmW, q)
-           : cudaLaunchKernelEx(&cfg, linear384_rw_kernel<false>, tmA, tmW, q);
+    void* args[3] = {&tmA, &tmW, &q};
+    e = cudaLaunchKernelExC(&cfg, fn, args);
     if (e != cudaSuccess) {
       set_error("linear384: launch failed: %s", cudaGetErrorString(e));
       return 1;

@@ -77,6 +77,7 @@ class Update:
         for k in _HEADS:
             self.head[k] = (torch.as_tensor(state_dict[k + ".weight"]).detach().to(dev, torch.float32).contiguous(),
                             torch.as_tensor(state_dict[k + ".bias"]).detach().to(dev, torch.float32).contiguous())
+        self.head_w = torch.cat([self.head["d.1"][0], self.head["w.1"][0]], 0).contiguous()   # [4, 384]
         self.corr_features = self.W["corr.0"].shape[1]
         self._side = None
 
@@ -148,10 +149,10 @@ class Update:
                    "expand_add")
         return out
 
-    def _gated_residual(self, name, x, ln=None):
+    def _gated_residual(self, name, x, ln=None, head=None):
         gate = self._lin(name + ".gate.0", x, act=2)
         r = self._lin(name + ".res.0", x, act=1)
-        return self._lin(name + ".res.2", r, gate=gate, res1=x, ln=ln)
+        return self._lin(name + ".res.2", r, gate=gate, res1=x, ln=ln, head=head)
 
     # ------------------------------------------------------------------ forward
     def __call__(self, net, inp, corr, flow, ii, jj, kk, n_frames=None, n_patches=None):
@@ -214,11 +215,12 @@ class Update:
             net = self._soft_agg("agg_ij", net, idx["ij"], ln=self.ln["gru.0"])
             # gated residual blocks (net.py:41-46,85)
             net = self._gated_residual("gru.1", net, ln=self.ln["gru.2"])
-            net = self._gated_residual("gru.3", net)
+            # ... the second one also accumulates the two 384->2 heads on ReLU(net) (net.py:57-66,88)
+            acc = torch.zeros((E, 4), dtype=torch.float32, device=net.device)
+            net = self._gated_residual("gru.3", net, head=(self.head_w, acc))
             delta = torch.empty((E, 2), dtype=torch.float32, device=net.device)
             weight = torch.empty((E, 2), dtype=torch.float32, device=net.device)
-            (wd, bd), (ww, bw) = self.head["d.1"], self.head["w.1"]
-            _lib.check(_L.dpvo_update_heads_f16(_lib.ptr(net), _lib.ptr(wd), _lib.ptr(bd), _lib.ptr(ww), _lib.ptr(bw),
-                                                _lib.c_i64(E), _lib.ptr(delta), _lib.ptr(weight),
-                                                _lib.stream_of(net)), "update_heads")
+            _lib.check(_L.dpvo_update_heads_finish(_lib.ptr(acc), _lib.ptr(self.head["d.1"][1]),
+                                                   _lib.ptr(self.head["w.1"][1]), _lib.c_i64(E), _lib.ptr(delta),
+                                                   _lib.ptr(weight), _lib.stream_of(net)), "update_heads_finish")
         return net[None], (delta[None], weight[None], None)

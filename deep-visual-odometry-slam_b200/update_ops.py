@@ -23,7 +23,8 @@ class _LinearParams(ctypes.Structure):
                 ("ln_gamma", ctypes.c_void_p), ("ln_beta", ctypes.c_void_p), ("ln_eps", ctypes.c_float),
                 ("act", ctypes.c_int32),
                 ("Y", ctypes.c_void_p),
-                ("M", ctypes.c_int64), ("K", ctypes.c_int32)]
+                ("M", ctypes.c_int64), ("K", ctypes.c_int32),
+                ("head_w", ctypes.c_void_p), ("head_acc", ctypes.c_void_p)]
 
 
 _lib.lib.dpvo_linear384_f16.argtypes = [ctypes.POINTER(_LinearParams), ctypes.c_void_p]
@@ -48,11 +49,12 @@ def _vec384(t, name):
     return t
 
 
-def linear384(A, W, bias=None, gate=None, res1=None, res2=None, idx=None, ln=None, act=0, out=None):
+def linear384(A, W, bias=None, gate=None, res1=None, res2=None, idx=None, ln=None, act=0, out=None, head=None):
     """Y = act(LN((A W^T + bias) * gate + res1 + res2[idx])) as float16 [M, 384].
 
     A: float16 [M, K] (row stride a multiple of 8 elements), W: float16 [384, K] (likewise);
-    ln = (gamma, beta, eps) or None; act: 0 none, 1 ReLU, 2 sigmoid."""
+    ln = (gamma, beta, eps) or None; act: 0 none, 1 ReLU, 2 sigmoid.
+    head = (w [4, 384] float32, acc [M, 4] float32 zeroed): acc += ReLU(Y) w^T (K = 384, no ln)."""
     _lib.require_cuda(A, W)
     if A.dtype != torch.float16 or W.dtype != torch.float16 or A.dim() != 2 or W.dim() != 2:
         raise RuntimeError("linear384: A and W must be 2-D float16")
@@ -72,13 +74,20 @@ def linear384(A, W, bias=None, gate=None, res1=None, res2=None, idx=None, ln=Non
         gamma, beta, eps = ln
         _vec384(gamma, "ln gamma"); _vec384(beta, "ln beta")
     _vec384(bias, "bias")
+    head_w = head_acc = None
+    if head is not None:
+        head_w, head_acc = head
+        if head_w.dtype != torch.float32 or tuple(head_w.shape) != (4, DIM) or not head_w.is_contiguous():
+            raise RuntimeError(f"linear384: head weights must be contiguous float32 [4, {DIM}]")
+        if head_acc.dtype != torch.float32 or tuple(head_acc.shape) != (M, 4) or not head_acc.is_contiguous():
+            raise RuntimeError("linear384: head accumulator must be contiguous float32 [M, 4]")
     Y = out if out is not None else torch.empty((M, DIM), dtype=torch.float16, device=A.device)
     _rows384(Y, "out", M)
     p = _LinearParams(A=_lib.ptr(A).value, lda=A.stride(0) if M > 1 else max(A.stride(0), K), W=_lib.ptr(W).value,
                       ldw=W.stride(0), bias=_lib.ptr(bias).value, gate=_lib.ptr(gate).value,
                       res1=_lib.ptr(res1).value, res2=_lib.ptr(res2).value, res2_index=_lib.ptr(idx).value,
                       ln_gamma=_lib.ptr(gamma).value, ln_beta=_lib.ptr(beta).value, ln_eps=float(eps), act=int(act),
-                      Y=_lib.ptr(Y).value, M=M, K=K)
+                      Y=_lib.ptr(Y).value, M=M, K=K, head_w=_lib.ptr(head_w).value, head_acc=_lib.ptr(head_acc).value)
     with torch.cuda.device(A.device):
         _lib.check(_lib.lib.dpvo_linear384_f16(ctypes.byref(p), _lib.stream_of(A)), "linear384")
     return Y

@@ -166,6 +166,10 @@ typedef struct dpvo_linear_params {
   int32_t act;
   void* Y;
   int64_t M; int32_t K;
+  /* optional (K = 384, no LayerNorm): the operator's two 384->2 heads on ReLU(v) (net.py:57-66,88):
+   * head_acc[row][h] += sum_n ReLU(v[row][n]) head_w[h][n], h = (d0, d1, w0, w1); head_acc is
+   * float32 [M,4], zeroed by the caller, finished by dpvo_update_heads_finish. */
+  const float* head_w; float* head_acc;
 } dpvo_linear_params;
 int dpvo_linear384_f16(const dpvo_linear_params* p, void* stream);
 /* Diagnostics: 16 per-role cycle counters of CTA 0 of the last K=384 launch made with the
@@ -201,6 +205,10 @@ int dpvo_expand_add_f16(const void* net, const void* hy, const int64_t* ids, int
  * wd / ww float32 [2,384], bd / bw float32 [2]; delta, weight: float32 [E,2]. */
 int dpvo_update_heads_f16(const void* net, const float* wd, const float* bd, const float* ww, const float* bw,
                           int64_t n_edges, float* delta, float* weight, void* stream);
+/* Same result from the dot products the last layer accumulated (dpvo_linear_params.head_acc):
+ * delta = acc[:, 0:2] + bd, weight = sigmoid(acc[:, 2:4] + bw). */
+int dpvo_update_heads_finish(const float* acc, const float* bd, const float* bw, int64_t n_edges,
+                             float* delta, float* weight, void* stream);
 
 /* Reprojection of all PxP pixels of patch kk[e] from frame ii[e] into frame jj[e] —
  * replaces cuda_ba.reproject (ba_cuda.cu:379-429,585-617).  coords: [E,2,P,P] float32. */
