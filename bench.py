@@ -168,12 +168,41 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def update_iteration(hotpath, dev, seq, steps):
+    """Extra, outside the headline metric: the whole body of DPVO.update (dpvo.py:328-354) — the hot
+    path above plus the Update operator between corr and BA — replayed as one CUDA
+    graph on the same 45,312-edge window."""
+    import torch
+    it = hotpath.UpdateIteration(dev, n_frames=40, seed=seq)
+    for _ in range(3):
+        it.step_full()
+    torch.cuda.synchronize(dev)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        it.step_full()
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
+    return {"what": "reproject + corr + Update operator (19 tcgen05 layers + row kernels) + BA, CUDA graph, "
+                    "device-resident inputs, random-initialised operator weights",
+            "ms_per_step": round(ms, 4), "frames_per_s": round(1e3 / ms, 1), "edges": it.E}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-update-iteration", action="store_true",
+                    help="skip the extra full-iteration measurement (hot path + Update operator)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="time stream launches instead of CUDA-graph replay")
     args = ap.parse_args()
@@ -306,6 +335,8 @@ def main():
                 line["roofline"]["traffic"] = json.load(f).get("dram_bytes_per_launch")
         except Exception:
             pass
+    if world == 1 and not args.no_update_iteration:
+        line["update_iteration"] = update_iteration(hotpath, dev, seq, args.steps)
     if world == 1 and not args.no_cpu_baseline:
         _, info = cpu_frame(hp.host, sample_edges=4096, steps=2)
         line["cpu_baseline"] = info

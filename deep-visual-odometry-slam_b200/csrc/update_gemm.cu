@@ -398,7 +398,9 @@ struct LinearRwDev {
 
 // LN: LayerNorm over the full 384-wide row.  The two CTAs of a pair then run as a cluster and swap the
 // per-row (sum, sum of squares) of their halves through each other's shared memory once per tile.
-template <bool LN, bool HEADS>
+// AMC: the pair runs as a cluster and shares every A chunk: each CTA loads 64 of its 128 rows and
+// multicasts them into both shared memories.
+template <bool LN, bool HEADS, bool AMC>
 __global__ void __launch_bounds__(kThreads, 1)
 linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                     const LinearRwDev p) {
@@ -441,7 +443,7 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_init(&wfull, 1);
       for (int s = 0; s < kRwStages; ++s) {
         mbar_init(&full[s], 1);
-        mbar_init(&empty[s], 1);
+        mbar_init(&empty[s], AMC ? 2 : 1);
       }
       for (int b = 0; b < 2; ++b) {
         mbar_init(&tmem_full[b], 1);
@@ -454,7 +456,7 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tmem_alloc(&tmem_base_s, kTmemCols);
   }
   tc_fence_before();
-  if (LN) cluster_sync_all(); else __syncthreads();   // the peer's ln_bar must exist before the first remote arrive
+  if (LN || AMC) cluster_sync_all(); else __syncthreads();   // the peer's barriers must exist before the first remote arrive
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
 
@@ -475,7 +477,11 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           mbar_wait(&empty[s], ph ^ 1);
           t_wait += clock64() - t0;
           mbar_arrive_expect_tx(&full[s], kABytes);
-          tma_load_2d(ring + s * kABytes, &tmA, &full[s], kb * BK, static_cast<int32_t>(tile * BM));
+          if (AMC)
+            tma_load_2d_mc(ring + s * kABytes + h * (kABytes / 2), &tmA, &full[s], kb * BK,
+                           static_cast<int32_t>(tile * BM + h * (BM / 2)), 3);
+          else
+            tma_load_2d(ring + s * kABytes, &tmA, &full[s], kb * BK, static_cast<int32_t>(tile * BM));
         }
       }
       if (prof) {
@@ -514,7 +520,7 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           for (int k = 0; k < BK / 16; ++k)
             mma_f16_ss(d, smem_desc_sw128(a0 + k * 32), smem_desc_sw128(w0 + kb * kRwWChunk + k * 32), idesc,
                        (kb | k) != 0 ? 1u : 0u);
-          mma_commit(&empty[s]);
+          if (AMC) mma_commit_mc(&empty[s], 3); else mma_commit(&empty[s]);
         }
         mma_commit(&tmem_full[buf]);
       }
@@ -673,7 +679,7 @@ linear384_rw_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
   tc_fence_before();
   __syncthreads();
-  if (LN) cluster_sync_all();                         // the peer may still be signalling this CTA's barriers
+  if (LN || AMC) cluster_sync_all();                  // the peer may still be signalling this CTA's barriers
   if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
 }
 
@@ -820,9 +826,15 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
     const bool ln = lp->ln_gamma != nullptr;
     if (ln) DPVO_REQUIRE(lp->ln_beta != nullptr, "linear384: LayerNorm needs both gamma and beta");
     const bool heads = lp->head_w != nullptr;
-    const void* fn = ln ? reinterpret_cast<const void*>(linear384_rw_kernel<true, false>)
-                        : heads ? reinterpret_cast<const void*>(linear384_rw_kernel<false, true>)
-                                : reinterpret_cast<const void*>(linear384_rw_kernel<false, false>);
+    static const bool amc = getenv("DPVO_LINEAR_AMC") != nullptr && getenv("DPVO_LINEAR_AMC")[0] == '1';
+    if (amc && make_map(&tmA, lp->A, lp->K, lp->M, lp->lda, BM / 2)) return 1;
+    const void* fn =
+        amc ? (ln ? reinterpret_cast<const void*>(linear384_rw_kernel<true, false, true>)
+                  : heads ? reinterpret_cast<const void*>(linear384_rw_kernel<false, true, true>)
+                          : reinterpret_cast<const void*>(linear384_rw_kernel<false, false, true>))
+            : (ln ? reinterpret_cast<const void*>(linear384_rw_kernel<true, false, false>)
+                  : heads ? reinterpret_cast<const void*>(linear384_rw_kernel<false, true, false>)
+                          : reinterpret_cast<const void*>(linear384_rw_kernel<false, false, false>));
     cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kRwSmemBytes);
     DPVO_REQUIRE(e == cudaSuccess, "linear384: cannot reserve %d bytes of shared memory: %s", kRwSmemBytes,
                  cudaGetErrorString(e));
@@ -833,7 +845,7 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = ln ? 2 : 1;
+    attr[0].val.clusterDim.x = (ln || amc) ? 2 : 1;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;

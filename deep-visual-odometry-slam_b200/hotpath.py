@@ -10,8 +10,9 @@ Mirrors what `DPVO.__call__` -> `DPVO.update` does per frame between the network
     neighbors       temporal neighbours of every edge                  net.py:76
     BA              2 Gauss-Newton iterations, 10-pose window          dpvo.py:351-354
 
-The Update network and the encoders that sit between these operators are outside this
-build's scope; `target` and `weight` (the network's outputs) are inputs.
+`UpdateHotPath` is the north-star path: the Update network's outputs `target` and `weight` are inputs.
+`UpdateIteration` adds the Update operator itself (update.py) between corr and BA, i.e.
+the whole body of `DPVO.update` (dpvo.py:328-354); the encoders (N3) stay outside.
 Used by bench.py and the tests; all tensors live on one CUDA device, all launches go to
 torch's current stream, nothing synchronises with the host.
 """
@@ -233,3 +234,42 @@ class UpdateHotPath:
         at the coords produced by reproject() on the initial state."""
         coords = self.reproject().cpu().numpy()
         return synth.corr_algorithmic_bytes(coords, [(synth.H1, synth.W1), (synth.H2, synth.W2)], [1.0, 0.25])
+
+
+class UpdateIteration(UpdateHotPath):
+    """The whole body of `DPVO.update` (dpvo.py:328-354) for one frame:
+
+        reproject -> corr -> Update operator -> target = centre + delta, weight -> BA
+
+    with the hidden state `net` carried from call to call like `self.pg.net`.  Random-initialised
+    operator parameters (synth.update_state_dict) — there is no checkpoint on the box."""
+
+    def __init__(self, device, n_frames=40, seed=0, **kw):
+        super().__init__(device, n_frames=n_frames, seed=seed, **kw)
+        from . import update as _update
+        sd = {k: torch.from_numpy(v) for k, v in synth.update_state_dict(seed + 3).items()}
+        self.update_op = _update.Update.from_state_dict(sd, device=self.device)
+        rng = np.random.default_rng(seed + 4)
+        half = lambda *shape: torch.from_numpy(rng.standard_normal(shape, dtype=np.float32)).to(self.device).half()
+        self.net = 0.5 * half(1, self.E, 384)
+        self.imap = half(self.n_patches, 384)              # context ring, dpvo.py:63 ([pmem*M, DIM] flattened)
+        self.ctx_index = (self.kk % self.n_patches).contiguous()
+        self.n_patch_ids = int(self.kk.max().item()) + 1
+
+    def step_full(self):
+        self.poses.copy_(self.poses0)
+        self.patches.copy_(self.patches0)
+        self.ring_write()
+        self.patchify()
+        coords = self.reproject()
+        us = self.kk % self.n_patches
+        vs = self.jj % self.mem
+        corr = altcorr.corr_pyramid(self.gmap, (self.fmap1, self.fmap2), coords, us, vs, 3, row_stride=896)
+        self.net, (delta, weight, _) = self.update_op(self.net, (self.imap, self.ctx_index), corr, None,
+                                                      self.ii, self.jj, self.kk, n_frames=self.n,
+                                                      n_patches=self.n_patch_ids)
+        P = coords.shape[-1]
+        target = coords[..., P // 2, P // 2] + delta       # dpvo.py:341
+        fastba.BA(self.poses, self.patches, self.intrinsics, target.contiguous(), weight, self.lmbda,
+                  self.ii, self.jj, self.kk, self.t0, self.t1, self.M, 2, False)
+        return delta, weight

@@ -176,3 +176,28 @@ def test_softagg_groups_match_torch():
     assert (y.float() - want).abs().max().item() <= 2e-3 * want.abs().max().item() + 1e-3
     empty = torch.ones(G, dtype=torch.bool, device="cuda"); empty[ids] = False
     assert empty.any() and (y[empty] == 0).all()
+
+
+def test_update_iteration_matches_staged_oracle():
+    """The full DPVO.update body (hotpath.UpdateIteration.step_full): its Update stage against the float32
+    oracle on the correlation features the same run produced, and target = centre + delta feeding BA."""
+    pkg = load_pkg()
+    hotpath = importlib.import_module(pkg.__name__ + ".hotpath")
+    synth = importlib.import_module(pkg.__name__ + ".synth")
+    it = hotpath.UpdateIteration("cuda:0", n_frames=12, seed=2, M=16)
+    net_in = it.net.clone()
+    poses_before = it.poses0.clone()
+    delta, weight = it.step_full()
+    torch.cuda.synchronize()
+    poses_after = it.poses.clone()
+    # replay the stages by hand for the oracle
+    it.poses.copy_(it.poses0); it.patches.copy_(it.patches0)
+    coords = it.reproject()
+    corr = it.corr(coords)                                               # contiguous [1,E,882] variant of the same lookup
+    sd = uo.state_dict_tensors(synth.update_state_dict(2 + 3), device="cuda")
+    with torch.no_grad():
+        w_net, w_delta, w_weight = uo.forward(sd, net_in[0].float(), it.imap.float()[it.ctx_index], corr[0].float(),
+                                              it.ii, it.jj, it.kk)
+    assert _rel(delta[0], w_delta) <= 1e-2 and _rel(weight[0], w_weight) <= 1e-2
+    assert _rel(it.net[0].float(), w_net) <= 1e-2
+    assert torch.isfinite(poses_after).all() and not torch.equal(poses_after, poses_before)   # BA moved the window

@@ -1,1 +1,1 @@
-for cl in 1 8; do echo "== cluster $cl"; DPVO_LINEAR_CLUSTER=$cl timeout 300 python tools/gemm_check.py 2>&1 | grep "timing\|BAD\|ALL\|rror" ; done
+for v in 0 1; do echo "== AMC $v"; DPVO_LINEAR_AMC=$v timeout 300 python tools/gemm_check.py 2>&1 | grep "timing\|BAD\|ALL\|rror" ; DPVO_LINEAR_AMC=$v timeout 300 python tools/time_update.py; done
