@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define DPVO_B200_ABI_VERSION 1
+#define DPVO_B200_ABI_VERSION 2
 
 typedef enum { DPVO_F16 = 0, DPVO_F32 = 1, DPVO_F64 = 2 } dpvo_dtype;
 

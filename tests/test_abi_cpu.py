@@ -108,7 +108,9 @@ def test_dropin_modules_import_by_bare_name():
             "assert all(hasattr(cuda_ba, n) for n in ('forward','neighbors','reproject','solve_system'))\n"
             "names = ['expm','logm','inv','mul','adj','adjT','act','act4']\n"
             "assert all(hasattr(lb, n) and hasattr(lb, n + '_backward') for n in names)\n"
-            "assert all(hasattr(lb, n) for n in ('as_matrix','projector','Jinv'))\n")
+            "assert all(hasattr(lb, n) for n in ('as_matrix','projector','Jinv'))\n"
+            "import dpvo_b200_update as u\n"
+            "assert callable(u.linear384) and hasattr(u.Update, 'from_reference')\n")
     env = dict(os.environ, PYTHONPATH=d)
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, cwd="/")
     assert r.returncode == 0, r.stderr[-2000:]
@@ -130,3 +132,18 @@ def test_lietorch_refuses_cpu_and_bad_groups():
     rc = lib.dpvo_lie_inv(ctypes.c_int32(3), ctypes.c_int32(0), one, one, ctypes.c_int64(5), null)
     assert rc != 0 and b"dtype" in lib.dpvo_last_error()
     assert lib.dpvo_lie_inv(ctypes.c_int32(3), ctypes.c_int32(1), null, null, ctypes.c_int64(0), null) == 0
+
+
+def test_update_operator_validation_without_gpu():
+    """Update operator host side: CPU devices / tensors and incomplete state dicts are refused (no fallback)."""
+    upd = load_pkg("update")
+    ops = load_pkg("update_ops")
+    synth = load_pkg("synth")
+    sd = {k: torch.from_numpy(v) for k, v in synth.update_state_dict(0).items()}
+    with pytest.raises(RuntimeError):
+        upd.Update(sd, device="cpu")
+    bad = dict(sd); bad.pop("gru.1.gate.0.weight")
+    with pytest.raises(RuntimeError):
+        upd.Update(bad, device="cuda")
+    with pytest.raises(RuntimeError):
+        ops.linear384(torch.zeros(4, 384, dtype=torch.float16), torch.zeros(384, 384, dtype=torch.float16))
