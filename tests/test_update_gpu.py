@@ -136,7 +136,7 @@ def test_update_vs_reference_golden(fused_ctx):
         assert e_ours <= 3 * e_auto + 1e-4, (name, e_ours, e_auto)
 
 
-@pytest.mark.parametrize("n_frames,M", [(3, 4), (14, 16), (22, 96)])
+@pytest.mark.parametrize("n_frames,M", [(2, 1), (3, 4), (5, 13), (14, 16), (22, 96)])
 def test_update_vs_oracle_sizes(n_frames, M):
     """Up to the default sliding window (22 frames x 96 patches): float32 oracle on the same device."""
     pkg = load_pkg()
@@ -201,3 +201,27 @@ def test_update_iteration_matches_staged_oracle():
     assert _rel(delta[0], w_delta) <= 1e-2 and _rel(weight[0], w_weight) <= 1e-2
     assert _rel(it.net[0].float(), w_net) <= 1e-2
     assert torch.isfinite(poses_after).all() and not torch.equal(poses_after, poses_before)   # BA moved the window
+
+
+def test_update_sparse_indices_and_contiguous_corr():
+    """Frame / patch indices far from zero (long sequence: absolute indices), a contiguous [1,E,882] corr tensor
+    (repacked to 16-byte rows inside) and bounds read from the index tensors (n_frames / n_patches not given)."""
+    pkg = load_pkg()
+    sd_np, d = _operator_case(pkg, 6, 8, seed_w=3, seed_x=9)
+    d = dict(d)
+    d["ii"] = d["ii"] + 900; d["jj"] = d["jj"] + 900; d["kk"] = d["kk"] + 900 * 8
+    net, delta, weight = _run_ours(pkg, sd_np, d, False)
+    w_net, w_delta, w_weight = _run_oracle(sd_np, d, autocast=False)
+    assert _rel(net, w_net) <= 1e-2 and _rel(delta, w_delta) <= 1e-2 and _rel(weight, w_weight) <= 1e-2
+
+
+def test_update_empty_edge_list():
+    pkg = load_pkg()
+    upd_mod = importlib.import_module(pkg.__name__ + ".update")
+    synth = importlib.import_module(pkg.__name__ + ".synth")
+    op = upd_mod.Update.from_state_dict({k: torch.from_numpy(v) for k, v in synth.update_state_dict(0).items()},
+                                        device="cuda")
+    z = torch.zeros(0, dtype=torch.int64, device="cuda")
+    net, (delta, weight, _) = op(torch.zeros(1, 0, 384, device="cuda").half(), torch.zeros(1, 0, 384, device="cuda").half(),
+                                 torch.zeros(1, 0, 882, device="cuda").half(), None, z, z, z)
+    assert net.shape == (1, 0, 384) and delta.shape == (1, 0, 2) and weight.shape == (1, 0, 2)

@@ -1,2 +1,1 @@
-mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_update_gpu.py -m gpu -x -q 2>&1 | tail -25
+timeout 900 python -m pytest tests/test_update_gpu.py -m gpu -x -q 2>&1 | tail -8
