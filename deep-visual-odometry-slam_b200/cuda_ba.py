@@ -14,7 +14,7 @@ to torch's current stream.
 """
 import torch
 
-from ._lib import lib, ptr, stream_of, check, require_cuda, c_i32, c_i64
+from ._lib import lib, ptr, stream_of, check, require_cuda, c_i32, c_i64, c_f32
 
 lib.dpvo_ba_workspace_bytes.restype = c_i64
 lib.dpvo_neighbors_workspace_bytes.restype = c_i64
@@ -132,6 +132,27 @@ def cholesky_solve(S, y):
     return x, info
 
 
-def solve_system(*args, **kwargs):
-    raise RuntimeError("cuda_ba.solve_system (classic loop-closure PGO, fastba/ba.cpp:120-180) is outside the "
-                       "hot path of this build (SURVEY.md §8f N5)")
+def solve_system(J_Ginv_i, J_Ginv_j, ii, jj, res, ep, lm, freen, n_poses=None, refinements=2, return_info=False):
+    """cuda_ba.solve_system (fastba/ba.cpp:120-180; caller loop_closure/optim_utils.py:229): one damped
+    Gauss-Newton step of the Sim(3) pose graph, on the device.  Returns [delta [n,7]] like the reference
+    ([delta, info] with return_info=True; info is a device int32 tensor: 0 ok, 1 factorisation failed,
+    2 self edge).  n = max(ii, jj) + 1 is read back from the index tensors like the reference does
+    (one host sync) unless `n_poses` is given."""
+    require_cuda(J_Ginv_i, J_Ginv_j, ii, jj, res)
+    Ji = _f32c(J_Ginv_i, "J_Ginv_i"); Jj = _f32c(J_Ginv_j, "J_Ginv_j"); res = _f32c(res, "res")
+    ii = _i64c(ii, "ii"); jj = _i64c(jj, "jj")
+    r = ii.numel()
+    if jj.numel() != r or Ji.shape != (r, 7, 7) or Jj.shape != (r, 7, 7) or res.numel() != r * 7:
+        raise RuntimeError("cuda_ba.solve_system: expected J_Ginv_i/j [r,7,7], ii/jj [r], res [r,7]")
+    if n_poses is None:
+        n_poses = (int(torch.maximum(ii.max(), jj.max()).item()) + 1) if r else 0
+    n_poses = int(n_poses)
+    delta = torch.empty((n_poses, 7), dtype=torch.float32, device=res.device)
+    info = torch.zeros(1, dtype=torch.int32, device=res.device)
+    lib.dpvo_pgo_workspace_bytes.restype = c_i64
+    nbytes = lib.dpvo_pgo_workspace_bytes(c_i32(n_poses), c_i32(int(freen)))
+    ws = torch.empty(int(nbytes), dtype=torch.uint8, device=res.device)   # large and rarely used: not cached
+    check(lib.dpvo_pgo_solve(ptr(Ji), ptr(Jj), ptr(ii), ptr(jj), ptr(res), c_i64(r), c_i32(n_poses), c_f32(float(ep)),
+                             c_f32(float(lm)), c_i32(int(freen)), c_i32(int(refinements)), ptr(delta), ptr(info),
+                             ptr(ws), c_i64(ws.numel()), stream_of(res)), "cuda_ba.solve_system")
+    return [delta, info] if return_info else [delta]

@@ -213,6 +213,20 @@ int dpvo_update_heads_f16(const void* net, const float* wd, const float* bd, con
 int dpvo_update_heads_finish(const float* acc, const float* bd, const float* bw, int64_t n_edges,
                              float* delta, float* weight, void* stream);
 
+/* cuda_ba.solve_system (fastba/ba.cpp:99-180): one Gauss-Newton step of the classic loop-closure
+ * pose graph over Sim(3).  J_Ginv_i / J_Ginv_j: float32 [r,7,7] blocks of edge x at poses ii[x] / jj[x]
+ * (int64), res: float32 [r,7].  A = J^T J, A.diag += A.diag * lm, A.diag += ep, b = -J^T res; the first
+ * `freen` poses are solved for (all n_poses when freen < 0), the others stay fixed.  delta: float32
+ * [n_poses,7] (zeros for fixed poses).  info (device int32): 0 ok, 1 factorisation failed, 2 self edge
+ * or negative index (the reference exit(1)s) — delta is zero then.  Normal equations in float64,
+ * float32 blocked Cholesky + `refinements` rounds of float64-residual iterative refinement (0..4).
+ * workspace: dpvo_pgo_workspace_bytes(n_poses, freen). */
+int64_t dpvo_pgo_workspace_bytes(int32_t n_poses, int32_t freen);
+int dpvo_pgo_solve(const float* J_Ginv_i, const float* J_Ginv_j, const int64_t* ii, const int64_t* jj,
+                   const float* res, int64_t n_edges, int32_t n_poses, float ep, float lm, int32_t freen,
+                   int32_t refinements, float* delta, int32_t* info, void* workspace, int64_t workspace_bytes,
+                   void* stream);
+
 /* Reprojection of all PxP pixels of patch kk[e] from frame ii[e] into frame jj[e] —
  * replaces cuda_ba.reproject (ba_cuda.cu:379-429,585-617).  coords: [E,2,P,P] float32. */
 int dpvo_reproject(const float* poses, const float* patches, const float* intrinsics,

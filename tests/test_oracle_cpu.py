@@ -294,3 +294,25 @@ def test_update_oracle_vs_reference():
     np.testing.assert_allclose(net.numpy(), g["net"], rtol=1e-4, atol=1e-5)
     np.testing.assert_allclose(delta.numpy(), g["delta"], rtol=1e-4, atol=1e-5)
     np.testing.assert_allclose(weight.numpy(), g["weight"], rtol=1e-4, atol=1e-5)
+
+
+def _pgo_cases():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden_pgo", os.path.join(os.path.dirname(__file__), "golden",
+                                                                                   "make_golden_pgo.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+def test_pgo_oracle_vs_reference():
+    """cuda_ba.solve_system: dense float64 restatement against the reference extension's own outputs."""
+    from oracle import pgo_oracle
+    m = _pgo_cases()
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_cpu_pgo.npz"))
+    for name, (n, loops, freen, seed) in m.CASES.items():
+        if n > 100:
+            continue                                     # dense numpy J^T J of the 300-pose case: GPU test only
+        Ji, Jj, ii, jj, res = m.pgo_case(n, loops, seed)
+        got = pgo_oracle.solve_system(Ji, Jj, ii, jj, res, m.EP, m.LM, freen)
+        np.testing.assert_allclose(got, g[name], rtol=2e-4, atol=2e-6, err_msg=name)
