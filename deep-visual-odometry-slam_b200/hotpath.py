@@ -63,6 +63,8 @@ class UpdateHotPath:
         self.stage_events = None
         self.overlap_neighbors = True
         self._side = None
+        self._side2 = None
+        self._side3 = None
         self._nb = None
 
     # ------------------------------------------------------------------ stages
@@ -95,6 +97,28 @@ class UpdateHotPath:
         fastba.BA(self.poses, self.patches, self.intrinsics, self.target, self.weight, self.lmbda,
                   self.ii, self.jj, self.kk, self.t0, self.t1, self.M, 2, False)
 
+    def _front(self, main, fork):
+        """Ring write, patchify and reproject only depend on the frame's inputs / the current state, not on
+        each other: three short branches after `fork` (ring write stays on the main stream), joined on
+        the main stream before the lookup.  Returns the reprojected coords."""
+        if self._side2 is None:
+            self._side2 = torch.cuda.Stream(self.device)
+            self._side3 = torch.cuda.Stream(self.device)
+        j2, j3 = torch.cuda.Event(), torch.cuda.Event()
+        self._side2.wait_event(fork)
+        self._side3.wait_event(fork)
+        with torch.cuda.stream(self._side2):
+            self._patches_new = self.patchify()
+            j2.record(self._side2)
+        with torch.cuda.stream(self._side3):
+            coords = self.reproject()
+            coords.record_stream(main)
+            j3.record(self._side3)
+        self.ring_write()
+        main.wait_event(j2)
+        main.wait_event(j3)
+        return coords
+
     # ------------------------------------------------------------------ one frame
     def step(self, events=None):
         """All hot-path operators of one frame.  `events`: optional dict name -> list of
@@ -126,9 +150,8 @@ class UpdateHotPath:
             with torch.cuda.stream(self._side):
                 self._nb = self.neighbors()
                 join.record(self._side)
-            self.ring_write()
-            self.patchify()
-            corr = self.corr(self.reproject())
+            coords = self._front(main, fork)
+            corr = self.corr(coords)
             main.wait_event(join)
             self.ba()
             return corr
@@ -259,9 +282,10 @@ class UpdateIteration(UpdateHotPath):
     def step_full(self):
         self.poses.copy_(self.poses0)
         self.patches.copy_(self.patches0)
-        self.ring_write()
-        self.patchify()
-        coords = self.reproject()
+        main = torch.cuda.current_stream(self.device)
+        fork = torch.cuda.Event()
+        fork.record(main)
+        coords = self._front(main, fork)
         us = self.kk % self.n_patches
         vs = self.jj % self.mem
         corr = altcorr.corr_pyramid(self.gmap, (self.fmap1, self.fmap2), coords, us, vs, 3, row_stride=896)
