@@ -875,18 +875,20 @@ extern "C" int64_t dpvo_ba_workspace_bytes(int64_t n_edges, int64_t n_patches_to
   return ba_carve(p, nullptr, n_edges, n_patches_total, n_poses_opt, eff_impl, ppf, n_frames_total) + 256;
 }
 
-extern "C" int dpvo_ba_forward(float* poses, float* patches, const float* intrinsics,
-                               const float* target, const float* weight, const float* lmbda,
-                               const int64_t* ii, const int64_t* jj, const int64_t* kk,
-                               int64_t n_edges, int64_t n_frames_total, int64_t n_patches_total, int32_t P,
-                               int32_t ppf, int32_t t0, int32_t t1, int32_t iterations, int32_t eff_impl,
-                               void* workspace, int64_t workspace_bytes, void* stream) {
+// mode 0: everything; 1: only the part that depends on the edge list and the window (patch bitmap,
+// compaction, per-patch edge lists, cleared accumulators); 2: the iterations, on a workspace mode 1 filled
+static int ba_forward_impl(int mode, float* poses, float* patches, const float* intrinsics,
+                           const float* target, const float* weight, const float* lmbda,
+                           const int64_t* ii, const int64_t* jj, const int64_t* kk,
+                           int64_t n_edges, int64_t n_frames_total, int64_t n_patches_total, int32_t P,
+                           int32_t ppf, int32_t t0, int32_t t1, int32_t iterations, int32_t eff_impl,
+                           void* workspace, int64_t workspace_bytes, void* stream) {
   DPVO_REQUIRE(n_edges >= 0 && n_frames_total > 0 && n_patches_total > 0 && P > 0, "ba_forward: bad sizes");
   DPVO_REQUIRE(t1 >= t0 && t0 >= 0 && t1 <= n_frames_total, "ba_forward: need 0 <= t0 <= t1 <= n_frames (t0=%d t1=%d)", t0, t1);
   DPVO_REQUIRE(P * P <= 64, "ba_forward: patch too large");
   if (n_edges == 0 || iterations <= 0) return 0;
-  DPVO_REQUIRE(poses && patches && intrinsics && target && weight && lmbda && ii && jj && kk && workspace,
-               "ba_forward: null pointer");
+  DPVO_REQUIRE(ii && jj && kk && workspace, "ba_forward: null pointer");
+  DPVO_REQUIRE(mode == 1 || (poses && patches && intrinsics && target && weight && lmbda), "ba_forward: null pointer");
   if (eff_impl) DPVO_REQUIRE(ppf > 0, "ba_forward: eff_impl needs patches-per-frame > 0");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int N = t1 - t0;
@@ -903,14 +905,16 @@ extern "C" int dpvo_ba_forward(float* poses, float* patches, const float* intrin
   DPVO_REQUIRE(eff_impl || N <= 2048, "ba_forward: dense path supports at most 2048 free poses (use eff_impl)");
   DPVO_REQUIRE(N <= 8192, "ba_forward: at most 8192 free poses");
   const int egrid = (int)(ceil_div64(n_edges, 256) < kNumSMs * 8 ? ceil_div64(n_edges, 256) : kNumSMs * 8);
-  cudaMemsetAsync(p.bitmap, 0, reinterpret_cast<char*>(p.meta) + 64 - reinterpret_cast<char*>(p.bitmap), st);
-  ba_prep_kernel<<<egrid, 256, 0, st>>>(p);
-  ba_prefix_kernel<<<1, 1024, 0, st>>>(p);
-  if (check_launch("ba_prefix")) return 1;
-
-  ba_scatter_kernel<<<egrid, 256, 0, st>>>(p);
-  if (eff_impl) {
+  if (mode != 2) {
+    cudaMemsetAsync(p.bitmap, 0, reinterpret_cast<char*>(p.meta) + 64 - reinterpret_cast<char*>(p.bitmap), st);
+    ba_prep_kernel<<<egrid, 256, 0, st>>>(p);
+    ba_prefix_kernel<<<1, 1024, 0, st>>>(p);
+    if (check_launch("ba_prefix")) return 1;
+    ba_scatter_kernel<<<egrid, 256, 0, st>>>(p);
     note_launches(3);
+  }
+  if (eff_impl) {
+    if (mode == 1) return check_launch("ba_prepare");
     return ba_eff_run(p, iterations, st);
   }
   const int n = p.n;
@@ -923,7 +927,11 @@ extern "C" int dpvo_ba_forward(float* poses, float* patches, const float* intrin
   const int bgrid = (int)(ceil_div64(p.Mmax, 8) < kNumSMs * 8 ? ceil_div64(p.Mmax, 8) : kNumSMs * 8);
 
   // accumulators are cleared once here; solve / backsub clear what they consumed for the next iteration
-  ba_zero_kernel<<<zgrid > 0 ? zgrid : 1, 256, 0, st>>>(p);
+  if (mode != 2) {
+    ba_zero_kernel<<<zgrid > 0 ? zgrid : 1, 256, 0, st>>>(p);
+    note_launches(1);
+  }
+  if (mode == 1) return check_launch("ba_prepare");
   for (int it = 0; it < iterations; ++it) {
     ba_launch_assemble(p, st);
     if (N > 0) {
@@ -933,8 +941,35 @@ extern "C" int dpvo_ba_forward(float* poses, float* patches, const float* intrin
     }
     ba_backsub_kernel<<<bgrid, 256, (size_t)(n + 1) * sizeof(float), st>>>(p);
   }
-  note_launches(4 + iterations);
+  note_launches(iterations);
   return check_launch("ba_forward");
+}
+
+extern "C" int dpvo_ba_forward(float* poses, float* patches, const float* intrinsics,
+                               const float* target, const float* weight, const float* lmbda,
+                               const int64_t* ii, const int64_t* jj, const int64_t* kk,
+                               int64_t n_edges, int64_t n_frames_total, int64_t n_patches_total, int32_t P,
+                               int32_t ppf, int32_t t0, int32_t t1, int32_t iterations, int32_t eff_impl,
+                               void* workspace, int64_t workspace_bytes, void* stream) {
+  return ba_forward_impl(0, poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, n_edges, n_frames_total,
+                         n_patches_total, P, ppf, t0, t1, iterations, eff_impl, workspace, workspace_bytes, stream);
+}
+
+extern "C" int dpvo_ba_prepare(const int64_t* ii, const int64_t* jj, const int64_t* kk, int64_t n_edges,
+                               int64_t n_frames_total, int64_t n_patches_total, int32_t P, int32_t ppf, int32_t t0,
+                               int32_t t1, int32_t eff_impl, void* workspace, int64_t workspace_bytes, void* stream) {
+  return ba_forward_impl(1, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, ii, jj, kk, n_edges, n_frames_total,
+                         n_patches_total, P, ppf, t0, t1, 1, eff_impl, workspace, workspace_bytes, stream);
+}
+
+extern "C" int dpvo_ba_forward_prepared(float* poses, float* patches, const float* intrinsics,
+                                        const float* target, const float* weight, const float* lmbda,
+                                        const int64_t* ii, const int64_t* jj, const int64_t* kk,
+                                        int64_t n_edges, int64_t n_frames_total, int64_t n_patches_total, int32_t P,
+                                        int32_t ppf, int32_t t0, int32_t t1, int32_t iterations, int32_t eff_impl,
+                                        void* workspace, int64_t workspace_bytes, void* stream) {
+  return ba_forward_impl(2, poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, n_edges, n_frames_total,
+                         n_patches_total, P, ppf, t0, t1, iterations, eff_impl, workspace, workspace_bytes, stream);
 }
 
 extern "C" int dpvo_reproject(const float* poses, const float* patches, const float* intrinsics,

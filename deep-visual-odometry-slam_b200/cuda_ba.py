@@ -46,7 +46,11 @@ def _i64c(t, name):
     return t.contiguous()
 
 
-def forward(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, PPF, t0, t1, iterations, eff_impl):
+def forward(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, PPF, t0, t1, iterations, eff_impl,
+            prepared=None):
+    """cuda_ba.forward (ba.cpp:32-57).  `prepared`: the workspace returned by `prepare(...)` for the same
+    edge list and window — the edge-list-only part of the call is then skipped (it may have run on
+    another stream while the inputs of this call were still being produced)."""
     require_cuda(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk)
     _f32c(poses, "poses"); _f32c(patches, "patches")
     intrinsics = _f32c(intrinsics, "intrinsics")
@@ -65,12 +69,39 @@ def forward(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, PPF, 
     t0, t1, iterations, PPF = int(t0), int(t1), int(iterations), int(PPF)
     nbytes = lib.dpvo_ba_workspace_bytes(c_i64(E), c_i64(n_patches), c_i32(max(t1 - t0, 0)), c_i32(bool(eff_impl)),
                                          c_i32(PPF), c_i64(n_frames))
-    ws = _workspace(poses.device, nbytes)
-    check(lib.dpvo_ba_forward(ptr(poses), ptr(patches), ptr(intrinsics), ptr(target), ptr(weight), ptr(lmbda),
-                              ptr(ii), ptr(jj), ptr(kk), c_i64(E), c_i64(n_frames), c_i64(n_patches), c_i32(P),
-                              c_i32(PPF), c_i32(t0), c_i32(t1), c_i32(iterations), c_i32(bool(eff_impl)),
-                              ptr(ws), c_i64(ws.numel()), stream_of(poses)), "cuda_ba.forward")
+    if prepared is not None:
+        ws, fn = prepared, lib.dpvo_ba_forward_prepared
+        if ws.numel() < nbytes or ws.device != poses.device:
+            raise RuntimeError("cuda_ba.forward: `prepared` workspace does not belong to this problem")
+    else:
+        ws, fn = _workspace(poses.device, nbytes), lib.dpvo_ba_forward
+    check(fn(ptr(poses), ptr(patches), ptr(intrinsics), ptr(target), ptr(weight), ptr(lmbda),
+             ptr(ii), ptr(jj), ptr(kk), c_i64(E), c_i64(n_frames), c_i64(n_patches), c_i32(P),
+             c_i32(PPF), c_i32(t0), c_i32(t1), c_i32(iterations), c_i32(bool(eff_impl)),
+             ptr(ws), c_i64(ws.numel()), stream_of(poses)), "cuda_ba.forward")
     return []
+
+
+def prepare(ii, jj, kk, n_frames, n_patches, P, PPF, t0, t1, eff_impl=False, workspace=None):
+    """The part of `forward` that only depends on the edge list and the window [t0, t1): the set of
+    patches seen, their compact numbering, the per-patch edge lists and the cleared accumulators.
+    Runs on torch's current stream; returns the workspace to hand to forward(..., prepared=ws).
+    Pass the previous call's workspace back in to reuse the allocation."""
+    require_cuda(ii, jj, kk)
+    ii = _i64c(ii, "ii"); jj = _i64c(jj, "jj"); kk = _i64c(kk, "kk")
+    E = ii.numel()
+    if jj.numel() != E or kk.numel() != E:
+        raise RuntimeError("cuda_ba.prepare: ii/jj/kk lengths differ")
+    t0, t1, PPF = int(t0), int(t1), int(PPF)
+    nbytes = lib.dpvo_ba_workspace_bytes(c_i64(E), c_i64(int(n_patches)), c_i32(max(t1 - t0, 0)), c_i32(bool(eff_impl)),
+                                         c_i32(PPF), c_i64(int(n_frames)))
+    ws = workspace
+    if ws is None or ws.numel() < nbytes or ws.device != ii.device:
+        ws = torch.empty(int(nbytes * 1.25) + 1024, dtype=torch.uint8, device=ii.device)
+    check(lib.dpvo_ba_prepare(ptr(ii), ptr(jj), ptr(kk), c_i64(E), c_i64(int(n_frames)), c_i64(int(n_patches)),
+                              c_i32(int(P)), c_i32(PPF), c_i32(t0), c_i32(t1), c_i32(bool(eff_impl)), ptr(ws),
+                              c_i64(ws.numel()), stream_of(ii)), "cuda_ba.prepare")
+    return ws
 
 
 def neighbors(ii, jj):

@@ -6,6 +6,14 @@ neighbors = cuda_ba.neighbors
 reproject = cuda_ba.reproject
 
 
-def BA(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0, t1, M, iterations, eff_impl=False):
+def BA(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0, t1, M, iterations, eff_impl=False,
+       prepared=None):
     return cuda_ba.forward(poses.data, patches, intrinsics, target, weight, lmbda, ii, jj, kk, M, t0, t1,
-                           iterations, eff_impl)
+                           iterations, eff_impl, prepared=prepared)
+
+
+def BA_prepare(poses, patches, ii, jj, kk, t0, t1, M, eff_impl=False, workspace=None):
+    """Edge-list-only part of BA (see cuda_ba.prepare); hand the result to BA(..., prepared=ws)."""
+    P = patches.shape[-1]
+    return cuda_ba.prepare(ii, jj, kk, poses.numel() // 7, patches.numel() // (3 * P * P), P, M, t0, t1, eff_impl,
+                           workspace=workspace)

@@ -62,6 +62,7 @@ class UpdateHotPath:
         self.host = dict(d=d, c=c)
         self.stage_events = None
         self.overlap_neighbors = True
+        self._ba_ws = None
         self._side = None
         self._side2 = None
         self._side3 = None
@@ -93,9 +94,15 @@ class UpdateHotPath:
     def neighbors(self):
         return fastba.neighbors(self.kk, self.jj)
 
-    def ba(self):
+    def ba(self, prepared=None):
         fastba.BA(self.poses, self.patches, self.intrinsics, self.target, self.weight, self.lmbda,
-                  self.ii, self.jj, self.kk, self.t0, self.t1, self.M, 2, False)
+                  self.ii, self.jj, self.kk, self.t0, self.t1, self.M, 2, False, prepared=prepared)
+
+    def ba_prepare(self):
+        """BA's edge-list-only part (patch set, compaction, per-patch edge lists, cleared accumulators)."""
+        self._ba_ws = fastba.BA_prepare(self.poses, self.patches, self.ii, self.jj, self.kk, self.t0, self.t1, self.M,
+                                        workspace=self._ba_ws)
+        return self._ba_ws
 
     def _front(self, main, fork):
         """Ring write, patchify and reproject only depend on the frame's inputs / the current state, not on
@@ -149,11 +156,12 @@ class UpdateHotPath:
             self._side.wait_event(fork)
             with torch.cuda.stream(self._side):
                 self._nb = self.neighbors()
+                ws = self.ba_prepare()                   # also edge-list-only: rides under the lookup too
                 join.record(self._side)
             coords = self._front(main, fork)
             corr = self.corr(coords)
             main.wait_event(join)
-            self.ba()
+            self.ba(prepared=ws)
             return corr
         timed("ring_write", self.ring_write)
         timed("patchify", self.patchify)
@@ -283,8 +291,14 @@ class UpdateIteration(UpdateHotPath):
         self.poses.copy_(self.poses0)
         self.patches.copy_(self.patches0)
         main = torch.cuda.current_stream(self.device)
-        fork = torch.cuda.Event()
+        fork, join = torch.cuda.Event(), torch.cuda.Event()
         fork.record(main)
+        if self._side is None:
+            self._side = torch.cuda.Stream(self.device)
+        self._side.wait_event(fork)
+        with torch.cuda.stream(self._side):
+            ws = self.ba_prepare()
+            join.record(self._side)
         coords = self._front(main, fork)
         us = self.kk % self.n_patches
         vs = self.jj % self.mem
@@ -294,6 +308,7 @@ class UpdateIteration(UpdateHotPath):
                                                       n_patches=self.n_patch_ids)
         P = coords.shape[-1]
         target = coords[..., P // 2, P // 2] + delta       # dpvo.py:341
+        main.wait_event(join)
         fastba.BA(self.poses, self.patches, self.intrinsics, target.contiguous(), weight, self.lmbda,
-                  self.ii, self.jj, self.kk, self.t0, self.t1, self.M, 2, False)
+                  self.ii, self.jj, self.kk, self.t0, self.t1, self.M, 2, False, prepared=ws)
         return delta, weight

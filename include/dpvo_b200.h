@@ -118,6 +118,18 @@ int dpvo_ba_forward(float* poses, float* patches, const float* intrinsics,
                     int64_t n_edges, int64_t n_frames_total, int64_t n_patches_total, int32_t P,
                     int32_t ppf, int32_t t0, int32_t t1, int32_t iterations, int32_t eff_impl,
                     void* workspace, int64_t workspace_bytes, void* stream);
+/* The same call in two parts.  dpvo_ba_prepare does what only depends on the edge list and the window
+ * (set of patches seen, compact numbering, per-patch edge lists, cleared accumulators) and may run ahead
+ * on another stream; dpvo_ba_forward_prepared then runs the iterations on the SAME workspace. */
+int dpvo_ba_prepare(const int64_t* ii, const int64_t* jj, const int64_t* kk, int64_t n_edges,
+                    int64_t n_frames_total, int64_t n_patches_total, int32_t P, int32_t ppf, int32_t t0, int32_t t1,
+                    int32_t eff_impl, void* workspace, int64_t workspace_bytes, void* stream);
+int dpvo_ba_forward_prepared(float* poses, float* patches, const float* intrinsics,
+                    const float* target, const float* weight, const float* lmbda,
+                    const int64_t* ii, const int64_t* jj, const int64_t* kk,
+                    int64_t n_edges, int64_t n_frames_total, int64_t n_patches_total, int32_t P,
+                    int32_t ppf, int32_t t0, int32_t t1, int32_t iterations, int32_t eff_impl,
+                    void* workspace, int64_t workspace_bytes, void* stream);
 
 /* Temporal neighbours — replaces cuda_ba.neighbors (fastba/ba.cpp:59-97), entirely on the
  * device (the reference round-trips through the host).  For edge e: ix[e] / jx[e] = index of

@@ -339,3 +339,30 @@ def test_blocked_cholesky_solve(n):
     S2 = S.copy(); S2[n // 2, n // 2] = -1.0
     x2, info2 = pkg.cuda_ba.cholesky_solve(_dev(S2), _dev(y))
     assert int(info2.item()) == 1 and float(x2.abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("eff", [False, True])
+def test_ba_prepare_then_forward_matches_single_call(eff):
+    """dpvo_ba_prepare on a side stream + dpvo_ba_forward_prepared on the main stream (what the frame graph
+    does) against the single call: same kernels on the same workspace, so within atomics-order noise."""
+    pkg = load_pkg(); synth = load_pkg("synth")
+    d = _with_loop_edges(synth, 30, 24, 5) if eff else synth.ba_inputs(16, seed=5, M=48)
+    t0, t1 = (8, 30) if eff else (6, 16)
+    one = _run_ours(pkg, d, t0, t1, eff=eff)
+    poses = _dev(d["poses"])[None].clone(); patches = _dev(d["patches"])[None].clone()
+    ii, jj, kk = _dev(d["ii"]), _dev(d["jj"]), _dev(d["kk"])
+    lm = torch.tensor([1e-4], device="cuda")
+    side = torch.cuda.Stream()
+    done = torch.cuda.Event()
+    with torch.cuda.stream(side):
+        ws = pkg.fastba.BA_prepare(poses, patches, ii, jj, kk, t0, t1, d["M"], eff_impl=eff)
+        done.record(side)
+    torch.cuda.current_stream().wait_event(done)
+    for _ in range(2):                                   # the prepared workspace is consumed: prepare again per call
+        poses.copy_(_dev(d["poses"])[None]); patches.copy_(_dev(d["patches"])[None])
+        pkg.fastba.BA(poses, patches, _dev(d["intrinsics"])[None], _dev(d["target"])[None], _dev(d["weight"])[None], lm,
+                      ii, jj, kk, t0, t1, d["M"], 2, eff, prepared=ws)
+        torch.cuda.synchronize()
+        got = poses[0].cpu().numpy(), patches[0].cpu().numpy()
+        assert _rel(got[0], one[0]) < 2e-5 and _rel(got[1][:, 2], one[1][:, 2]) < 2e-5
+        ws = pkg.fastba.BA_prepare(poses, patches, ii, jj, kk, t0, t1, d["M"], eff_impl=eff, workspace=ws)
