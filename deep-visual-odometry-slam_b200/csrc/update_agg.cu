@@ -94,8 +94,8 @@ __device__ __forceinline__ void store4(__half* p, const float (&f)[4]) {
   *reinterpret_cast<uint2*>(p) = u;
 }
 
-constexpr int kAggSlices = 4;
-
+// kAggSlices: how many ways a group's edges are dealt out inside its CTA (more for few large groups)
+template <int kAggSlices>
 __global__ void __launch_bounds__(96 * kAggSlices)
 softagg_kernel(const __half* __restrict__ F, const __half* __restrict__ Gm, const int* __restrict__ offs,
                const int* __restrict__ perm, __half* __restrict__ Y) {
@@ -332,8 +332,14 @@ extern "C" int dpvo_softagg_f16(const void* f, const void* g, const int64_t* ids
   if (!prepared && dpvo_softagg_prepare(ids, n_edges, group_bound, workspace, workspace_bytes, stream)) return 1;
   const int G = (int)group_bound;
   const AggWs w = carve_agg(workspace, G);
-  softagg_kernel<<<G, 96 * kAggSlices, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __half*>(f), static_cast<const __half*>(g), w.offs, w.perm, static_cast<__half*>(y));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const __half* fp = static_cast<const __half*>(f);
+  const __half* gp = static_cast<const __half*>(g);
+  __half* yp = static_cast<__half*>(y);
+  const int64_t avg = n_edges / group_bound;          // lower bound on the mean group size
+  if (avg >= 24) softagg_kernel<8><<<G, 96 * 8, 0, st>>>(fp, gp, w.offs, w.perm, yp);
+  else if (avg >= 6) softagg_kernel<4><<<G, 96 * 4, 0, st>>>(fp, gp, w.offs, w.perm, yp);
+  else softagg_kernel<2><<<G, 96 * 2, 0, st>>>(fp, gp, w.offs, w.perm, yp);
   note_launches(1);
   return check_launch("softagg");
 }
