@@ -88,7 +88,16 @@ struct LevelBox {
   bool interior;   // ... and the box lies inside the feature map
 };
 
-template <int NLEV>
+// 32-byte read-only global load (sm_100: one LDG.256 per lane; four lanes cover a pixel's 128-byte line half)
+__device__ __forceinline__ void ldg256(const void* p, uint32_t* w) {
+  asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+               : "l"(p));
+}
+
+// WIDE: feature maps 32-byte aligned -> each lane reads 16 consecutive channels per load (two LDG.256 per
+// tile, every 128-byte L1 wavefront fully used) instead of 8 (four LDG.128, half-used wavefronts).
+template <int NLEV, bool WIDE>
 __global__ void __launch_bounds__(kWarps * 32, 4)
 corr_fwd_mma_f16_kernel(const __grid_constant__ CorrParams prm) {
   constexpr int R = 3, P = 3;
@@ -179,7 +188,7 @@ corr_fwd_mma_f16_kernel(const __grid_constant__ CorrParams prm) {
       const int sc = (int)prm.g_sc;
 #pragma unroll
       for (int s = 0; s < 8; ++s) {
-        const int c0 = 32 * (s >> 1) + 8 * t + 4 * (s & 1);
+        const int c0 = WIDE ? 64 * (s >> 2) + 16 * t + 4 * (s & 3) : 32 * (s >> 1) + 8 * t + 4 * (s & 1);
         uint32_t lo01 = 0, lo23 = 0, hi01 = 0, hi23 = 0;
         if (off_lo >= 0) {
           lo01 = (uint32_t)sp[off_lo + (c0 + 0) * sc] | ((uint32_t)sp[off_lo + (c0 + 1) * sc] << 16);
@@ -207,41 +216,46 @@ corr_fwd_mma_f16_kernel(const __grid_constant__ CorrParams prm) {
         const int sx = (int)L.sx, sy = (int)L.sy;
         // this lane's pixel walks the box row-major in steps of 8 (bw >= 8: at most one wrap per step)
         int uidx = g, ux = g, py = y0;
-        const __half* ptr = fmv + (int64_t)y0 * sy + (int64_t)(x0 + g) * sx + 8 * t;
+        const __half* ptr = fmv + (int64_t)y0 * sy + (int64_t)(x0 + g) * sx + (WIDE ? 16 : 8) * t;
         const int step = 8 * sx, wrap = sy - bw * sx;
 
-        auto load_tile = [&](uint4 (&q)[4]) {
+        auto load_tile = [&](uint32_t (&q)[16]) {
           bool ok = v_ok && (uidx < nU);
           if (!interior) {
             const int px = x0 + ux;
             ok = ok && (py >= 0) && (py < L.H2) && (px >= 0) && (px < L.W2);
           }
           if (ok) {
+            if (WIDE) {
+              ldg256(ptr, q);
+              ldg256(ptr + 64, q + 8);
+            } else {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) q[j] = ldg128(ptr + 32 * j);
+              for (int j = 0; j < 4; ++j) {
+                const uint4 v4 = ldg128(ptr + 32 * j);
+                q[4 * j] = v4.x; q[4 * j + 1] = v4.y; q[4 * j + 2] = v4.z; q[4 * j + 3] = v4.w;
+              }
+            }
           } else {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) q[j] = make_uint4(0, 0, 0, 0);
+            for (int j = 0; j < 16; ++j) q[j] = 0u;
           }
           uidx += 8;
           ux += 8;
           ptr += step;
           if (ux >= bw) { ux -= bw; ++py; ptr += wrap; }
         };
-        auto compute_tile = [&](const uint4 (&q)[4], int tile) {
+        auto compute_tile = [&](const uint32_t (&q)[16], int tile) {
           float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            mma_16816(acc, a[2 * j], q[j].x, q[j].y);
-            mma_16816(acc, a[2 * j + 1], q[j].z, q[j].w);
-          }
+          for (int j = 0; j < 8; ++j) mma_16816(acc, a[j], q[2 * j], q[2 * j + 1]);
           const int col = tile * 8 + 2 * t;
           *reinterpret_cast<__half2*>(&s_raw[wid][l][g][col]) = __floats2half2_rn(acc[0], acc[1]);   // g < 8 < PP
           if (g + 8 < PP)
             *reinterpret_cast<__half2*>(&s_raw[wid][l][g + 8][col]) = __floats2half2_rn(acc[2], acc[3]);
         };
 
-        uint4 q0[4], q1[4], q2[4];
+        uint32_t q0[16], q1[16], q2[16];
         load_tile(q0);
         load_tile(q1);
         for (int tile = 0; tile < ntile; tile += 3) {
@@ -524,10 +538,19 @@ extern "C" int dpvo_corr_forward(dpvo_dtype dtype,
     const int64_t nedge = (int64_t)B * M;
     int64_t want = ceil_div64(nedge, kWarps);
     int grid = (int)(want < (int64_t)kNumSMs * 64 ? want : (int64_t)kNumSMs * 64);
-    if (nlev == 1)
-      corr_fwd_mma_f16_kernel<1><<<grid, kWarps * 32, 0, st>>>(prm);
-    else
-      corr_fwd_mma_f16_kernel<2><<<grid, kWarps * 32, 0, st>>>(prm);
+    bool wide = getenv("DPVO_CORR_NARROW") == nullptr;
+    for (int l = 0; l < nlev && wide; ++l) {
+      const CorrLevelDev& L = prm.lev[l];
+      wide = ((reinterpret_cast<uintptr_t>(L.fmap) & 31) == 0) && (L.sx % 16 == 0) && (L.sy % 16 == 0) &&
+             (L.sn % 16 == 0) && (L.sb % 16 == 0);
+    }
+    if (nlev == 1) {
+      if (wide) corr_fwd_mma_f16_kernel<1, true><<<grid, kWarps * 32, 0, st>>>(prm);
+      else corr_fwd_mma_f16_kernel<1, false><<<grid, kWarps * 32, 0, st>>>(prm);
+    } else {
+      if (wide) corr_fwd_mma_f16_kernel<2, true><<<grid, kWarps * 32, 0, st>>>(prm);
+      else corr_fwd_mma_f16_kernel<2, false><<<grid, kWarps * 32, 0, st>>>(prm);
+    }
     note_launches(1);
     return check_launch("corr_fwd_mma_f16");
   }
