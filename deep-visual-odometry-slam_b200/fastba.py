@@ -8,8 +8,8 @@ reproject = cuda_ba.reproject
 
 def BA(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0, t1, M, iterations, eff_impl=False,
        prepared=None):
-    return cuda_ba.forward(poses.data, patches, intrinsics, target, weight, lmbda, ii, jj, kk, M, t0, t1,
-                           iterations, eff_impl, prepared=prepared)
+    args = (poses.data, patches, intrinsics, target, weight, lmbda, ii, jj, kk, M, t0, t1, iterations, eff_impl)
+    return cuda_ba.forward(*args) if prepared is None else cuda_ba.forward(*args, prepared=prepared)
 
 
 def BA_prepare(poses, patches, ii, jj, kk, t0, t1, M, eff_impl=False, workspace=None):

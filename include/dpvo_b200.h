@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define DPVO_B200_ABI_VERSION 2
+#define DPVO_B200_ABI_VERSION 3
 
 typedef enum { DPVO_F16 = 0, DPVO_F32 = 1, DPVO_F64 = 2 } dpvo_dtype;
 
@@ -313,6 +313,58 @@ int dpvo_lie_as_matrix(int32_t group, dpvo_dtype dt, const void* X, void* T4x4 /
 int dpvo_lie_projector(int32_t group, dpvo_dtype dt, const void* X, void* P /*[n,N,N]*/, int64_t n, void* stream);
 int dpvo_lie_jinv(int32_t group, dpvo_dtype dt, const void* X, const void* a /*[n,K]*/, void* b /*[n,K]*/, int64_t n,
                   void* stream);
+
+/* ---- patch-graph edge bookkeeping on the device -------------------------------
+ * Replaces the torch.cat / boolean-mask edits of dpvo.py:215-239 (append_factors, remove_factors),
+ * :262-310 (keyframe) and :362-375 (__edges_forw/__edges_back), and the numba reduce_edges of
+ * loop_closure/optim_utils.py:27-64.  The edge list lives in caller-owned fixed-capacity device arrays;
+ * the live count is a device scalar, so none of these calls synchronises.  `bound` is any host-known upper
+ * bound on the live count (<= capacity) and only sizes the launch.  `info` is a caller-zeroed device flag:
+ * 1 = a capacity was exceeded (extra edges dropped), 2 = a patch index outside ix. */
+typedef struct dpvo_edge_store {
+  int64_t* ii;       /* [capacity] source frame  */
+  int64_t* jj;       /* [capacity] target frame  */
+  int64_t* kk;       /* [capacity] patch index   */
+  void* net;         /* fp16 hidden state rows [capacity, net_ld], or NULL */
+  int64_t net_ld;    /* row stride in elements (even) */
+  int32_t net_dim;   /* columns that are live (even; 384 in DPVO) */
+  int32_t reserved;
+  float* target;     /* [capacity, 2] or NULL */
+  float* weight;     /* [capacity, 2] or NULL */
+  int64_t* count;    /* device scalar: live edges */
+  int64_t capacity;
+} dpvo_edge_store;
+
+/* append_factors(ii=kk_new, jj=jj_new): kk += kk_new, jj += jj_new, ii += ix[kk_new], zero net/target/weight rows */
+int dpvo_edges_append(const dpvo_edge_store* store, const int64_t* ix, int64_t n_ix, const int64_t* kk_new,
+                      const int64_t* jj_new, int64_t n_new, int32_t* info, void* stream);
+/* append_factors(*flatmeshgrid(arange(kk0,kk1), arange(jj0,jj1), indexing='ij')) without materialising the grid */
+int dpvo_edges_append_grid(const dpvo_edge_store* store, const int64_t* ix, int64_t n_ix, int64_t kk0, int64_t kk1,
+                           int64_t jj0, int64_t jj1, int32_t* info, void* stream);
+int64_t dpvo_edges_workspace_bytes(int64_t capacity, int32_t net_dim);
+/* remove_factors(m, store): edges with mask != 0 leave the list (order of the rest kept); with `inactive`
+ * non-NULL (store=True) their ii/jj/kk/target/weight are appended, in order, to that list. */
+int dpvo_edges_remove(const dpvo_edge_store* store, const uint8_t* mask, const dpvo_edge_store* inactive,
+                      int64_t bound, int32_t* info, void* workspace, int64_t workspace_bytes, void* stream);
+/* keyframe(): mask = (ii == k) | (jj == k)  (dpvo.py:280) */
+int dpvo_edges_mask_keyframe(const dpvo_edge_store* store, int64_t k, uint8_t* mask, int64_t bound, void* stream);
+/* keyframe(): mask = ix[kk] < n - removal_window, minus loop-closure edges (jj - ii > 30 and
+ * jj > n - optimization_window) when loop_closure != 0  (dpvo.py:304-309) */
+int dpvo_edges_mask_window(const dpvo_edge_store* store, const int64_t* ix, int64_t n_ix, int64_t n,
+                           int64_t removal_window, int32_t loop_closure, int64_t optimization_window, uint8_t* mask,
+                           int64_t bound, void* stream);
+/* keyframe(): kk[ii > k] -= M; ii[ii > k] -= 1; jj[jj > k] -= 1  (dpvo.py:283-285) */
+int dpvo_edges_renumber(const dpvo_edge_store* store, int64_t k, int64_t patches_per_frame, int64_t bound,
+                        void* stream);
+/* keyframe(): for i in range(k, n-1): buf[i % mod] = buf[(i+1) % mod] over slots of slot_bytes (dpvo.py:287-297) */
+int dpvo_frames_shift(void* buf, int64_t slot_bytes, int32_t mod, int32_t k, int32_t n, void* stream);
+/* reduce_edges(flow_mag, ii, jj, max_num_edges, nms): greedy pick in ascending flow magnitude (ties: lower
+ * index), skipping j - i < 30 and magnitude >= 1000, suppressing source frames i-nms..i+nms at the same
+ * target.  ni / nj: any bounds > max(ii) / max(jj).  out_edges [max_num_edges, 2], out_count device scalar. */
+int64_t dpvo_edges_reduce_workspace_bytes(int64_t n, int64_t ni, int64_t nj);
+int dpvo_edges_reduce(const float* flow_mag, const int64_t* ii, const int64_t* jj, int64_t n, int64_t ni, int64_t nj,
+                      int32_t max_num_edges, int32_t nms, int64_t* out_edges, int64_t* out_count, void* workspace,
+                      int64_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

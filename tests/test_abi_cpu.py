@@ -147,3 +147,27 @@ def test_update_operator_validation_without_gpu():
         upd.Update(bad, device="cuda")
     with pytest.raises(RuntimeError):
         ops.linear384(torch.zeros(4, 384, dtype=torch.float16), torch.zeros(384, 384, dtype=torch.float16))
+
+
+def test_edge_bookkeeping_validation_without_gpu():
+    """N4 host side: CPU devices / tensors are refused, workspace queries are host-only, bad stores are errors."""
+    pg = load_pkg("patchgraph")
+    lib = load_pkg()._lib.lib
+    with pytest.raises(RuntimeError):
+        pg.EdgeList(16, "cpu")
+    with pytest.raises(RuntimeError):
+        pg.PatchGraphEdges(torch.zeros(8, dtype=torch.int64), 4, 16)
+    with pytest.raises(RuntimeError):
+        pg.frames_shift(torch.zeros(4, 4), 0, 3)
+    lib.dpvo_edges_workspace_bytes.restype = ctypes.c_int64
+    f = lambda cap, dim: lib.dpvo_edges_workspace_bytes(ctypes.c_int64(cap), ctypes.c_int32(dim))
+    assert 0 < f(0, 0) < f(1000, 0) < f(1000, 384) < f(60000, 384)
+    assert f(-1, 0) < 0
+    lib.dpvo_last_error.restype = ctypes.c_char_p
+    null = ctypes.c_void_p(0)
+    rc = lib.dpvo_edges_append_grid(null, null, ctypes.c_int64(0), ctypes.c_int64(0), ctypes.c_int64(4), ctypes.c_int64(0),
+                                    ctypes.c_int64(2), null, null)
+    assert rc != 0 and b"edge store" in lib.dpvo_last_error()
+    rc = lib.dpvo_frames_shift(null, ctypes.c_int64(64), ctypes.c_int32(0), ctypes.c_int32(0), ctypes.c_int32(4), null)
+    assert rc != 0
+    assert lib.dpvo_frames_shift(null, ctypes.c_int64(64), ctypes.c_int32(8), ctypes.c_int32(3), ctypes.c_int32(4), null) == 0

@@ -316,3 +316,56 @@ def test_pgo_oracle_vs_reference():
         Ji, Jj, ii, jj, res = m.pgo_case(n, loops, seed)
         got = pgo_oracle.solve_system(Ji, Jj, ii, jj, res, m.EP, m.LM, freen)
         np.testing.assert_allclose(got, g[name], rtol=2e-4, atol=2e-6, err_msg=name)
+
+
+# ---------------------------------------------------------------- N4: patch-graph edge bookkeeping
+class _OracleEdges:
+    def __init__(self, m, seed):
+        from oracle import edges_oracle as eo
+        self.eo, self.m = eo, m
+        N, M = m.CFG["BUFFER_SIZE"], m.CFG["PATCHES_PER_FRAME"]
+        self.e = eo.Edges(np.repeat(np.arange(N), M), M, m.DIM)
+        self.buf = m.initial_buffers(seed)
+        self.r = m.CFG["PATCH_LIFETIME"]
+
+    def forw(self, n): self.e.append_factors(*self.eo.edges_forw(n, self.e.M, self.r))
+    def back(self, n): self.e.append_factors(*self.eo.edges_back(n, self.e.M, self.r))
+    def count(self): return self.e.ii.size
+    def set_rows(self, net, target, weight): self.e.net, self.e.target, self.e.weight = net, target, weight
+    def remove_frame(self, k): self.e.remove_frame(k)
+    def remove_old(self, *a): self.e.remove_old(*a)
+
+    def shift(self, k, n):
+        b, m = self.buf, self.m
+        for key in ("tstamps_", "colors_", "poses_", "patches_", "intrinsics_"):
+            self.eo.frames_shift(b[key], k, n)
+        self.eo.frames_shift(b["imap_"], k, n, m.PMEM)
+        self.eo.frames_shift(b["gmap_"], k, n, m.PMEM)
+        self.eo.frames_shift(b["fmap1_"][0], k, n, m.MEM)
+        self.eo.frames_shift(b["fmap2_"][0], k, n, m.MEM)
+
+    def snapshot(self):
+        return {k: getattr(self.e, k) for k in ("ii", "jj", "kk", "ii_inac", "jj_inac", "kk_inac")}
+
+    def final(self):
+        out = {k: getattr(self.e, k) for k in ("net", "target", "weight", "target_inac", "weight_inac")}
+        out.update(self.buf)
+        return out
+
+
+@pytest.mark.parametrize("name,seed,lc", [("plain", 0, False), ("loop", 1, True)])
+def test_edges_oracle_vs_reference(name, seed, lc):
+    """oracle/edges_oracle.py against the reference's own append_factors / remove_factors / keyframe run on CPU."""
+    import edges_replay
+    m = edges_replay.golden_module()
+    assert edges_replay.replay(_OracleEdges(m, seed), name, seed, lc) == 14
+
+
+def test_reduce_edges_oracle_vs_reference():
+    import edges_replay
+    from oracle import edges_oracle as eo
+    m, g = edges_replay.golden_module(), edges_replay.golden()
+    for i, c in enumerate(m.REDUCE_CASES):
+        mag, ii, jj = m.reduce_case(c)
+        got = eo.reduce_edges(mag, ii, jj, c["max_num_edges"], c["nms"])
+        assert np.array_equal(got, g[f"reduce{i}"]), i
