@@ -366,6 +366,17 @@ int dpvo_edges_reduce(const float* flow_mag, const int64_t* ii, const int64_t* j
                       int32_t max_num_edges, int32_t nms, int64_t* out_edges, int64_t* out_count, void* workspace,
                       int64_t workspace_bytes, void* stream);
 
+/* ---- DPViewer's CUDA helpers, headless: plain device buffers, no window / GL interop ----
+ * poseToMatrix (modules/DPViewer/dpviewer/viewer_cuda.cu:221-277): mat4x4[n,4,4] = matrix of the INVERSE of each
+ * pose (tx ty tz qx qy qz qw). */
+int dpvo_viewer_pose_to_matrix(const float* poses /*[n,7]*/, float* mat4x4 /*[n,4,4]*/, int64_t n, void* stream);
+/* iproj_kernel (viewer_cuda.cu:56-164): back-projects frame `index` (disps [N,ht,wd], intrinsics [N,4] at 1/8
+ * resolution, images u8 [N,3,ht,wd] BGR) into points [ht*wd,3] / colors [ht*wd,3] (RGB) and counts, per pixel, the
+ * other frames whose disparity agrees within thresh percent (count -100 marks a depth edge). Border pixels: zeros. */
+int dpvo_viewer_iproj(int32_t index, int32_t n_frames, float thresh, const uint8_t* images, const float* poses,
+                      const float* disps, const float* intrinsics, int32_t ht, int32_t wd, float* points,
+                      uint8_t* colors, float* count, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

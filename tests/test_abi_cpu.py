@@ -171,3 +171,17 @@ def test_edge_bookkeeping_validation_without_gpu():
     rc = lib.dpvo_frames_shift(null, ctypes.c_int64(64), ctypes.c_int32(0), ctypes.c_int32(0), ctypes.c_int32(4), null)
     assert rc != 0
     assert lib.dpvo_frames_shift(null, ctypes.c_int64(64), ctypes.c_int32(8), ctypes.c_int32(3), ctypes.c_int32(4), null) == 0
+
+
+def test_viewer_helpers_validation_without_gpu():
+    v = load_pkg("viewer_ops")
+    with pytest.raises(RuntimeError):
+        v.poseToMatrix(torch.zeros(3, 7))
+    lib = load_pkg()._lib.lib
+    lib.dpvo_last_error.restype = ctypes.c_char_p
+    null = ctypes.c_void_p(0)
+    assert lib.dpvo_viewer_pose_to_matrix(null, null, ctypes.c_int64(0), null) == 0
+    assert lib.dpvo_viewer_pose_to_matrix(null, null, ctypes.c_int64(-1), null) != 0
+    rc = lib.dpvo_viewer_iproj(ctypes.c_int32(3), ctypes.c_int32(2), ctypes.c_float(1.0), null, null, null, null,
+                               ctypes.c_int32(4), ctypes.c_int32(4), null, null, null, null)
+    assert rc != 0 and b"index" in lib.dpvo_last_error()

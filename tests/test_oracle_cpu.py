@@ -369,3 +369,21 @@ def test_reduce_edges_oracle_vs_reference():
         mag, ii, jj = m.reduce_case(c)
         got = eo.reduce_edges(mag, ii, jj, c["max_num_edges"], c["nms"])
         assert np.array_equal(got, g[f"reduce{i}"]), i
+
+
+def test_viewer_oracle_pose_to_matrix_vs_lietorch_oracle():
+    """N5: oracle/viewer_oracle.pose_to_matrix (unpinned restatement) agrees with the pinned lietorch oracle:
+    the 4x4 matrix of the inverse pose."""
+    from oracle import viewer_oracle as vo, lietorch_oracle as lo
+    rng = np.random.default_rng(11)
+    q = rng.standard_normal((64, 4)); q /= np.linalg.norm(q, axis=1, keepdims=True)
+    p = np.concatenate([rng.standard_normal((64, 3)), q], 1).astype(np.float32)
+    m = vo.pose_to_matrix(p)
+    assert m.shape == (64, 4, 4) and m.dtype == np.float32
+    assert np.abs(m - lo.matrix(lo.inv(p.astype(np.float64)))).max() < 1e-5
+    # identical frames under identity poses confirm every inner pixel once per other frame
+    N, ht, wd = 3, 6, 7
+    poses = np.zeros((N, 7), np.float32); poses[:, 6] = 1
+    pts, col, cnt, _, inner = vo.iproj(0, N, 5.0, np.zeros((N, 3, ht, wd), np.uint8), poses,
+                                       np.full((N, ht, wd), 0.3, np.float32), np.tile(np.float32([[1, 1, 0.4, 0.3]]), (N, 1)))
+    assert np.all(cnt[inner] == N - 1) and np.all(cnt[~inner] == 0)

@@ -1,0 +1,88 @@
+"""GPU tests for the headless DPViewer helpers (N5) through the C ABI (dpvo_viewer_pose_to_matrix,
+dpvo_viewer_iproj) against oracle/viewer_oracle.py (numpy float32 restatement; parity UNPINNED — see its header).
+Tolerances: pose_to_matrix 2e-6 absolute (unit quaternions, products of O(1) terms; the device contracts
+a*b+c into FMAs); iproj points 1e-5 relative; colours exact; the per-pixel counts exact wherever no comparison
+of the kernel sits within 1e-3 of its decision boundary (those pixels are skipped and must stay below 5 %)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_pkg
+
+pytestmark = pytest.mark.gpu
+
+
+def _poses(rng, n, spread):
+    q = rng.standard_normal((n, 4))
+    q[:, :3] *= spread
+    q[:, 3] = 1.0
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    return np.concatenate([rng.standard_normal((n, 3)) * spread, q], 1).astype(np.float32)
+
+
+@pytest.mark.parametrize("n", [1, 7, 1000])
+def test_pose_to_matrix(n):
+    from oracle import viewer_oracle as vo, lietorch_oracle as lo
+    v = load_pkg("viewer_ops")
+    p = _poses(np.random.default_rng(n), n, 1.0)
+    got = v.poseToMatrix(torch.from_numpy(p).cuda()).cpu().numpy()
+    assert np.abs(got - vo.pose_to_matrix(p)).max() < 2e-6 * max(1.0, np.abs(p[:, :3]).max())
+    # the oracle itself against the pinned lietorch oracle: matrix of the inverse pose
+    ref = lo.matrix(lo.inv(p.astype(np.float64)))
+    assert np.abs(vo.pose_to_matrix(p) - ref).max() < 1e-5
+    assert v.poseToMatrix(torch.zeros((0, 7), device="cuda")).shape == (0, 4, 4)
+    with pytest.raises(RuntimeError):
+        v.poseToMatrix(torch.zeros((3, 7)))
+
+
+@pytest.mark.parametrize("N,ht,wd,index,thresh", [(5, 30, 40, 2, 5.0), (70, 17, 23, 69, 2.0), (1, 8, 8, 0, 1.0),
+                                                  (3, 60, 80, 0, 0.5)])
+def test_iproj(N, ht, wd, index, thresh):
+    from oracle import viewer_oracle as vo
+    v = load_pkg("viewer_ops")
+    rng = np.random.default_rng(N * 100 + ht)
+    images = rng.integers(0, 255, (N, 3, ht, wd)).astype(np.uint8)
+    # smooth disparity with a few depth edges; small camera motion so that most pixels reproject inside
+    yy, xx = np.meshgrid(np.arange(ht), np.arange(wd), indexing="ij")
+    disps = np.stack([0.25 + 0.002 * np.sin(0.3 * xx + f) + 0.002 * np.cos(0.2 * yy) + 0.08 * (xx > wd * 0.6)
+                      for f in range(N)]).astype(np.float32)
+    disps += (rng.random(disps.shape) * 0.004).astype(np.float32)
+    poses = _poses(rng, N, 0.02)
+    intr = np.tile(np.array([[wd / 8.0, wd / 8.0, wd / 16.0, ht / 16.0]], np.float32), (N, 1))
+    dev = lambda x: torch.from_numpy(x).cuda()
+    pts, col, cnt = v.iproj(index, N, thresh, dev(images), dev(poses), dev(disps), dev(intr))
+    o_pts, o_col, o_cnt, margin, inner = vo.iproj(index, N, thresh, images, poses, disps, intr)
+    pts, col, cnt = pts.cpu().numpy(), col.cpu().numpy(), cnt.cpu().numpy()
+    assert np.array_equal(col, o_col)
+    assert np.allclose(pts, o_pts, rtol=1e-5, atol=1e-6)
+    assert np.all(cnt[~inner] == 0) and np.all(pts[~inner] == 0)
+    safe = margin > 1e-3
+    assert safe.mean() > 0.95 or N == 1          # 69 other frames = 69 chances per pixel to sit near a boundary
+    assert np.array_equal(cnt[safe], o_cnt[safe])
+    assert len(np.unique(o_cnt)) > (1 if N > 1 else 0)          # the case exercises hits, misses and depth edges
+
+
+def test_backproject_and_filter_selection_and_errors():
+    v = load_pkg("viewer_ops")
+    rng = np.random.default_rng(3)
+    N, ht, wd = 4, 20, 24
+    images = torch.from_numpy(rng.integers(0, 255, (N, 3, ht, wd)).astype(np.uint8)).cuda()
+    disps = torch.full((N, ht, wd), 0.3, device="cuda")
+    poses = torch.zeros((N, 7), device="cuda"); poses[:, 6] = 1
+    intr = torch.tensor([[3.0, 3.0, 1.5, 1.25]], device="cuda").repeat(N, 1)
+    masks = torch.zeros((N, ht, wd), device="cuda"); masks[:, :, wd // 2:] = 1.0
+    pts_all, col_all, cnt = v.iproj(1, N, 5.0, images, poses, disps, intr)
+    # identical frames, identity poses: every inner pixel is confirmed by the 3 other frames
+    inner = ((torch.arange(ht * wd, device="cuda") // wd < ht - 1) & (torch.arange(ht * wd, device="cuda") % wd < wd - 1))
+    assert torch.all(cnt[inner] == 3) and torch.all(cnt[~inner] == 0)
+    n_fg, p_fg, c_fg = v.backproject_and_filter(1, N, 5.0, True, False, images, poses, disps, masks, intr)
+    n_bg, p_bg, c_bg = v.backproject_and_filter(1, N, 5.0, False, True, images, poses, disps, masks, intr)
+    n_both, p_both, _ = v.backproject_and_filter(1, N, 5.0, True, True, images, poses, disps, masks, intr)
+    m = masks[1].reshape(-1)
+    assert n_fg == int((m < 0.5).sum()) and n_bg == int(((m > 0.5) & inner).sum()) and n_both == n_fg + n_bg
+    assert torch.equal(p_both, torch.cat([p_fg, p_bg])) and c_fg.dtype == torch.uint8 and p_fg.shape[1] == 3
+    assert v.backproject_and_filter(1, N, 5.0, False, False, images, poses, disps, masks, intr)[0] == 0
+    with pytest.raises(RuntimeError):
+        v.iproj(4, N, 5.0, images, poses, disps, intr)
+    with pytest.raises(RuntimeError):
+        v.iproj(0, N, 5.0, images.cpu(), poses, disps, intr)

@@ -1,0 +1,1 @@
+timeout 900 python -m pytest tests/test_viewer_gpu.py -m gpu -x -q 2>&1 | tail -25
