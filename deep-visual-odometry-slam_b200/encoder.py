@@ -1,0 +1,127 @@
+"""Per-frame feature encoders on the device.
+
+`BasicEncoder4` mirrors methods/dpvo/dpvo/extractor.py:200-264 as `Patchifier` uses it (net.py:95-96): the
+reference `state_dict` keys, the reference call (`images [b, n, 3, H, W]` float32 in, feature map out), inference
+only.  Every layer is a kernel of libdpvo_b200.so (csrc/encoder.cu); activations are channels-last fp16 and the
+result is returned as a `[b, n, C, H/4, W/4]` VIEW of the channels-last buffer (`.nhwc` holds the buffer itself, which
+is what the feature ring stores).  No CPU path.
+"""
+import torch
+
+from ._lib import lib, ptr, stream_of, check, require_cuda, c_i32, c_i64, c_f32, c_p
+
+_EPS = 1e-5      # nn.InstanceNorm2d default
+
+
+def _conv(x, w, b, n, H, W, cin, cout, k, s, scale, stats):
+    pad = k // 2
+    OH, OW = (H + 2 * pad - k) // s + 1, (W + 2 * pad - k) // s + 1
+    out = torch.empty((n, OH, OW, cout), dtype=torch.float16, device=x.device)
+    check(lib.dpvo_encoder_conv(ptr(x), ptr(w), ptr(b), c_i32(n), c_i32(H), c_i32(W), c_i32(cin), c_i32(cout), c_i32(k),
+                                c_i32(s), c_f32(scale), ptr(out), ptr(stats) if stats is not None else c_p(0),
+                                stream_of(x)), "encoder.conv")
+    return out
+
+
+def _norm_act(raw, stats, skip=None, skip_stats=None):
+    n, H, W, C = raw.shape
+    out = torch.empty_like(raw)
+    z = c_p(0)
+    check(lib.dpvo_encoder_norm_act(ptr(raw), ptr(stats) if stats is not None else z, ptr(skip) if skip is not None else z,
+                                    ptr(skip_stats) if skip_stats is not None else z, c_i32(n), c_i64(H * W), c_i32(C),
+                                    c_f32(_EPS), ptr(out), stream_of(raw)), "encoder.norm_act")
+    return out
+
+
+def avg_pool4(x_nhwc):
+    """F.avg_pool2d(x, 4, 4) on a channels-last fp16 map [n, H, W, C] (dpvo.py:438)."""
+    require_cuda(x_nhwc)
+    if x_nhwc.dtype != torch.float16 or x_nhwc.dim() != 4 or not x_nhwc.is_contiguous() or x_nhwc.shape[3] % 8:
+        raise RuntimeError("encoder.avg_pool4: expected a contiguous fp16 [n, H, W, C] tensor, C a multiple of 8")
+    n, H, W, C = x_nhwc.shape
+    out = torch.empty((n, H // 4, W // 4, C), dtype=torch.float16, device=x_nhwc.device)
+    check(lib.dpvo_avgpool4_nhwc_f16(ptr(x_nhwc), c_i32(n), c_i32(H), c_i32(W), c_i32(C), ptr(out), stream_of(x_nhwc)),
+          "encoder.avg_pool4")
+    return out
+
+
+class FeatureMap:
+    """Result of an encoder call: `.nhwc` [n, h, w, C] fp16 buffer, `.nchw5` the reference-shaped [1, n, C, h, w] view."""
+    def __init__(self, nhwc):
+        self.nhwc = nhwc
+        self.nchw5 = nhwc.permute(0, 3, 1, 2)[None]
+
+
+class BasicEncoder4:
+    _CONVS = ["conv1", "layer1.0.conv1", "layer1.0.conv2", "layer1.1.conv1", "layer1.1.conv2", "layer2.0.conv1",
+              "layer2.0.conv2", "layer2.0.downsample.0", "layer2.1.conv1", "layer2.1.conv2", "conv2"]
+
+    def __init__(self, state_dict, norm_fn, device="cuda", output_scale=1.0):
+        """state_dict: the reference module's (`fnet.` / `inet.` prefix stripped).  norm_fn: 'instance' or 'none'.
+        output_scale: folded into the last layer (Patchifier divides both maps by 4, net.py:108-109)."""
+        dev = torch.device(device)
+        if dev.type != "cuda":
+            raise RuntimeError("encoder.BasicEncoder4: needs a CUDA device (no CPU path)")
+        if norm_fn not in ("instance", "none"):
+            raise RuntimeError("encoder.BasicEncoder4: norm_fn must be 'instance' or 'none' (the two DPVO uses)")
+        self.norm, self.device, self.scale = norm_fn == "instance", dev, float(output_scale)
+        self.w, self.b = {}, {}
+        for name in self._CONVS:
+            for suffix in (".weight", ".bias"):
+                if name + suffix not in state_dict:
+                    raise RuntimeError(f"encoder.BasicEncoder4: state dict lacks {name + suffix}")
+            w = torch.as_tensor(state_dict[name + ".weight"]).to(dev, torch.float32)
+            self.b[name] = torch.as_tensor(state_dict[name + ".bias"]).to(dev, torch.float32).contiguous()
+            if name == "conv1":
+                if tuple(w.shape) != (32, 3, 7, 7):
+                    raise RuntimeError("encoder.BasicEncoder4: conv1.weight must be [32, 3, 7, 7]")
+                self.w[name] = w.contiguous()
+            else:                                    # [cout, cin, k, k] -> fp16 [cout, k*k, cin]
+                co, ci, k, _ = w.shape
+                self.w[name] = w.permute(0, 2, 3, 1).reshape(co, k * k, ci).to(torch.float16).contiguous()
+        self.out_dim = self.w["conv2"].shape[0]
+        if self.out_dim % 64:
+            raise RuntimeError("encoder.BasicEncoder4: output_dim must be a multiple of 64")
+
+    @classmethod
+    def from_reference(cls, module, output_scale=1.0):
+        return cls({k: v.detach() for k, v in module.state_dict().items()}, module.norm_fn, output_scale=output_scale)
+
+    def _stats(self, n, c):
+        return torch.zeros((n, c, 2), dtype=torch.float64, device=self.device) if self.norm else None
+
+    def _block(self, x, name, cin, cout, stride):
+        n, H, W, _ = x.shape
+        s1 = self._stats(n, cout)
+        r1 = _conv(x, self.w[name + ".conv1"], self.b[name + ".conv1"], n, H, W, cin, cout, 3, stride, 1.0, s1)
+        y = _norm_act(r1, s1)
+        _, OH, OW, _ = y.shape
+        s2 = self._stats(n, cout)
+        r2 = _conv(y, self.w[name + ".conv2"], self.b[name + ".conv2"], n, OH, OW, cout, cout, 3, 1, 1.0, s2)
+        if stride == 1:
+            return _norm_act(r2, s2, skip=x)
+        s3 = self._stats(n, cout)
+        r3 = _conv(x, self.w[name + ".downsample.0"], self.b[name + ".downsample.0"], n, H, W, cin, cout, 1, stride, 1.0, s3)
+        if self.norm:
+            return _norm_act(r2, s2, skip=r3, skip_stats=s3)
+        return _norm_act(r2, None, skip=r3)
+
+    def __call__(self, images):
+        require_cuda(images)
+        if images.dim() != 5 or images.shape[2] != 3 or images.dtype != torch.float32:
+            raise RuntimeError("encoder.BasicEncoder4: images must be float32 [b, n, 3, H, W]")
+        b, n, _, H, W = images.shape
+        x = images.reshape(b * n, 3, H, W).contiguous()
+        OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+        s0 = self._stats(b * n, 32)
+        r0 = torch.empty((b * n, OH, OW, 32), dtype=torch.float16, device=x.device)
+        check(lib.dpvo_encoder_conv7x7s2(ptr(x), ptr(self.w["conv1"]), ptr(self.b["conv1"]), c_i32(b * n), c_i32(H), c_i32(W),
+                                         ptr(r0), ptr(s0) if s0 is not None else c_p(0), stream_of(x)), "encoder.conv1")
+        y = _norm_act(r0, s0)
+        y = self._block(y, "layer1.0", 32, 32, 1)
+        y = self._block(y, "layer1.1", 32, 32, 1)
+        y = self._block(y, "layer2.0", 32, 64, 2)
+        y = self._block(y, "layer2.1", 64, 64, 1)
+        _, h, w, _ = y.shape
+        out = _conv(y, self.w["conv2"], self.b["conv2"], b * n, h, w, 64, self.out_dim, 1, 1, self.scale, None)
+        return FeatureMap(out)

@@ -238,3 +238,30 @@ def update_inputs(n_frames=12, M=8, seed=0, P=3, dim=UPDATE_DIM, n_ctx=None):
                 net=(0.5 * rng.standard_normal((E, dim))).astype(np.float32),
                 corr=rng.standard_normal((E, 2 * 49 * P * P)).astype(np.float32),
                 imap=rng.standard_normal((n_ctx, dim)).astype(np.float32))
+
+
+def encoder_state_dict(out_dim, seed):
+    """Seeded parameters with the reference BasicEncoder4's state-dict keys and shapes (extractor.py:200-244);
+    kaiming-style scale (fan_out) like its initialiser, small non-zero biases so that they are exercised."""
+    rng = np.random.default_rng(seed)
+    shapes = [("conv1", 32, 3, 7)]
+    for blk, cin, cout in (("layer1.0", 32, 32), ("layer1.1", 32, 32), ("layer2.0", 32, 64), ("layer2.1", 64, 64)):
+        shapes += [(blk + ".conv1", cout, cin, 3), (blk + ".conv2", cout, cout, 3)]
+        if cin != cout:
+            shapes.append((blk + ".downsample.0", cout, cin, 1))
+    shapes.append(("conv2", out_dim, 64, 1))
+    sd = {}
+    for name, co, ci, k in shapes:
+        std = np.sqrt(2.0 / (co * k * k))
+        sd[name + ".weight"] = (rng.standard_normal((co, ci, k, k)) * std).astype(np.float32)
+        sd[name + ".bias"] = (rng.standard_normal(co) * 0.05).astype(np.float32)
+    return sd
+
+
+def encoder_images(n, H, W, seed):
+    """[1, n, 3, H, W] float32 in the range dpvo.py:389 produces (2 * (u8 / 255) - 0.5), smooth + texture."""
+    rng = np.random.default_rng(seed)
+    yy, xx = np.meshgrid(np.arange(H), np.arange(W), indexing="ij")
+    base = np.stack([128 + 100 * np.sin(0.07 * xx + c + f) * np.cos(0.05 * yy - c) for f in range(n) for c in range(3)])
+    u8 = np.clip(base.reshape(n, 3, H, W) + rng.integers(-25, 25, (n, 3, H, W)), 0, 255).astype(np.uint8)
+    return (2 * (u8.astype(np.float32) / 255.0) - 0.5)[None]

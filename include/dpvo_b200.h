@@ -377,6 +377,26 @@ int dpvo_viewer_iproj(int32_t index, int32_t n_frames, float thresh, const uint8
                       const float* disps, const float* intrinsics, int32_t ht, int32_t wd, float* points,
                       uint8_t* colors, float* count, void* stream);
 
+/* ---- per-frame feature encoders: BasicEncoder4, methods/dpvo/dpvo/extractor.py:200-264 -------
+ * Channels-last fp16 activations [img, H, W, C]; fp32 accumulation.  `stats` ([img, C, 2] float64, caller-zeroed, or
+ * NULL) receives each (image, channel) plane's sum and sum of squares for the InstanceNorm2d that follows. */
+/* conv1: nn.Conv2d(3, 32, 7, stride=2, padding=3) on the fp32 NCHW image; weight [32,3,7,7] fp32 */
+int dpvo_encoder_conv7x7s2(const float* images, const float* weight, const float* bias, int32_t n_img, int32_t H,
+                           int32_t W, void* out, double* stats, void* stream);
+/* 3x3 (padding 1) / 1x1 (padding 0) convolutions of the residual blocks and the output layer; weight fp16
+ * [cout, ksize*ksize, cin]; out = (conv + bias) * scale.  Layers: 3x3 s1 32->32, 3x3 s2 32->64, 3x3 s1 64->64,
+ * 1x1 s2 32->64, 1x1 s1 64->(multiple of 64). */
+int dpvo_encoder_conv(const void* in, const void* weight, const float* bias, int32_t n_img, int32_t H, int32_t W,
+                      int32_t cin, int32_t cout, int32_t ksize, int32_t stride, float scale, void* out, double* stats,
+                      void* stream);
+/* out = relu(norm(raw)), or relu(skipv + relu(norm(raw))) with skipv = skip or norm(skip) (ResidualBlock.forward,
+ * extractor.py:47-55); norm = InstanceNorm2d(affine=False, eps) from `stats`, identity when stats is NULL */
+int dpvo_encoder_norm_act(const void* raw, const double* stats, const void* skip, const double* skip_stats,
+                          int32_t n_img, int64_t hw, int32_t channels, float eps, void* out, void* stream);
+/* F.avg_pool2d(x, 4, 4) on a channels-last fp16 map (pyramid level 2, dpvo.py:438) */
+int dpvo_avgpool4_nhwc_f16(const void* in, int32_t n_img, int32_t H, int32_t W, int32_t channels, void* out,
+                           void* stream);
+
 #ifdef __cplusplus
 }
 #endif

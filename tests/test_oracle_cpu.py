@@ -387,3 +387,26 @@ def test_viewer_oracle_pose_to_matrix_vs_lietorch_oracle():
     pts, col, cnt, _, inner = vo.iproj(0, N, 5.0, np.zeros((N, 3, ht, wd), np.uint8), poses,
                                        np.full((N, ht, wd), 0.3, np.float32), np.tile(np.float32([[1, 1, 0.4, 0.3]]), (N, 1)))
     assert np.all(cnt[inner] == N - 1) and np.all(cnt[~inner] == 0)
+
+
+def _encoder_golden():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden_encoder", os.path.join(os.path.dirname(__file__), "golden",
+                                                                                       "make_golden_encoder.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m, np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_cpu_encoder.npz"))
+
+
+@pytest.mark.parametrize("name", ["fnet", "inet"])
+def test_encoder_oracle_vs_reference(name):
+    """N3: oracle/encoder_oracle.py against the reference BasicEncoder4 module's own float32 outputs."""
+    from oracle import encoder_oracle as eo
+    from conftest import load_pkg
+    synth = load_pkg("synth")
+    m, g = _encoder_golden()
+    c = m.CASES[name]
+    got = eo.basic_encoder4(synth.encoder_state_dict(c["out_dim"], c["seed"]),
+                            synth.encoder_images(m.N_IMG, m.H, m.W, m.IMG_SEED), c["norm_fn"])[0]
+    assert got.shape == g[name].shape
+    assert np.abs(got - g[name]).max() < 2e-5 * max(1.0, np.abs(g[name]).max())
