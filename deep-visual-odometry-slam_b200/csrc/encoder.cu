@@ -14,6 +14,8 @@
 namespace dpvo {
 namespace {
 
+constexpr int kStatReplicas = DPVO_ENCODER_STATS_REPLICAS;   // atomics of different CTAs land on different L2 lines
+
 __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile(
       "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
@@ -82,7 +84,8 @@ conv7x7s2_kernel(const float* __restrict__ img, const float* __restrict__ wgt /*
       const int o = threadIdx.x >> 1, j = threadIdx.x & 1;
       double t = 0;
       for (int w8 = 0; w8 < 8; ++w8) t += (double)s_red[w8][o][j];
-      atomicAdd(&stats[((int64_t)n * kC1Out + o) * 2 + j], t);
+      const int rep = (blockIdx.x + blockIdx.y * gridDim.x) % kStatReplicas;
+      atomicAdd(&stats[(((int64_t)n * kStatReplicas + rep) * kC1Out + o) * 2 + j], t);
     }
   }
 }
@@ -109,6 +112,7 @@ conv_mma_kernel(const ConvParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __half* s_in = reinterpret_cast<__half*>(smem_raw);                 // [IH][IW][CP]
   __half* s_w = s_in + IH * IW * CP;                                  // [KS*KS][NC][CP]
+  __shared__ float s_red[4 * NC * 2];
   const int n = blockIdx.z / p.nchunks, chunk = blockIdx.z % p.nchunks;
   const int ox0 = blockIdx.x * TW, oy0 = blockIdx.y * TH;
   const int ix0 = ox0 * S - PAD, iy0 = oy0 * S - PAD;
@@ -190,10 +194,19 @@ conv_mma_kernel(const ConvParams p) {
         s1 += __shfl_xor_sync(0xffffffffu, s1, d); q1 += __shfl_xor_sync(0xffffffffu, q1, d);
       }
       if (g == 0) {
-        double* st = p.stats + ((int64_t)n * p.COUT + ch) * 2;
-        atomicAdd(st + 0, (double)s0); atomicAdd(st + 1, (double)q0);
-        atomicAdd(st + 2, (double)s1); atomicAdd(st + 3, (double)q1);
+        float* r = s_red + (wid * NC + nt * 8 + 2 * t) * 2;
+        r[0] = s0; r[1] = q0; r[2] = s1; r[3] = q1;
       }
+    }
+  }
+  if (p.stats) {
+    // the four warps' partial sums -> one float64 atomic per (channel, moment) per CTA, on this CTA's replica
+    __syncthreads();
+    if (threadIdx.x < NC * 2) {
+      const double tot = (double)s_red[threadIdx.x] + (double)s_red[NC * 2 + threadIdx.x] +
+                         (double)s_red[NC * 4 + threadIdx.x] + (double)s_red[NC * 6 + threadIdx.x];
+      const int rep = (blockIdx.x + blockIdx.y * gridDim.x) % kStatReplicas;
+      atomicAdd(p.stats + (((int64_t)n * kStatReplicas + rep) * p.COUT + chunk * NC) * 2 + threadIdx.x, tot);
     }
   }
 }
@@ -218,24 +231,46 @@ int launch_conv(const ConvParams& p, int n_img, cudaStream_t st) {
 // out = relu(skipv + relu(norm(raw))), skipv = skip or norm(skip) when skip_stats is given (the down-sampled branch)
 // norm(x) = (x - mean) * rsqrt(var + eps) with the biased variance of the (image, channel) plane; identity when
 // stats == null (norm_fn='none').  fp32 arithmetic, one rounding to fp16.  8 channels (16 bytes) per thread.
-__device__ __forceinline__ void plane_stats(const double* st, int64_t idx, double inv_n, float eps, float& mean, float& rstd) {
-  const double m = st[idx * 2] * inv_n;
-  double var = st[idx * 2 + 1] * inv_n - m * m;
+__device__ __forceinline__ void plane_stats(const double* st, int64_t n, int C, int c, double inv_n, float eps, float& mean,
+                                            float& rstd) {
+  double s = 0, q = 0;
+#pragma unroll 4
+  for (int r = 0; r < kStatReplicas; ++r) {
+    const double* p = st + (((n * kStatReplicas + r) * C) + c) * 2;
+    s += p[0]; q += p[1];
+  }
+  const double m = s * inv_n;
+  double var = q * inv_n - m * m;
   var = var < 0 ? 0 : var;
   mean = (float)m;
   rstd = (float)(1.0 / sqrt(var + (double)eps));
 }
 
+constexpr int kNormMaxC = 128;
+
 __global__ void __launch_bounds__(256)
 norm_act_kernel(const __half* __restrict__ raw, const double* __restrict__ stats, const __half* __restrict__ skip,
                 const double* __restrict__ skip_stats, int64_t hw, int C, float eps, __half* __restrict__ out,
                 int64_t total_vec) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= total_vec) return;
+  // mean / rstd of the image this block starts in, once per block (a block that straddles two images recomputes
+  // the second image's values per thread)
+  __shared__ float s_tab[2][kNormMaxC][2];
   const int cv = C / 8;
+  const double inv_n = 1.0 / (double)hw;
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x;
+  const int64_t n0 = i0 / ((int64_t)cv * hw);
+  if (stats || skip_stats) {
+    for (int x = threadIdx.x; x < 2 * C; x += blockDim.x) {
+      const int which = x / C, c = x % C;
+      const double* st = which ? skip_stats : stats;
+      if (st) plane_stats(st, n0, C, c, inv_n, eps, s_tab[which][c][0], s_tab[which][c][1]);
+    }
+    __syncthreads();
+  }
+  const int64_t i = i0 + threadIdx.x;
+  if (i >= total_vec) return;
   const int c0 = (int)(i % cv) * 8;
   const int64_t n = i / ((int64_t)cv * hw);
-  const double inv_n = 1.0 / (double)hw;
   const uint4 rv = reinterpret_cast<const uint4*>(raw)[i];
   uint4 sv = make_uint4(0, 0, 0, 0);
   if (skip) sv = reinterpret_cast<const uint4*>(skip)[i];
@@ -247,7 +282,8 @@ norm_act_kernel(const __half* __restrict__ raw, const double* __restrict__ stats
     float v = __half2float(rh[c]);
     if (stats) {
       float m, r;
-      plane_stats(stats, n * C + c0 + c, inv_n, eps, m, r);
+      if (n == n0) { m = s_tab[0][c0 + c][0]; r = s_tab[0][c0 + c][1]; }
+      else plane_stats(stats, n, C, c0 + c, inv_n, eps, m, r);
       v = (v - m) * r;
     }
     v = fmaxf(v, 0.f);
@@ -255,7 +291,8 @@ norm_act_kernel(const __half* __restrict__ raw, const double* __restrict__ stats
       float s = __half2float(sh[c]);
       if (skip_stats) {
         float m, r;
-        plane_stats(skip_stats, n * C + c0 + c, inv_n, eps, m, r);
+        if (n == n0) { m = s_tab[1][c0 + c][0]; r = s_tab[1][c0 + c][1]; }
+        else plane_stats(skip_stats, n, C, c0 + c, inv_n, eps, m, r);
         s = (s - m) * r;
       }
       v = fmaxf(s + v, 0.f);
@@ -339,7 +376,8 @@ extern "C" int dpvo_encoder_conv(const void* in, const void* weight, const float
 
 extern "C" int dpvo_encoder_norm_act(const void* raw, const double* stats, const void* skip, const double* skip_stats,
                                      int32_t n_img, int64_t hw, int32_t channels, float eps, void* out, void* stream) {
-  DPVO_REQUIRE(n_img >= 0 && hw >= 0 && channels > 0 && channels % 8 == 0, "encoder_norm_act: bad sizes");
+  DPVO_REQUIRE(n_img >= 0 && hw >= 0 && channels > 0 && channels % 8 == 0 && channels <= kNormMaxC,
+               "encoder_norm_act: bad sizes");
   DPVO_REQUIRE(!skip_stats || skip, "encoder_norm_act: skip_stats without skip");
   const int64_t total = (int64_t)n_img * hw * (channels / 8);
   if (total == 0) return 0;

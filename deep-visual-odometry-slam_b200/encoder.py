@@ -11,6 +11,7 @@ import torch
 from ._lib import lib, ptr, stream_of, check, require_cuda, c_i32, c_i64, c_f32, c_p
 
 _EPS = 1e-5      # nn.InstanceNorm2d default
+_REPLICAS = 16   # DPVO_ENCODER_STATS_REPLICAS
 
 
 def _conv(x, w, b, n, H, W, cin, cout, k, s, scale, stats):
@@ -88,7 +89,13 @@ class BasicEncoder4:
         return cls({k: v.detach() for k, v in module.state_dict().items()}, module.norm_fn, output_scale=output_scale)
 
     def _stats(self, n, c):
-        return torch.zeros((n, c, 2), dtype=torch.float64, device=self.device) if self.norm else None
+        """One plane-statistics block out of the per-call arena (zeroed once per call)."""
+        if not self.norm:
+            return None
+        size = n * _REPLICAS * c * 2
+        out = self._arena[self._used:self._used + size]
+        self._used += size
+        return out
 
     def _block(self, x, name, cin, cout, stride):
         n, H, W, _ = x.shape
@@ -113,6 +120,9 @@ class BasicEncoder4:
         b, n, _, H, W = images.shape
         x = images.reshape(b * n, 3, H, W).contiguous()
         OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+        if self.norm:                       # 32 x 5 + 64 x 5 channels of statistics over the ten normalised layers
+            self._arena = torch.zeros(b * n * _REPLICAS * 2 * (32 * 5 + 64 * 5), dtype=torch.float64, device=x.device)
+            self._used = 0
         s0 = self._stats(b * n, 32)
         r0 = torch.empty((b * n, OH, OW, 32), dtype=torch.float16, device=x.device)
         check(lib.dpvo_encoder_conv7x7s2(ptr(x), ptr(self.w["conv1"]), ptr(self.b["conv1"]), c_i32(b * n), c_i32(H), c_i32(W),

@@ -378,8 +378,11 @@ int dpvo_viewer_iproj(int32_t index, int32_t n_frames, float thresh, const uint8
                       uint8_t* colors, float* count, void* stream);
 
 /* ---- per-frame feature encoders: BasicEncoder4, methods/dpvo/dpvo/extractor.py:200-264 -------
- * Channels-last fp16 activations [img, H, W, C]; fp32 accumulation.  `stats` ([img, C, 2] float64, caller-zeroed, or
- * NULL) receives each (image, channel) plane's sum and sum of squares for the InstanceNorm2d that follows. */
+ * Channels-last fp16 activations [img, H, W, C]; fp32 accumulation.  `stats` ([img, DPVO_ENCODER_STATS_REPLICAS, C, 2]
+ * float64, caller-zeroed, or NULL) receives each (image, channel) plane's sum and sum of squares for the
+ * InstanceNorm2d that follows, spread over replicas (different CTAs add to different cache lines; the consumer sums
+ * them). */
+#define DPVO_ENCODER_STATS_REPLICAS 16
 /* conv1: nn.Conv2d(3, 32, 7, stride=2, padding=3) on the fp32 NCHW image; weight [32,3,7,7] fp32 */
 int dpvo_encoder_conv7x7s2(const float* images, const float* weight, const float* bias, int32_t n_img, int32_t H,
                            int32_t W, void* out, double* stats, void* stream);
