@@ -24,68 +24,109 @@ __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], 
 }
 
 // ------------------------------------------------------------------------------------------------ conv1: 7x7 s2, 3 -> 32
-// fp32 image [img, 3, H, W] (NCHW, as dpvo.py:389 builds it) -> fp16 [img, OH, OW, 32].  CUDA cores: K = 147 only.
-constexpr int kC1Out = 32, kC1Tile = 16, kC1In = (kC1Tile - 1) * 2 + 7;
+// fp32 image [img, 3, H, W] (NCHW, as dpvo.py:389 builds it) -> fp16 [img, OH, OW, 32] on the tensor cores.
+// The image patch is staged in shared memory as fp16 with the 3 channels interleaved, so for a fixed kernel row ky
+// the 7 x 3 = 21 inputs of an output pixel are CONTIGUOUS (starting 6 halves after its left neighbour's): that row is
+// one K-slice of 32 (21 live + 11 columns whose weights are zero), two k16 steps.  K = 7 x 32 = 224 in all.
+// One CTA = 8 x 16 output pixels, 4 warps x 2 rows, N = 32.  Weights: fp16 [ky][n][32] (k = kx * 3 + c, zero padded).
+constexpr int kC1Out = 32, kC1TH = 8, kC1TW = 16;
+constexpr int kC1Rows = (kC1TH - 1) * 2 + 7;          // 21 input rows
+constexpr int kC1Cols = (kC1TW - 1) * 2 + 7;          // 37 input pixels
+constexpr int kC1RowHalves = 136;                     // >= 6 * 15 + 32 = 122, 68 words: rows land on different banks
+constexpr int kC1WP = 40;                             // padded K stride of the weight rows
 
-__global__ void __launch_bounds__(256)
-conv7x7s2_kernel(const float* __restrict__ img, const float* __restrict__ wgt /*[32][3][7][7]*/,
+__global__ void __launch_bounds__(128)
+conv7x7s2_kernel(const float* __restrict__ img, const __half* __restrict__ wgt /*[7][32][32]*/,
                  const float* __restrict__ bias, int H, int W, int OH, int OW, __half* __restrict__ out,
-                 double* __restrict__ stats /*[img][32][2] or null*/) {
-  __shared__ float s_in[3][kC1In][kC1In + 1];
-  __shared__ float s_w[147][kC1Out];
-  __shared__ float s_red[8][kC1Out][2];
+                 double* __restrict__ stats) {
+  __shared__ __align__(16) __half s_img[kC1Rows][kC1RowHalves];
+  __shared__ __align__(16) __half s_w[7][kC1Out][kC1WP];
+  __shared__ float s_red[4 * kC1Out * 2];
   const int n = blockIdx.z;
-  const int ox0 = blockIdx.x * kC1Tile, oy0 = blockIdx.y * kC1Tile;
+  const int ox0 = blockIdx.x * kC1TW, oy0 = blockIdx.y * kC1TH;
   const int ix0 = ox0 * 2 - 3, iy0 = oy0 * 2 - 3;
-  for (int i = threadIdx.x; i < 3 * kC1In * kC1In; i += 256) {
-    const int c = i / (kC1In * kC1In), r = (i / kC1In) % kC1In, x = i % kC1In;
+  for (int i = threadIdx.x; i < kC1Rows * kC1RowHalves; i += 128) {
+    const int r = i / kC1RowHalves, e = i % kC1RowHalves;
+    const int x = e / 3, c = e % 3;
     const int iy = iy0 + r, ix = ix0 + x;
-    s_in[c][r][x] = (iy >= 0 && iy < H && ix >= 0 && ix < W) ? img[((int64_t)(n * 3 + c) * H + iy) * W + ix] : 0.f;
+    float v = 0.f;
+    if (x < kC1Cols && iy >= 0 && iy < H && ix >= 0 && ix < W) v = img[((int64_t)(n * 3 + c) * H + iy) * W + ix];
+    s_img[r][e] = __float2half_rn(v);
   }
-  for (int i = threadIdx.x; i < 147 * kC1Out; i += 256) {
-    const int k = i / kC1Out, o = i % kC1Out;                 // k = (c, ky, kx) flattened like the torch weight
-    s_w[k][o] = wgt[o * 147 + k];
+  for (int i = threadIdx.x; i < 7 * kC1Out * 4; i += 128) {          // 32 halves = 4 x 16 bytes per (ky, n)
+    const int v = i % 4, o = (i / 4) % kC1Out, ky = i / (4 * kC1Out);
+    *reinterpret_cast<uint4*>(&s_w[ky][o][v * 8]) = *reinterpret_cast<const uint4*>(wgt + ((ky * kC1Out + o) * 32 + v * 8));
   }
   __syncthreads();
-  const int px = threadIdx.x % kC1Tile, py = threadIdx.x / kC1Tile;
-  float acc[kC1Out];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+  float acc[2][4][4];
 #pragma unroll
-  for (int o = 0; o < kC1Out; ++o) acc[o] = bias[o];
-  for (int c = 0; c < 3; ++c)
-    for (int ky = 0; ky < 7; ++ky)
+  for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
-      for (int kx = 0; kx < 7; ++kx) {
-        const float v = s_in[c][py * 2 + ky][px * 2 + kx];
-        const float* wr = &s_w[(c * 7 + ky) * 7 + kx][0];
+    for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
-        for (int o = 0; o < kC1Out; ++o) acc[o] = fmaf(v, wr[o], acc[o]);
+      for (int c = 0; c < 4; ++c) acc[mt][nt][c] = 0.f;
+#pragma unroll
+  for (int ky = 0; ky < 7; ++ky)
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks) {
+      uint32_t a[2][4];
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) {
+        const __half* r0 = &s_img[(wid * 2 + mt) * 2 + ky][6 * g + 16 * ks + 2 * t];
+        const __half* r1 = r0 + 6 * 8;
+        a[mt][0] = *reinterpret_cast<const uint32_t*>(r0);
+        a[mt][1] = *reinterpret_cast<const uint32_t*>(r1);
+        a[mt][2] = *reinterpret_cast<const uint32_t*>(r0 + 8);
+        a[mt][3] = *reinterpret_cast<const uint32_t*>(r1 + 8);
       }
-  const int oy = oy0 + py, ox = ox0 + px;
-  const bool ok = oy < OH && ox < OW;
-  __half h[kC1Out];
 #pragma unroll
-  for (int o = 0; o < kC1Out; ++o) h[o] = __float2half_rn(acc[o]);
-  if (ok) {
-    uint4* dst = reinterpret_cast<uint4*>(out + (((int64_t)n * OH + oy) * OW + ox) * kC1Out);
+      for (int nt = 0; nt < 4; ++nt) {
+        const __half* br = &s_w[ky][nt * 8 + g][16 * ks + 2 * t];
+        const uint32_t b0 = *reinterpret_cast<const uint32_t*>(br);
+        const uint32_t b1 = *reinterpret_cast<const uint32_t*>(br + 8);
+        mma16816(acc[0][nt], a[0], b0, b1);
+        mma16816(acc[1][nt], a[1], b0, b1);
+      }
+    }
 #pragma unroll
-    for (int v = 0; v < 4; ++v) dst[v] = reinterpret_cast<const uint4*>(h)[v];
+  for (int nt = 0; nt < 4; ++nt) {
+    const int ch = nt * 8 + 2 * t;
+    const float b0 = bias[ch], b1 = bias[ch + 1];
+    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt) {
+      const int oy = oy0 + wid * 2 + mt;
+#pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {
+        const int ox = ox0 + g + 8 * hf;
+        if (oy < OH && ox < OW) {
+          const __half2 h = __floats2half2_rn(acc[mt][nt][2 * hf] + b0, acc[mt][nt][2 * hf + 1] + b1);
+          *reinterpret_cast<__half2*>(out + (((int64_t)n * OH + oy) * OW + ox) * kC1Out + ch) = h;
+          const float2 f = __half22float2(h);
+          s0 += f.x; q0 += f.x * f.x; s1 += f.y; q1 += f.y * f.y;
+        }
+      }
+    }
+    if (stats) {
+#pragma unroll
+      for (int d = 4; d < 32; d <<= 1) {
+        s0 += __shfl_xor_sync(0xffffffffu, s0, d); q0 += __shfl_xor_sync(0xffffffffu, q0, d);
+        s1 += __shfl_xor_sync(0xffffffffu, s1, d); q1 += __shfl_xor_sync(0xffffffffu, q1, d);
+      }
+      if (g == 0) {
+        float* r = s_red + (wid * kC1Out + ch) * 2;
+        r[0] = s0; r[1] = q0; r[2] = s1; r[3] = q1;
+      }
+    }
   }
   if (stats) {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-#pragma unroll
-    for (int o = 0; o < kC1Out; ++o) {
-      float s = ok ? __half2float(h[o]) : 0.f, q = s * s;
-#pragma unroll
-      for (int d = 16; d > 0; d >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, d); q += __shfl_xor_sync(0xffffffffu, q, d); }
-      if (lane == 0) { s_red[wid][o][0] = s; s_red[wid][o][1] = q; }
-    }
     __syncthreads();
     if (threadIdx.x < kC1Out * 2) {
-      const int o = threadIdx.x >> 1, j = threadIdx.x & 1;
-      double t = 0;
-      for (int w8 = 0; w8 < 8; ++w8) t += (double)s_red[w8][o][j];
+      const double tot = (double)s_red[threadIdx.x] + (double)s_red[kC1Out * 2 + threadIdx.x] +
+                         (double)s_red[kC1Out * 4 + threadIdx.x] + (double)s_red[kC1Out * 6 + threadIdx.x];
       const int rep = (blockIdx.x + blockIdx.y * gridDim.x) % kStatReplicas;
-      atomicAdd(&stats[(((int64_t)n * kStatReplicas + rep) * kC1Out + o) * 2 + j], t);
+      atomicAdd(stats + ((int64_t)n * kStatReplicas + rep) * kC1Out * 2 + threadIdx.x, tot);
     }
   }
 }
@@ -330,16 +371,17 @@ avgpool4_kernel(const __half* __restrict__ in, int H, int W, int C, int OH, int 
 
 using namespace dpvo;
 
-extern "C" int dpvo_encoder_conv7x7s2(const float* images, const float* weight, const float* bias, int32_t n_img, int32_t H,
+extern "C" int dpvo_encoder_conv7x7s2(const float* images, const void* weight, const float* bias, int32_t n_img, int32_t H,
                                       int32_t W, void* out, double* stats, void* stream) {
   DPVO_REQUIRE(n_img >= 0 && H >= 0 && W >= 0, "encoder_conv7x7s2: bad sizes");
   if (n_img == 0 || H == 0 || W == 0) return 0;
   DPVO_REQUIRE(images && weight && bias && out, "encoder_conv7x7s2: null pointer");
-  DPVO_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0, "encoder_conv7x7s2: output must be 16-byte aligned");
+  DPVO_REQUIRE(((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(weight)) & 15) == 0,
+               "encoder_conv7x7s2: weight / output must be 16-byte aligned");
   const int OH = (H + 6 - 7) / 2 + 1, OW = (W + 6 - 7) / 2 + 1;
-  dim3 grid((OW + kC1Tile - 1) / kC1Tile, (OH + kC1Tile - 1) / kC1Tile, n_img);
-  conv7x7s2_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(images, weight, bias, H, W, OH, OW,
-                                                                             reinterpret_cast<__half*>(out), stats);
+  dim3 grid((OW + kC1TW - 1) / kC1TW, (OH + kC1TH - 1) / kC1TH, n_img);
+  conv7x7s2_kernel<<<grid, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      images, reinterpret_cast<const __half*>(weight), bias, H, W, OH, OW, reinterpret_cast<__half*>(out), stats);
   note_launches(1);
   return check_launch("encoder_conv7x7s2");
 }

@@ -76,7 +76,9 @@ class BasicEncoder4:
             if name == "conv1":
                 if tuple(w.shape) != (32, 3, 7, 7):
                     raise RuntimeError("encoder.BasicEncoder4: conv1.weight must be [32, 3, 7, 7]")
-                self.w[name] = w.contiguous()
+                packed = torch.zeros((7, 32, 32), dtype=torch.float16, device=dev)      # [ky][cout][kx * 3 + c]
+                packed[:, :, :21] = w.permute(2, 0, 3, 1).reshape(7, 32, 21).to(torch.float16)
+                self.w[name] = packed
             else:                                    # [cout, cin, k, k] -> fp16 [cout, k*k, cin]
                 co, ci, k, _ = w.shape
                 self.w[name] = w.permute(0, 2, 3, 1).reshape(co, k * k, ci).to(torch.float16).contiguous()

@@ -383,8 +383,9 @@ int dpvo_viewer_iproj(int32_t index, int32_t n_frames, float thresh, const uint8
  * InstanceNorm2d that follows, spread over replicas (different CTAs add to different cache lines; the consumer sums
  * them). */
 #define DPVO_ENCODER_STATS_REPLICAS 16
-/* conv1: nn.Conv2d(3, 32, 7, stride=2, padding=3) on the fp32 NCHW image; weight [32,3,7,7] fp32 */
-int dpvo_encoder_conv7x7s2(const float* images, const float* weight, const float* bias, int32_t n_img, int32_t H,
+/* conv1: nn.Conv2d(3, 32, 7, stride=2, padding=3) on the fp32 NCHW image; weight fp16 packed [ky=7][cout=32][32]
+ * with k = kx * 3 + c for the 21 live columns and zeros in the other 11 (torch weight [32,3,7,7] permuted) */
+int dpvo_encoder_conv7x7s2(const float* images, const void* weight, const float* bias, int32_t n_img, int32_t H,
                            int32_t W, void* out, double* stats, void* stream);
 /* 3x3 (padding 1) / 1x1 (padding 0) convolutions of the residual blocks and the output layer; weight fp16
  * [cout, ksize*ksize, cin]; out = (conv + bias) * scale.  Layers: 3x3 s1 32->32, 3x3 s2 32->64, 3x3 s1 64->64,
