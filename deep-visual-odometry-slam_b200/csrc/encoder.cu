@@ -10,6 +10,7 @@
 // that follows; the norm, ReLU and residual add are one elementwise pass over the fp16 map.
 #include "common.cuh"
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 namespace dpvo {
 namespace {
@@ -21,6 +22,22 @@ __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], 
       "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
       : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// mean / rstd of one (image, channel) plane from the replicated float64 sums (biased variance, like InstanceNorm2d)
+__device__ __forceinline__ void plane_stats(const double* st, int64_t n, int C, int c, double inv_n, float eps, float& mean,
+                                            float& rstd) {
+  double s = 0, q = 0;
+#pragma unroll 4
+  for (int r = 0; r < kStatReplicas; ++r) {
+    const double* p = st + (((n * kStatReplicas + r) * C) + c) * 2;
+    s += p[0]; q += p[1];
+  }
+  const double m = s * inv_n;
+  double var = q * inv_n - m * m;
+  var = var < 0 ? 0 : var;
+  mean = (float)m;
+  rstd = (float)(1.0 / sqrt(var + (double)eps));
 }
 
 // ------------------------------------------------------------------------------------------------ conv1: 7x7 s2, 3 -> 32
@@ -38,7 +55,7 @@ constexpr int kC1WP = 40;                             // padded K stride of the 
 __global__ void __launch_bounds__(128)
 conv7x7s2_kernel(const float* __restrict__ img, const __half* __restrict__ wgt /*[7][32][32]*/,
                  const float* __restrict__ bias, int H, int W, int OH, int OW, __half* __restrict__ out,
-                 double* __restrict__ stats) {
+                 double* __restrict__ stats, int relu) {
   __shared__ __align__(16) __half s_img[kC1Rows][kC1RowHalves];
   __shared__ __align__(16) __half s_w[7][kC1Out][kC1WP];
   __shared__ float s_red[4 * kC1Out * 2];
@@ -101,7 +118,9 @@ conv7x7s2_kernel(const float* __restrict__ img, const __half* __restrict__ wgt /
       for (int hf = 0; hf < 2; ++hf) {
         const int ox = ox0 + g + 8 * hf;
         if (oy < OH && ox < OW) {
-          const __half2 h = __floats2half2_rn(acc[mt][nt][2 * hf] + b0, acc[mt][nt][2 * hf + 1] + b1);
+          float v0 = acc[mt][nt][2 * hf] + b0, v1 = acc[mt][nt][2 * hf + 1] + b1;
+          if (relu) { v0 = fmaxf(v0, 0.f); v1 = fmaxf(v1, 0.f); }
+          const __half2 h = __floats2half2_rn(v0, v1);
           *reinterpret_cast<__half2*>(out + (((int64_t)n * OH + oy) * OW + ox) * kC1Out + ch) = h;
           const float2 f = __half22float2(h);
           s0 += f.x; q0 += f.x * f.x; s1 += f.y; q1 += f.y * f.y;
@@ -140,21 +159,31 @@ struct ConvParams {
   const __half* wgt;    // [COUT, KS*KS, CIN]
   const float* bias;    // [COUT]
   __half* out;          // [img, OH, OW, COUT]
-  double* stats;        // [img, COUT, 2] or null
+  double* stats;        // [img, replicas, COUT, 2] or null
+  const double* in_stats;  // statistics of `in`: instance norm + ReLU applied while the patch is staged, or null
+  const __half* skip;   // [img, OH, OW, COUT] or null: out = relu(skip + relu(conv)) (ResidualBlock without norm)
+  int relu;             // out = relu(conv) (norm_fn='none' only: with a norm the ReLU follows the statistics)
+  float eps;
   int H, W, OH, OW, COUT, nchunks;
   float scale;          // applied after the bias (conv2's "/ 4")
 };
 
-template <int KS, int S, int CIN, int NC>
+template <int KS, int S, int CIN, int NC, int MT>
 __global__ void __launch_bounds__(128)
 conv_mma_kernel(const ConvParams p) {
-  constexpr int TH = 8, TW = 16, IH = (TH - 1) * S + KS, IW = (TW - 1) * S + KS, CP = CIN + 8, NT = NC / 8;
+  constexpr int TH = 4 * MT, TW = 16, IH = (TH - 1) * S + KS, IW = (TW - 1) * S + KS, CP = CIN + 8, NT = NC / 8;
   constexpr int PAD = KS / 2;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __half* s_in = reinterpret_cast<__half*>(smem_raw);                 // [IH][IW][CP]
   __half* s_w = s_in + IH * IW * CP;                                  // [KS*KS][NC][CP]
   __shared__ float s_red[4 * NC * 2];
+  __shared__ float s_norm[CIN][2];
   const int n = blockIdx.z / p.nchunks, chunk = blockIdx.z % p.nchunks;
+  if (p.in_stats) {
+    if (threadIdx.x < CIN)
+      plane_stats(p.in_stats, n, CIN, threadIdx.x, 1.0 / ((double)p.H * p.W), p.eps, s_norm[threadIdx.x][0], s_norm[threadIdx.x][1]);
+    __syncthreads();
+  }
   const int ox0 = blockIdx.x * TW, oy0 = blockIdx.y * TH;
   const int ix0 = ox0 * S - PAD, iy0 = oy0 * S - PAD;
   constexpr int CV = CIN / 8;                                         // 16-byte vectors per pixel
@@ -162,8 +191,15 @@ conv_mma_kernel(const ConvParams p) {
     const int v = i % CV, x = (i / CV) % IW, r = i / (CV * IW);
     const int iy = iy0 + r, ix = ix0 + x;
     uint4 val = make_uint4(0, 0, 0, 0);
-    if (iy >= 0 && iy < p.H && ix >= 0 && ix < p.W)
+    if (iy >= 0 && iy < p.H && ix >= 0 && ix < p.W) {
       val = *reinterpret_cast<const uint4*>(p.in + (((int64_t)n * p.H + iy) * p.W + ix) * CIN + v * 8);
+      if (p.in_stats) {                       // the zero padding applies to the NORMALISED map: only live pixels change
+        __half* h = reinterpret_cast<__half*>(&val);
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+          h[c] = __float2half_rn(fmaxf((__half2float(h[c]) - s_norm[v * 8 + c][0]) * s_norm[v * 8 + c][1], 0.f));
+      }
+    }
     *reinterpret_cast<uint4*>(s_in + (r * IW + x) * CP + v * 8) = val;
   }
   for (int i = threadIdx.x; i < KS * KS * NC * CV; i += 128) {
@@ -174,9 +210,9 @@ conv_mma_kernel(const ConvParams p) {
   __syncthreads();
 
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
-  float acc[2][NT][4];
+  float acc[MT][NT][4];
 #pragma unroll
-  for (int mt = 0; mt < 2; ++mt)
+  for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
@@ -186,10 +222,10 @@ conv_mma_kernel(const ConvParams p) {
     const int ky = tap / KS, kx = tap % KS;
 #pragma unroll
     for (int ks = 0; ks < CIN / 16; ++ks) {
-      uint32_t a[2][4];
+      uint32_t a[MT][4];
 #pragma unroll
-      for (int mt = 0; mt < 2; ++mt) {
-        const int py = wid * 2 + mt;
+      for (int mt = 0; mt < MT; ++mt) {
+        const int py = wid * MT + mt;
         const __half* r0 = s_in + ((py * S + ky) * IW + (g * S + kx)) * CP + ks * 16 + 2 * t;
         const __half* r1 = r0 + 8 * S * CP;
         a[mt][0] = *reinterpret_cast<const uint32_t*>(r0);
@@ -202,8 +238,8 @@ conv_mma_kernel(const ConvParams p) {
         const __half* br = s_w + (tap * NC + nt * 8 + g) * CP + ks * 16 + 2 * t;
         const uint32_t b0 = *reinterpret_cast<const uint32_t*>(br);
         const uint32_t b1 = *reinterpret_cast<const uint32_t*>(br + 8);
-        mma16816(acc[0][nt], a[0], b0, b1);
-        mma16816(acc[1][nt], a[1], b0, b1);
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) mma16816(acc[mt][nt], a[mt], b0, b1);
       }
     }
   }
@@ -215,14 +251,21 @@ conv_mma_kernel(const ConvParams p) {
     const float b0 = p.bias[ch], b1 = p.bias[ch + 1];
     float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
-    for (int mt = 0; mt < 2; ++mt) {
-      const int oy = oy0 + wid * 2 + mt;
+    for (int mt = 0; mt < MT; ++mt) {
+      const int oy = oy0 + wid * MT + mt;
 #pragma unroll
       for (int hf = 0; hf < 2; ++hf) {
         const int ox = ox0 + g + 8 * hf;
         if (oy < p.OH && ox < p.OW) {
-          const __half2 h = __floats2half2_rn((acc[mt][nt][2 * hf] + b0) * p.scale, (acc[mt][nt][2 * hf + 1] + b1) * p.scale);
-          *reinterpret_cast<__half2*>(p.out + (((int64_t)n * p.OH + oy) * p.OW + ox) * p.COUT + ch) = h;
+          float v0 = (acc[mt][nt][2 * hf] + b0) * p.scale, v1 = (acc[mt][nt][2 * hf + 1] + b1) * p.scale;
+          const int64_t o = (((int64_t)n * p.OH + oy) * p.OW + ox) * p.COUT + ch;
+          if (p.relu) { v0 = fmaxf(v0, 0.f); v1 = fmaxf(v1, 0.f); }
+          if (p.skip) {
+            const float2 sk = __half22float2(*reinterpret_cast<const __half2*>(p.skip + o));
+            v0 = fmaxf(sk.x + v0, 0.f); v1 = fmaxf(sk.y + v1, 0.f);
+          }
+          const __half2 h = __floats2half2_rn(v0, v1);
+          *reinterpret_cast<__half2*>(p.out + o) = h;
           const float2 f = __half22float2(h);
           s0 += f.x; q0 += f.x * f.x; s1 += f.y; q1 += f.y * f.y;
         }
@@ -252,19 +295,28 @@ conv_mma_kernel(const ConvParams p) {
   }
 }
 
-template <int KS, int S, int CIN, int NC>
-int launch_conv(const ConvParams& p, int n_img, cudaStream_t st) {
-  constexpr int IH = 7 * S + KS, IW = 15 * S + KS, CP = CIN + 8;
+template <int KS, int S, int CIN, int NC, int MT>
+int launch_conv_mt(const ConvParams& p, int n_img, cudaStream_t st) {
+  constexpr int IH = (4 * MT - 1) * S + KS, IW = 15 * S + KS, CP = CIN + 8;
   constexpr int smem = (IH * IW * CP + KS * KS * NC * CP) * 2;
   static bool once = false;
   if (!once) {
-    cudaFuncSetAttribute(conv_mma_kernel<KS, S, CIN, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaFuncSetAttribute(conv_mma_kernel<KS, S, CIN, NC, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     once = true;
   }
-  dim3 grid((p.OW + 15) / 16, (p.OH + 7) / 8, n_img * p.nchunks);
-  conv_mma_kernel<KS, S, CIN, NC><<<grid, 128, smem, st>>>(p);
+  dim3 grid((p.OW + 15) / 16, (p.OH + 4 * MT - 1) / (4 * MT), n_img * p.nchunks);
+  conv_mma_kernel<KS, S, CIN, NC, MT><<<grid, 128, smem, st>>>(p);
   note_launches(1);
   return check_launch("encoder_conv");
+}
+
+// rows per warp: 2 (8 x 16 pixel tiles).  4 x 16 tiles (DPVO_ENC_MT=1: twice the CTAs, two resident per SM) were measured
+// slower on every layer of a 480x640 frame (fnet 0.216 vs 0.191 ms): each CTA re-stages the layer's weights.
+template <int KS, int S, int CIN, int NC>
+int launch_conv(const ConvParams& p, int n_img, cudaStream_t st) {
+  static const int forced = getenv("DPVO_ENC_MT") ? atoi(getenv("DPVO_ENC_MT")) : 0;
+  const int mt = forced == 1 ? 1 : 2;
+  return mt == 2 ? launch_conv_mt<KS, S, CIN, NC, 2>(p, n_img, st) : launch_conv_mt<KS, S, CIN, NC, 1>(p, n_img, st);
 }
 
 // ------------------------------------------------------------------- instance norm + ReLU (+ residual add + ReLU)
@@ -272,21 +324,6 @@ int launch_conv(const ConvParams& p, int n_img, cudaStream_t st) {
 // out = relu(skipv + relu(norm(raw))), skipv = skip or norm(skip) when skip_stats is given (the down-sampled branch)
 // norm(x) = (x - mean) * rsqrt(var + eps) with the biased variance of the (image, channel) plane; identity when
 // stats == null (norm_fn='none').  fp32 arithmetic, one rounding to fp16.  8 channels (16 bytes) per thread.
-__device__ __forceinline__ void plane_stats(const double* st, int64_t n, int C, int c, double inv_n, float eps, float& mean,
-                                            float& rstd) {
-  double s = 0, q = 0;
-#pragma unroll 4
-  for (int r = 0; r < kStatReplicas; ++r) {
-    const double* p = st + (((n * kStatReplicas + r) * C) + c) * 2;
-    s += p[0]; q += p[1];
-  }
-  const double m = s * inv_n;
-  double var = q * inv_n - m * m;
-  var = var < 0 ? 0 : var;
-  mean = (float)m;
-  rstd = (float)(1.0 / sqrt(var + (double)eps));
-}
-
 constexpr int kNormMaxC = 128;
 
 __global__ void __launch_bounds__(256)
@@ -372,8 +409,9 @@ avgpool4_kernel(const __half* __restrict__ in, int H, int W, int C, int OH, int 
 using namespace dpvo;
 
 extern "C" int dpvo_encoder_conv7x7s2(const float* images, const void* weight, const float* bias, int32_t n_img, int32_t H,
-                                      int32_t W, void* out, double* stats, void* stream) {
+                                      int32_t W, int32_t relu, void* out, double* stats, void* stream) {
   DPVO_REQUIRE(n_img >= 0 && H >= 0 && W >= 0, "encoder_conv7x7s2: bad sizes");
+  DPVO_REQUIRE(!(relu && stats), "encoder_conv7x7s2: relu and stats are exclusive (the ReLU follows the norm)");
   if (n_img == 0 || H == 0 || W == 0) return 0;
   DPVO_REQUIRE(images && weight && bias && out, "encoder_conv7x7s2: null pointer");
   DPVO_REQUIRE(((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(weight)) & 15) == 0,
@@ -381,15 +419,18 @@ extern "C" int dpvo_encoder_conv7x7s2(const float* images, const void* weight, c
   const int OH = (H + 6 - 7) / 2 + 1, OW = (W + 6 - 7) / 2 + 1;
   dim3 grid((OW + kC1TW - 1) / kC1TW, (OH + kC1TH - 1) / kC1TH, n_img);
   conv7x7s2_kernel<<<grid, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      images, reinterpret_cast<const __half*>(weight), bias, H, W, OH, OW, reinterpret_cast<__half*>(out), stats);
+      images, reinterpret_cast<const __half*>(weight), bias, H, W, OH, OW, reinterpret_cast<__half*>(out), stats, relu);
   note_launches(1);
   return check_launch("encoder_conv7x7s2");
 }
 
 extern "C" int dpvo_encoder_conv(const void* in, const void* weight, const float* bias, int32_t n_img, int32_t H, int32_t W,
-                                 int32_t cin, int32_t cout, int32_t ksize, int32_t stride, float scale, void* out,
+                                 int32_t cin, int32_t cout, int32_t ksize, int32_t stride, float scale,
+                                 const double* in_stats, float eps, int32_t relu, const void* skip, void* out,
                                  double* stats, void* stream) {
   DPVO_REQUIRE(n_img >= 0 && H >= 0 && W >= 0, "encoder_conv: bad sizes");
+  DPVO_REQUIRE(!((relu || skip) && stats), "encoder_conv: relu / skip and stats are exclusive (the ReLU follows the norm)");
+  DPVO_REQUIRE((reinterpret_cast<uintptr_t>(skip) & 3) == 0, "encoder_conv: skip must be 4-byte aligned");
   if (n_img == 0 || H == 0 || W == 0) return 0;
   DPVO_REQUIRE(in && weight && bias && out, "encoder_conv: null pointer");
   DPVO_REQUIRE(((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(weight) | reinterpret_cast<uintptr_t>(out)) & 15) == 0,
@@ -397,6 +438,7 @@ extern "C" int dpvo_encoder_conv(const void* in, const void* weight, const float
   ConvParams p;
   p.in = reinterpret_cast<const __half*>(in); p.wgt = reinterpret_cast<const __half*>(weight); p.bias = bias;
   p.out = reinterpret_cast<__half*>(out); p.stats = stats;
+  p.in_stats = in_stats; p.eps = eps; p.relu = relu; p.skip = reinterpret_cast<const __half*>(skip);
   const int pad = ksize / 2;
   p.H = H; p.W = W; p.OH = (H + 2 * pad - ksize) / stride + 1; p.OW = (W + 2 * pad - ksize) / stride + 1;
   p.COUT = cout; p.scale = scale;

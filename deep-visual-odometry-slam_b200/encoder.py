@@ -14,13 +14,15 @@ _EPS = 1e-5      # nn.InstanceNorm2d default
 _REPLICAS = 16   # DPVO_ENCODER_STATS_REPLICAS
 
 
-def _conv(x, w, b, n, H, W, cin, cout, k, s, scale, stats):
+def _conv(x, w, b, n, H, W, cin, cout, k, s, scale, stats, in_stats=None, relu=False, skip=None):
     pad = k // 2
     OH, OW = (H + 2 * pad - k) // s + 1, (W + 2 * pad - k) // s + 1
     out = torch.empty((n, OH, OW, cout), dtype=torch.float16, device=x.device)
+    z = c_p(0)
     check(lib.dpvo_encoder_conv(ptr(x), ptr(w), ptr(b), c_i32(n), c_i32(H), c_i32(W), c_i32(cin), c_i32(cout), c_i32(k),
-                                c_i32(s), c_f32(scale), ptr(out), ptr(stats) if stats is not None else c_p(0),
-                                stream_of(x)), "encoder.conv")
+                                c_i32(s), c_f32(scale), ptr(in_stats) if in_stats is not None else z, c_f32(_EPS),
+                                c_i32(1 if relu else 0), ptr(skip) if skip is not None else z, ptr(out),
+                                ptr(stats) if stats is not None else z, stream_of(x)), "encoder.conv")
     return out
 
 
@@ -100,20 +102,26 @@ class BasicEncoder4:
         return out
 
     def _block(self, x, name, cin, cout, stride):
+        """ResidualBlock.forward (extractor.py:47-55).  With the instance norm: conv1 -> [norm + ReLU folded into conv2's
+        patch staging] -> conv2 -> one norm / ReLU / add / ReLU pass.  Without a norm everything is a conv epilogue."""
         n, H, W, _ = x.shape
+        w, b = self.w, self.b
+        if not self.norm:
+            y = _conv(x, w[name + ".conv1"], b[name + ".conv1"], n, H, W, cin, cout, 3, stride, 1.0, None, relu=True)
+            _, OH, OW, _ = y.shape
+            if stride != 1:
+                x = _conv(x, w[name + ".downsample.0"], b[name + ".downsample.0"], n, H, W, cin, cout, 1, stride, 1.0, None)
+            return _conv(y, w[name + ".conv2"], b[name + ".conv2"], n, OH, OW, cout, cout, 3, 1, 1.0, None, relu=True, skip=x)
         s1 = self._stats(n, cout)
-        r1 = _conv(x, self.w[name + ".conv1"], self.b[name + ".conv1"], n, H, W, cin, cout, 3, stride, 1.0, s1)
-        y = _norm_act(r1, s1)
-        _, OH, OW, _ = y.shape
+        r1 = _conv(x, w[name + ".conv1"], b[name + ".conv1"], n, H, W, cin, cout, 3, stride, 1.0, s1)
+        _, OH, OW, _ = r1.shape
         s2 = self._stats(n, cout)
-        r2 = _conv(y, self.w[name + ".conv2"], self.b[name + ".conv2"], n, OH, OW, cout, cout, 3, 1, 1.0, s2)
+        r2 = _conv(r1, w[name + ".conv2"], b[name + ".conv2"], n, OH, OW, cout, cout, 3, 1, 1.0, s2, in_stats=s1)
         if stride == 1:
             return _norm_act(r2, s2, skip=x)
         s3 = self._stats(n, cout)
-        r3 = _conv(x, self.w[name + ".downsample.0"], self.b[name + ".downsample.0"], n, H, W, cin, cout, 1, stride, 1.0, s3)
-        if self.norm:
-            return _norm_act(r2, s2, skip=r3, skip_stats=s3)
-        return _norm_act(r2, None, skip=r3)
+        r3 = _conv(x, w[name + ".downsample.0"], b[name + ".downsample.0"], n, H, W, cin, cout, 1, stride, 1.0, s3)
+        return _norm_act(r2, s2, skip=r3, skip_stats=s3)
 
     def __call__(self, images):
         require_cuda(images)
@@ -128,8 +136,9 @@ class BasicEncoder4:
         s0 = self._stats(b * n, 32)
         r0 = torch.empty((b * n, OH, OW, 32), dtype=torch.float16, device=x.device)
         check(lib.dpvo_encoder_conv7x7s2(ptr(x), ptr(self.w["conv1"]), ptr(self.b["conv1"]), c_i32(b * n), c_i32(H), c_i32(W),
-                                         ptr(r0), ptr(s0) if s0 is not None else c_p(0), stream_of(x)), "encoder.conv1")
-        y = _norm_act(r0, s0)
+                                         c_i32(0 if self.norm else 1), ptr(r0), ptr(s0) if s0 is not None else c_p(0),
+                                         stream_of(x)), "encoder.conv1")
+        y = _norm_act(r0, s0) if self.norm else r0
         y = self._block(y, "layer1.0", 32, 32, 1)
         y = self._block(y, "layer1.1", 32, 32, 1)
         y = self._block(y, "layer2.0", 32, 64, 2)
@@ -137,3 +146,53 @@ class BasicEncoder4:
         _, h, w, _ = y.shape
         out = _conv(y, self.w["conv2"], self.b["conv2"], b * n, h, w, 64, self.out_dim, 1, 1, self.scale, None)
         return FeatureMap(out)
+
+
+class Patchifier:
+    """`Patchifier.forward` (net.py:106-153) for inference: both encoders, the three patch gathers, the patch grid.
+
+    fnet / inet: BasicEncoder4 instances built with output_scale=0.25 (the reference divides both maps by 4).
+    Returns the reference's tuple (fmap, gmap, imap, patches, index[, clr]); `fmap` is the [1, n, 128, h, w] view of the
+    channels-last buffer, which is also kept as `.fmap_nhwc` together with its 4x4 average pool `.fmap2_nhwc` — the two
+    pyramid levels in the layout the feature ring stores (dpvo.py:437-438), so the ring write is a plain copy.
+    Patch centres: `coords` ([n, M, 2] float32, integer valued) or, like the reference's 'RANDOM' strategy, uniform in
+    [1, w-1) x [1, h-1).  'GRADIENT_BIAS' (net.py:117-129) is not built."""
+
+    def __init__(self, fnet, inet, patch_size=3):
+        self.fnet, self.inet, self.patch_size = fnet, inet, patch_size
+
+    @classmethod
+    def from_reference(cls, module):
+        return cls(BasicEncoder4.from_reference(module.fnet, 0.25), BasicEncoder4.from_reference(module.inet, 0.25),
+                   module.patch_size)
+
+    def __call__(self, images, patches_per_image=80, disps=None, centroid_sel_strat="RANDOM", return_color=False,
+                 coords=None):
+        from . import altcorr
+        if centroid_sel_strat != "RANDOM":
+            raise NotImplementedError(f"Patch centroid selection not built: {centroid_sel_strat}")
+        f = self.fnet(images)
+        i = self.inet(images)
+        self.fmap_nhwc = f.nhwc
+        self.fmap2_nhwc = avg_pool4(f.nhwc)
+        fmap, imap = f.nchw5, i.nchw5
+        b, n, c, h, w = fmap.shape
+        P = self.patch_size
+        dev = images.device
+        if coords is None:
+            x = torch.randint(1, w - 1, size=[n, patches_per_image], device=dev)
+            y = torch.randint(1, h - 1, size=[n, patches_per_image], device=dev)
+            coords = torch.stack([x, y], dim=-1).float()
+        imap_p = altcorr.patchify(imap[0], coords, 0).view(b, -1, imap.shape[2], 1, 1)
+        gmap = altcorr.patchify(fmap[0], coords, P // 2).view(b, -1, c, P, P)
+        if disps is None:
+            disps = torch.ones(b, n, h, w, device=dev)
+        ys, xs = torch.meshgrid(torch.arange(h, device=dev, dtype=torch.float32),
+                                torch.arange(w, device=dev, dtype=torch.float32), indexing="ij")
+        grid = torch.stack([xs.expand(b, n, h, w), ys.expand(b, n, h, w), disps], dim=2)     # utils.py:39-50
+        patches = altcorr.patchify(grid[0], coords, P // 2).view(b, -1, 3, P, P)
+        index = torch.arange(n, device=dev).view(n, 1).repeat(1, coords.shape[1]).reshape(-1)
+        if return_color:
+            clr = altcorr.patchify(images[0], 4 * (coords + 0.5), 0).view(b, -1, 3)
+            return fmap, gmap, imap_p, patches, index, clr
+        return fmap, gmap, imap_p, patches, index

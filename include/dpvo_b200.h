@@ -386,13 +386,15 @@ int dpvo_viewer_iproj(int32_t index, int32_t n_frames, float thresh, const uint8
 /* conv1: nn.Conv2d(3, 32, 7, stride=2, padding=3) on the fp32 NCHW image; weight fp16 packed [ky=7][cout=32][32]
  * with k = kx * 3 + c for the 21 live columns and zeros in the other 11 (torch weight [32,3,7,7] permuted) */
 int dpvo_encoder_conv7x7s2(const float* images, const void* weight, const float* bias, int32_t n_img, int32_t H,
-                           int32_t W, void* out, double* stats, void* stream);
+                           int32_t W, int32_t relu, void* out, double* stats, void* stream);
 /* 3x3 (padding 1) / 1x1 (padding 0) convolutions of the residual blocks and the output layer; weight fp16
  * [cout, ksize*ksize, cin]; out = (conv + bias) * scale.  Layers: 3x3 s1 32->32, 3x3 s2 32->64, 3x3 s1 64->64,
- * 1x1 s2 32->64, 1x1 s1 64->(multiple of 64). */
+ * 1x1 s2 32->64, 1x1 s1 64->(multiple of 64).  Fusions: in_stats != NULL applies relu(InstanceNorm(in)) while the
+ * input patch is staged (the producer's statistics, eps); relu != 0 and skip != NULL ([img, OH, OW, cout]) give
+ * out = relu(conv) and out = relu(skip + relu(conv)) for the norm-free encoder (exclusive with `stats`). */
 int dpvo_encoder_conv(const void* in, const void* weight, const float* bias, int32_t n_img, int32_t H, int32_t W,
-                      int32_t cin, int32_t cout, int32_t ksize, int32_t stride, float scale, void* out, double* stats,
-                      void* stream);
+                      int32_t cin, int32_t cout, int32_t ksize, int32_t stride, float scale, const double* in_stats,
+                      float eps, int32_t relu, const void* skip, void* out, double* stats, void* stream);
 /* out = relu(norm(raw)), or relu(skipv + relu(norm(raw))) with skipv = skip or norm(skip) (ResidualBlock.forward,
  * extractor.py:47-55); norm = InstanceNorm2d(affine=False, eps) from `stats`, identity when stats is NULL */
 int dpvo_encoder_norm_act(const void* raw, const double* stats, const void* skip, const double* skip_stats,

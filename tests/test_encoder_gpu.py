@@ -81,3 +81,37 @@ def test_avg_pool4_and_errors():
         e(torch.zeros(1, 1, 3, 16, 16))                       # CPU tensor
     with pytest.raises(RuntimeError):
         e(torch.zeros(1, 3, 16, 16, device="cuda"))
+
+
+def test_patchifier_matches_reference_gathers():
+    """Patchifier (net.py:106-153): with integer centres the three gathers are pure copies of the encoder maps, the
+    patch grid is (x + dx, y + dy, 1) and level 2 of the pyramid is the 4x4 average of level 1."""
+    enc, synth = load_pkg("encoder"), load_pkg("synth")
+    mk = lambda dim, norm, seed: enc.BasicEncoder4({k: torch.from_numpy(v) for k, v in synth.encoder_state_dict(dim, seed).items()},
+                                                   norm, output_scale=0.25)
+    pf = enc.Patchifier(mk(128, "instance", 1), mk(384, "none", 2))
+    images = torch.from_numpy(synth.encoder_images(2, 64, 96, 3)).cuda()
+    rng = np.random.default_rng(0)
+    h, w, M = 16, 24, 10
+    xy = np.stack([rng.integers(1, w - 1, (2, M)), rng.integers(1, h - 1, (2, M))], -1).astype(np.float32)
+    fmap, gmap, imap, patches, index, clr = pf(images, patches_per_image=M, return_color=True, coords=torch.from_numpy(xy).cuda())
+    assert fmap.shape == (1, 2, 128, h, w) and gmap.shape == (1, 2 * M, 128, 3, 3) and imap.shape == (1, 2 * M, 384, 1, 1)
+    assert patches.shape == (1, 2 * M, 3, 3, 3) and index.tolist() == [0] * M + [1] * M and clr.shape == (1, 2 * M, 3)
+    f = fmap[0].float().cpu().numpy()
+    i_full = pf.inet(images).nchw5[0].float().cpu().numpy()
+    g, im, p = gmap[0].float().cpu().numpy(), imap[0].float().cpu().numpy(), patches[0].cpu().numpy()
+    for n in range(2):
+        for m in range(M):
+            x, y = int(xy[n, m, 0]), int(xy[n, m, 1])
+            assert np.array_equal(g[n * M + m], f[n, :, y - 1:y + 2, x - 1:x + 2])
+            assert np.array_equal(im[n * M + m, :, 0, 0], i_full[n, :, y, x])
+            assert np.array_equal(p[n * M + m, 0], np.tile(np.arange(x - 1, x + 2, dtype=np.float32), (3, 1)))
+            assert np.array_equal(p[n * M + m, 1], np.tile(np.arange(y - 1, y + 2, dtype=np.float32)[:, None], (1, 3)))
+            assert np.all(p[n * M + m, 2] == 1)
+    lvl2 = pf.fmap2_nhwc.float().cpu().numpy()
+    want = pf.fmap_nhwc.float().cpu().numpy().reshape(2, h // 4, 4, w // 4, 4, 128).mean((2, 4))
+    assert lvl2.shape == (2, h // 4, w // 4, 128) and np.abs(lvl2 - want).max() < 2e-3 * max(1.0, np.abs(want).max())
+    with pytest.raises(NotImplementedError):
+        pf(images, centroid_sel_strat="GRADIENT_BIAS")
+    fmap_r, *_ = pf(images, patches_per_image=7)            # the reference's RANDOM strategy
+    assert fmap_r.shape == fmap.shape
