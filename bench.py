@@ -195,6 +195,35 @@ def update_iteration(hotpath, dev, seq, steps):
             "ms_per_step": round(ms, 4), "frames_per_s": round(1e3 / ms, 1), "edges": it.E}
 
 
+def bind_near_gpu(index):
+    """Pin this process to the CPUs of the GPU's NUMA node BEFORE any pinned host buffer is allocated, so the e2e leg's
+    staging memory is node-local (first touch).  Without it the 20.7 MB/frame host->device copy ran anywhere between
+    16 and 42 GB/s from one launch to the next.  (On this pool's boxes — 16 vCPUs, one NUMA node — it turns out to be
+    a no-op: the variation is external to the process.)  Returns the cpu list used, or None."""
+    try:
+        import subprocess
+        import torch
+        pr = torch.cuda.get_device_properties(index)
+        if hasattr(pr, "pci_bus_id"):
+            bus = f"{getattr(pr, 'pci_domain_id', 0):04x}:{pr.pci_bus_id:02x}:{getattr(pr, 'pci_device_id', 0):02x}.0"
+        else:
+            q = subprocess.run(["nvidia-smi", "-i", str(index), "--query-gpu=pci.bus_id", "--format=csv,noheader"],
+                               capture_output=True, text=True, timeout=10).stdout.strip().lower()
+            bus = q[-12:]
+        text = open(f"/sys/bus/pci/devices/{bus}/local_cpulist").read().strip()
+        cpus = set()
+        for part in text.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return text
+    except Exception:
+        return None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -222,6 +251,7 @@ def main():
         raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    host_cpus = None if os.environ.get("DPVO_BENCH_NO_BIND") else bind_near_gpu(local_rank)
 
     pkg = importlib.import_module(PKG)
     hotpath = importlib.import_module(PKG + ".hotpath")
@@ -294,13 +324,18 @@ def main():
         hp.capture_host()
     for _ in range(3):
         h2d, d2h = hp.step_host(hin, hout)
-    barrier()
-    e0.record()
-    for _ in range(args.steps):
-        h2d, d2h = hp.step_host(hin, hout)
-    e1.record()
-    barrier()
-    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+    # the host->device rate of these (virtualised) boxes moves between 20 and 42 GB/s from one minute to the next, so
+    # the K-step leg is run three times back to back and the MEDIAN is reported (all three are in e2e.repeats_ms)
+    e2e_runs = []
+    for _ in range(3):
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            h2d, d2h = hp.step_host(hin, hout)
+        e1.record()
+        barrier()
+        e2e_runs.append(max_over_ranks(e0.elapsed_time(e1)))
+    ms_e2e = sorted(e2e_runs)[1]
 
     if rank != 0:
         if world > 1:
@@ -316,9 +351,12 @@ def main():
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16 corr (f32 accumulate) / f32 BA",
         "data": "synthetic",
         "config": {"workload": WORKLOAD, "edges": hp.E, "parallelism": f"{world} independent sequence(s), no collective",
-                   "l2": "inputs larger than L2 (feature rings 188 MB + 80 MB correlation output per frame); no flush"},
+                   "l2": "inputs larger than L2 (feature rings 188 MB + 80 MB correlation output per frame); no flush",
+                   "host_cpus": host_cpus},
         "e2e": {"value": world * args.steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-                "d2h_bytes_per_step": int(d2h)},
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps,
+                "h2d_gbps_if_copy_bound": h2d * args.steps / (ms_e2e * 1e-3) / 1e9,
+                "repeats_ms": [round(x, 3) for x in e2e_runs]},
         "gpu_launches": int(round(launches_per_step * args.steps)),
         "launch_mode": launch_mode, "kernels_per_step": launches_per_step,
         "ms_per_step_stream_launch": ms_stream / args.steps,
