@@ -195,6 +195,30 @@ def update_iteration(hotpath, dev, seq, steps):
             "ms_per_step": round(ms, 4), "frames_per_s": round(1e3 / ms, 1), "edges": it.E}
 
 
+def image_frame(hotpath, dev, seq, steps):
+    """Extra, outside the headline metric: the hot-path frame fed from the 480x640 IMAGE — both encoders of
+    Patchifier in front of ring write / patchify / reproject / corr / BA, one CUDA graph."""
+    import torch
+    hp = hotpath.ImageFrontHotPath(dev, n_frames=40, seed=seq)
+    for _ in range(2):
+        hp.step()
+    torch.cuda.synchronize(dev)
+    hp.capture()
+    for _ in range(3):
+        hp.replay()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    e0.record()
+    for _ in range(steps):
+        hp.replay()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
+    return {"what": "fnet + inet (BasicEncoder4, 480x640 image) + level-2 pool + ring write + patchify + reproject + corr + BA, "
+                    "CUDA graph, device-resident image, random-initialised encoder weights",
+            "ms_per_step": round(ms, 4), "frames_per_s": round(1e3 / ms, 1), "h2d_bytes_if_streamed": int(hp.image.numel() * 4)}
+
+
 def bind_near_gpu(index):
     """Pin this process to the CPUs of the GPU's NUMA node BEFORE any pinned host buffer is allocated, so the e2e leg's
     staging memory is node-local (first touch).  Without it the 20.7 MB/frame host->device copy ran anywhere between
@@ -375,6 +399,10 @@ def main():
             pass
     if world == 1 and not args.no_update_iteration:
         line["update_iteration"] = update_iteration(hotpath, dev, seq, args.steps)
+        try:
+            line["image_frame"] = image_frame(hotpath, dev, seq, args.steps)
+        except Exception as ex:                      # an extra: never lose the headline line over it
+            line["image_frame"] = {"error": str(ex)[:200]}
     if world == 1 and not args.no_cpu_baseline:
         _, info = cpu_frame(hp.host, sample_edges=4096, steps=2)
         line["cpu_baseline"] = info

@@ -312,3 +312,40 @@ class UpdateIteration(UpdateHotPath):
         fastba.BA(self.poses, self.patches, self.intrinsics, target.contiguous(), weight, self.lmbda,
                   self.ii, self.jj, self.kk, self.t0, self.t1, self.M, 2, False, prepared=ws)
         return delta, weight
+
+
+class ImageFrontHotPath(UpdateHotPath):
+    """The hot-path frame fed from the IMAGE (SURVEY.md §8 row N3 in front of the north-star path): `Patchifier`'s
+    two encoders run on the device, their channels-last outputs are copied straight into the feature-ring slot
+    (dpvo.py:437-438: no transpose, level 2 = the fused 4x4 average pool) and the patch gathers read the strided views.
+    Same state, edge list and BA as UpdateHotPath; only the per-frame inputs come from the encoders instead of being
+    given (random-initialised encoder weights: synthetic, like everything else in the bench)."""
+
+    def __init__(self, device, n_frames=40, seed=0):
+        super().__init__(device, n_frames=n_frames, seed=seed)
+        from . import encoder
+        mk = lambda dim, norm, s: encoder.BasicEncoder4(
+            {k: torch.from_numpy(v) for k, v in synth.encoder_state_dict(dim, s).items()}, norm, device=device,
+            output_scale=0.25)
+        self._enc = encoder
+        self.fnet, self.inet = mk(128, "instance", 100 + seed), mk(384, "none", 200 + seed)
+        self.image = torch.from_numpy(synth.encoder_images(1, 4 * synth.H1, 4 * synth.W1, seed)).to(device)
+
+    def encode(self):
+        self._f = self.fnet(self.image)
+        self._i = self.inet(self.image)
+        self._f2 = self._enc.avg_pool4(self._f.nhwc)
+
+    def ring_write(self):
+        slot = (self.n - 1) % self.mem
+        self.fmap1[0, slot].permute(1, 2, 0).copy_(self._f.nhwc[0])       # ring memory is [H, W, C]
+        self.fmap2[0, slot].permute(1, 2, 0).copy_(self._f2[0])
+
+    def patchify(self):
+        g, = cuda_corr.patchify_forward(self._f.nchw5[0], self.centres, 1)
+        i, = cuda_corr.patchify_forward(self._i.nchw5[0], self.centres, 0)
+        return g, i
+
+    def step(self, events=None):
+        self.encode()
+        return super().step(events)

@@ -115,3 +115,25 @@ def test_patchifier_matches_reference_gathers():
         pf(images, centroid_sel_strat="GRADIENT_BIAS")
     fmap_r, *_ = pf(images, patches_per_image=7)            # the reference's RANDOM strategy
     assert fmap_r.shape == fmap.shape
+
+
+def test_image_fed_hot_path_writes_the_encoders_output_into_the_ring():
+    """hotpath.ImageFrontHotPath: the ring slot of the newest frame holds fnet(image) / 4 and its 4x4 average,
+    the gathered patches come from the same maps, and the frame still runs end to end (stream launches and graph)."""
+    hotpath = load_pkg("hotpath")
+    hp = hotpath.ImageFrontHotPath(torch.device("cuda", 0), n_frames=12, seed=1)
+    hp.step()
+    torch.cuda.synchronize()
+    slot = (hp.n - 1) % hp.mem
+    assert torch.equal(hp.fmap1[0, slot].permute(1, 2, 0), hp._f.nhwc[0])
+    assert torch.equal(hp.fmap2[0, slot].permute(1, 2, 0), hp._f2[0])
+    g, i = hp._patches_new
+    xy = hp.centres[0].long()
+    x, y = int(xy[5, 0]), int(xy[5, 1])
+    assert torch.equal(g[0, 5], hp._f.nchw5[0, 0, :, y - 1:y + 3, x - 1:x + 3])
+    assert torch.equal(i[0, 5, :, 0, 0], hp._i.nchw5[0, 0, :, y, x])
+    poses = hp.poses.clone()
+    hp.capture()
+    hp.replay()
+    torch.cuda.synchronize()
+    assert torch.isfinite(hp.poses).all() and torch.allclose(hp.poses, poses, atol=1e-5)
