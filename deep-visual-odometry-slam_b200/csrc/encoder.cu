@@ -24,6 +24,12 @@ __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], 
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, bool pred) {
+  const unsigned dst = (unsigned)__cvta_generic_to_shared(smem);
+  const int bytes = pred ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(gmem), "r"(bytes) : "memory");
+}
+
 // mean / rstd of one (image, channel) plane from the replicated float64 sums (biased variance, like InstanceNorm2d)
 __device__ __forceinline__ void plane_stats(const double* st, int64_t n, int C, int c, double inv_n, float eps, float& mean,
                                             float& rstd) {
@@ -187,27 +193,39 @@ conv_mma_kernel(const ConvParams p) {
   const int ox0 = blockIdx.x * TW, oy0 = blockIdx.y * TH;
   const int ix0 = ox0 * S - PAD, iy0 = oy0 * S - PAD;
   constexpr int CV = CIN / 8;                                         // 16-byte vectors per pixel
+  // staging with cp.async: every 16-byte piece of the patch and of the weights is in flight at once (with plain
+  // loads the kernel sat on the long scoreboard: ~50 dependent L2 round trips per thread, 4 warps per SM)
   for (int i = threadIdx.x; i < IH * IW * CV; i += 128) {
     const int v = i % CV, x = (i / CV) % IW, r = i / (CV * IW);
     const int iy = iy0 + r, ix = ix0 + x;
-    uint4 val = make_uint4(0, 0, 0, 0);
-    if (iy >= 0 && iy < p.H && ix >= 0 && ix < p.W) {
-      val = *reinterpret_cast<const uint4*>(p.in + (((int64_t)n * p.H + iy) * p.W + ix) * CIN + v * 8);
-      if (p.in_stats) {                       // the zero padding applies to the NORMALISED map: only live pixels change
+    const bool live = iy >= 0 && iy < p.H && ix >= 0 && ix < p.W;
+    const __half* src = live ? p.in + (((int64_t)n * p.H + iy) * p.W + ix) * CIN + v * 8 : p.in;
+    cp_async16(s_in + (r * IW + x) * CP + v * 8, src, live);          // out of bounds: zero fill
+  }
+  for (int i = threadIdx.x; i < KS * KS * NC * CV; i += 128) {
+    const int v = i % CV, o = (i / CV) % NC, tap = i / (CV * NC);
+    cp_async16(s_w + (tap * NC + o) * CP + v * 8, p.wgt + ((int64_t)(chunk * NC + o) * KS * KS + tap) * CIN + v * 8, true);
+  }
+  asm volatile("cp.async.commit_group;\n" ::: "memory");
+  asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+  __syncthreads();
+  if (p.in_stats) {
+    // relu(InstanceNorm(in)) in place on the live pixels (the zero padding applies to the NORMALISED map)
+    for (int i = threadIdx.x; i < IH * IW * CV; i += 128) {
+      const int v = i % CV, x = (i / CV) % IW, r = i / (CV * IW);
+      const int iy = iy0 + r, ix = ix0 + x;
+      if (iy >= 0 && iy < p.H && ix >= 0 && ix < p.W) {
+        uint4* q = reinterpret_cast<uint4*>(s_in + (r * IW + x) * CP + v * 8);
+        uint4 val = *q;
         __half* h = reinterpret_cast<__half*>(&val);
 #pragma unroll
         for (int c = 0; c < 8; ++c)
           h[c] = __float2half_rn(fmaxf((__half2float(h[c]) - s_norm[v * 8 + c][0]) * s_norm[v * 8 + c][1], 0.f));
+        *q = val;
       }
     }
-    *reinterpret_cast<uint4*>(s_in + (r * IW + x) * CP + v * 8) = val;
+    __syncthreads();
   }
-  for (int i = threadIdx.x; i < KS * KS * NC * CV; i += 128) {
-    const int v = i % CV, o = (i / CV) % NC, tap = i / (CV * NC);
-    const uint4 val = *reinterpret_cast<const uint4*>(p.wgt + ((int64_t)(chunk * NC + o) * KS * KS + tap) * CIN + v * 8);
-    *reinterpret_cast<uint4*>(s_w + (tap * NC + o) * CP + v * 8) = val;
-  }
-  __syncthreads();
 
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
   float acc[MT][NT][4];

@@ -171,10 +171,20 @@ class Patchifier:
         from . import altcorr
         if centroid_sel_strat != "RANDOM":
             raise NotImplementedError(f"Patch centroid selection not built: {centroid_sel_strat}")
+        main = torch.cuda.current_stream(images.device)          # inet beside fnet on a side stream (independent nets)
+        if getattr(self, "_side", None) is None:
+            self._side = torch.cuda.Stream(images.device)
+        fork, join = torch.cuda.Event(), torch.cuda.Event()
+        fork.record(main)
+        self._side.wait_event(fork)
+        with torch.cuda.stream(self._side):
+            i = self.inet(images)
+            i.nhwc.record_stream(main)
+            join.record(self._side)
         f = self.fnet(images)
-        i = self.inet(images)
         self.fmap_nhwc = f.nhwc
         self.fmap2_nhwc = avg_pool4(f.nhwc)
+        main.wait_event(join)
         fmap, imap = f.nchw5, i.nchw5
         b, n, c, h, w = fmap.shape
         P = self.patch_size

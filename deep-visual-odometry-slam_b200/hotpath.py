@@ -332,9 +332,21 @@ class ImageFrontHotPath(UpdateHotPath):
         self.image = torch.from_numpy(synth.encoder_images(1, 4 * synth.H1, 4 * synth.W1, seed)).to(device)
 
     def encode(self):
+        """The two encoders are independent and each layer fills a fraction of the GPU (150-600 CTAs of 4 warps):
+        inet runs on a side stream beside fnet (two branches of the frame graph)."""
+        main = torch.cuda.current_stream(self.device)
+        if getattr(self, "_enc_side", None) is None:
+            self._enc_side = torch.cuda.Stream(self.device)
+        fork, join = torch.cuda.Event(), torch.cuda.Event()
+        fork.record(main)
+        self._enc_side.wait_event(fork)
+        with torch.cuda.stream(self._enc_side):
+            self._i = self.inet(self.image)
+            self._i.nhwc.record_stream(main)
+            join.record(self._enc_side)
         self._f = self.fnet(self.image)
-        self._i = self.inet(self.image)
         self._f2 = self._enc.avg_pool4(self._f.nhwc)
+        main.wait_event(join)
 
     def ring_write(self):
         slot = (self.n - 1) % self.mem
