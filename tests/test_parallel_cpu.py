@@ -4,6 +4,7 @@ data-parallel flat-buffer gradient all-reduce with the folded found-inf flag."""
 import os
 import socket
 
+import numpy as np
 import pytest
 import torch
 import torch.distributed as dist
@@ -45,8 +46,9 @@ def _worker(rank, world, port, q):
     model(x).square().sum().backward()
     local = red.flat[:red.numel].clone()
     inf = red.allreduce()
-    out["local"] = local
-    out["reduced"] = red.flat[:red.numel].clone()
+    # plain numpy through the queue: torch tensors travel by fd passing, which races with this worker's exit
+    out["local"] = local.numpy().copy()
+    out["reduced"] = red.flat[:red.numel].clone().numpy().copy()
     out["grad_is_view"] = all(p.grad.data_ptr() >= red.flat.data_ptr() for p in model.parameters())
     out["inf"] = bool(inf)
     # --- overflow on ONE rank must make EVERY rank skip
@@ -82,10 +84,10 @@ def test_two_rank_gloo_group():
     # gradient all-reduce == mean of the per-rank gradients, identical on both ranks, in place
     mean = 0.5 * (res[0]["local"] + res[1]["local"])
     for r in range(world):
-        assert torch.allclose(res[r]["reduced"], mean, rtol=1e-6, atol=1e-7)
+        assert np.allclose(res[r]["reduced"], mean, rtol=1e-6, atol=1e-7)
         assert res[r]["grad_is_view"] and not res[r]["inf"]
         assert res[r]["inf2"] and res[r]["finite_after"]
-    assert torch.equal(res[0]["reduced"], res[1]["reduced"])
+    assert np.array_equal(res[0]["reduced"], res[1]["reduced"])
 
 
 def test_shard_sequences_properties():
