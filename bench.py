@@ -219,6 +219,48 @@ def image_frame(hotpath, dev, seq, steps):
             "ms_per_step": round(ms, 4), "frames_per_s": round(1e3 / ms, 1), "h2d_bytes_if_streamed": int(hp.image.numel() * 4)}
 
 
+def full_frame(hotpath, dev, seq, steps):
+    """Extra, outside the headline metric: one steady-state frame of DPVO.__call__ from the uint8 image to the
+    updated window (hotpath.FullFrame: normalisation, both encoders, gathers, slot writes, edge appends, reproject,
+    corr, Update operator, BA, point cloud, keyframe edits) as ONE CUDA graph; then the same frame with the image
+    coming from pinned host memory and the window's poses read back every frame."""
+    import torch
+    ff = hotpath.FullFrame(dev, n_frames=40, seed=seq)
+    ff.capture_frame()
+    for _ in range(3):
+        ff.replay_frame()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    e0.record()
+    for _ in range(steps):
+        ff.replay_frame()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
+    himg, hposes = ff.make_host_image()
+    for _ in range(3):
+        ff.step_frame_host(himg, hposes)
+    torch.cuda.synchronize(dev)
+    reps = []
+    for _ in range(3):
+        e0.record()
+        for _ in range(steps):
+            h2d, d2h = ff.step_frame_host(himg, hposes)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        reps.append(e0.elapsed_time(e1) / steps)
+    ms_host = sorted(reps)[1]
+    ff.edges.check_info()
+    return {"what": "uint8 image -> normalise + fnet + inet + gathers + slot writes + edge appends + reproject + corr + "
+                    "Update operator + BA + point cloud + keyframe edits (remove frame n-4, renumber, slot shifts, window "
+                    "removal), ONE CUDA graph, steady state, random-initialised weights",
+            "ms_per_step": round(ms, 4), "frames_per_s": round(1e3 / ms, 1), "edges": ff.E,
+            "edge_list_steady_count": ff.steady_edges,
+            "e2e": {"value": round(1e3 / ms_host, 1), "unit": "frames/s", "ms_per_step": round(ms_host, 4),
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "repeats_ms": [round(r, 4) for r in reps]}}
+
+
 def bind_near_gpu(index):
     """Pin this process to the CPUs of the GPU's NUMA node BEFORE any pinned host buffer is allocated, so the e2e leg's
     staging memory is node-local (first touch).  Without it the 20.7 MB/frame host->device copy ran anywhere between
@@ -403,6 +445,10 @@ def main():
             line["image_frame"] = image_frame(hotpath, dev, seq, args.steps)
         except Exception as ex:                      # an extra: never lose the headline line over it
             line["image_frame"] = {"error": str(ex)[:200]}
+        try:
+            line["full_frame"] = full_frame(hotpath, dev, seq, args.steps)
+        except Exception as ex:
+            line["full_frame"] = {"error": str(ex)[:300]}
     if world == 1 and not args.no_cpu_baseline:
         _, info = cpu_frame(hp.host, sample_edges=4096, steps=2)
         line["cpu_baseline"] = info
