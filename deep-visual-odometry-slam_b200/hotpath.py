@@ -503,6 +503,24 @@ class FullFrame(ImageFrontHotPath, UpdateIteration):
         self.keyframe()
         return out
 
+    def _rest(self):
+        """step_frame() without normalise + encode (they only depend on the image: see make_pipeline)."""
+        main = torch.cuda.current_stream(self.device)
+        if self._edge_side is None:
+            self._edge_side = torch.cuda.Stream(self.device)
+        fork, join = torch.cuda.Event(), torch.cuda.Event()
+        fork.record(main)
+        self._edge_side.wait_event(fork)
+        with torch.cuda.stream(self._edge_side):
+            self._edges_append()
+            self.motion_model()
+            join.record(self._edge_side)
+        out = self.step_full()
+        self.point_cloud()
+        main.wait_event(join)
+        self.keyframe()
+        return out
+
     def capture_frame(self):
         for _ in range(2):
             self.step_frame()
@@ -544,5 +562,60 @@ class FullFrame(ImageFrontHotPath, UpdateIteration):
         compute.wait_event(self._cp_done[b])
         self._frame_graphs[b].replay()
         self._cp_free[b].record(compute)
+        hposes.copy_(self.poses[0, self.t0:self.t1], non_blocking=True)
+        return himg.numel(), hposes.numel() * 4
+
+    # ---- software pipeline: frame t+1's encoders under frame t's update ------------------------------------
+    def make_pipeline(self):
+        """The encoders are the only stateless part of a frame (they read the image, nothing else): as their own CUDA
+        graph on their own stream, frame t+1's normalise + fnet + inet run UNDER frame t's update iteration; the rest of
+        the frame (gathers, slot writes, edge edits, update, keyframe) stays strictly sequential from frame to frame, as
+        DPVO's state requires.  Two sets of image / encoder-output buffers; events order copy -> encoders -> rest per
+        buffer and keep a buffer from being overwritten while the frame two back still reads it.  Per-frame latency is
+        unchanged, throughput goes from the sum towards the maximum of the two parts."""
+        dev = self.device
+        src = self.image_u8
+        self._u8 = [src.clone() for _ in range(2)]
+        self._cp, self._enc_stream = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        ev = lambda: [torch.cuda.Event() for _ in range(2)]
+        self._copied, self._enc_done, self._rest_done = ev(), ev(), ev()
+        self._enc_graphs, self._rest_graphs, self._enc_out = [], [], []
+        for b in range(2):
+            self.image_u8 = self._u8[b]
+            for _ in range(2):
+                self.step_frame()
+            torch.cuda.synchronize(dev)
+            ge = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(ge):
+                self.normalise()
+                self.encode()
+            ge.replay()
+            self._enc_out.append((self.image, self._f, self._i, self._f2))
+            torch.cuda.synchronize(dev)
+            self.edges.active.count()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr):
+                self._pipe_out = self._rest()
+            self._enc_graphs.append(ge)
+            self._rest_graphs.append(gr)
+        self._fi = 0
+        return src.cpu().pin_memory(), torch.empty((self.t1 - self.t0, 7), dtype=torch.float32).pin_memory()
+
+    def step_pipelined(self, himg, hposes):
+        b = self._fi & 1
+        self._fi += 1
+        compute = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(self._cp):
+            self._cp.wait_event(self._enc_done[b])            # frame t-2's encoders have read image buffer b
+            self._u8[b].copy_(himg, non_blocking=True)
+            self._copied[b].record(self._cp)
+        with torch.cuda.stream(self._enc_stream):
+            self._enc_stream.wait_event(self._copied[b])
+            self._enc_stream.wait_event(self._rest_done[b])   # frame t-2's gathers / ring write have read outputs b
+            self._enc_graphs[b].replay()
+            self._enc_done[b].record(self._enc_stream)
+        compute.wait_event(self._enc_done[b])
+        self._rest_graphs[b].replay()
+        self._rest_done[b].record(compute)
         hposes.copy_(self.poses[0, self.t0:self.t1], non_blocking=True)
         return himg.numel(), hposes.numel() * 4

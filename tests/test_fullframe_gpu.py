@@ -57,3 +57,22 @@ def test_full_frame_stream_and_graph():
     assert torch.isfinite(hposes).all()
     assert e.active.count() == ff.steady_edges
     e.check_info()
+
+
+def test_full_frame_pipelined_encoders():
+    """make_pipeline / step_pipelined: frame t+1's encoders under frame t's update.  Same image every frame, so the
+    ring slot written by each pipelined frame must equal what the in-order frame writes, whatever the overlap."""
+    hotpath = load_pkg("hotpath")
+    ff = hotpath.FullFrame(torch.device("cuda", 0), n_frames=12, seed=2, inactive_capacity=400_000)
+    ff.step_frame()
+    torch.cuda.synchronize()
+    slot = (ff.n - 1) % ff.mem
+    want = ff.fmap1[0, slot - 1].clone()                    # after the keyframe shift the new frame sits in slot n-2
+    himg, hposes = ff.make_pipeline()
+    for _ in range(7):
+        ff.step_pipelined(himg, hposes)
+    torch.cuda.synchronize()
+    assert torch.equal(ff.fmap1[0, slot - 1], want)
+    assert torch.isfinite(hposes).all()
+    assert ff.edges.active.count() == ff.steady_edges
+    ff.edges.check_info()
