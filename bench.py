@@ -37,6 +37,8 @@ UNIT = "frames/s"
 WORKLOAD = ("dpvo_default_480x640_M96_steady_state: E=45312 edges, fmap rings 36x128x120x160 + 36x128x30x40 fp16, "
             "BA window 10 poses x 2 iterations")
 
+_STDOUT = sys.stdout
+
 
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -165,7 +167,7 @@ def run_reference(args, rank, world):
             "vs_baseline": None, "dtype": "f16 features, f32 correlation / f64 BA (CPU)", "data": "synthetic",
             "config": {"workload": WORKLOAD}, "cpu_baseline": info, "wall_s": wall,
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_STDOUT, flush=True)
 
 
 def update_iteration(hotpath, dev, seq, steps):
@@ -325,6 +327,12 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly ONE JSON line: libraries that print there (NCCL writes "NCCL version ..." to stdout when
+    # the box sets NCCL_DEBUG) are sent to stderr by pointing fd 1 at fd 2; the line goes out through the saved fd.
+    global _STDOUT
+    sys.stdout.flush()
+    _STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
     if args.impl == "reference":
         run_reference(args, rank, world)
@@ -471,7 +479,7 @@ def main():
     if world == 1 and not args.no_cpu_baseline:
         _, info = cpu_frame(hp.host, sample_edges=4096, steps=2)
         line["cpu_baseline"] = info
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_STDOUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
