@@ -454,7 +454,7 @@ def main():
         "launch_mode": launch_mode, "kernels_per_step": launches_per_step,
         "ms_per_step_stream_launch": ms_stream / args.steps,
         "stage_ms": {k: round(v, 4) for k, v in stage_ms.items()},
-        "roofline": {"kernel": "corr_fwd_mma_f16_kernel<2,3,3>", "bound": "hbm", "achieved": achieved, "peak": peak,
+        "roofline": {"kernel": "corr_fwd_mma_f16_kernel<2, 1>", "bound": "hbm", "achieved": achieved, "peak": peak,
                      "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                      "algorithmic_bytes_per_launch": int(alg_bytes), "ms_per_launch": corr_ms},
         "clocks": clocks,
