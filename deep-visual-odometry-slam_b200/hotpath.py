@@ -466,16 +466,26 @@ class FullFrame(ImageFrontHotPath, UpdateIteration):
         ii, jj, kk = self._mm
         flow, _ = self._pops.flow_mag(self.poses, self.patches, self.intrinsics, ii, jj, kk, beta=0.5)
         self.motion = flow.mean()                                     # device scalar; the reference reads it (.item())
+        # the slot shifts touch the frame buffers, the edge edits the edge list: two branches
+        main = torch.cuda.current_stream(self.device)
+        if getattr(self, "_shift_side", None) is None:
+            self._shift_side = torch.cuda.Stream(self.device)
+        fork, join = torch.cuda.Event(), torch.cuda.Event()
+        fork.record(main)
+        self._shift_side.wait_event(fork)
+        with torch.cuda.stream(self._shift_side):
+            k, n, M = self.n - self.KEYFRAME_INDEX, self.n, self.M
+            shift = self._pg.frames_shift
+            shift(self.fmap1.permute(0, 1, 3, 4, 2)[0], k, n, mod=self.mem)
+            shift(self.fmap2.permute(0, 1, 3, 4, 2)[0], k, n, mod=self.mem)
+            shift(self.gmap[0].view(self.mem, -1), k, n, mod=self.mem)
+            shift(self.imap.view(self.mem, -1), k, n, mod=self.mem)
+            shift(self.poses[0], k, n)
+            shift(self.patches[0].view(-1, M * 27), k, n)
+            shift(self.intrinsics[0], k, n)
+            join.record(self._shift_side)
         self._edges_keyframe()
-        k, n, M = self.n - self.KEYFRAME_INDEX, self.n, self.M
-        shift = self._pg.frames_shift
-        shift(self.poses[0], k, n)
-        shift(self.patches[0].view(-1, M * 27), k, n)
-        shift(self.intrinsics[0], k, n)
-        shift(self.imap.view(self.mem, -1), k, n, mod=self.mem)
-        shift(self.gmap[0].view(self.mem, -1), k, n, mod=self.mem)
-        shift(self.fmap1.permute(0, 1, 3, 4, 2)[0], k, n, mod=self.mem)
-        shift(self.fmap2.permute(0, 1, 3, 4, 2)[0], k, n, mod=self.mem)
+        main.wait_event(join)
 
     def point_cloud(self):
         """dpvo.py:356-358."""

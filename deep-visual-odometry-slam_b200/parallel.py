@@ -108,9 +108,14 @@ class FlatGradAllReducer:
             torch.nan_to_num_(g, nan=0.0, posinf=0.0, neginf=0.0)
         self.flat[self.numel] = flag
         if dist.is_initialized():
-            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
-            if average:
-                g.mul_(1.0 / dist.get_world_size())
+            if average and dist.get_backend() == "nccl":
+                # NCCL averages inside the collective (no extra pass over the buffer); the flag slot becomes
+                # (ranks that overflowed) / world, still > 0 exactly when any rank overflowed
+                dist.all_reduce(self.flat, op=dist.ReduceOp.AVG)
+            else:
+                dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
+                if average:
+                    g.mul_(1.0 / dist.get_world_size())
         return self.flat[self.numel] > 0
 
     def nbytes(self):
