@@ -459,6 +459,20 @@ def main():
                      "algorithmic_bytes_per_launch": int(alg_bytes), "ms_per_launch": corr_ms},
         "clocks": clocks,
     }
+    # The lookup hits L2 for ~2/3 of its sectors (neighbouring edges share window pixels), so DRAM is not what binds it:
+    # the same bytes as an L2->SM delivery rate, against the two ceilings on record (profiles/r01_notes.md: 33 B/clk/SM
+    # measured by tools/tma_probe.py with all SMs pulling; ~6,300 B/clk chip-wide LTS cap in the microarchitecture notes).
+    try:
+        import torch
+        n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+        mhz = clocks.get("sm_mhz") or clocks.get("sm_max_mhz")
+        if mhz:
+            per_sm = alg_bytes / (corr_ms * 1e-3) / (mhz * 1e6) / n_sm
+            line["roofline"]["l2_to_sm"] = {"achieved_B_per_clk_per_SM": round(per_sm, 2), "probe_ceiling": 33.0,
+                                            "lts_cap": round(6300.0 / n_sm, 1), "frac_of_probe_ceiling": round(per_sm / 33.0, 3),
+                                            "sm_mhz": mhz, "sms": n_sm}
+    except Exception:
+        pass
     tr = os.path.join(ROOT, "profiles", "corr_traffic.json")
     if os.path.exists(tr):
         try:
