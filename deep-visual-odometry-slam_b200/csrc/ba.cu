@@ -509,18 +509,43 @@ ba_solve_reg_kernel(const __grid_constant__ BADev p) {
     if (tid == 0) p.meta[1] = 1;  // tells backsub to skip the depth update too
     return;
   }
-  for (int i = tid; i < n; i += 256) x[i] = Ls[i * ldL + n];   // z
-  __syncthreads();
-  if (wid == 0) {
-    for (int j = n - 1; j >= 0; --j) {
-      const float xj = x[j] * dinv[j];
-      __syncwarp();
-      if (lane == 0) x[j] = xj;
-      for (int i = lane; i < j; i += 32) x[i] -= Ls[i * ldL + j] * xj;
-      __syncwarp();
+  if (TS == 4) {
+    // n < 64: L^T x = z by one warp with x in registers (lane l holds x[l] and x[l + 32]); the only chain per column
+    // is shuffle -> multiply -> fused multiply-add, the L entries are independent loads the scheduler hoists
+    __syncthreads();
+    if (wid == 0) {
+      const int i0 = lane, i1 = lane + 32;
+      float x0 = i0 < n ? Ls[i0 * ldL + n] : 0.f, x1 = i1 < n ? Ls[i1 * ldL + n] : 0.f;   // z
+      const float d0 = i0 < n ? dinv[i0] : 0.f, d1 = i1 < n ? dinv[i1] : 0.f;
+      for (int j = n - 1; j >= 32; --j) {
+        const float xj = __shfl_sync(0xffffffffu, x1 * d1, j - 32);
+        if (i1 == j) x1 = xj;
+        x0 -= Ls[i0 * ldL + j] * xj;                       // i0 < 32 <= j
+        if (i1 < j) x1 -= Ls[i1 * ldL + j] * xj;
+      }
+      for (int j = (n < 32 ? n : 32) - 1; j >= 0; --j) {
+        const float xj = __shfl_sync(0xffffffffu, x0 * d0, j);
+        if (i0 == j) x0 = xj;
+        if (i0 < j) x0 -= Ls[i0 * ldL + j] * xj;
+      }
+      if (i0 < n) x[i0] = x0;
+      if (i1 < n) x[i1] = x1;
     }
+    __syncthreads();
+  } else {
+    for (int i = tid; i < n; i += 256) x[i] = Ls[i * ldL + n];   // z
+    __syncthreads();
+    if (wid == 0) {
+      for (int j = n - 1; j >= 0; --j) {
+        const float xj = x[j] * dinv[j];
+        __syncwarp();
+        if (lane == 0) x[j] = xj;
+        for (int i = lane; i < j; i += 32) x[i] -= Ls[i * ldL + j] * xj;
+        __syncwarp();
+      }
+    }
+    __syncthreads();
   }
-  __syncthreads();
   for (int i = tid; i < n; i += 256) p.dX[i] = x[i];
   if (tid == 0) p.meta[1] = 0;
   for (int i = tid; i < N; i += 256) {
