@@ -303,6 +303,11 @@ class UpdateIteration(UpdateHotPath):
         us = self.kk % self.n_patches
         vs = self.jj % self.mem
         corr = altcorr.corr_pyramid(self.gmap, (self.fmap1, self.fmap2), coords, us, vs, 3, row_stride=896)
+        if torch.cuda.is_current_stream_capturing():
+            # the hidden state read by a captured frame is baked into the graph as a pointer, and the attribute is
+            # rebound to the graph's output just below: keep the input alive, or the caching allocator may hand its
+            # block out again — or unmap it at the next capture's empty_cache() — under the graph's feet
+            self._captured_inputs = getattr(self, "_captured_inputs", []) + [self.net]
         self.net, (delta, weight, _) = self.update_op(self.net, (self.imap, self.ctx_index), corr, None,
                                                       self.ii, self.jj, self.kk, n_frames=self.n,
                                                       n_patches=self.n_patch_ids)

@@ -41,6 +41,7 @@ def test_full_frame_stream_and_graph():
     # the graph replays the same frame
     d0, w0 = delta.clone(), weight.clone()
     ff.capture_frame()
+    torch.cuda.empty_cache()        # a graph must own or keep alive everything it reads (every later capture does this too)
     d1, w1 = ff.replay_frame()
     torch.cuda.synchronize()
     assert torch.isfinite(d1.float()).all() and d1.shape == d0.shape and w1.shape == w0.shape
@@ -51,6 +52,7 @@ def test_full_frame_stream_and_graph():
     e.check_info()
     # host-buffer variant: uint8 image in, window poses out
     himg, hposes = ff.make_host_image()
+    torch.cuda.empty_cache()
     for _ in range(4):
         ff.step_frame_host(himg, hposes)
     torch.cuda.synchronize()
@@ -69,6 +71,7 @@ def test_full_frame_pipelined_encoders():
     slot = (ff.n - 1) % ff.mem
     want = ff.fmap1[0, slot - 1].clone()                    # after the keyframe shift the new frame sits in slot n-2
     himg, hposes = ff.make_pipeline()
+    torch.cuda.empty_cache()
     for _ in range(7):
         ff.step_pipelined(himg, hposes)
     torch.cuda.synchronize()
