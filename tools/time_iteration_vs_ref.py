@@ -8,7 +8,8 @@
 
 The reference side is given every advantage that is cheap to give: cuda_ba.reproject instead of the
 lietorch + projective_ops chain it really calls (dpvo.py:209-213), neighbours computed once per iteration.
-Test / measurement infrastructure: this is one of the places allowed to load oracle/_ref.
+Development-time measurement tool (like tools/time_corr.py --ref): it is not part of the package, the tests or bench.py, and
+nothing in the product path loads oracle/.
 """
 import importlib
 import json
