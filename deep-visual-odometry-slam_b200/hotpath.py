@@ -543,6 +543,7 @@ class FullFrame(ImageFrontHotPath, UpdateIteration):
         self.edges.active.count()
         self.edges.check_info()
         self._frame_graph = torch.cuda.CUDAGraph()
+        self._captured_inputs = getattr(self, "_captured_inputs", []) + [self.image_u8]   # the graph reads this buffer
         with torch.cuda.graph(self._frame_graph):
             self._frame_out = self.step_frame()
         return self._frame_graph
@@ -590,13 +591,13 @@ class FullFrame(ImageFrontHotPath, UpdateIteration):
         unchanged, throughput goes from the sum towards the maximum of the two parts."""
         dev = self.device
         src = self.image_u8
-        self._u8 = [src.clone() for _ in range(2)]
-        self._cp, self._enc_stream = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        self._pu8 = [src.clone() for _ in range(2)]
+        self._pcp, self._enc_stream = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
         ev = lambda: [torch.cuda.Event() for _ in range(2)]
-        self._copied, self._enc_done, self._rest_done = ev(), ev(), ev()
+        self._pcopied, self._enc_done, self._rest_done = ev(), ev(), ev()
         self._enc_graphs, self._rest_graphs, self._enc_out = [], [], []
         for b in range(2):
-            self.image_u8 = self._u8[b]
+            self.image_u8 = self._pu8[b]
             for _ in range(2):
                 self.step_frame()
             torch.cuda.synchronize(dev)
@@ -613,19 +614,19 @@ class FullFrame(ImageFrontHotPath, UpdateIteration):
                 self._pipe_out = self._rest()
             self._enc_graphs.append(ge)
             self._rest_graphs.append(gr)
-        self._fi = 0
+        self._pfi = 0
         return src.cpu().pin_memory(), torch.empty((self.t1 - self.t0, 7), dtype=torch.float32).pin_memory()
 
     def step_pipelined(self, himg, hposes):
-        b = self._fi & 1
-        self._fi += 1
+        b = self._pfi & 1
+        self._pfi += 1
         compute = torch.cuda.current_stream(self.device)
-        with torch.cuda.stream(self._cp):
-            self._cp.wait_event(self._enc_done[b])            # frame t-2's encoders have read image buffer b
-            self._u8[b].copy_(himg, non_blocking=True)
-            self._copied[b].record(self._cp)
+        with torch.cuda.stream(self._pcp):
+            self._pcp.wait_event(self._enc_done[b])            # frame t-2's encoders have read image buffer b
+            self._pu8[b].copy_(himg, non_blocking=True)
+            self._pcopied[b].record(self._pcp)
         with torch.cuda.stream(self._enc_stream):
-            self._enc_stream.wait_event(self._copied[b])
+            self._enc_stream.wait_event(self._pcopied[b])
             self._enc_stream.wait_event(self._rest_done[b])   # frame t-2's gathers / ring write have read outputs b
             self._enc_graphs[b].replay()
             self._enc_done[b].record(self._enc_stream)
