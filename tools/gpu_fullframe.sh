@@ -1,3 +1,4 @@
+# hotpath.FullFrame tests + the bench line with its extras.
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests/test_fullframe_gpu.py -x -q 2>&1 | tail -30
 timeout 900 python bench.py --no-cpu-baseline > gpurun_out/bench_n.json 2>gpurun_out/bench_n.err; echo rc=$?; python -c "

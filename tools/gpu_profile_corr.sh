@@ -1,3 +1,4 @@
+# ncu --set full of the correlation lookup + launch list of the default bench command (stream launches).
 mkdir -p gpurun_out
 timeout 300 python tools/time_corr.py --iters 5 > gpurun_out/time_corr_p.log 2>&1; echo rc=$?; tail -1 gpurun_out/time_corr_p.log
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:corr_fwd -c 2 -f -o gpurun_out/corr_full_r01b python tools/time_corr.py --iters 1 > gpurun_out/ncu_corr_full.log 2>&1; echo ncu rc=$?

@@ -1,3 +1,5 @@
+# Full check on one B200: GPU test suite, smoke(), both bench arms, ncu launch list of the full frame.
+# gpurun --timeout 3000 -- "bash tools/gpu_verify.sh"
 mkdir -p gpurun_out
 timeout 2400 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
 timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -3
