@@ -70,3 +70,26 @@ def require_cuda(*tensors):
     for t in tensors:
         if not t.is_cuda:
             raise RuntimeError("dpvo_b200: expected CUDA tensors (no CPU path is provided for this operator)")
+
+
+class device_guard:
+    """Make the tensor's device current for the duration of a ctypes launch (kernels are launched on
+    that device's current torch stream; the reference extensions rely on the caller for this)."""
+    __slots__ = ("idx", "prev")
+
+    def __init__(self, t):
+        self.idx = t.device.index if t is not None and t.is_cuda else None
+        self.prev = None
+
+    def __enter__(self):
+        if self.idx is not None:
+            cur = torch.cuda.current_device()
+            if cur != self.idx:
+                self.prev = cur
+                torch.cuda.set_device(self.idx)
+        return self
+
+    def __exit__(self, *exc):
+        if self.prev is not None:
+            torch.cuda.set_device(self.prev)
+        return False

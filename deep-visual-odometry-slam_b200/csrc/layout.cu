@@ -3,17 +3,20 @@
 // correlation gather reads whole 16-byte vectors).  Tiled through shared memory
 // so both the read (along HW) and the write (along C) are coalesced.
 #include "common.cuh"
+#include <algorithm>
 
 namespace dpvo {
 
 template <typename T>
 __global__ void __launch_bounds__(256)
-nchw_to_nhwc_kernel(const T* __restrict__ src, T* __restrict__ dst, int C, int64_t HW, int64_t tiles_hw, int tiles_c) {
+nchw_to_nhwc_kernel(const T* __restrict__ src, T* __restrict__ dst, int C, int64_t HW, int64_t tiles_hw, int tiles_c,
+                    const unsigned long long* __restrict__ hnew, const unsigned long long* __restrict__ hold) {
   // tile: 64 pixels x 64 channels
   __shared__ T tile[64][64 + 2];
   const int64_t blk = blockIdx.x;
   const int64_t per_img = tiles_hw * tiles_c;
   const int64_t n = blk / per_img;
+  if (hnew != nullptr && hnew[n] == hold[n]) return;   // slot unchanged since the last sync
   const int64_t r = blk - n * per_img;
   const int tc = (int)(r / tiles_hw);
   const int64_t th = r - (int64_t)tc * tiles_hw;
@@ -41,11 +44,13 @@ nchw_to_nhwc_kernel(const T* __restrict__ src, T* __restrict__ dst, int C, int64
 // instruction = 64 consecutive channels of one pixel (128 B).  4-byte accesses on both sides.
 __global__ void __launch_bounds__(256)
 nchw_to_nhwc_u16_kernel(const unsigned short* __restrict__ src, unsigned short* __restrict__ dst, int C, int64_t HW,
-                        int64_t tiles_hw, int tiles_c) {
+                        int64_t tiles_hw, int tiles_c,
+                        const unsigned long long* __restrict__ hnew, const unsigned long long* __restrict__ hold) {
   __shared__ uint32_t tile[64][64 + 1];          // [pixel][channel pair]
   const int64_t blk = blockIdx.x;
   const int64_t per_img = tiles_hw * tiles_c;
   const int64_t n = blk / per_img;
+  if (hnew != nullptr && hnew[n] == hold[n]) return;   // slot unchanged since the last sync
   const int64_t r = blk - n * per_img;
   const int tc = (int)(r / tiles_hw);
   const int64_t p0 = (r - (int64_t)tc * tiles_hw) * 64;
@@ -81,8 +86,48 @@ nchw_to_nhwc_u16_kernel(const unsigned short* __restrict__ src, unsigned short* 
   }
 }
 
+// Per-slot 64-bit content hash of the source ring: sum over 16-byte words of a position-keyed
+// splitmix64 finaliser (order-independent accumulation, so CTAs add with one atomic each).
+// One pass over the source (the cheapest possible "which slots changed" test: the slot writes of
+// the unmodified reference, dpvo.py:435-438,296-299, are plain torch copies this library never sees).
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+  z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL;
+  z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+  return z ^ (z >> 31);
+}
+
+__global__ void __launch_bounds__(256)
+slot_hash_kernel(const uint4* __restrict__ src, int64_t words_per_slot, int chunks, unsigned long long* __restrict__ hash) {
+  const int64_t n = blockIdx.x / chunks;
+  const int chunk = blockIdx.x - (int)(n * chunks);
+  const int64_t per = ceil_div64(words_per_slot, chunks);
+  const int64_t w0 = (int64_t)chunk * per;
+  const int64_t w1 = min(words_per_slot, w0 + per);
+  const uint4* s = src + n * words_per_slot;
+  unsigned long long acc = 0;
+  for (int64_t w = w0 + threadIdx.x; w < w1; w += 256) {
+    const uint4 v = __ldg(s + w);
+    const unsigned long long a = ((unsigned long long)v.y << 32) | v.x;
+    const unsigned long long b = ((unsigned long long)v.w << 32) | v.z;
+    const unsigned long long key = (unsigned long long)w * 0x9e3779b97f4a7c15ULL;
+    acc += mix64(a + key) + mix64(b ^ (key + 0x632be59bd9b4e019ULL));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  __shared__ unsigned long long part[8];
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long t = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += part[i];
+    atomicAdd(hash + n, t + 1ULL);   // +1 per chunk: an all-zero slot does not hash to the memset value
+  }
+}
+
 template <typename T>
-static int launch(const void* src, void* dst, int64_t N, int C, int64_t HW, cudaStream_t st) {
+static int launch(const void* src, void* dst, int64_t N, int C, int64_t HW, cudaStream_t st,
+                  const unsigned long long* hnew = nullptr, const unsigned long long* hold = nullptr) {
   const int64_t tiles_hw = ceil_div64(HW, 64);
   const int tiles_c = (C + 63) / 64;
   const int64_t blocks = N * tiles_hw * tiles_c;
@@ -93,12 +138,13 @@ static int launch(const void* src, void* dst, int64_t N, int C, int64_t HW, cuda
     const int64_t blocks2 = N * tiles_hw * tc2;
     note_launches(1);
     nchw_to_nhwc_u16_kernel<<<(unsigned)blocks2, 256, 0, st>>>(
-        reinterpret_cast<const unsigned short*>(src), reinterpret_cast<unsigned short*>(dst), C, HW, tiles_hw, tc2);
+        reinterpret_cast<const unsigned short*>(src), reinterpret_cast<unsigned short*>(dst), C, HW, tiles_hw, tc2,
+        hnew, hold);
     return check_launch("nchw_to_nhwc");
   }
   note_launches(1);
   nchw_to_nhwc_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(
-      reinterpret_cast<const T*>(src), reinterpret_cast<T*>(dst), C, HW, tiles_hw, tiles_c);
+      reinterpret_cast<const T*>(src), reinterpret_cast<T*>(dst), C, HW, tiles_hw, tiles_c, hnew, hold);
   return check_launch("nchw_to_nhwc");
 }
 
@@ -115,5 +161,37 @@ extern "C" int dpvo_nchw_to_nhwc(dpvo_dtype dtype, const void* src, void* dst,
     case DPVO_F64: return dpvo::launch<double>(src, dst, N, C, HW, st);
   }
   dpvo::set_error("nchw_to_nhwc: unknown dtype");
+  return 1;
+}
+
+extern "C" int dpvo_ring_sync(dpvo_dtype dtype, const void* src, void* dst, int64_t N, int32_t C, int64_t HW,
+                              void* hashes, int32_t parity, void* stream) {
+  DPVO_REQUIRE(src && dst && hashes, "ring_sync: null pointer");
+  DPVO_REQUIRE(N >= 0 && C > 0 && HW >= 0, "ring_sync: bad sizes");
+  DPVO_REQUIRE(parity == 0 || parity == 1, "ring_sync: parity must be 0 or 1");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int64_t esz = dtype == DPVO_F16 ? 2 : dtype == DPVO_F32 ? 4 : 8;
+  const int64_t slot_bytes = (int64_t)C * HW * esz;
+  DPVO_REQUIRE(slot_bytes % 16 == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0,
+               "ring_sync: slots must be 16-byte multiples and aligned (use dpvo_nchw_to_nhwc)");
+  if (N == 0 || slot_bytes == 0) return 0;
+  unsigned long long* hnew = reinterpret_cast<unsigned long long*>(hashes) + (int64_t)parity * N;
+  const unsigned long long* hold = reinterpret_cast<unsigned long long*>(hashes) + (int64_t)(1 - parity) * N;
+  if (cudaMemsetAsync(hnew, 0, sizeof(unsigned long long) * N, st) != cudaSuccess) {
+    dpvo::set_error("ring_sync: memset failed");
+    return 1;
+  }
+  const int64_t words = slot_bytes / 16;
+  int chunks = (int)dpvo::ceil_div64(dpvo::kNumSMs * 8, N);
+  chunks = (int)std::max<int64_t>(1, std::min<int64_t>(chunks, dpvo::ceil_div64(words, 1024)));
+  dpvo::note_launches(1);
+  dpvo::slot_hash_kernel<<<(unsigned)(N * chunks), 256, 0, st>>>(reinterpret_cast<const uint4*>(src), words, chunks, hnew);
+  if (dpvo::check_launch("ring_sync: hash")) return 1;
+  switch (dtype) {
+    case DPVO_F16: return dpvo::launch<unsigned short>(src, dst, N, C, HW, st, hnew, hold);
+    case DPVO_F32: return dpvo::launch<float>(src, dst, N, C, HW, st, hnew, hold);
+    case DPVO_F64: return dpvo::launch<double>(src, dst, N, C, HW, st, hnew, hold);
+  }
+  dpvo::set_error("ring_sync: unknown dtype");
   return 1;
 }

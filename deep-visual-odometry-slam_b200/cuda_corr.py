@@ -15,6 +15,7 @@ Everything here is plumbing: shape/dtype validation, output allocation through
 torch's caching allocator and one ctypes call into libdpvo_b200.so on torch's
 current stream.
 """
+import collections
 import ctypes
 import weakref
 
@@ -27,46 +28,92 @@ from ._lib import lib, CorrLevel, ptr, stream_of, check, dtype_code, require_cud
 # The reference DPVO keeps its feature ring NCHW (dpvo.py:72-73).  The sm_100a
 # gather wants channels-last.  A caller that allocates the ring channels-last
 # (e.g. torch.zeros(1,N,H,W,C).permute(0,1,4,2,3)) is used zero-copy; for an
-# NCHW ring a channels-last shadow is kept per tensor object and refreshed when
-# the tensor's version counter moves.
-_shadow = {}  # id(tensor) -> (weakref, version, data_ptr, shadow)
-_SHADOW_MAX = 8
-shadow_refreshes = 0  # instrumentation for tests / bench
+# NCHW ring a channels-last shadow is kept per tensor object.  When the tensor's
+# version counter has moved (the reference writes one slot per frame and shifts a
+# few on keyframe removal, dpvo.py:435-438,296-299), `dpvo_ring_sync` hashes every
+# slot of the source in one read pass and re-transposes only the slots whose
+# content changed — no host synchronisation, ~1/3 of the traffic of a full refresh.
+# Writes that do not move the version counter (raw-pointer kernels, CUDA-graph
+# replays, `.data` writes) need `invalidate(fmap)`; tensors without a version
+# counter (inference mode) are re-hashed on every call.
+_shadow = collections.OrderedDict()  # id(tensor) -> _Shadow  (LRU)
+_SHADOW_MAX = 16
+shadow_refreshes = 0  # number of sync passes issued (instrumentation for tests / bench)
+shadow_hits = 0
 
 
-def _drop_shadow(key):
-    _shadow.pop(key, None)
+class _Shadow:
+    __slots__ = ("ref", "version", "data_ptr", "view", "hashes", "parity")
+
+
+def _version_of(t):
+    try:
+        return t._version
+    except Exception:          # inference-mode tensors do not track a version
+        return None
+
+
+def invalidate(fmap=None):
+    """Force the next lookup to re-examine the ring (all rings if `fmap` is None).  Needed only after
+    writes torch does not see: raw-pointer kernels, CUDA-graph replays, `.data` assignments."""
+    if fmap is None:
+        for ent in _shadow.values():
+            ent.version = -1
+    else:
+        ent = _shadow.get(id(fmap))
+        if ent is not None:
+            ent.version = -1
+
+
+def shadow_stats():
+    return {"entries": len(_shadow), "syncs": shadow_refreshes, "hits": shadow_hits,
+            "bytes": sum(e.view.numel() * e.view.element_size() for e in _shadow.values())}
 
 
 def _channels_last_view(fmap):
     """Return a tensor with the same logical [B,N,C,H,W] shape whose channel stride is 1."""
-    global shadow_refreshes
+    global shadow_refreshes, shadow_hits
     if fmap.stride(2) == 1 or fmap.shape[2] == 1:
         return fmap
     key = id(fmap)
     ent = _shadow.get(key)
+    ver = _version_of(fmap)
     if ent is not None:
-        ref, ver, dptr, shadow = ent
-        if ref() is fmap and dptr == fmap.data_ptr() and shadow.shape == fmap.shape:
-            if ver == fmap._version:
-                return shadow
+        if ent.ref() is fmap and ent.data_ptr == fmap.data_ptr() and ent.view.shape == fmap.shape:
+            _shadow.move_to_end(key)
+            if ver is not None and ent.version == ver:
+                shadow_hits += 1
+                return ent.view
         else:
+            _shadow.pop(key, None)
             ent = None
     B, N, C, H, W = fmap.shape
     if ent is None:
-        if len(_shadow) >= _SHADOW_MAX:
-            _shadow.pop(next(iter(_shadow)))
-        store = torch.empty((B, N, H, W, C), dtype=fmap.dtype, device=fmap.device)
-        shadow = store.permute(0, 1, 4, 2, 3)
-        ref = weakref.ref(fmap, lambda _r, k=key: _drop_shadow(k))
-    else:
-        ref, _, _, shadow = ent
-    src = fmap if fmap.is_contiguous() else fmap.contiguous()
-    check(lib.dpvo_nchw_to_nhwc(dtype_code(fmap), ptr(src), ptr(shadow), c_i64(B * N), c_i32(C), c_i64(H * W),
-                                stream_of(fmap)), "nchw_to_nhwc")
+        while len(_shadow) >= _SHADOW_MAX:
+            _shadow.popitem(last=False)
+        ent = _Shadow()
+        store = torch.zeros((B, N, H, W, C), dtype=fmap.dtype, device=fmap.device)
+        ent.view = store.permute(0, 1, 4, 2, 3)
+        ent.ref = weakref.ref(fmap, lambda _r, k=key: _shadow.pop(k, None))
+        ent.hashes = torch.full((2 * B * N,), -1, dtype=torch.int64, device=fmap.device)   # 0xFF..: matches nothing
+        ent.parity = 0
+        _shadow[key] = ent
+    src = fmap.detach()
+    if not src.is_contiguous():
+        src = src.contiguous()
+    slot_bytes = C * H * W * fmap.element_size()
+    with _lib.device_guard(fmap):
+        if slot_bytes % 16 == 0 and src.data_ptr() % 16 == 0:
+            ent.parity ^= 1
+            check(lib.dpvo_ring_sync(dtype_code(fmap), ptr(src), ptr(ent.view), c_i64(B * N), c_i32(C), c_i64(H * W),
+                                     ptr(ent.hashes), c_i32(ent.parity), stream_of(fmap)), "ring_sync")
+        else:
+            check(lib.dpvo_nchw_to_nhwc(dtype_code(fmap), ptr(src), ptr(ent.view), c_i64(B * N), c_i32(C), c_i64(H * W),
+                                        stream_of(fmap)), "nchw_to_nhwc")
     shadow_refreshes += 1
-    _shadow[key] = (ref, fmap._version, fmap.data_ptr(), shadow)
-    return shadow
+    ent.version = ver if ver is not None else -1
+    ent.data_ptr = fmap.data_ptr()
+    return ent.view
 
 
 def _check_corr_args(fmap1, fmap2, coords, ii, jj):

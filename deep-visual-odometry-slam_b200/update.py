@@ -51,8 +51,12 @@ def _rows(t, name, width):
     return t
 
 
-class Update:
+class Update(torch.nn.Module):
+    """An nn.Module (no registered parameters: inference only) so that it can be assigned over the
+    reference's `network.update` child module (dpvo.py:100-112 keeps `self.network` an nn.Module)."""
+
     def __init__(self, state_dict, device=None):
+        super().__init__()
         dev = torch.device(device if device is not None else "cuda")
         if dev.type != "cuda":
             raise RuntimeError("Update: CUDA device required (no CPU fallback)")
@@ -96,10 +100,7 @@ class Update:
             device = next(iter(sd.values())).device
         return cls(sd, device)
 
-    def eval(self):
-        return self
-
-    def cuda(self):
+    def cuda(self, device=None):
         return self
 
     # ------------------------------------------------------------------ pieces
@@ -155,7 +156,7 @@ class Update:
         return self._lin(name + ".res.2", r, gate=gate, res1=x, ln=ln, head=head)
 
     # ------------------------------------------------------------------ forward
-    def __call__(self, net, inp, corr, flow, ii, jj, kk, n_frames=None, n_patches=None):
+    def forward(self, net, inp, corr, flow, ii, jj, kk, n_frames=None, n_patches=None):
         """inp: [1, E, 384] tensor, or a (table [n, 384], index int64 [E]) pair — the context gather
         `imap[:, kk % n]` of dpvo.py:333 then happens inside the layer that consumes it.
         n_frames / n_patches: exclusive upper bounds of jj / ii and kk (size the group tables);

@@ -77,6 +77,20 @@ int dpvo_corr_backward(dpvo_dtype dtype,
                        void* fmap1_grad, void* fmap2_grad, float* acc1, float* acc2,
                        void* stream);
 
+/* Same operator, training fast path: fp16 features, C = 128, 3x3 patches, radius 3 (the only shape
+ * net.py:156-169 produces).  fmap1: dense patches [B][N1][128][3][3] (batch / patch strides g_sb, g_sn);
+ * fmap2: CHANNELS-LAST ring (channel stride 1; strides sb, sn, sy, sx in elements) — the layout the
+ * forward lookup already reads; fmap2_grad_nhwc: contiguous [B][N2][H2][W2][128] fp16 (return it to
+ * autograd as a permuted view); fmap1_grad: contiguous like fmap1.  acc1 ([B*N1*1152]) and acc2
+ * ([B*N2*H2*W2*128]) are ZEROED float32 scratch; both gradients are written in full (no pre-zeroing). */
+int dpvo_corr_backward_f16_nhwc(
+    const void* fmap1, int64_t g_sb, int64_t g_sn,
+    const void* fmap2, int64_t sb, int64_t sn, int64_t sy, int64_t sx,
+    int32_t N1, int32_t N2, int32_t H2, int32_t W2,
+    const float* coords, const int64_t* us, const int64_t* vs, int32_t B, int32_t M,
+    const void* corr_grad, int64_t cg_sb, int64_t cg_sm, int64_t cg_sx, int64_t cg_sy, int64_t cg_si, int64_t cg_sj,
+    void* fmap1_grad, void* fmap2_grad_nhwc, float* acc1, float* acc2, void* stream);
+
 /* Patch gather — replaces cuda_corr.patchify_forward (correlation_kernel.cu:17-48,289-308).
  * net: [B, C, H, W] strides n_*; coords: [B, M, 2] float32 contiguous;
  * patches: [B, M, C, D, D] contiguous (D = 2*radius+2), fully written (zeros outside). */
@@ -96,6 +110,15 @@ int dpvo_patchify_backward(dpvo_dtype dtype, const void* patch_grad,
 /* Layout helper for the feature ring: src [N, C, HW] -> dst [N, HW, C] (fp16/fp32). */
 int dpvo_nchw_to_nhwc(dpvo_dtype dtype, const void* src, void* dst,
                       int64_t N, int32_t C, int64_t HW, void* stream);
+
+/* Incremental form of the above for a ring the CALLER keeps in the reference's NCHW layout
+ * (dpvo/dpvo.py:72-73; its slot writes at :435-438 and :296-299 are plain torch copies): hashes
+ * every slot of `src` (one read pass), and re-transposes into `dst` only the slots whose hash
+ * differs from the previous call's.  `hashes` = 2*N uint64 of device memory owned by the caller,
+ * filled with 0xFF bytes before the first call; `parity` alternates 0,1,0,... between calls on
+ * the same ring.  No host synchronisation. */
+int dpvo_ring_sync(dpvo_dtype dtype, const void* src, void* dst, int64_t N, int32_t C, int64_t HW,
+                   void* hashes, int32_t parity, void* stream);
 
 /* ------------------------------------------------------------------- fastba */
 

@@ -12,7 +12,14 @@ Modules built (names are the ones the reference imports by bare name):
   cuda_ba            methods/dpvo/dpvo/fastba/{ba.cpp,ba_cuda.cu,block_e.cu}
   lietorch_backends  methods/dpvo/dpvo/lietorch/src/{lietorch.cpp,lietorch_gpu.cu,lietorch_cpu.cpp}
 
-Usage:  python oracle/build_ref.py [cuda_corr cuda_ba lietorch_backends]
+It also INSTALLS the reference's pure-Python package (what `pip install --target` of the
+reference would place in site-packages: methods/dpvo/dpvo/**/*.py, utils/utils.py and
+config/default.yaml) into oracle/_ref/site/, so that the unmodified `dpvo.dpvo.DPVO`,
+`dpvo.net.VONet` and the loss of train.py can run on the GPU box on top of either the
+reference extensions above or this repo's drop-in modules (tools/refdpvo.py).  The
+install is git-ignored like the .so files; no reference source enters the history.
+
+Usage:  python oracle/build_ref.py [cuda_corr cuda_ba lietorch_backends site]
 Only tests/, __graft_entry__.smoke() and bench.py's reference legs may load the
 results (see oracle/README.md).
 """
@@ -57,12 +64,40 @@ def build_one(name):
     print("built", os.path.join(OUT, name + ".so"), flush=True)
 
 
+def install_site():
+    """Copy the reference's Python package (sources untouched) into oracle/_ref/site/."""
+    site = os.path.join(OUT, "site")
+    shutil.rmtree(site, ignore_errors=True)
+    n = 0
+    for base, sub in ((os.path.join(REF, "dpvo"), "dpvo"), (os.path.join(REF, "utils"), "utils")):
+        for d, dirs, files in os.walk(base):
+            dirs[:] = [x for x in dirs if x not in ("__pycache__", "include", "src", "retrieval", "test")]
+            for f in files:
+                if f.endswith(".py"):
+                    rel = os.path.relpath(os.path.join(d, f), base)
+                    dst = os.path.join(site, sub, rel)
+                    os.makedirs(os.path.dirname(dst), exist_ok=True)
+                    shutil.copy2(os.path.join(d, f), dst)
+                    n += 1
+    os.makedirs(os.path.join(site, "config"), exist_ok=True)
+    shutil.copy2(os.path.join(REF, "config", "default.yaml"), os.path.join(site, "config", "default.yaml"))
+    if not os.path.exists(os.path.join(site, "utils", "__init__.py")):
+        open(os.path.join(site, "utils", "__init__.py"), "w").close()
+    print(f"installed {n} reference .py files into {site}", flush=True)
+
+
 def main(argv):
     if not os.path.isdir(REF):
         print("reference tree absent (GPU box): using prebuilt oracle/_ref/*.so")
         return 0
     os.makedirs(OUT, exist_ok=True)
-    names = argv or list(SPECS)
+    names = argv or (list(SPECS) + ["site"])
+    if "site" in names:
+        names = [n for n in names if n != "site"]
+        if not os.path.isdir(os.path.join(OUT, "site", "dpvo")) or os.environ.get("REF_REBUILD"):
+            install_site()
+        else:
+            print("up to date: site")
     for n in names:
         if os.path.exists(os.path.join(OUT, n + ".so")) and not os.environ.get("REF_REBUILD"):
             print("up to date:", n)

@@ -1,0 +1,88 @@
+"""Row X1 / (b) / A18: the reference's OWN `dpvo.dpvo.DPVO` class (dpvo/dpvo.py, untouched copy installed by
+oracle/build_ref.py under oracle/_ref/site) runs a synthetic 480x640 sequence twice — once on the reference's CUDA
+extensions (oracle/_ref/*.so), once on this repo's drop-in `cuda_corr` / `cuda_ba` / `lietorch_backends` — with identical
+seeds, weights, images and teacher (tools/refdpvo.py).  Each arm is its own process because the reference binds the
+extension modules at import time.
+
+Asserted (north star): per-frame edge bookkeeping ii/jj/kk BIT-EXACT (sha1 per frame + full lists on event frames) over
+120 frames that include the 8-frame initialisation with 12 updates (dpvo.py:461-466), keyframe removals
+(dpvo.py:266-310), proximity loop-closure edges (patchgraph.py:56-82) and global bundle adjustments with eff_impl=True
+(dpvo.py:312-326); poses of the window within POSE_TOL of the reference arm's at every frame (the two arms differ by
+fp16 rounding in the lookup and fp32 summation order in BA; the teacher keeps the trajectory contracting, so the
+difference stays at that level instead of growing chaotically)."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+import refdpvo  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+FRAMES = 120
+POSE_TOL = 2e-3          # absolute, on poses of a trajectory of extent ~3 (translations) / unit quaternions
+
+
+def _run(backend, out, update="reference", frames=FRAMES):
+    cmd = [sys.executable, os.path.join(ROOT, "tools", "refdpvo.py"), "--backend", backend, "--mode", "parity",
+           "--frames", str(frames), "--update", update, "--out", out]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, r.stderr[-3000:]
+    summary = json.loads(r.stdout.strip().splitlines()[-1])
+    return summary, dict(np.load(out)), r.stderr
+
+
+@pytest.fixture(scope="module")
+def arms(tmp_path_factory):
+    if not (refdpvo.have_reference_install() and refdpvo.have_reference_ext()):
+        pytest.skip("oracle/_ref (reference extensions + python package) not built")
+    d = tmp_path_factory.mktemp("refdpvo")
+    ref = _run("ref", str(d / "ref.npz"))
+    ours = _run("dropin", str(d / "dropin.npz"))
+    return ref, ours
+
+
+def _compare(ref, ours, tag):
+    (sr, a, _), (so, b, err) = ref, ours
+    assert "dropin" in so["modules"]["cuda_corr"] and "_ref" in sr["modules"]["cuda_corr"], (sr["modules"], so["modules"])
+    assert "Warning BA failed" not in err, "the drop-in cuda_ba raised inside DPVO.update (dpvo.py:355-356 swallows it)"
+    # the sequence exercises everything the state machine has
+    assert sr["removed"] >= 3 and sr["gba"] >= 3 and sr["loop_added"] >= 1, sr
+    first_bad = None
+    for k in ("n", "m", "E", "Einac", "removed", "gba", "loop_added", "h_ii", "h_jj", "h_kk"):
+        ne = np.nonzero(a[k] != b[k])[0]
+        if len(ne):
+            first_bad = (k, int(ne[0]))
+            break
+    dpose = np.abs(a["poses_tail"] - b["poses_tail"]).reshape(len(a["n"]), -1).max(1)
+    rec = {"what": tag, "frames": int(len(a["n"])), "final_n": int(a["final_n"]), "removed": int(a["removed"].sum()),
+           "global_ba": int(a["gba"].sum()), "loop_edge_batches": int(a["loop_added"].sum()),
+           "edges_last": int(a["E"][-1]), "inactive_last": int(a["Einac"][-1]),
+           "first_bookkeeping_mismatch": first_bad, "pose_absdiff_max": float(dpose.max()),
+           "pose_absdiff_by_frame": [float(f"{x:.3e}") for x in dpose[::10]]}
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", "refdpvo_parity.jsonl"), "a") as f:
+        f.write(json.dumps(rec) + "\n")
+    assert first_bad is None, rec
+    for key in a:
+        if key[:3] in ("ii_", "jj_", "kk_"):
+            assert np.array_equal(a[key], b[key]), key
+    assert dpose.max() < POSE_TOL, rec
+    assert np.array_equal(a["tstamps"], b["tstamps"])
+    d_depth = np.abs(a["final_depths"] - b["final_depths"]).max()
+    assert d_depth < 5e-3, d_depth
+
+
+def test_reference_dpvo_class_on_dropins_matches_reference_extensions(arms):
+    _compare(arms[0], arms[1], "dpvo.DPVO unmodified: drop-in cuda_corr/cuda_ba/lietorch_backends vs reference extensions")
+
+
+def test_reference_dpvo_class_with_b200_update_operator(arms, tmp_path):
+    """Same sequence with `network.update` bound to the tcgen05 Update operator."""
+    ours = _run("dropin", str(tmp_path / "dropin_upd.npz"), update="b200")
+    _compare(arms[0], ours, "dpvo.DPVO unmodified + dpvo_b200_update.Update vs reference extensions + torch Update")
