@@ -17,6 +17,7 @@ current stream.
 """
 import collections
 import ctypes
+import os
 import weakref
 
 import torch
@@ -159,6 +160,11 @@ def _launch(fmap1, coords, ii, jj, radius, levels):
     B, M = coords.shape[0], coords.shape[1]
     arr = (CorrLevel * len(levels))(*levels)
     g = fmap1.stride()
+    with _lib.device_guard(fmap1):
+        _launch_checked(fmap1, coords, ii, jj, radius, levels, arr, g, B, M)
+
+
+def _launch_checked(fmap1, coords, ii, jj, radius, levels, arr, g, B, M):
     check(lib.dpvo_corr_forward(
         c_i32(dtype_code(fmap1)), ptr(fmap1), c_i64(g[0]), c_i64(g[1]), c_i64(g[2]), c_i64(g[3]), c_i64(g[4]),
         c_i32(fmap1.shape[1]), c_i32(fmap1.shape[2]), c_i32(fmap1.shape[3]), c_i32(fmap1.shape[4]),
@@ -272,7 +278,15 @@ def patchify_backward(net, coords, gradient, radius):
     return [grad]
 
 
+def _backward_fast_ok(fmap1, fmap2, coords, radius):
+    return (fmap1.dtype == torch.float16 and fmap2.dtype == torch.float16 and radius == 3
+            and fmap1.shape[2] == 128 and tuple(fmap1.shape[3:]) == (3, 3) and tuple(coords.shape[3:]) == (3, 3))
+
+
 def backward(fmap1, fmap2, coords, ii, jj, corr_grad, radius):
+    """[fmap1_grad, fmap2_grad].  fp16 / C=128 / 3x3 / radius 3 (the training shape, net.py:156-169) takes the
+    warp-per-edge kernel over the channels-last ring (the forward's shadow is reused) and returns fmap2_grad as a
+    [B,N,C,H,W] VIEW of a channels-last buffer; everything else takes the generic kernel."""
     _check_corr_args(fmap1, fmap2, coords, ii, jj)
     radius = int(radius)
     coords = coords.contiguous()
@@ -283,6 +297,31 @@ def backward(fmap1, fmap2, coords, ii, jj, corr_grad, radius):
     if tuple(corr_grad.shape) != (B, M, DO, DO, PH, PW):
         raise RuntimeError("cuda_corr.backward: corr_grad must be [B,M,2r+1,2r+1,P,P]")
     corr_grad = corr_grad.to(fmap1.dtype)
+    cg = corr_grad.stride()
+    if _backward_fast_ok(fmap1, fmap2, coords, radius) and not os.environ.get("DPVO_CORR_BWD_GENERIC"):
+        f2 = _channels_last_view(fmap2.detach())
+        f1 = fmap1.detach()
+        if tuple(f1.stride()[2:]) != (9, 3, 1) or f1.stride(1) % 4 or f1.stride(0) % 4 or f1.data_ptr() % 8:
+            f1 = f1.contiguous()
+        _, N1, C = f1.shape[:3]
+        _, N2, _, H2, W2 = f2.shape
+        dev = fmap1.device
+        g1 = torch.empty((B, N1, C, 3, 3), dtype=torch.float16, device=dev)
+        g2 = torch.empty((B, N2, H2, W2, C), dtype=torch.float16, device=dev)
+        if B * M == 0:
+            return [g1.zero_(), g2.zero_().permute(0, 1, 4, 2, 3)]
+        acc1 = torch.zeros((B * N1 * C * 9,), dtype=torch.float32, device=dev)
+        acc2 = torch.zeros((B * N2 * H2 * W2 * C,), dtype=torch.float32, device=dev)
+        s1, s2 = f1.stride(), f2.stride()
+        with _lib.device_guard(fmap1):
+            check(lib.dpvo_corr_backward_f16_nhwc(
+                ptr(f1), c_i64(s1[0]), c_i64(s1[1]),
+                ptr(f2), c_i64(s2[0]), c_i64(s2[1]), c_i64(s2[3]), c_i64(s2[4]),
+                c_i32(N1), c_i32(N2), c_i32(H2), c_i32(W2),
+                ptr(coords), ptr(ii), ptr(jj), c_i32(B), c_i32(M),
+                ptr(corr_grad), c_i64(cg[0]), c_i64(cg[1]), c_i64(cg[2]), c_i64(cg[3]), c_i64(cg[4]), c_i64(cg[5]),
+                ptr(g1), ptr(g2), ptr(acc1), ptr(acc2), stream_of(fmap1)), "cuda_corr.backward")
+        return [g1, g2.permute(0, 1, 4, 2, 3)]
     g1 = torch.zeros(fmap1.shape, dtype=fmap1.dtype, device=fmap1.device)
     g2 = torch.zeros(fmap2.shape, dtype=fmap2.dtype, device=fmap2.device)
     if B * M == 0:
@@ -291,14 +330,15 @@ def backward(fmap1, fmap2, coords, ii, jj, corr_grad, radius):
     if fmap1.dtype == torch.float16:
         acc1 = torch.zeros(fmap1.shape, dtype=torch.float32, device=fmap1.device)
         acc2 = torch.zeros(fmap2.shape, dtype=torch.float32, device=fmap2.device)
-    s1, s2, cg = fmap1.stride(), fmap2.stride(), corr_grad.stride()
-    check(lib.dpvo_corr_backward(
-        c_i32(dtype_code(fmap1)),
-        ptr(fmap1), c_i64(s1[0]), c_i64(s1[1]), c_i64(s1[2]), c_i64(s1[3]), c_i64(s1[4]),
-        ptr(fmap2), c_i64(s2[0]), c_i64(s2[1]), c_i64(s2[2]), c_i64(s2[3]), c_i64(s2[4]),
-        c_i32(fmap1.shape[1]), c_i32(fmap2.shape[1]), c_i32(fmap1.shape[2]), c_i32(PH), c_i32(PW),
-        c_i32(fmap2.shape[3]), c_i32(fmap2.shape[4]),
-        ptr(coords), ptr(ii), ptr(jj), c_i32(B), c_i32(M), c_i32(radius),
-        ptr(corr_grad), c_i64(cg[0]), c_i64(cg[1]), c_i64(cg[2]), c_i64(cg[3]), c_i64(cg[4]), c_i64(cg[5]),
-        ptr(g1), ptr(g2), ptr(acc1), ptr(acc2), stream_of(fmap1)), "cuda_corr.backward")
+    s1, s2 = fmap1.stride(), fmap2.stride()
+    with _lib.device_guard(fmap1):
+        check(lib.dpvo_corr_backward(
+            c_i32(dtype_code(fmap1)),
+            ptr(fmap1), c_i64(s1[0]), c_i64(s1[1]), c_i64(s1[2]), c_i64(s1[3]), c_i64(s1[4]),
+            ptr(fmap2), c_i64(s2[0]), c_i64(s2[1]), c_i64(s2[2]), c_i64(s2[3]), c_i64(s2[4]),
+            c_i32(fmap1.shape[1]), c_i32(fmap2.shape[1]), c_i32(fmap1.shape[2]), c_i32(PH), c_i32(PW),
+            c_i32(fmap2.shape[3]), c_i32(fmap2.shape[4]),
+            ptr(coords), ptr(ii), ptr(jj), c_i32(B), c_i32(M), c_i32(radius),
+            ptr(corr_grad), c_i64(cg[0]), c_i64(cg[1]), c_i64(cg[2]), c_i64(cg[3]), c_i64(cg[4]), c_i64(cg[5]),
+            ptr(g1), ptr(g2), ptr(acc1), ptr(acc2), stream_of(fmap1)), "cuda_corr.backward")
     return [g1, g2]

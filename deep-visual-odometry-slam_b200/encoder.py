@@ -148,7 +148,7 @@ class BasicEncoder4:
         return FeatureMap(out)
 
 
-class Patchifier:
+class Patchifier(torch.nn.Module):
     """`Patchifier.forward` (net.py:106-153) for inference: both encoders, the three patch gathers, the patch grid.
 
     fnet / inet: BasicEncoder4 instances built with output_scale=0.25 (the reference divides both maps by 4).
@@ -159,6 +159,7 @@ class Patchifier:
     [1, w-1) x [1, h-1).  'GRADIENT_BIAS' (net.py:117-129) is not built."""
 
     def __init__(self, fnet, inet, patch_size=3):
+        super().__init__()      # an nn.Module (no parameters) so it can replace `network.patchify` (net.py:175)
         self.fnet, self.inet, self.patch_size = fnet, inet, patch_size
 
     @classmethod
@@ -166,8 +167,8 @@ class Patchifier:
         return cls(BasicEncoder4.from_reference(module.fnet, 0.25), BasicEncoder4.from_reference(module.inet, 0.25),
                    module.patch_size)
 
-    def __call__(self, images, patches_per_image=80, disps=None, centroid_sel_strat="RANDOM", return_color=False,
-                 coords=None):
+    def forward(self, images, patches_per_image=80, disps=None, centroid_sel_strat="RANDOM", return_color=False,
+                coords=None):
         from . import altcorr
         if centroid_sel_strat != "RANDOM":
             raise NotImplementedError(f"Patch centroid selection not built: {centroid_sel_strat}")

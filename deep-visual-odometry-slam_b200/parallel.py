@@ -84,27 +84,54 @@ class FlatGradAllReducer:
         device = device or self.params[0].device
         self.numel = sum(p.numel() for p in self.params)
         self.flat = torch.zeros(self.numel + 1, dtype=torch.float32, device=device)
+        self.slices = []
         off = 0
         for p in self.params:
             if p.dtype != torch.float32:
                 raise ValueError("FlatGradAllReducer: master parameters must be float32")
-            p.grad = self.flat[off:off + p.numel()].view_as(p)
+            self.slices.append(self.flat[off:off + p.numel()].view_as(p))
             off += p.numel()
+        self.rebinds = 0          # how many gradients had to be copied back into the buffer (instrumentation)
+        self._bind(copy=False)
+
+    def _bind(self, copy=True):
+        """Make every `p.grad` a view of the flat buffer again.  `optimizer.zero_grad()` defaults to
+        set_to_none=True (the reference calls it, train.py:295), after which backward allocates fresh
+        gradient tensors OUTSIDE the buffer; those are copied into their slices here and re-pointed, so the
+        collective never runs over a stale buffer.  A parameter that received no gradient gets zeros."""
+        for p, sl in zip(self.params, self.slices):
+            g = p.grad
+            if g is not None and g.data_ptr() == sl.data_ptr() and g.shape == sl.shape and g.is_contiguous():
+                continue
+            if copy:
+                if g is None:
+                    sl.zero_()
+                else:
+                    sl.copy_(g)
+                self.rebinds += 1
+            p.grad = sl
 
     def zero_grad(self):
+        """Use this (or `optimizer.zero_grad(set_to_none=False)`) instead of a bare `optimizer.zero_grad()` to keep
+        backward writing straight into the buffer; the bare call still works, at the cost of one copy per step."""
         self.flat.zero_()
+        self._bind(copy=False)
 
-    def allreduce(self, found_inf=None, average=True):
+    def allreduce(self, found_inf=None, average=True, sanitize=True):
         """Sum (or mean) the gradients over all ranks in place.  `found_inf`: this rank's overflow
         flag (bool / 0-d tensor) or None to derive it from the gradients.  Returns the global flag
-        as a 0-d tensor on the buffer's device (no host synchronisation)."""
+        as a 0-d tensor on the buffer's device (no host synchronisation).
+        sanitize=True zeroes non-finite gradients before the sum (the caller skips the step on the returned flag);
+        sanitize=False leaves them in, so inf/NaN reach every rank and `GradScaler.unscale_` finds them itself —
+        the plain-DDP behaviour the reference's AMP loop (train.py:341-345) needs with no further change."""
+        self._bind(copy=True)
         g = self.flat[:self.numel]
         if found_inf is None:
             flag = (~torch.isfinite(g).all()).to(torch.float32)
         else:
             flag = torch.as_tensor(found_inf, device=self.flat.device).to(torch.float32).reshape(())
         # keep non-finite values out of the sum: the step is skipped anyway, and NaN * 0 != 0
-        if found_inf is None:
+        if found_inf is None and sanitize:
             torch.nan_to_num_(g, nan=0.0, posinf=0.0, neginf=0.0)
         self.flat[self.numel] = flag
         if dist.is_initialized():

@@ -288,3 +288,56 @@ def test_nchw_to_nhwc_bit_exact(dtype, shape):
     want = src.permute(0, 2, 3, 1).contiguous()
     iv = {2: torch.int16, 4: torch.int32}[src.element_size()]
     assert torch.equal(dst.view(iv), want.view(iv))
+
+
+def test_ring_sync_refreshes_only_changed_slots():
+    """The NCHW-ring shadow (cuda_corr._channels_last_view): after the first full sync, writing two slots the way
+    the reference does (dpvo.py:435-438: `fmap1_[:, n % mem] = ...`) must refresh exactly those; a raw write the
+    version counter does not see needs `invalidate`."""
+    pkg = load_pkg()
+    cc = pkg.cuda_corr
+    torch.manual_seed(5)
+    ring = torch.randn(1, 9, 128, 30, 40, device="cuda").half()
+    want = lambda: ring.permute(0, 1, 3, 4, 2).contiguous()
+    s0 = cc.shadow_stats()["syncs"]
+    v = cc._channels_last_view(ring)
+    assert v.shape == ring.shape and v.stride(2) == 1
+    assert torch.equal(v.permute(0, 1, 3, 4, 2).contiguous(), want())
+    assert cc._channels_last_view(ring) is v and cc.shadow_stats()["syncs"] == s0 + 1      # unchanged: cache hit
+    # poison the shadow of an UNCHANGED slot: a selective sync must not touch it
+    v[0, 3].fill_(7.0)
+    ring[:, 2] = torch.randn(128, 30, 40, device="cuda").half()
+    ring[0, 7] = ring[0, 8]
+    v2 = cc._channels_last_view(ring)
+    assert v2 is v and cc.shadow_stats()["syncs"] == s0 + 2
+    got = v.permute(0, 1, 3, 4, 2).contiguous()
+    w = want()
+    for slot in (0, 1, 2, 4, 5, 6, 7, 8):
+        assert torch.equal(got[0, slot], w[0, slot]), slot
+    assert bool((got[0, 3] == 7.0).all())                       # untouched because its source did not change
+    # a write torch's version counter does not see
+    ring.data[0, 3, 0, 0, 0] += 1.0
+    cc.invalidate(ring)
+    v3 = cc._channels_last_view(ring)
+    assert torch.equal(v3.permute(0, 1, 3, 4, 2).contiguous(), want())
+
+
+def test_corr_backward_fast_path_matches_generic_kernel_at_training_shape():
+    """Config 4's shape (15-frame clip, 80 patches/frame, fp16, level 1 = 120x160): the warp-per-edge kernel over the
+    channels-last ring against this repo's generic one-CTA-per-edge kernel (both fp32-accumulating, independent code)."""
+    import os
+    pkg = load_pkg()
+    synth = load_pkg("synth")
+    E = 3600
+    d = synth.corr_inputs(E, seed=4, mem=15, n_patches=15 * 80, oob_frac=0.03)
+    g = _dev(d["gmap"]).half(); f = _dev(d["fmap1"]).half(); c = _dev(d["coords"]); us = _dev(d["us"]); vs = _dev(d["vs"])
+    grad = torch.randn(1, E, 7, 7, 3, 3, device="cuda", generator=torch.Generator("cuda").manual_seed(1)).half()
+    a1, a2 = pkg.cuda_corr.backward(g, f, c, us, vs, grad, 3)
+    assert a2.shape == f.shape and a2.stride(2) == 1             # channels-last view
+    os.environ["DPVO_CORR_BWD_GENERIC"] = "1"
+    try:
+        b1, b2 = pkg.cuda_corr.backward(g, f, c, us, vs, grad, 3)
+    finally:
+        del os.environ["DPVO_CORR_BWD_GENERIC"]
+    assert _rel(a1.float().cpu().numpy(), b1.float().cpu().numpy()) < 2e-4
+    assert _rel(a2.float().cpu().numpy(), b2.float().cpu().numpy()) < 2e-4

@@ -110,3 +110,34 @@ def test_single_process_reducer_is_local():
     assert not bool(red.allreduce())
     assert torch.equal(before, red.flat[:red.numel])
     assert red.nbytes() == 4 * (sum(p.numel() for p in model.parameters()) + 1)
+
+
+def test_reducer_survives_optimizer_zero_grad_set_to_none():
+    """The reference's loop calls `optimizer.zero_grad()` (train.py:295), which on torch >= 2 sets `.grad = None`;
+    backward then allocates gradients outside the flat buffer.  allreduce() must pick them up (copy + re-point)
+    instead of reducing a stale buffer."""
+    par = load_pkg("parallel")
+    model = _model(3)
+    opt = torch.optim.SGD(model.parameters(), lr=0.1)
+    red = par.FlatGradAllReducer(model.parameters())
+    x = torch.ones(2, 7)
+    for step in range(3):
+        opt.zero_grad()                                   # set_to_none=True
+        assert all(p.grad is None for p in model.parameters())
+        (model(x) * (step + 1)).square().sum().backward()
+        want = torch.cat([p.grad.reshape(-1).clone() for p in model.parameters()])
+        assert not bool(red.allreduce(sanitize=False))
+        assert torch.equal(red.flat[:red.numel], want)
+        for p, sl in zip(red.params, red.slices):
+            assert p.grad.data_ptr() == sl.data_ptr()     # re-pointed into the buffer
+        opt.step()
+    assert red.rebinds == 3 * len(red.params)
+    # with the reducer's own zero_grad nothing is copied
+    red.zero_grad()
+    model(x).sum().backward()
+    n = red.rebinds
+    red.allreduce()
+    assert red.rebinds == n
+    # sanitize=False keeps a non-finite gradient visible to GradScaler.unscale_
+    red.flat[0] = float("nan")
+    assert bool(red.allreduce(sanitize=False)) and not bool(torch.isfinite(red.flat[:red.numel]).all())

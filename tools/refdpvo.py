@@ -313,7 +313,7 @@ def make_teacher(inner, slam, seq, alpha):
 
 # --------------------------------------------------------------------------- building a DPVO instance
 def build_slam(seed=1234, cfg=None, ht=480, wd=640, seq=None, alpha=0.25, teacher=True, update_impl="reference",
-               cpu_dryrun=False):
+               patchify_impl="reference", cpu_dryrun=False):
     """Unmodified reference DPVO (dpvo.py:22-112) with a seeded random-init VONet (no checkpoint in the image)."""
     import torch
     dpvo_mod = importlib.import_module("dpvo.dpvo")
@@ -326,6 +326,9 @@ def build_slam(seed=1234, cfg=None, ht=480, wd=640, seq=None, alpha=0.25, teache
         # the one-line binding of the Update operator (next row N1)
         import dpvo_b200_update
         slam.network.update = dpvo_b200_update.Update.from_reference(slam.network.update)
+    if patchify_impl == "b200":
+        import dpvo_b200_patchify
+        slam.network.patchify = dpvo_b200_patchify.Patchifier.from_reference(slam.network.patchify)
     if teacher:
         if seq is None:
             raise ValueError("teacher needs the sequence (ground truth)")
@@ -368,10 +371,16 @@ def run_parity(slam, seq, frames, keep_every=10, dev="cuda"):
         ran1 = int(slam.ran_global_ba.sum())
         log["gba"].append(int(ran1 > ran0)); gba_count += int(ran1 > ran0)
         log["loop_added"].append(int(getattr(slam, "last_global_ba", None) != last_gba0))
+        # monocular scale is a gauge freedom of the window (only pose 0 is held fixed, dpvo.py:352): log the poses in
+        # the normalisation DPVO itself applies before every global BA (patchgraph.py:84-90: mean inverse depth = 1)
         P = torch.zeros(64, 7)
         k = min(slam.n, 64)
-        P[:k] = pg.poses_[slam.n - k:slam.n].cpu()
+        s = pg.patches_[:slam.n, :, 2].mean() if slam.n > 0 else torch.ones(())
+        Pn = pg.poses_[slam.n - k:slam.n].clone()
+        Pn[:, :3] *= s
+        P[:k] = Pn.cpu()
         poses.append(P.numpy())
+        log.setdefault("scale", []).append(float(s))
         if t % keep_every == 0 or log["removed"][-1] or log["gba"][-1] or log["loop_added"][-1]:
             kept[f"ii_{t}"] = pg.ii.cpu().numpy().astype(np.int32)
             kept[f"jj_{t}"] = pg.jj.cpu().numpy().astype(np.int32)
@@ -416,14 +425,54 @@ def run_fps(slam, seq, frames, host_frames, terminate=True, dev="cuda"):
     return out
 
 
+def instrument(slam):
+    """--mode profile: wall time per stage with a device synchronisation on both sides of every stage (so the
+    total is slower than --mode fps; the SHARES are what this is for)."""
+    import torch
+    acc = {}
+
+    def wrap(fn, key):
+        def timed(*a, **k):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            try:
+                return fn(*a, **k)
+            finally:
+                torch.cuda.synchronize()
+                c = acc.setdefault(key, [0, 0.0])
+                c[0] += 1
+                c[1] += time.perf_counter() - t0
+        return timed
+
+    dm = sys.modules["dpvo.dpvo"]
+    slam.update = wrap(slam.update, "update (whole)")
+    slam.keyframe = wrap(slam.keyframe, "keyframe")
+    slam.corr = wrap(slam.corr, "  corr x2 + stack")
+    slam.reproject = wrap(slam.reproject, "  reproject (pops.transform)")
+    slam.motion_probe = wrap(slam.motion_probe, "motion_probe")
+    slam.pg.edges_loop = wrap(slam.pg.edges_loop, "edges_loop")
+    slam.network.patchify.forward = wrap(slam.network.patchify.forward, "patchify (encoders + gathers)")
+    slam.network.update.forward = wrap(slam.network.update.forward, "  Update operator (+teacher)")
+    orig_ba = dm.fastba.BA
+
+    def ba(*a, **k):
+        key = "  BA global (eff_impl)" if k.get("eff_impl") else "  BA window"
+        return wrap(orig_ba, key)(*a, **k)
+
+    dm.fastba.BA = ba
+    dm.pops.point_cloud = wrap(dm.pops.point_cloud, "  point_cloud")
+    return acc
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--backend", default="dropin", choices=["ref", "dropin"])
-    ap.add_argument("--mode", default="parity", choices=["parity", "fps"])
+    ap.add_argument("--mode", default="parity", choices=["parity", "fps", "profile"])
     ap.add_argument("--frames", type=int, default=120)
     ap.add_argument("--seed", type=int, default=1234)
     ap.add_argument("--alpha", type=float, default=0.25)
     ap.add_argument("--update", default="reference", choices=["reference", "b200"])
+    ap.add_argument("--patchify", default="reference", choices=["reference", "b200"])
     ap.add_argument("--no-teacher", action="store_true")
     ap.add_argument("--no-loop-closure", action="store_true")
     ap.add_argument("--patches", type=int, default=None)
@@ -448,7 +497,7 @@ def main():
     torch.set_grad_enabled(False)             # evaluate_tartan.py:46 runs DPVO under @torch.no_grad()
     try:
         slam = build_slam(seed=args.seed, cfg=make_cfg(**over), seq=seq, alpha=args.alpha, teacher=not args.no_teacher,
-                          update_impl=args.update, cpu_dryrun=args.cpu_dryrun)
+                          update_impl=args.update, patchify_impl=args.patchify, cpu_dryrun=args.cpu_dryrun)
         if args.mode == "parity":
             res = run_parity(slam, seq, args.frames, dev=dev)
             import numpy as np
@@ -461,8 +510,12 @@ def main():
             print(json.dumps(summary), flush=True)
         else:
             hf = seq.host_frames(pin=not args.cpu_dryrun)
+            acc = instrument(slam) if args.mode == "profile" else None
             res = run_fps(slam, seq, args.frames, hf, dev=dev)
-            res.update(backend=args.backend, update=args.update, modules=files)
+            if acc is not None:
+                res["stages"] = {k: {"calls": c, "s": round(t, 3), "ms_per_call": round(1e3 * t / max(c, 1), 3)}
+                                 for k, (c, t) in sorted(acc.items(), key=lambda kv: -kv[1][1])}
+            res.update(backend=args.backend, update=args.update, patchify=args.patchify, modules=files)
             if args.out:
                 with open(args.out, "w") as f:
                     json.dump(res, f)
