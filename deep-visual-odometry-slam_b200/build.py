@@ -22,6 +22,8 @@ FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-li
          "-Xcompiler", "-fPIC", "--use_fast_math=false", "-I", INC]
 # --use_fast_math=false is not an nvcc switch; keep IEEE math by simply not enabling it.
 FLAGS = [f for f in FLAGS if f != "--use_fast_math=false"]
+if os.environ.get("DPVO_DEBUG_HOOKS"):          # development switches read from the environment (common.cuh)
+    FLAGS.append("-DDPVO_DEBUG_HOOKS")
 
 
 def _headers():

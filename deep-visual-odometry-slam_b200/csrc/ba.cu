@@ -561,169 +561,6 @@ ba_solve_reg_kernel(const __grid_constant__ BADev p) {
   }
 }
 
-// ----------------------------------------------------------------- solve (small)
-// One CTA, system resident in shared memory: A is (n+1) x ld, rows 0..n-1 hold the lower
-// triangle of S = B - E Q E^T (+ damping), row n holds y^T, so the forward substitution
-// L z = y falls out of the factorisation.  Right-looking Cholesky with ONE barrier per column:
-// the unscaled column j is read from the lower triangle while the scaled L(:,j) is written to
-// the (unused) upper triangle, A[j][i] = L[i][j].  Then L^T x = z by one warp, dX -> global,
-// pose retraction (ba_cuda.cu:178-206).  Also clears U, v, G, g for the next iteration.
-__global__ void __launch_bounds__(256)
-ba_solve_small_kernel(const __grid_constant__ BADev p) {
-  extern __shared__ float sm[];
-  const int n = p.n, N = p.N;
-  const int ld = (n + 2) | 1;
-  float* A = sm;                       // (n+1) * ld
-  float* dinv = sm + (n + 1) * ld;     // n
-  float* x = dinv + n;                 // n
-  __shared__ int s_fail;
-  const int T = blockDim.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = T >> 5;
-  if (tid == 0) s_fail = 0;
-  for (int a = wid; a < n; a += nw)
-    for (int b = lane; b <= a; b += 32) {
-      float s = (float)(p.U[a * n + b] + p.U[b * n + a] - 0.5 * (p.G[a * n + b] + p.G[b * n + a]));
-      if (a == b) s += 1e-4f * s + 1.0f;
-      A[a * ld + b] = s;
-    }
-  for (int i = tid; i < n; i += T) A[n * ld + i] = (float)(p.v[i] - p.g[i]);
-  __syncthreads();
-  for (int i = tid; i < 2 * n * n + 2 * n; i += T) p.U[i] = 0.0;   // U, v, G, g contiguous
-
-  // thread -> (row group rg, column lane cl): owns columns k == cl (mod 64) and rows i == rg (mod T/64)
-  const int cl = tid & 63, rg = tid >> 6, nrg = T >> 6;
-  for (int j = 0; j < n; ++j) {
-    const float d = A[j * ld + j];
-    if (!(d > 0.f)) { if (tid == 0) s_fail = 1; break; }   // uniform: every thread reads the same d
-    const float r = 1.0f / sqrtf(d);
-    const float invd = 1.0f / d;
-    if (tid == 0) dinv[j] = r;
-    // scaled column j -> upper triangle (row j), rows (j, n]
-    for (int i = j + 1 + tid; i <= n; i += T) A[j * ld + i] = A[i * ld + j] * r;
-    // trailing update of the lower triangle: A[i][k] -= A[i][j] A[k][j] / d, j < k <= min(i, n-1), i <= n
-    for (int k = j + 1 + cl; k < n; k += 64) {
-      const float f = A[k * ld + j] * invd;
-      int i = k + ((rg - k) % nrg + nrg) % nrg;   // first row >= k in this thread's row class
-#pragma unroll 4
-      for (; i <= n; i += nrg) A[i * ld + k] -= A[i * ld + j] * f;
-    }
-    __syncthreads();
-  }
-  __syncthreads();
-  if (s_fail) {
-    for (int i = tid; i < n; i += T) p.dX[i] = 0.f;
-    if (tid == 0) p.meta[1] = 1;  // tells backsub to skip the depth update too
-    return;
-  }
-  for (int i = tid; i < n; i += T) x[i] = A[i * ld + n];   // z
-  __syncthreads();
-  if (wid == 0) {
-    // L^T x = z, column oriented: once x_j is known, z_i -= L[j][i] x_j for i < j (L[j][i] = A[i][j], upper)
-    for (int j = n - 1; j >= 0; --j) {
-      const float xj = x[j] * dinv[j];
-      __syncwarp();
-      if (lane == 0) x[j] = xj;
-      for (int i = lane; i < j; i += 32) x[i] -= A[i * ld + j] * xj;
-      __syncwarp();
-    }
-  }
-  __syncthreads();
-  for (int i = tid; i < n; i += T) p.dX[i] = x[i];
-  if (tid == 0) p.meta[1] = 0;
-  for (int i = tid; i < N; i += T) {
-    float* ps = p.poses + (int64_t)(p.t0 + i) * 7;
-    const Vec3 t = {ps[0], ps[1], ps[2]};
-    const Quat q = {ps[3], ps[4], ps[5], ps[6]};
-    const float xi[6] = {x[6 * i + 0], x[6 * i + 1], x[6 * i + 2], x[6 * i + 3], x[6 * i + 4], x[6 * i + 5]};
-    Vec3 t1;
-    Quat q1;
-    retr_se3(xi, t, q, t1, q1);
-    ps[0] = t1.x; ps[1] = t1.y; ps[2] = t1.z;
-    ps[3] = q1.x; ps[4] = q1.y; ps[5] = q1.z; ps[6] = q1.w;
-  }
-}
-
-// ----------------------------------------------------------------------- solve
-// One CTA.  S = (U + U^T) - G, y = v - g, S_dd += 1e-4 S_dd + 1, Cholesky, solves,
-// dX -> global, pose retraction.  S lives in shared memory when it fits.
-__global__ void __launch_bounds__(512)
-ba_solve_big_kernel(const __grid_constant__ BADev p, int s_in_smem) {
-  extern __shared__ float sm[];
-  const int n = p.n, N = p.N;
-  const int T = blockDim.x, tid = threadIdx.x;
-  float* y = sm;                       // n
-  float* S = s_in_smem ? sm + n : p.Sg;  // n*n (lower triangle used)
-  __shared__ int s_fail;
-  if (tid == 0) s_fail = 0;
-  for (int i = tid; i < n * n; i += T) {
-    const int a = i / n, b = i - a * n;
-    if (b <= a) {
-      float s = (float)(p.U[(int64_t)a * n + b] + p.U[(int64_t)b * n + a] - 0.5 * (p.G[(int64_t)a * n + b] + p.G[(int64_t)b * n + a]));
-      if (a == b) s += 1e-4f * s + 1.0f;
-      S[(int64_t)a * n + b] = s;
-    }
-  }
-  for (int i = tid; i < n; i += T) y[i] = (float)(p.v[i] - p.g[i]);
-  __syncthreads();
-  for (int i = tid; i < 2 * n * n + 2 * n; i += T) p.U[i] = 0.0;   // U, v, G, g contiguous: clear for the next iteration
-
-  for (int j = 0; j < n; ++j) {
-    if (tid == 0) {
-      const float d = S[(int64_t)j * n + j];
-      if (!(d > 0.f)) s_fail = 1;
-      S[(int64_t)j * n + j] = sqrtf(d);
-    }
-    __syncthreads();
-    if (s_fail) break;
-    const float inv = 1.0f / S[(int64_t)j * n + j];
-    for (int i = j + 1 + tid; i < n; i += T) S[(int64_t)i * n + j] *= inv;
-    __syncthreads();
-    const int m = n - j - 1;
-    for (int idx = tid; idx < m * m; idx += T) {
-      const int r = idx / m, c = idx - r * m;
-      if (c <= r) {
-        const int i = j + 1 + r, k = j + 1 + c;
-        S[(int64_t)i * n + k] -= S[(int64_t)i * n + j] * S[(int64_t)k * n + j];
-      }
-    }
-    __syncthreads();
-  }
-  if (s_fail) {
-    for (int i = tid; i < n; i += T) p.dX[i] = 0.f;
-    if (tid == 0) p.meta[1] = 1;  // tells backsub to skip the depth update too
-    return;
-  }
-  // forward: L z = y
-  for (int j = 0; j < n; ++j) {
-    if (tid == 0) y[j] /= S[(int64_t)j * n + j];
-    __syncthreads();
-    const float yj = y[j];
-    for (int i = j + 1 + tid; i < n; i += T) y[i] -= S[(int64_t)i * n + j] * yj;
-    __syncthreads();
-  }
-  // backward: L^T x = z
-  for (int j = n - 1; j >= 0; --j) {
-    if (tid == 0) y[j] /= S[(int64_t)j * n + j];
-    __syncthreads();
-    const float yj = y[j];
-    for (int i = tid; i < j; i += T) y[i] -= S[(int64_t)j * n + i] * yj;
-    __syncthreads();
-  }
-  for (int i = tid; i < n; i += T) p.dX[i] = y[i];
-  if (tid == 0) p.meta[1] = 0;
-  // pose retraction (ba_cuda.cu:178-206)
-  for (int i = tid; i < N; i += T) {
-    float* ps = p.poses + (int64_t)(p.t0 + i) * 7;
-    const Vec3 t = {ps[0], ps[1], ps[2]};
-    const Quat q = {ps[3], ps[4], ps[5], ps[6]};
-    const float xi[6] = {y[6 * i + 0], y[6 * i + 1], y[6 * i + 2], y[6 * i + 3], y[6 * i + 4], y[6 * i + 5]};
-    Vec3 t1;
-    Quat q1;
-    retr_se3(xi, t, q, t1, q1);
-    ps[0] = t1.x; ps[1] = t1.y; ps[2] = t1.z;
-    ps[3] = q1.x; ps[4] = q1.y; ps[5] = q1.z; ps[6] = q1.w;
-  }
-}
-
 // --------------------------------------------------------------------- backsub
 __global__ void __launch_bounds__(256)
 ba_backsub_kernel(const __grid_constant__ BADev p) {

@@ -345,7 +345,7 @@ int64_t chol_scratch_floats(int n) { return 3 * (int64_t)n + 64 + (int64_t)((n +
 int ba_chol_solve(const BADev& p, float* A, int lda, float* xbuf, cudaStream_t st) {
   const int n = p.n;
   int launches = 0;
-  static const bool dbg = getenv("DPVO_DEBUG_SYNC") != nullptr;
+  static const bool dbg = debug_env("DPVO_DEBUG_SYNC") != nullptr;
   int p0 = -1;
   float* z = xbuf;
   float* acc = z + n;
@@ -426,7 +426,7 @@ extern "C" int dpvo_chol_solve(const float* S, const float* y, int32_t n, float*
   const int grid = (int)(ceil_div64(tot, 256) < kNumSMs * 8 ? ceil_div64(tot, 256) : kNumSMs * 8);
   chol_pack_kernel<<<grid, 256, 0, st>>>(S, y, n, A, lda, p.meta);
   note_launches(1);
-  if (getenv("DPVO_DEBUG_SYNC")) {
+  if (debug_env("DPVO_DEBUG_SYNC")) {
     cudaError_t e_ = cudaStreamSynchronize(st);
     if (e_ != cudaSuccess) { set_error("chol_solve: pack: %s", cudaGetErrorString(e_)); return 1; }
   }

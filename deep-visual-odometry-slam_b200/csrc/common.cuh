@@ -26,6 +26,15 @@ inline int check_launch(const char* what) {
   return 0;
 }
 
+// Development switches (DPVO_LINEAR_*, DPVO_CORR_NARROW, DPVO_ENC_MT, DPVO_DEBUG_SYNC) exist only in a library
+// built with -DDPVO_DEBUG_HOOKS (DPVO_DEBUG_HOOKS=1 python build.py); the shipped library never reads the environment.
+#ifdef DPVO_DEBUG_HOOKS
+#include <stdlib.h>
+inline const char* debug_env(const char* name) { return getenv(name); }
+#else
+inline const char* debug_env(const char*) { return nullptr; }
+#endif
+
 #define DPVO_REQUIRE(cond, ...)            \
   do {                                     \
     if (!(cond)) {                         \

@@ -172,12 +172,12 @@ constexpr int kFB = 12;                 // largest box side held in the weight t
 constexpr int kFBWarps = 4;
 
 struct CorrBwdFastParams {
-  const __half* fmap1; int64_t g_sb, g_sn;                 // [B][N1][128][3][3] dense patches
-  const __half* fmap2; int64_t sb, sn, sy, sx;             // channels-last: channel stride 1
+  const void* fmap1; int64_t g_sb, g_sn;                   // [B][N1][128][3][3] dense patches
+  const void* fmap2; int64_t sb, sn, sy, sx;               // channels-last: channel stride 1
   int N1, N2, H2, W2;
   const float* coords; const int64_t* us; const int64_t* vs;
   int B, M;
-  const __half* cg; int64_t cg_sb, cg_sm, cg_sx, cg_sy, cg_si, cg_sj;
+  const void* cg; int64_t cg_sb, cg_sm, cg_sx, cg_sy, cg_si, cg_sj;
   float* acc1;                                             // [B][N1][128][9]  fp32, zeroed
   float* acc2;                                             // [B][N2][H2][W2][128] fp32, zeroed
 };
@@ -189,18 +189,33 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 __device__ __forceinline__ float h_rnd(float v) { return __half2float(__float2half_rn(v)); }
 
 // adjoint of the bilinear blend at raw-window tap (a: y offset, bb: x offset), reference rounding
-__device__ __forceinline__ float blend_adjoint(const __half* gp, int64_t sx, int64_t sy, int a, int bb,
+template <typename T>
+__device__ __forceinline__ float blend_adjoint(const T* gp, int64_t sx, int64_t sy, int a, int bb,
                                                float dx, float dy, float mdx, float mdy) {
   constexpr int D = 8;
-  auto G = [&](int yy, int xx) -> float { return __half2float(gp[xx * sx + yy * sy]); };
+  auto G = [&](int yy, int xx) -> float { return BwdT<T>::ld(gp + xx * sx + yy * sy); };
+  auto rnd = [](float v) -> float { return BwdT<T>::rnd(v); };
   float s = 0.f;
-  if (a < D - 1 && bb < D - 1) s = h_rnd(h_rnd(mdx * mdy) * G(a, bb));
-  if (a < D - 1 && bb >= 1) s = h_rnd(s + h_rnd(h_rnd(dx * mdy) * G(a, bb - 1)));
-  if (a >= 1 && bb < D - 1) s = h_rnd(s + h_rnd(h_rnd(mdx * dy) * G(a - 1, bb)));
-  if (a >= 1 && bb >= 1) s = h_rnd(s + h_rnd(h_rnd(dx * dy) * G(a - 1, bb - 1)));
+  if (a < D - 1 && bb < D - 1) s = rnd(rnd(mdx * mdy) * G(a, bb));
+  if (a < D - 1 && bb >= 1) s = rnd(s + rnd(rnd(dx * mdy) * G(a, bb - 1)));
+  if (a >= 1 && bb < D - 1) s = rnd(s + rnd(rnd(mdx * dy) * G(a - 1, bb)));
+  if (a >= 1 && bb >= 1) s = rnd(s + rnd(rnd(dx * dy) * G(a - 1, bb - 1)));
   return s;
 }
 
+// this lane's 4 channels of one channels-last pixel
+__device__ __forceinline__ void load4(const __half* p, float (&v)[4]) {
+  const uint2 raw = __ldg(reinterpret_cast<const uint2*>(p));
+  const __half2 h01 = *reinterpret_cast<const __half2*>(&raw.x);
+  const __half2 h23 = *reinterpret_cast<const __half2*>(&raw.y);
+  v[0] = __low2float(h01); v[1] = __high2float(h01); v[2] = __low2float(h23); v[3] = __high2float(h23);
+}
+__device__ __forceinline__ void load4(const float* p, float (&v)[4]) {
+  const float4 raw = __ldg(reinterpret_cast<const float4*>(p));
+  v[0] = raw.x; v[1] = raw.y; v[2] = raw.z; v[3] = raw.w;
+}
+
+template <typename T>
 __global__ void __launch_bounds__(kFBWarps * 32)
 corr_bwd_fast_kernel(const __grid_constant__ CorrBwdFastParams prm) {
   constexpr int R = 3, D = 8, PP = 9, C = 128;
@@ -225,9 +240,9 @@ corr_bwd_fast_kernel(const __grid_constant__ CorrBwdFastParams prm) {
       const float y = prm.coords[e * (2 * PP) + PP + lane];
       s_fx[wid][lane] = floor_to_int(x);
       s_fy[wid][lane] = floor_to_int(y);
-      const float dx = h_rnd(x - floorf(x)), dy = h_rnd(y - floorf(y));
+      const float dx = BwdT<T>::rnd(x - floorf(x)), dy = BwdT<T>::rnd(y - floorf(y));
       s_fr[wid][lane][0] = dx; s_fr[wid][lane][1] = dy;
-      s_fr[wid][lane][2] = h_rnd(1.f - dx); s_fr[wid][lane][3] = h_rnd(1.f - dy);
+      s_fr[wid][lane][2] = BwdT<T>::rnd(1.f - dx); s_fr[wid][lane][3] = BwdT<T>::rnd(1.f - dy);
     }
     __syncwarp();
     int mnx = s_fx[wid][0], mxx = mnx, mny = s_fy[wid][0], mxy = mny;
@@ -241,18 +256,20 @@ corr_bwd_fast_kernel(const __grid_constant__ CorrBwdFastParams prm) {
     if (bx0 >= W2 || by0 >= H2 || bx0 + bw <= 0 || by0 + bh <= 0) continue;
 
     // patch features of this lane's 4 channels: f1[p][k], 36 contiguous halfs at channel 4*lane
-    const __half* f1p = prm.fmap1 + b * prm.g_sb + u * prm.g_sn + (int64_t)lane * 4 * PP;
+    const T* f1p = reinterpret_cast<const T*>(prm.fmap1) + b * prm.g_sb + u * prm.g_sn + (int64_t)lane * 4 * PP;
     float f1[PP][4];
     {
-      __half tmp[36];
-      const uint2* src = reinterpret_cast<const uint2*>(f1p);
-      uint2* dst = reinterpret_cast<uint2*>(tmp);
+      float tmp[36];
 #pragma unroll
-      for (int i = 0; i < 9; ++i) dst[i] = __ldg(src + i);
+      for (int i = 0; i < 9; ++i) {
+        float q[4];
+        load4(f1p + 4 * i, q);
+        tmp[4 * i] = q[0]; tmp[4 * i + 1] = q[1]; tmp[4 * i + 2] = q[2]; tmp[4 * i + 3] = q[3];
+      }
 #pragma unroll
       for (int k = 0; k < 4; ++k)
 #pragma unroll
-        for (int p = 0; p < PP; ++p) f1[p][k] = __half2float(tmp[k * PP + p]);
+        for (int p = 0; p < PP; ++p) f1[p][k] = tmp[k * PP + p];
     }
     float a1[PP][4];
 #pragma unroll
@@ -260,9 +277,9 @@ corr_bwd_fast_kernel(const __grid_constant__ CorrBwdFastParams prm) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) a1[p][k] = 0.f;
 
-    const __half* f2 = prm.fmap2 + b * prm.sb + v * prm.sn + lane * 4;
+    const T* f2 = reinterpret_cast<const T*>(prm.fmap2) + b * prm.sb + v * prm.sn + lane * 4;
     float* g2 = prm.acc2 + (((int64_t)b * prm.N2 + v) * H2) * (int64_t)W2 * C + lane * 4;
-    const __half* cgb = prm.cg + b * prm.cg_sb + m * prm.cg_sm;
+    const T* cgb = reinterpret_cast<const T*>(prm.cg) + b * prm.cg_sb + m * prm.cg_sm;
 
     if (bw <= kFB && bh <= kFB) {
       const int nbox = bw * bh;
@@ -289,14 +306,12 @@ corr_bwd_fast_kernel(const __grid_constant__ CorrBwdFastParams prm) {
         for (int qx = qx0; qx < qx1; ++qx) {
           const int j1 = bx0 + qx;
           const int64_t pix = (int64_t)i1 * prm.sy + (int64_t)j1 * prm.sx;
-          const uint2 raw = __ldg(reinterpret_cast<const uint2*>(f2 + pix));
+          float fv[4];
+          load4(f2 + pix, fv);
           const float4 w0 = *reinterpret_cast<const float4*>(&wtab[qy * bw + qx][0]);
           const float4 w1 = *reinterpret_cast<const float4*>(&wtab[qy * bw + qx][4]);
           const float w8 = wtab[qy * bw + qx][8];
           const float w[PP] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w8};
-          const __half2 h01 = *reinterpret_cast<const __half2*>(&raw.x);
-          const __half2 h23 = *reinterpret_cast<const __half2*>(&raw.y);
-          const float fv[4] = {__low2float(h01), __high2float(h01), __low2float(h23), __high2float(h23)};
           float s[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
           for (int p = 0; p < PP; ++p) {
@@ -311,9 +326,11 @@ corr_bwd_fast_kernel(const __grid_constant__ CorrBwdFastParams prm) {
       }
     } else {
       // ---- rare: a patch stretched over more than kFB pixels — tap by tap, weights recomputed by every lane
+#pragma unroll
       for (int p = 0; p < PP; ++p) {
         const int i0 = p / 3, j0 = p - 3 * i0;
         const int x0 = s_fx[wid][p] - R, y0 = s_fy[wid][p] - R;
+#pragma unroll 1
         for (int t = 0; t < D * D; ++t) {
           const int a = t / D, bb = t - a * D;
           const int i1 = y0 + a, j1 = x0 + bb;
@@ -321,17 +338,13 @@ corr_bwd_fast_kernel(const __grid_constant__ CorrBwdFastParams prm) {
           const float w = blend_adjoint(cgb + i0 * prm.cg_si + j0 * prm.cg_sj, prm.cg_sx, prm.cg_sy, a, bb,
                                         s_fr[wid][p][0], s_fr[wid][p][1], s_fr[wid][p][2], s_fr[wid][p][3]);
           if (w == 0.f) continue;
-          const uint2 raw = __ldg(reinterpret_cast<const uint2*>(f2 + (int64_t)i1 * prm.sy + (int64_t)j1 * prm.sx));
-          const __half2 h01 = *reinterpret_cast<const __half2*>(&raw.x);
-          const __half2 h23 = *reinterpret_cast<const __half2*>(&raw.y);
-          const float fv[4] = {__low2float(h01), __high2float(h01), __low2float(h23), __high2float(h23)};
+          float fv[4];
+          load4(f2 + (int64_t)i1 * prm.sy + (int64_t)j1 * prm.sx, fv);
           float s[4];
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             s[k] = w * f1[p][k];
-#pragma unroll
-            for (int pp = 0; pp < PP; ++pp)
-              if (pp == p) a1[pp][k] = fmaf(w, fv[k], a1[pp][k]);
+            a1[p][k] = fmaf(w, fv[k], a1[p][k]);
           }
           red_add_v4(g2 + ((int64_t)i1 * W2 + j1) * C, s[0], s[1], s[2], s[3]);
         }
@@ -430,41 +443,51 @@ extern "C" int dpvo_corr_backward(dpvo_dtype dtype,
 
 // Fast path entry: see the comment above corr_bwd_fast_kernel.  fmap2 and fmap2_grad are CHANNELS-LAST
 // ([B][N2][H2][W2][128], channel stride 1); fmap1_grad has fmap1's dense [B][N1][128][3][3] layout.
-extern "C" int dpvo_corr_backward_f16_nhwc(
+extern "C" int dpvo_corr_backward_nhwc(
+    dpvo_dtype dtype,
     const void* fmap1, int64_t g_sb, int64_t g_sn,
     const void* fmap2, int64_t sb, int64_t sn, int64_t sy, int64_t sx,
     int32_t N1, int32_t N2, int32_t H2, int32_t W2,
     const float* coords, const int64_t* us, const int64_t* vs, int32_t B, int32_t M,
     const void* corr_grad, int64_t cg_sb, int64_t cg_sm, int64_t cg_sx, int64_t cg_sy, int64_t cg_si, int64_t cg_sj,
     void* fmap1_grad, void* fmap2_grad_nhwc, float* acc1, float* acc2, void* stream) {
-  DPVO_REQUIRE(B >= 0 && M >= 0 && N1 > 0 && N2 > 0 && H2 > 0 && W2 > 0, "corr_backward_f16_nhwc: bad sizes");
+  DPVO_REQUIRE(dtype == DPVO_F16 || dtype == DPVO_F32, "corr_backward_nhwc: float16 or float32 features");
+  DPVO_REQUIRE(B >= 0 && M >= 0 && N1 > 0 && N2 > 0 && H2 > 0 && W2 > 0, "corr_backward_nhwc: bad sizes");
   if ((int64_t)B * M == 0) return 0;
-  DPVO_REQUIRE(fmap1 && fmap2 && coords && us && vs && corr_grad && fmap1_grad && fmap2_grad_nhwc && acc1 && acc2,
-               "corr_backward_f16_nhwc: null pointer");
-  DPVO_REQUIRE((reinterpret_cast<uintptr_t>(fmap1) & 7) == 0 && g_sn % 4 == 0 && g_sb % 4 == 0,
-               "corr_backward_f16_nhwc: fmap1 must be 8-byte aligned dense patches");
-  DPVO_REQUIRE((reinterpret_cast<uintptr_t>(fmap2) & 7) == 0 && sn % 4 == 0 && sy % 4 == 0 && sx % 4 == 0 && sb % 4 == 0,
-               "corr_backward_f16_nhwc: fmap2 must be channels-last with 8-byte aligned pixels");
-  DPVO_REQUIRE((reinterpret_cast<uintptr_t>(acc1) & 15) == 0 && (reinterpret_cast<uintptr_t>(acc2) & 15) == 0,
-               "corr_backward_f16_nhwc: scratch must be 16-byte aligned");
+  DPVO_REQUIRE(fmap1 && fmap2 && coords && us && vs && corr_grad && fmap1_grad && fmap2_grad_nhwc,
+               "corr_backward_nhwc: null pointer");
+  const bool half = dtype == DPVO_F16;
+  DPVO_REQUIRE(!half || (acc1 && acc2), "corr_backward_nhwc: float16 needs the float32 scratch buffers");
+  const uintptr_t amask = half ? 7 : 15;
+  DPVO_REQUIRE((reinterpret_cast<uintptr_t>(fmap1) & amask) == 0 && g_sn % 4 == 0 && g_sb % 4 == 0,
+               "corr_backward_nhwc: fmap1 must be dense patches, each lane's 4-channel group vector aligned");
+  DPVO_REQUIRE((reinterpret_cast<uintptr_t>(fmap2) & amask) == 0 && sn % 4 == 0 && sy % 4 == 0 && sx % 4 == 0 && sb % 4 == 0,
+               "corr_backward_nhwc: fmap2 must be channels-last with vector-aligned pixels");
+  float* a1 = half ? acc1 : reinterpret_cast<float*>(fmap1_grad);
+  float* a2 = half ? acc2 : reinterpret_cast<float*>(fmap2_grad_nhwc);
+  DPVO_REQUIRE((reinterpret_cast<uintptr_t>(a1) & 15) == 0 && (reinterpret_cast<uintptr_t>(a2) & 15) == 0,
+               "corr_backward_nhwc: accumulation buffers must be 16-byte aligned");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   CorrBwdFastParams p;
   memset(&p, 0, sizeof(p));
-  p.fmap1 = reinterpret_cast<const __half*>(fmap1); p.g_sb = g_sb; p.g_sn = g_sn;
-  p.fmap2 = reinterpret_cast<const __half*>(fmap2); p.sb = sb; p.sn = sn; p.sy = sy; p.sx = sx;
+  p.fmap1 = fmap1; p.g_sb = g_sb; p.g_sn = g_sn;
+  p.fmap2 = fmap2; p.sb = sb; p.sn = sn; p.sy = sy; p.sx = sx;
   p.N1 = N1; p.N2 = N2; p.H2 = H2; p.W2 = W2;
   p.coords = coords; p.us = us; p.vs = vs; p.B = B; p.M = M;
-  p.cg = reinterpret_cast<const __half*>(corr_grad);
+  p.cg = corr_grad;
   p.cg_sb = cg_sb; p.cg_sm = cg_sm; p.cg_sx = cg_sx; p.cg_sy = cg_sy; p.cg_si = cg_si; p.cg_sj = cg_sj;
-  p.acc1 = acc1; p.acc2 = acc2;
+  p.acc1 = a1; p.acc2 = a2;
   const int64_t nedge = (int64_t)B * M;
   const int64_t want = ceil_div64(nedge, kFBWarps);
   const int grid = (int)(want < (int64_t)kNumSMs * 4 ? want : (int64_t)kNumSMs * 4);
-  note_launches(3);
-  corr_bwd_fast_kernel<<<grid, kFBWarps * 32, 0, st>>>(p);
+  note_launches(1);
+  if (half) corr_bwd_fast_kernel<__half><<<grid, kFBWarps * 32, 0, st>>>(p);
+  else corr_bwd_fast_kernel<float><<<grid, kFBWarps * 32, 0, st>>>(p);
   if (check_launch("corr_bwd_fast")) return 1;
+  if (!half) return 0;
   const int64_t n1 = (int64_t)B * N1 * 128 * 9 / 4, n2 = (int64_t)B * N2 * H2 * W2 * 128 / 4;
   auto blocks = [](int64_t n4) { const int64_t b = ceil_div64(n4, 256 * 4); return (int)(b < kNumSMs * 16 ? (b > 0 ? b : 1) : kNumSMs * 16); };
+  note_launches(2);
   f32_to_f16_vec4_kernel<<<blocks(n1), 256, 0, st>>>(reinterpret_cast<const float4*>(acc1),
                                                      reinterpret_cast<uint2*>(fmap1_grad), n1);
   f32_to_f16_vec4_kernel<<<blocks(n2), 256, 0, st>>>(reinterpret_cast<const float4*>(acc2),

@@ -481,6 +481,9 @@ static bool is_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p)
 
 using namespace dpvo;
 
+static const char* g_last_corr_kernel = "";
+extern "C" const char* dpvo_corr_last_kernel(void) { return g_last_corr_kernel; }
+
 extern "C" int dpvo_corr_forward(dpvo_dtype dtype,
                                  const void* fmap1, int64_t g_sb, int64_t g_sn, int64_t g_sc, int64_t g_sy, int64_t g_sx,
                                  int32_t N1, int32_t C, int32_t PH, int32_t PW,
@@ -538,7 +541,8 @@ extern "C" int dpvo_corr_forward(dpvo_dtype dtype,
     const int64_t nedge = (int64_t)B * M;
     int64_t want = ceil_div64(nedge, kWarps);
     int grid = (int)(want < (int64_t)kNumSMs * 64 ? want : (int64_t)kNumSMs * 64);
-    bool wide = getenv("DPVO_CORR_NARROW") == nullptr;
+    static const bool narrow_env = debug_env("DPVO_CORR_NARROW") != nullptr;   // read once (debug switch)
+    bool wide = !narrow_env;
     for (int l = 0; l < nlev && wide; ++l) {
       const CorrLevelDev& L = prm.lev[l];
       wide = ((reinterpret_cast<uintptr_t>(L.fmap) & 31) == 0) && (L.sx % 16 == 0) && (L.sy % 16 == 0) &&
@@ -551,10 +555,14 @@ extern "C" int dpvo_corr_forward(dpvo_dtype dtype,
       if (wide) corr_fwd_mma_f16_kernel<2, true><<<grid, kWarps * 32, 0, st>>>(prm);
       else corr_fwd_mma_f16_kernel<2, false><<<grid, kWarps * 32, 0, st>>>(prm);
     }
+    g_last_corr_kernel = nlev == 1 ? (wide ? "corr_fwd_mma_f16_kernel<1, 1>" : "corr_fwd_mma_f16_kernel<1, 0>")
+                                   : (wide ? "corr_fwd_mma_f16_kernel<2, 1>" : "corr_fwd_mma_f16_kernel<2, 0>");
     note_launches(1);
     return check_launch("corr_fwd_mma_f16");
   }
   (void)D;
+  g_last_corr_kernel = dtype == DPVO_F16 ? "corr_fwd_generic_kernel<__half>"
+                       : dtype == DPVO_F32 ? "corr_fwd_generic_kernel<float>" : "corr_fwd_generic_kernel<double>";
   switch (dtype) {
     case DPVO_F16: return launch_generic<__half>(prm, st);
     case DPVO_F32: return launch_generic<float>(prm, st);

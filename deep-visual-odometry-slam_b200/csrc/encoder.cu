@@ -332,7 +332,7 @@ int launch_conv_mt(const ConvParams& p, int n_img, cudaStream_t st) {
 // slower on every layer of a 480x640 frame (fnet 0.216 vs 0.191 ms): each CTA re-stages the layer's weights.
 template <int KS, int S, int CIN, int NC>
 int launch_conv(const ConvParams& p, int n_img, cudaStream_t st) {
-  static const int forced = getenv("DPVO_ENC_MT") ? atoi(getenv("DPVO_ENC_MT")) : 0;
+  static const int forced = debug_env("DPVO_ENC_MT") ? atoi(debug_env("DPVO_ENC_MT")) : 0;
   const int mt = forced == 1 ? 1 : 2;
   return mt == 2 ? launch_conv_mt<KS, S, CIN, NC, 2>(p, n_img, st) : launch_conv_mt<KS, S, CIN, NC, 1>(p, n_img, st);
 }

@@ -720,7 +720,7 @@ int make_map(CUtensorMap* m, const void* base, int64_t K, int64_t rows, int64_t 
 bool use_resident_w() {
   static int v = -1;
   if (v < 0) {
-    const char* e = getenv("DPVO_LINEAR_RW");
+    const char* e = debug_env("DPVO_LINEAR_RW");
     v = (e && e[0] == '0') ? 0 : 1;
   }
   return v == 1;
@@ -730,7 +730,7 @@ bool use_resident_w() {
 int cluster_size() {
   static int cl = 0;
   if (!cl) {
-    const char* e = getenv("DPVO_LINEAR_CLUSTER");
+    const char* e = debug_env("DPVO_LINEAR_CLUSTER");
     const int v = e ? atoi(e) : 0;
     cl = (v == 1 || v == 2 || v == 4 || v == 8) ? v : 1;
   }
@@ -807,7 +807,7 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
   if (lp->K == kDim && use_resident_w()) {
     if (make_map(&tmW, lp->W, lp->K, kDim, lp->ldw, kHalf)) return 1;
     LinearRwDev q;
-    q.profile = getenv("DPVO_LINEAR_PROFILE") ? 1 : 0;
+    q.profile = debug_env("DPVO_LINEAR_PROFILE") ? 1 : 0;
     q.bias = lp->bias;
     q.gate = static_cast<const __half*>(lp->gate);
     q.res1 = static_cast<const __half*>(lp->res1);
@@ -817,7 +817,7 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
     q.ln_beta = lp->ln_beta;
     q.ln_eps = lp->ln_eps;
     q.act = lp->act;
-    q.Y = getenv("DPVO_LINEAR_DEBUG_NOSTORE") ? nullptr : static_cast<__half*>(lp->Y);
+    q.Y = debug_env("DPVO_LINEAR_DEBUG_NOSTORE") ? nullptr : static_cast<__half*>(lp->Y);
     q.M = lp->M;
     q.head_w = lp->head_w;
     q.head_acc = lp->head_acc;
@@ -826,7 +826,7 @@ extern "C" int dpvo_linear384_f16(const dpvo_linear_params* lp, void* stream) {
     const bool ln = lp->ln_gamma != nullptr;
     if (ln) DPVO_REQUIRE(lp->ln_beta != nullptr, "linear384: LayerNorm needs both gamma and beta");
     const bool heads = lp->head_w != nullptr;
-    static const bool amc = getenv("DPVO_LINEAR_AMC") != nullptr && getenv("DPVO_LINEAR_AMC")[0] == '1';
+    static const bool amc = debug_env("DPVO_LINEAR_AMC") != nullptr && debug_env("DPVO_LINEAR_AMC")[0] == '1';
     if (amc && make_map(&tmA, lp->A, lp->K, lp->M, lp->lda, BM / 2)) return 1;
     const void* fn =
         amc ? (ln ? reinterpret_cast<const void*>(linear384_rw_kernel<true, false, true>)

@@ -279,7 +279,7 @@ def patchify_backward(net, coords, gradient, radius):
 
 
 def _backward_fast_ok(fmap1, fmap2, coords, radius):
-    return (fmap1.dtype == torch.float16 and fmap2.dtype == torch.float16 and radius == 3
+    return (fmap1.dtype in (torch.float16, torch.float32) and fmap2.dtype == fmap1.dtype and radius == 3
             and fmap1.shape[2] == 128 and tuple(fmap1.shape[3:]) == (3, 3) and tuple(coords.shape[3:]) == (3, 3))
 
 
@@ -301,21 +301,23 @@ def backward(fmap1, fmap2, coords, ii, jj, corr_grad, radius):
     if _backward_fast_ok(fmap1, fmap2, coords, radius) and not os.environ.get("DPVO_CORR_BWD_GENERIC"):
         f2 = _channels_last_view(fmap2.detach())
         f1 = fmap1.detach()
-        if tuple(f1.stride()[2:]) != (9, 3, 1) or f1.stride(1) % 4 or f1.stride(0) % 4 or f1.data_ptr() % 8:
+        if tuple(f1.stride()[2:]) != (9, 3, 1) or f1.stride(1) % 4 or f1.stride(0) % 4 or f1.data_ptr() % 16:
             f1 = f1.contiguous()
         _, N1, C = f1.shape[:3]
         _, N2, _, H2, W2 = f2.shape
         dev = fmap1.device
-        g1 = torch.empty((B, N1, C, 3, 3), dtype=torch.float16, device=dev)
-        g2 = torch.empty((B, N2, H2, W2, C), dtype=torch.float16, device=dev)
+        half = fmap1.dtype == torch.float16
+        alloc = torch.empty if half else torch.zeros
+        g1 = alloc((B, N1, C, 3, 3), dtype=fmap1.dtype, device=dev)
+        g2 = alloc((B, N2, H2, W2, C), dtype=fmap1.dtype, device=dev)
         if B * M == 0:
             return [g1.zero_(), g2.zero_().permute(0, 1, 4, 2, 3)]
-        acc1 = torch.zeros((B * N1 * C * 9,), dtype=torch.float32, device=dev)
-        acc2 = torch.zeros((B * N2 * H2 * W2 * C,), dtype=torch.float32, device=dev)
+        acc1 = torch.zeros((B * N1 * C * 9,), dtype=torch.float32, device=dev) if half else None
+        acc2 = torch.zeros((B * N2 * H2 * W2 * C,), dtype=torch.float32, device=dev) if half else None
         s1, s2 = f1.stride(), f2.stride()
         with _lib.device_guard(fmap1):
-            check(lib.dpvo_corr_backward_f16_nhwc(
-                ptr(f1), c_i64(s1[0]), c_i64(s1[1]),
+            check(lib.dpvo_corr_backward_nhwc(
+                c_i32(dtype_code(fmap1)), ptr(f1), c_i64(s1[0]), c_i64(s1[1]),
                 ptr(f2), c_i64(s2[0]), c_i64(s2[1]), c_i64(s2[3]), c_i64(s2[4]),
                 c_i32(N1), c_i32(N2), c_i32(H2), c_i32(W2),
                 ptr(coords), ptr(ii), ptr(jj), c_i32(B), c_i32(M),

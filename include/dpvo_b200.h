@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define DPVO_B200_ABI_VERSION 3
+#define DPVO_B200_ABI_VERSION 4
 
 typedef enum { DPVO_F16 = 0, DPVO_F32 = 1, DPVO_F64 = 2 } dpvo_dtype;
 
@@ -60,6 +60,9 @@ int dpvo_corr_forward(dpvo_dtype dtype,
                       const dpvo_corr_level* levels, int32_t nlev,
                       void* stream);
 
+/* Name of the kernel the last dpvo_corr_forward call launched (static string; instrumentation for bench.py). */
+const char* dpvo_corr_last_kernel(void);
+
 /* Correlation backward — replaces cuda_corr.backward (correlation_kernel.cu:140-191,237-287).
  * corr_grad: logical [B, M, D-1(x), D-1(y), PH, PW] with element strides cg_*.
  * fmap1_grad / fmap2_grad: contiguous, same logical shape as the fmaps, PRE-ZEROED
@@ -77,13 +80,15 @@ int dpvo_corr_backward(dpvo_dtype dtype,
                        void* fmap1_grad, void* fmap2_grad, float* acc1, float* acc2,
                        void* stream);
 
-/* Same operator, training fast path: fp16 features, C = 128, 3x3 patches, radius 3 (the only shape
- * net.py:156-169 produces).  fmap1: dense patches [B][N1][128][3][3] (batch / patch strides g_sb, g_sn);
- * fmap2: CHANNELS-LAST ring (channel stride 1; strides sb, sn, sy, sx in elements) — the layout the
- * forward lookup already reads; fmap2_grad_nhwc: contiguous [B][N2][H2][W2][128] fp16 (return it to
- * autograd as a permuted view); fmap1_grad: contiguous like fmap1.  acc1 ([B*N1*1152]) and acc2
- * ([B*N2*H2*W2*128]) are ZEROED float32 scratch; both gradients are written in full (no pre-zeroing). */
-int dpvo_corr_backward_f16_nhwc(
+/* Same operator, training fast path: fp16 or fp32 features, C = 128, 3x3 patches, radius 3 (the only
+ * shape net.py:156-169 produces).  fmap1: dense patches [B][N1][128][3][3] (batch / patch strides g_sb,
+ * g_sn); fmap2: CHANNELS-LAST ring (channel stride 1; strides sb, sn, sy, sx in elements) — the layout the
+ * forward lookup already reads; fmap2_grad_nhwc: contiguous [B][N2][H2][W2][128] (return it to autograd as
+ * a permuted view); fmap1_grad: contiguous like fmap1.
+ * F16: acc1 ([B*N1*1152]) and acc2 ([B*N2*H2*W2*128]) are ZEROED float32 scratch and both gradients are
+ * written in full.  F32: acc1/acc2 are ignored, the gradients must be PRE-ZEROED and are accumulated in place. */
+int dpvo_corr_backward_nhwc(
+    dpvo_dtype dtype,
     const void* fmap1, int64_t g_sb, int64_t g_sn,
     const void* fmap2, int64_t sb, int64_t sn, int64_t sy, int64_t sx,
     int32_t N1, int32_t N2, int32_t H2, int32_t W2,

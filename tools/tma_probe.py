@@ -5,6 +5,15 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 pkg = importlib.import_module("deep-visual-odometry-slam_b200")
 lib = pkg._lib
+# the probe is a development micro-benchmark: it is NOT part of libdpvo_b200.so; build it on demand next to this file
+import subprocess
+_CS = os.path.join(ROOT, "deep-visual-odometry-slam_b200", "csrc")
+_SO = os.path.join(ROOT, "tools", "libtma_probe.so")
+if not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(os.path.join(ROOT, "tools", "tma_probe.cu")):
+    subprocess.check_call(["/usr/local/cuda/bin/nvcc", "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
+                           "-Xcompiler", "-fPIC", "-shared", "-I", _CS, "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tools", "tma_probe.cu"), os.path.join(_CS, "api.cu"), "-o", _SO, "-lcudart"])
+_probe = ctypes.CDLL(_SO)
 import sys as _s
 rows, K = (45312 * 6, 64) if "--chunked" in _s.argv else (45312, 384)
 A = torch.randn(rows, K, device="cuda").half()
@@ -16,7 +25,7 @@ for grid in (148, 16):
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        lib.check(lib.lib.dpvo_debug_tma_probe(lib.ptr(A), lib.c_i64(rows), lib.c_i32(K), lib.c_i32(stages),
+        lib.check(_probe.dpvo_debug_tma_probe(lib.ptr(A), lib.c_i64(rows), lib.c_i32(K), lib.c_i32(stages),
                                                lib.c_i32(4), lib.c_i32(grid), lib.ptr(cyc), lib.stream_of(A)), "probe")
         e1.record(); torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
