@@ -213,11 +213,9 @@ typedef struct dpvo_linear_params {
 } dpvo_linear_params;
 int dpvo_linear384_f16(const dpvo_linear_params* p, void* stream);
 /* Diagnostics: 16 per-role cycle counters of CTA 0 of the last K=384 launch made with the
- * environment variable DPVO_LINEAR_PROFILE=1 (csrc/update_gemm.cu).  Synchronises the device. */
+ * environment variable DPVO_LINEAR_PROFILE=1 in a library built with -DDPVO_DEBUG_HOOKS (csrc/update_gemm.cu).
+ * Synchronises the device. */
 int dpvo_linear_profile_read(long long* out16);
-/* Diagnostics: TMA ingest probe (csrc/tma_probe.cu, tools/tma_probe.py) — not part of the product path. */
-int dpvo_debug_tma_probe(const void* A, int64_t rows, int32_t K, int32_t stages, int32_t iters, int32_t grid,
-                         long long* cycles, void* stream);
 
 /* out[r] = index[r] >= 0 ? src[index[r]] : 0 for fp16 rows of `dim` elements (dim % 8 == 0) —
  * `mask * net[:, ix]` of Update.forward (net.py:76-80; ix from fastba.neighbors, -1 = no neighbour). */
