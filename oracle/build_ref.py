@@ -11,6 +11,8 @@ Modules built (names are the ones the reference imports by bare name):
   cuda_corr          methods/dpvo/dpvo/altcorr/{correlation.cpp,correlation_kernel.cu}
   cuda_ba            methods/dpvo/dpvo/fastba/{ba.cpp,ba_cuda.cu,block_e.cu}
   lietorch_backends  methods/dpvo/dpvo/lietorch/src/{lietorch.cpp,lietorch_gpu.cu,lietorch_cpu.cpp}
+  dpviewer_cuda      modules/DPViewer/dpviewer/viewer_cuda.cu behind oracle/viewer_ref_binding.cpp (this repo's
+                     pybind wrapper: the reference only reaches these kernels through its OpenGL viewer class)
 
 It also INSTALLS the reference's pure-Python package (what `pip install --target` of the
 reference would place in site-packages: methods/dpvo/dpvo/**/*.py, utils/utils.py and
@@ -39,6 +41,10 @@ SPECS = {
     "cuda_ba": dict(
         sources=["dpvo/fastba/ba.cpp", "dpvo/fastba/ba_cuda.cu", "dpvo/fastba/block_e.cu"],
         includes=[EIGEN]),
+    # the viewer's two plain CUDA kernels, headless (the window / GL interop in viewer.cpp is not built)
+    "dpviewer_cuda": dict(
+        sources=[os.path.join(HERE, "viewer_ref_binding.cpp"), "/root/reference/modules/DPViewer/dpviewer/viewer_cuda.cu"],
+        includes=["/root/reference/modules/DPViewer/dpviewer"]),
     "lietorch_backends": dict(
         sources=["dpvo/lietorch/src/lietorch.cpp", "dpvo/lietorch/src/lietorch_gpu.cu",
                  "dpvo/lietorch/src/lietorch_cpu.cpp"],
@@ -52,7 +58,7 @@ def build_one(name):
     bdir = os.path.join(OUT, "_build_" + name)
     os.makedirs(bdir, exist_ok=True)
     load(name=name,
-         sources=[os.path.join(REF, s) for s in spec["sources"]],
+         sources=[s if os.path.isabs(s) else os.path.join(REF, s) for s in spec["sources"]],
          extra_include_paths=spec["includes"],
          extra_cflags=["-O3"],
          extra_cuda_cflags=["-O3", "-Wno-deprecated-gpu-targets",
