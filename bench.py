@@ -431,6 +431,9 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="frame", choices=["frame", "train"],
+                    help="train: BASELINE config 4, the reference's VONet training step on the drop-ins (tools/reftrain.py); "
+                         "under torchrun it is data parallel with one NCCL all-reduce of the flat gradient buffer per step")
     ap.add_argument("--sequence-frames", type=int, default=1000)
     ap.add_argument("--no-sequence", action="store_true", help="skip the 1000-frame reference-DPVO-class legs (~2 min)")
     ap.add_argument("--no-reference-ext", action="store_true")
@@ -449,6 +452,15 @@ def main():
     sys.stdout.flush()
     _STDOUT = os.fdopen(os.dup(1), "w")
     os.dup2(2, 1)
+
+    if args.workload == "train":
+        # config 4 — clips/s; `--impl reference` runs the same step on the reference's own CUDA extensions (oracle/_ref)
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import reftrain
+        os.dup2(_STDOUT.fileno(), 1)
+        sys.argv = [sys.argv[0], "--backend", "ref" if args.impl == "reference" else "dropin", "--no-amp", "--mode", "bench",
+                    "--steps", str(args.steps), "--warmup", str(min(args.warmup, 3))]
+        return reftrain.main()
 
     if args.impl == "reference":
         run_reference(args, rank, world)

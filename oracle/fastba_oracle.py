@@ -196,6 +196,92 @@ def ba(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, PPF, t0, t
     return poses, patches
 
 
+def _group_sum(keys, values):
+    """sum `values` rows over equal `keys`: returns (unique keys ascending, sums).  Sorting + reduceat (np.add.at is
+    unbuffered and far too slow for millions of edges)."""
+    order = np.argsort(keys, kind="stable")
+    ks = keys[order]
+    if len(ks) == 0:
+        return ks, values[:0]
+    starts = np.flatnonzero(np.concatenate([[True], ks[1:] != ks[:-1]]))
+    return ks[starts], np.add.reduceat(values[order], starts, axis=0)
+
+
+def ba_sparse(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, PPF, t0, t1, iterations):
+    """Same normal equations and update rule as `ba()` (ba_cuda.cu:232-376, :447-582, :178-229), assembled as
+    scipy.sparse matrices (6x6 blocks summed per frame pair, E entries per (frame, patch)) and solved with a sparse
+    direct solver in float64 — for global-BA sizes (BASELINE config 5: 1,000+ keyframes, 2.4 M edges) where the dense
+    E of `ba()` (6N x #patches) does not fit.  Checked against `ba()` on a small window in tests/test_oracle_cpu.py.
+    Returns (poses, patches, [(dX, dZ, kx) per iteration])."""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spl
+    poses = np.array(poses, dtype=np.float64).reshape(-1, 7).copy()
+    P = patches.shape[-1]
+    patches = np.array(patches, dtype=np.float64).reshape(-1, 3, P, P).copy()
+    intrinsics = np.asarray(intrinsics, np.float64).reshape(-1, 4)
+    target = np.asarray(target, np.float64).reshape(-1, 2)
+    weight = np.asarray(weight, np.float64).reshape(-1, 2)
+    lm = float(np.asarray(lmbda).reshape(-1)[0])
+    ii = np.asarray(ii, np.int64); jj = np.asarray(jj, np.int64); kk = np.asarray(kk, np.int64)
+    kx, ku = np.unique(kk, return_inverse=True)
+    N, M = t1 - t0, len(kx)
+    n = 6 * N
+    a6 = np.arange(6)
+    ups = []
+    for _ in range(iterations):
+        r, w, Ji, Jj, Jz = edge_terms(poses, patches, intrinsics, target, weight, ii, jj, kk)
+        ix, jx = ii - t0, jj - t0
+        vi = (ix >= 0) & (ix < N)
+        vj = (jx >= 0) & (jx < N)
+        vij = vi & vj
+        # per-edge 6x6 blocks / 6-vectors summed over the two residual rows
+        Bii = np.einsum("er,era,erb->eab", w, Ji, Ji)
+        Bjj = np.einsum("er,era,erb->eab", w, Jj, Jj)
+        Bij = -np.einsum("er,era,erb->eab", w, Ji, Jj)
+        Ei = -np.einsum("er,er,era->ea", w, Jz, Ji)
+        Ej = np.einsum("er,er,era->ea", w, Jz, Jj)
+        vi6 = -np.einsum("er,er,era->ea", w, r, Ji)
+        vj6 = np.einsum("er,er,era->ea", w, r, Jj)
+        C = np.bincount(ku, weights=(w * Jz * Jz).sum(1), minlength=M)
+        u = np.bincount(ku, weights=(w * r * Jz).sum(1), minlength=M)
+        Q = 1.0 / (C + lm)
+        if N > 0:
+            keys = np.concatenate([ix[vi] * N + ix[vi], jx[vj] * N + jx[vj], ix[vij] * N + jx[vij], jx[vij] * N + ix[vij]])
+            blks = np.concatenate([Bii[vi], Bjj[vj], Bij[vij], np.swapaxes(Bij[vij], 1, 2)])
+            pk, pb = _group_sum(keys, blks.reshape(len(keys), 36))
+            fa, fb = pk // N, pk % N
+            rows = (6 * fa)[:, None, None] + a6[None, :, None] + 0 * a6[None, None, :]
+            cols = (6 * fb)[:, None, None] + 0 * a6[None, :, None] + a6[None, None, :]
+            Bm = sp.coo_matrix((pb.ravel(), (rows.ravel(), cols.ravel())), shape=(n, n)).tocsr()
+            ekeys = np.concatenate([ix[vi] * M + ku[vi], jx[vj] * M + ku[vj]])
+            ek, eb = _group_sum(ekeys, np.concatenate([Ei[vi], Ej[vj]]))
+            ef, ep = ek // M, ek % M
+            Em = sp.coo_matrix((eb.ravel(), (((6 * ef)[:, None] + a6[None]).ravel(), np.repeat(ep, 6))), shape=(n, M)).tocsr()
+            fk, fv = _group_sum(np.concatenate([ix[vi], jx[vj]]), np.concatenate([vi6[vi], vj6[vj]]))
+            v = np.zeros((N, 6)); v[fk] = fv
+            v = v.reshape(n)
+            EQ = Em.multiply(Q[None, :]).tocsr()
+            S = (Bm - EQ @ Em.T).tocsc()
+            y = v - EQ @ u
+            S = S + sp.diags(1e-4 * S.diagonal() + 1.0)           # ba_cuda.cu:546,560: S += I * (1e-4 * S + 1)
+            dX = spl.splu(S.tocsc()).solve(y)
+            dZ = Q * (u - Em.T @ dX)
+            dXr = dX.reshape(N, 6)
+            for i in range(N):
+                t_new, q_new = _retr_se3(dXr[i], poses[t0 + i, :3], poses[t0 + i, 3:])
+                poses[t0 + i, :3] = t_new
+                poses[t0 + i, 3:] = q_new
+        else:
+            dXr = np.zeros((0, 6))
+            dZ = Q * u
+        d = patches[kx, 2, 0, 0] + dZ
+        d = np.where(d > 20, 1.0, d)
+        d = np.maximum(d, 1e-4)
+        patches[kx, 2] = d[:, None, None]
+        ups.append((dXr.copy(), dZ.copy(), kx.copy()))
+    return poses, patches, ups
+
+
 def neighbors(ii, jj):
     """cuda_ba.neighbors (ba.cpp:59-97): for every edge, the index of the previous / next edge
     of the same ii-group ordered by jj (stable), -1 at the ends."""

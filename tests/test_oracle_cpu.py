@@ -410,3 +410,24 @@ def test_encoder_oracle_vs_reference(name):
                             synth.encoder_images(m.N_IMG, m.H, m.W, m.IMG_SEED), c["norm_fn"])[0]
     assert got.shape == g[name].shape
     assert np.abs(got - g[name]).max() < 2e-5 * max(1.0, np.abs(g[name]).max())
+
+
+def test_sparse_ba_oracle_equals_dense_ba_oracle():
+    """oracle/fastba_oracle.ba_sparse (scipy.sparse float64, used at global-BA sizes) against the dense float64
+    restatement `ba()` (itself pinned to the reference extension on the GPU box) on a window both can hold."""
+    import importlib
+    from oracle import fastba_oracle as fo
+    synth = importlib.import_module("deep-visual-odometry-slam_b200.synth") if False else None
+    import importlib.util, os
+    spec = importlib.util.spec_from_file_location("_synth", os.path.join(os.path.dirname(os.path.dirname(__file__)),
+                                                  "deep-visual-odometry-slam_b200", "synth.py"))
+    synth = importlib.util.module_from_spec(spec); spec.loader.exec_module(synth)
+    d = synth.ba_inputs(18, seed=5, M=8, n_buf=24)
+    args = (d["poses"], d["patches"], d["intrinsics"], d["target"], d["weight"], 1e-4, d["ii"], d["jj"], d["kk"], 8, 3, 18, 2)
+    p0, z0, u0 = fo.ba(*args, return_updates=True)
+    p1, z1, u1 = fo.ba_sparse(*args)
+    assert np.abs(p0 - p1).max() < 1e-9 and np.abs(z0 - z1).max() < 1e-9
+    for (dx0, dz0, k0), (dx1, dz1, k1) in zip(u0, u1):
+        assert np.array_equal(k0, k1)
+        assert np.abs(dx0 - dx1).max() < 1e-9 * max(1.0, np.abs(dx0).max())
+        assert np.abs(dz0 - dz1).max() < 1e-9 * max(1.0, np.abs(dz0).max())
