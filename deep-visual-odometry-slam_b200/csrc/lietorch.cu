@@ -1,5 +1,7 @@
-// lietorch_backends replacement: element-wise Lie-group operators (SO3, SE3) and their
-// vector-Jacobian products, float32 / float64.
+// lietorch_backends replacement: element-wise Lie-group operators (SO3, RxSO3, SE3, Sim3) and their
+// vector-Jacobian products, float32 / float64, on the device (kernels below) and on the host
+// (dpvo_lie_host: the same templates in a plain loop — the reference module dispatches on the tensor's device,
+// lietorch/include/dispatch.h:12-43, src/lietorch_cpu.cpp).
 //
 // Replaces /root/reference/methods/dpvo/dpvo/lietorch/src/lietorch_gpu.cu (kernels :20-290,
 // launchers :296-601) behind the C ABI in include/dpvo_b200.h.  Gradient conventions are the
@@ -51,7 +53,7 @@ template <class G, int OP> __host__ __device__ constexpr Widths widths() {
 }
 
 // row vector (K) times KxK matrix
-template <typename T, int K> __device__ __forceinline__ void rowvec(const T* g, const T (&A)[K][K], T* out) {
+template <typename T, int K> LIE_HD void rowvec(const T* g, const T (&A)[K][K], T* out) {
 #pragma unroll
   for (int j = 0; j < K; ++j) {
     T s = T(0);
@@ -60,7 +62,7 @@ template <typename T, int K> __device__ __forceinline__ void rowvec(const T* g, 
     out[j] = s;
   }
 }
-template <typename T, int K> __device__ __forceinline__ void matvec(const T (&A)[K][K], const T* a, T* out) {
+template <typename T, int K> LIE_HD void matvec(const T (&A)[K][K], const T* a, T* out) {
 #pragma unroll
   for (int i = 0; i < K; ++i) {
     T s = T(0);
@@ -69,16 +71,16 @@ template <typename T, int K> __device__ __forceinline__ void matvec(const T (&A)
     out[i] = s;
   }
 }
-template <typename T, int K> __device__ __forceinline__ void matTvec(const T (&A)[K][K], const T* a, T* out) {
+template <typename T, int K> LIE_HD void matTvec(const T (&A)[K][K], const T* a, T* out) {
   rowvec<T, K>(a, A, out);
 }
-template <typename T, int K, int N> __device__ __forceinline__ void pad_store(const T* v, T* row, T sign = T(1)) {
+template <typename T, int K, int N> LIE_HD void pad_store(const T* v, T* row, T sign = T(1)) {
 #pragma unroll
   for (int i = 0; i < N; ++i) row[i] = (i < K) ? sign * v[i] : T(0);
 }
 
 template <class G, typename T, int OP>
-__device__ __forceinline__ void apply(const T* r0, const T* r1, const T* r2, T* w0, T* w1) {
+LIE_HD void apply(const T* r0, const T* r1, const T* r2, T* w0, T* w1) {
   constexpr int K = G::K, N = G::N;
   if constexpr (OP == OP_EXP) {
     G::Exp(r0).store(w0);
@@ -277,7 +279,48 @@ int launch(const char* name, int group, dpvo_dtype dt, const void* i0, const voi
     return dt == DPVO_F32 ? launch_t<SO3<float>, float, OP>(i0, i1, i2, o0, o1, n, st)
                           : launch_t<SO3<double>, double, OP>(i0, i1, i2, o0, o1, n, st);
   }
-  set_error("%s: group %d is not provided (SO3=1 and SE3=3 are; DPVO's update path uses SE3 only)", name, group);
+  if (group == DPVO_LIE_RXSO3) {
+    return dt == DPVO_F32 ? launch_t<RxSO3<float>, float, OP>(i0, i1, i2, o0, o1, n, st)
+                          : launch_t<RxSO3<double>, double, OP>(i0, i1, i2, o0, o1, n, st);
+  }
+  if (group == DPVO_LIE_SIM3) {
+    return dt == DPVO_F32 ? launch_t<Sim3<float>, float, OP>(i0, i1, i2, o0, o1, n, st)
+                          : launch_t<Sim3<double>, double, OP>(i0, i1, i2, o0, o1, n, st);
+  }
+  set_error("%s: unknown group %d (SO3=1, RxSO3=2, SE3=3, Sim3=4)", name, group);
+  return 1;
+}
+
+// ------------------------------------------------------------------------------------ host path
+template <class G, typename T, int OP>
+int host_t(const void* i0, const void* i1, const void* i2, void* o0, void* o1, int64_t n) {
+  constexpr Widths w = widths<G, OP>();
+  const T* a0 = static_cast<const T*>(i0);
+  const T* a1 = static_cast<const T*>(i1);
+  const T* a2 = static_cast<const T*>(i2);
+  T* b0 = static_cast<T*>(o0);
+  T* b1 = static_cast<T*>(o1);
+  T z0[1] = {T(0)};
+  for (int64_t r = 0; r < n; ++r)
+    apply<G, T, OP>(w.i0 ? a0 + r * w.i0 : z0, w.i1 ? a1 + r * w.i1 : z0, w.i2 ? a2 + r * w.i2 : z0,
+                    b0 + r * w.o0, w.o1 ? b1 + r * w.o1 : b0);
+  return 0;
+}
+
+template <int OP>
+int host_op(int group, dpvo_dtype dt, const void* i0, const void* i1, const void* i2, void* o0, void* o1, int64_t n) {
+  constexpr bool two_in = (OP != OP_EXP && OP != OP_LOG && OP != OP_INV && OP != OP_MATRIX && OP != OP_PROJ);
+  constexpr bool three_in = (OP == OP_MUL_BWD || OP == OP_ADJ_BWD || OP == OP_ADJT_BWD || OP == OP_ACT_BWD || OP == OP_ACT4_BWD);
+  DPVO_REQUIRE(i0 && o0 && (!two_in || i1) && (!three_in || (i2 && o1)), "lie_host: null pointer");
+  DPVO_REQUIRE(dt == DPVO_F32 || dt == DPVO_F64, "lie_host: dtype must be float32 or float64");
+  const bool f = dt == DPVO_F32;
+  switch (group) {
+    case DPVO_LIE_SO3:   return f ? host_t<SO3<float>, float, OP>(i0, i1, i2, o0, o1, n) : host_t<SO3<double>, double, OP>(i0, i1, i2, o0, o1, n);
+    case DPVO_LIE_RXSO3: return f ? host_t<RxSO3<float>, float, OP>(i0, i1, i2, o0, o1, n) : host_t<RxSO3<double>, double, OP>(i0, i1, i2, o0, o1, n);
+    case DPVO_LIE_SE3:   return f ? host_t<SE3<float>, float, OP>(i0, i1, i2, o0, o1, n) : host_t<SE3<double>, double, OP>(i0, i1, i2, o0, o1, n);
+    case DPVO_LIE_SIM3:  return f ? host_t<Sim3<float>, float, OP>(i0, i1, i2, o0, o1, n) : host_t<Sim3<double>, double, OP>(i0, i1, i2, o0, o1, n);
+  }
+  set_error("lie_host: unknown group %d (SO3=1, RxSO3=2, SE3=3, Sim3=4)", group);
   return 1;
 }
 
@@ -328,3 +371,27 @@ LIE_BINARY_BWD(dpvo_lie_act4_backward, OP_ACT4_BWD)
 LIE_UNARY(dpvo_lie_as_matrix, OP_MATRIX)
 LIE_UNARY(dpvo_lie_projector, OP_PROJ)
 LIE_BINARY(dpvo_lie_jinv, OP_JINV)
+
+// Host (CPU-tensor) form of every operator above: `op` is a dpvo_lie_op code, pointers are HOST memory, rows as in the
+// device entry points (in0 / in1 / in2 and out0 / out1 in the order the device function of that op takes them).
+extern "C" int dpvo_lie_host(int32_t op, int32_t group, dpvo_dtype dt, const void* in0, const void* in1, const void* in2,
+                             void* out0, void* out1, int64_t n) {
+  DPVO_REQUIRE(n >= 0, "lie_host: negative batch size");
+  if (n == 0) return 0;
+  switch (op) {
+#define LIE_HOST_CASE(CODE, OP) case CODE: return host_op<OP>(group, dt, in0, in1, in2, out0, out1, n);
+    LIE_HOST_CASE(DPVO_LIE_OP_EXP, OP_EXP) LIE_HOST_CASE(DPVO_LIE_OP_EXP_BWD, OP_EXP_BWD)
+    LIE_HOST_CASE(DPVO_LIE_OP_LOG, OP_LOG) LIE_HOST_CASE(DPVO_LIE_OP_LOG_BWD, OP_LOG_BWD)
+    LIE_HOST_CASE(DPVO_LIE_OP_INV, OP_INV) LIE_HOST_CASE(DPVO_LIE_OP_INV_BWD, OP_INV_BWD)
+    LIE_HOST_CASE(DPVO_LIE_OP_MUL, OP_MUL) LIE_HOST_CASE(DPVO_LIE_OP_MUL_BWD, OP_MUL_BWD)
+    LIE_HOST_CASE(DPVO_LIE_OP_ADJ, OP_ADJ) LIE_HOST_CASE(DPVO_LIE_OP_ADJ_BWD, OP_ADJ_BWD)
+    LIE_HOST_CASE(DPVO_LIE_OP_ADJT, OP_ADJT) LIE_HOST_CASE(DPVO_LIE_OP_ADJT_BWD, OP_ADJT_BWD)
+    LIE_HOST_CASE(DPVO_LIE_OP_ACT, OP_ACT) LIE_HOST_CASE(DPVO_LIE_OP_ACT_BWD, OP_ACT_BWD)
+    LIE_HOST_CASE(DPVO_LIE_OP_ACT4, OP_ACT4) LIE_HOST_CASE(DPVO_LIE_OP_ACT4_BWD, OP_ACT4_BWD)
+    LIE_HOST_CASE(DPVO_LIE_OP_MATRIX, OP_MATRIX) LIE_HOST_CASE(DPVO_LIE_OP_PROJECTOR, OP_PROJ)
+    LIE_HOST_CASE(DPVO_LIE_OP_JINV, OP_JINV)
+#undef LIE_HOST_CASE
+  }
+  set_error("lie_host: unknown op %d", op);
+  return 1;
+}

@@ -5,28 +5,35 @@ Same function names, argument order and return conventions: every function takes
 contiguous `[batch, width]` float32 / float64 (CHECK_CONTIGUOUS, lietorch.cpp:7), forward ops return
 a tensor, backward ops return a list of tensors in input order.  Outputs are allocated through
 torch's caching allocator; the arithmetic runs in libdpvo_b200.so (csrc/lietorch.cu) on torch's
-current stream.  SO3 and SE3 are provided (DPVO only instantiates SE3, projective_ops.py:60-65,
-dpvo.py:419-420); other groups and CPU tensors raise RuntimeError — there is no CPU fallback.
+current stream.  All four groups are provided.  Like the reference (lietorch/include/dispatch.h:12-43) the module
+dispatches on the tensors' device: CUDA tensors run the sm_100a kernels, CPU tensors (data readers, evaluation scripts)
+run the same templates compiled for the host (`dpvo_lie_host`) — that is the reference's own device dispatch, not a
+fallback: a CUDA tensor never takes the host path.
 """
 import torch
 
 from . import _lib
 
 _L = _lib.lib
-_DIMS = {1: (3, 4), 3: (6, 7)}  # group id -> (K tangent, N embedding)
+_DIMS = {1: (3, 4), 2: (4, 5), 3: (6, 7), 4: (7, 8)}  # group id -> (K tangent, N embedding)
+# device entry point -> (dpvo_lie_op code, number of input pointers) for the host form
+_HOST = {"dpvo_lie_expm": (0, 1), "dpvo_lie_expm_backward": (1, 2), "dpvo_lie_logm": (2, 1), "dpvo_lie_logm_backward": (3, 2),
+         "dpvo_lie_inv": (4, 1), "dpvo_lie_inv_backward": (5, 2), "dpvo_lie_mul": (6, 2), "dpvo_lie_mul_backward": (7, 3),
+         "dpvo_lie_adj": (8, 2), "dpvo_lie_adj_backward": (9, 3), "dpvo_lie_adjT": (10, 2), "dpvo_lie_adjT_backward": (11, 3),
+         "dpvo_lie_act": (12, 2), "dpvo_lie_act_backward": (13, 3), "dpvo_lie_act4": (14, 2), "dpvo_lie_act4_backward": (15, 3),
+         "dpvo_lie_as_matrix": (16, 1), "dpvo_lie_projector": (17, 1), "dpvo_lie_jinv": (18, 2)}
 
 
 def _dims(group):
     try:
         return _DIMS[int(group)]
     except KeyError:
-        raise RuntimeError(f"lietorch_backends: group {group} is not provided (SO3=1, SE3=3 are)")
+        raise RuntimeError(f"lietorch_backends: unknown group {group} (SO3=1, RxSO3=2, SE3=3, Sim3=4)")
 
 
 def _check(group, *specs):
     """specs: (tensor, name, width).  Returns (batch, dtype code)."""
     first = specs[0][0]
-    _lib.require_cuda(*[s[0] for s in specs])
     if first.dtype not in (torch.float32, torch.float64):
         raise RuntimeError(f"lietorch_backends: expected float32/float64, got {first.dtype}")
     n = first.shape[0] if first.dim() == 2 else -1
@@ -41,6 +48,13 @@ def _check(group, *specs):
 
 
 def _call(fn, what, group, dt, n, ref, *ptr_tensors):
+    if not ref.is_cuda:
+        op, n_in = _HOST[fn.__name__]
+        ins = [_lib.ptr(t) for t in ptr_tensors[:n_in]] + [_lib.c_p(0)] * (3 - n_in)
+        outs = [_lib.ptr(t) for t in ptr_tensors[n_in:]]
+        outs += [_lib.c_p(0)] * (2 - len(outs))
+        _lib.check(_L.dpvo_lie_host(_lib.c_i32(op), _lib.c_i32(int(group)), _lib.c_i32(dt), *ins, *outs, _lib.c_i64(n)), what)
+        return
     args = [_lib.c_i32(int(group)), _lib.c_i32(dt)] + [_lib.ptr(t) for t in ptr_tensors] + \
            [_lib.c_i64(n), _lib.stream_of(ref)]
     with torch.cuda.device(ref.device):

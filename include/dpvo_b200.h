@@ -340,6 +340,18 @@ int dpvo_lie_projector(int32_t group, dpvo_dtype dt, const void* X, void* P /*[n
 int dpvo_lie_jinv(int32_t group, dpvo_dtype dt, const void* X, const void* a /*[n,K]*/, void* b /*[n,K]*/, int64_t n,
                   void* stream);
 
+/* The same operators on HOST memory (CPU tensors): the reference module dispatches on the tensor's device
+ * (lietorch/include/dispatch.h:12-43, src/lietorch_cpu.cpp).  `op` selects the operator; in0..in2 / out0..out1 are the
+ * pointer arguments of the device entry point of that operator, in its order (unused ones NULL). */
+typedef enum {
+  DPVO_LIE_OP_EXP = 0, DPVO_LIE_OP_EXP_BWD, DPVO_LIE_OP_LOG, DPVO_LIE_OP_LOG_BWD, DPVO_LIE_OP_INV, DPVO_LIE_OP_INV_BWD,
+  DPVO_LIE_OP_MUL, DPVO_LIE_OP_MUL_BWD, DPVO_LIE_OP_ADJ, DPVO_LIE_OP_ADJ_BWD, DPVO_LIE_OP_ADJT, DPVO_LIE_OP_ADJT_BWD,
+  DPVO_LIE_OP_ACT, DPVO_LIE_OP_ACT_BWD, DPVO_LIE_OP_ACT4, DPVO_LIE_OP_ACT4_BWD, DPVO_LIE_OP_MATRIX, DPVO_LIE_OP_PROJECTOR,
+  DPVO_LIE_OP_JINV
+} dpvo_lie_op;
+int dpvo_lie_host(int32_t op, int32_t group, dpvo_dtype dt, const void* in0, const void* in1, const void* in2,
+                  void* out0, void* out1, int64_t n);
+
 /* ---- patch-graph edge bookkeeping on the device -------------------------------
  * Replaces the torch.cat / boolean-mask edits of dpvo.py:215-239 (append_factors, remove_factors),
  * :262-310 (keyframe) and :362-375 (__edges_forw/__edges_back), and the numba reduce_edges of

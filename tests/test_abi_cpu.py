@@ -1,6 +1,7 @@
 """CPU suite, part 2: the C-ABI library loads and exports every symbol include/dpvo_b200.h declares,
 argument validation fails loudly without touching a GPU, and the Python operator surface refuses
-CPU tensors (there is no CPU fallback in the product path)."""
+CPU tensors (there is no CPU fallback in the product path; the one exception is lietorch_backends, whose reference
+dispatches on the tensor's device and whose CPU form is therefore part of its interface)."""
 import ctypes
 import os
 import re
@@ -116,18 +117,22 @@ def test_dropin_modules_import_by_bare_name():
     assert r.returncode == 0, r.stderr[-2000:]
 
 
-def test_lietorch_refuses_cpu_and_bad_groups():
+def test_lietorch_dispatches_cpu_tensors_and_refuses_bad_groups():
+    """CPU tensors take the host form of the same templates (the reference's device dispatch, dispatch.h:12-43);
+    unknown groups and wrong row widths fail loudly."""
     lb = load_pkg("lietorch_backends")
     X = torch.zeros(3, 7)
+    X[:, 6] = 1
+    assert torch.equal(lb.inv(3, X), X)
     with pytest.raises(RuntimeError):
-        lb.inv(3, X)
+        lb.inv(2, X)                     # RxSO3 rows are 5 wide
     with pytest.raises(RuntimeError):
-        lb.inv(2, X)
+        lb.inv(9, X)
     lib = load_pkg()._lib.lib
     lib.dpvo_last_error.restype = ctypes.c_char_p
     null = ctypes.c_void_p(0)
     one = ctypes.c_void_p(256)   # never dereferenced: the group check fails first
-    rc = lib.dpvo_lie_inv(ctypes.c_int32(4), ctypes.c_int32(1), one, one, ctypes.c_int64(5), null)
+    rc = lib.dpvo_lie_inv(ctypes.c_int32(9), ctypes.c_int32(1), one, one, ctypes.c_int64(5), null)
     assert rc != 0 and b"group" in lib.dpvo_last_error()
     rc = lib.dpvo_lie_inv(ctypes.c_int32(3), ctypes.c_int32(0), one, one, ctypes.c_int64(5), null)
     assert rc != 0 and b"dtype" in lib.dpvo_last_error()

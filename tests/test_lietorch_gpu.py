@@ -150,12 +150,16 @@ def test_empty_and_errors():
     assert lb.logm(SE3, e).shape == (0, 6)
     X = torch.zeros(4, 7, device="cuda")
     X[:, 6] = 1
-    with pytest.raises(RuntimeError):
-        lb.inv(SE3, X.cpu())                      # no CPU path
+    # CPU tensors are dispatched to the host form of the same templates (the reference dispatches on the device too)
+    assert torch.allclose(lb.inv(SE3, X.cpu()), lb.inv(SE3, X).cpu())
     with pytest.raises(RuntimeError):
         lb.inv(SE3, X.t().contiguous().t())       # non-contiguous
     with pytest.raises(RuntimeError):
-        lb.inv(4, X)                              # Sim3 not provided
+        lb.inv(4, X)                              # Sim3 rows are 8 wide
+    with pytest.raises(RuntimeError):
+        lb.inv(7, X)                              # unknown group
+    with pytest.raises(RuntimeError):
+        lb.mul(SE3, X, X.cpu())                   # mixed devices
     with pytest.raises(RuntimeError):
         lb.mul(SE3, X, X[:2])                     # batch mismatch
 
@@ -191,3 +195,40 @@ def test_jacobians_stable_near_zero_angle():
     _close(lb.Jinv(SE3, f(X), f(a6)), lo.jinv(X.astype(np.float32), a6.astype(np.float32)), 2e-5)
     _close(lb.expm_backward(SE3, f(gX), f(xi))[0], lo.exp_backward(gX.astype(np.float32), xi.astype(np.float32)), 2e-5)
     _close(lb.logm_backward(SE3, f(g6), f(X))[0], lo.log_backward(g6.astype(np.float32), X.astype(np.float32)), 2e-5)
+
+
+@pytest.mark.parametrize("G", [1, 2, 3, 4])
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.float64, 1e-10)])
+def test_all_groups_device_path_vs_reference_cpu_golden(G, dtype, tol):
+    """SO3, RxSO3, SE3, Sim3 (lietorch/groups.py:236-290) on the device against the golden vectors of the reference's
+    CPU backend (tests/golden/ref_cpu_lie_groups.npz, make_golden_lie_groups.py)."""
+    from lie_groups_common import check_group
+    check_group(load_pkg("lietorch_backends"), G, dtype, "cuda", tol)
+
+
+@pytest.mark.parametrize("G", [1, 2, 4])
+def test_other_groups_vs_reference_cuda_extension(G):
+    from lie_groups_common import DIMS, JAC_OPS, all_ops
+    ref = load_ref("lietorch_backends")
+    if ref is None:
+        pytest.skip("oracle/_ref/lietorch_backends.so not built")
+    lb = load_pkg("lietorch_backends")
+    K, N = DIMS[G]
+    g = torch.Generator().manual_seed(50 + G)
+    n = 4096
+    a = (torch.randn(n, K, generator=g) * 0.6)
+    if G in (2, 4):
+        a[:, K - 1] *= 0.4
+    a = a.cuda()
+    rn = lambda w: torch.randn(n, w, generator=g).cuda()
+    d = dict(a=a, X=ref.expm(G, a), Y=ref.expm(G, 0.5 * rn(K)), p3=rn(3), p4=rn(4), aK=rn(K), gN=rn(N), gK=rn(K), g3=rn(3),
+             g4=rn(4))
+    want = all_ops(ref, G, d)
+    got = all_ops(lb, G, d)
+    rot = slice(0, 3) if G in (1, 2) else slice(3, 6)
+    ok = (a[:, rot].norm(dim=1) > 1e-2).cpu().numpy()
+    for k in want:
+        w, h = want[k].cpu().numpy(), got[k].cpu().numpy()
+        if k in JAC_OPS:
+            w, h = w[ok], h[ok]
+        _close(h, w, 3e-5)
