@@ -180,6 +180,7 @@ struct CorrBwdFastParams {
   const void* cg; int64_t cg_sb, cg_sm, cg_sx, cg_sy, cg_si, cg_sj;
   float* acc1;                                             // [B][N1][128][9]  fp32, zeroed
   float* acc2;                                             // [B][N2][H2][W2][128] fp32, zeroed
+  const int32_t* perm;                                     // optional processing order (csrc/corr_order.cu)
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -229,7 +230,8 @@ corr_bwd_fast_kernel(const __grid_constant__ CorrBwdFastParams prm) {
   const int H2 = prm.H2, W2 = prm.W2;
   float(*wtab)[12] = s_w[wid];
 
-  for (int64_t e = warp0; e < nedge; e += nwarps) {
+  for (int64_t es = warp0; es < nedge; es += nwarps) {
+    const int64_t e = prm.perm ? (int64_t)prm.perm[es] : es;
     const int b = (int)(e / prm.M);
     const int m = (int)(e - (int64_t)b * prm.M);
     const int64_t u = prm.us[m], v = prm.vs[m];
@@ -450,7 +452,7 @@ extern "C" int dpvo_corr_backward_nhwc(
     int32_t N1, int32_t N2, int32_t H2, int32_t W2,
     const float* coords, const int64_t* us, const int64_t* vs, int32_t B, int32_t M,
     const void* corr_grad, int64_t cg_sb, int64_t cg_sm, int64_t cg_sx, int64_t cg_sy, int64_t cg_si, int64_t cg_sj,
-    void* fmap1_grad, void* fmap2_grad_nhwc, float* acc1, float* acc2, void* stream) {
+    void* fmap1_grad, void* fmap2_grad_nhwc, float* acc1, float* acc2, const int32_t* perm, void* stream) {
   DPVO_REQUIRE(dtype == DPVO_F16 || dtype == DPVO_F32, "corr_backward_nhwc: float16 or float32 features");
   DPVO_REQUIRE(B >= 0 && M >= 0 && N1 > 0 && N2 > 0 && H2 > 0 && W2 > 0, "corr_backward_nhwc: bad sizes");
   if ((int64_t)B * M == 0) return 0;
@@ -477,6 +479,7 @@ extern "C" int dpvo_corr_backward_nhwc(
   p.cg = corr_grad;
   p.cg_sb = cg_sb; p.cg_sm = cg_sm; p.cg_sx = cg_sx; p.cg_sy = cg_sy; p.cg_si = cg_si; p.cg_sj = cg_sj;
   p.acc1 = a1; p.acc2 = a2;
+  p.perm = perm;
   const int64_t nedge = (int64_t)B * M;
   const int64_t want = ceil_div64(nedge, kFBWarps);
   const int grid = (int)(want < (int64_t)kNumSMs * 4 ? want : (int64_t)kNumSMs * 4);

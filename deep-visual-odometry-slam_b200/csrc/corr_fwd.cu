@@ -44,6 +44,7 @@ struct CorrParams {
   const int64_t* vs;
   int B, M, R, nlev;
   int pair;  // nlev==2 and the two outputs interleave element-wise (half2 stores)
+  const int32_t* perm;  // optional processing order (csrc/corr_order.cu); results still land at the edge's own index
   CorrLevelDev lev[2];
 };
 
@@ -120,7 +121,8 @@ corr_fwd_mma_f16_kernel(const __grid_constant__ CorrParams prm) {
   const int64_t nedge = (int64_t)prm.B * prm.M;
   const __half* fmap1 = reinterpret_cast<const __half*>(prm.fmap1);
 
-  for (int64_t e = (int64_t)blockIdx.x * kWarps + wid; e < nedge; e += (int64_t)gridDim.x * kWarps) {
+  for (int64_t es = (int64_t)blockIdx.x * kWarps + wid; es < nedge; es += (int64_t)gridDim.x * kWarps) {
+    const int64_t e = prm.perm ? (int64_t)prm.perm[es] : es;
     const int b = (int)(e / prm.M);
     const int m = (int)(e - (int64_t)b * prm.M);
     const int64_t u = prm.us[m];
@@ -484,12 +486,12 @@ using namespace dpvo;
 static const char* g_last_corr_kernel = "";
 extern "C" const char* dpvo_corr_last_kernel(void) { return g_last_corr_kernel; }
 
-extern "C" int dpvo_corr_forward(dpvo_dtype dtype,
-                                 const void* fmap1, int64_t g_sb, int64_t g_sn, int64_t g_sc, int64_t g_sy, int64_t g_sx,
-                                 int32_t N1, int32_t C, int32_t PH, int32_t PW,
-                                 const float* coords, const int64_t* us, const int64_t* vs,
-                                 int32_t B, int32_t M, int32_t radius,
-                                 const dpvo_corr_level* levels, int32_t nlev, void* stream) {
+static int corr_forward_impl(dpvo_dtype dtype,
+                             const void* fmap1, int64_t g_sb, int64_t g_sn, int64_t g_sc, int64_t g_sy, int64_t g_sx,
+                             int32_t N1, int32_t C, int32_t PH, int32_t PW,
+                             const float* coords, const int64_t* us, const int64_t* vs,
+                             int32_t B, int32_t M, int32_t radius,
+                             const dpvo_corr_level* levels, int32_t nlev, const int32_t* perm, void* stream) {
   DPVO_REQUIRE(nlev == 1 || nlev == 2, "corr_forward: nlev must be 1 or 2 (got %d)", nlev);
   DPVO_REQUIRE(radius >= 0 && PH > 0 && PW > 0 && C > 0, "corr_forward: bad sizes");
   DPVO_REQUIRE(B >= 0 && M >= 0, "corr_forward: negative batch/edge count");
@@ -504,6 +506,7 @@ extern "C" int dpvo_corr_forward(dpvo_dtype dtype,
   prm.N1 = N1; prm.C = C; prm.PH = PH; prm.PW = PW;
   prm.coords = coords; prm.us = us; prm.vs = vs;
   prm.B = B; prm.M = M; prm.R = radius; prm.nlev = nlev;
+  prm.perm = perm;
   const int D = 2 * radius + 2;
   for (int l = 0; l < nlev; ++l) {
     DPVO_REQUIRE(levels[l].fmap && levels[l].out, "corr_forward: null level pointer");
@@ -570,4 +573,27 @@ extern "C" int dpvo_corr_forward(dpvo_dtype dtype,
   }
   set_error("corr_forward: unknown dtype %d", (int)dtype);
   return 1;
+}
+
+extern "C" int dpvo_corr_forward(dpvo_dtype dtype,
+                                 const void* fmap1, int64_t g_sb, int64_t g_sn, int64_t g_sc, int64_t g_sy, int64_t g_sx,
+                                 int32_t N1, int32_t C, int32_t PH, int32_t PW,
+                                 const float* coords, const int64_t* us, const int64_t* vs,
+                                 int32_t B, int32_t M, int32_t radius,
+                                 const dpvo_corr_level* levels, int32_t nlev, void* stream) {
+  return corr_forward_impl(dtype, fmap1, g_sb, g_sn, g_sc, g_sy, g_sx, N1, C, PH, PW, coords, us, vs, B, M, radius, levels,
+                           nlev, nullptr, stream);
+}
+
+// Same lookup walked in the order `perm` (a permutation of [0, B*M) from dpvo_corr_order, or any other); every edge's
+// result is written at its own index, so the output is bit-identical to dpvo_corr_forward.  The generic (non fp16 /
+// non channels-last) path ignores `perm`.
+extern "C" int dpvo_corr_forward_ordered(dpvo_dtype dtype,
+                                         const void* fmap1, int64_t g_sb, int64_t g_sn, int64_t g_sc, int64_t g_sy,
+                                         int64_t g_sx, int32_t N1, int32_t C, int32_t PH, int32_t PW,
+                                         const float* coords, const int64_t* us, const int64_t* vs,
+                                         int32_t B, int32_t M, int32_t radius,
+                                         const dpvo_corr_level* levels, int32_t nlev, const int32_t* perm, void* stream) {
+  return corr_forward_impl(dtype, fmap1, g_sb, g_sn, g_sc, g_sy, g_sx, N1, C, PH, PW, coords, us, vs, B, M, radius, levels,
+                           nlev, perm, stream);
 }

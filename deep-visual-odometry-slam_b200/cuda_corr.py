@@ -156,20 +156,36 @@ def _level(fmap2, scale, out, out_edge_stride, out_elem_stride):
     return lv
 
 
-def _launch(fmap1, coords, ii, jj, radius, levels):
+# Locality order (csrc/corr_order.cu): on for edge lists large enough to span several SMs' worth of warps.
+# DPVO_CORR_ORDER=0 turns it off (A/B measurements); the output is bit-identical either way.
+ORDER_EDGES = os.environ.get("DPVO_CORR_ORDER", "1") != "0"
+ORDER_MIN_EDGES = 4096
+lib.dpvo_corr_order_workspace_bytes.restype = c_i64
+
+
+def edge_order(coords, jj, n_slots, h, w, tile):
+    """int32 permutation of the B = 1 edge list grouping edges by (target-frame slot, tile x tile pixel tile of the patch
+    centre); coords in the pixel units of the (h, w) map.  Device side, no synchronisation."""
+    M = coords.shape[1]
+    perm = torch.empty((M,), dtype=torch.int32, device=coords.device)
+    nbytes = int(lib.dpvo_corr_order_workspace_bytes(c_i64(M), c_i32(n_slots), c_i32(h), c_i32(w), c_i32(tile)))
+    ws = torch.empty((max(nbytes, 1),), dtype=torch.uint8, device=coords.device)
+    with _lib.device_guard(coords):
+        check(lib.dpvo_corr_order(ptr(coords), ptr(jj), c_i64(M), c_i32(n_slots), c_i32(h), c_i32(w), c_i32(tile),
+                                  ptr(perm), ptr(ws), c_i64(nbytes), stream_of(coords)), "cuda_corr.edge_order")
+    return perm
+
+
+def _launch(fmap1, coords, ii, jj, radius, levels, perm=None):
     B, M = coords.shape[0], coords.shape[1]
     arr = (CorrLevel * len(levels))(*levels)
     g = fmap1.stride()
     with _lib.device_guard(fmap1):
-        _launch_checked(fmap1, coords, ii, jj, radius, levels, arr, g, B, M)
-
-
-def _launch_checked(fmap1, coords, ii, jj, radius, levels, arr, g, B, M):
-    check(lib.dpvo_corr_forward(
-        c_i32(dtype_code(fmap1)), ptr(fmap1), c_i64(g[0]), c_i64(g[1]), c_i64(g[2]), c_i64(g[3]), c_i64(g[4]),
-        c_i32(fmap1.shape[1]), c_i32(fmap1.shape[2]), c_i32(fmap1.shape[3]), c_i32(fmap1.shape[4]),
-        ptr(coords), ptr(ii), ptr(jj), c_i32(B), c_i32(M), c_i32(radius),
-        arr, c_i32(len(levels)), stream_of(fmap1)), "cuda_corr.forward")
+        check(lib.dpvo_corr_forward_ordered(
+            c_i32(dtype_code(fmap1)), ptr(fmap1), c_i64(g[0]), c_i64(g[1]), c_i64(g[2]), c_i64(g[3]), c_i64(g[4]),
+            c_i32(fmap1.shape[1]), c_i32(fmap1.shape[2]), c_i32(fmap1.shape[3]), c_i32(fmap1.shape[4]),
+            ptr(coords), ptr(ii), ptr(jj), c_i32(B), c_i32(M), c_i32(radius),
+            arr, c_i32(len(levels)), ptr(perm), stream_of(fmap1)), "cuda_corr.forward")
 
 
 def forward(fmap1, fmap2, coords, ii, jj, radius):
@@ -184,12 +200,16 @@ def forward(fmap1, fmap2, coords, ii, jj, radius):
     out = torch.empty((B, M, DO, DO, PH, PW), dtype=fmap1.dtype, device=fmap1.device)
     if B * M == 0:
         return [out]
+    perm = None
     if _wants_fast(fmap1, radius):
         fmap2 = _channels_last_view(fmap2)
         if not _dense_patch_blob(fmap1):
             fmap1 = fmap1.contiguous()
+        if ORDER_EDGES and B == 1 and M >= ORDER_MIN_EDGES:
+            H2, W2 = fmap2.shape[3], fmap2.shape[4]
+            perm = edge_order(coords, jj, fmap2.shape[1], H2, W2, 32 if max(H2, W2) > 64 else 8)
     lv = _level(fmap2, 1.0, out.data_ptr(), DO * DO * PH * PW, 1)
-    _launch(fmap1, coords, ii, jj, radius, [lv])
+    _launch(fmap1, coords, ii, jj, radius, [lv], perm)
     return [out]
 
 
@@ -226,14 +246,18 @@ def pyramid_forward(fmap1, pyramid, scales, coords, ii, jj, radius, row_stride=N
     out = torch.empty((B, M, stride), dtype=fmap1.dtype, device=fmap1.device)[:, :, :per * L]
     if B * M == 0:
         return out
+    perm = None
     if _wants_fast(fmap1, radius):
         pyramid = [_channels_last_view(fm) for fm in pyramid]
         if not _dense_patch_blob(fmap1):
             fmap1 = fmap1.contiguous()
+        if ORDER_EDGES and B == 1 and M >= ORDER_MIN_EDGES and float(scales[0]) == 1.0:
+            H1, W1 = pyramid[0].shape[3], pyramid[0].shape[4]
+            perm = edge_order(coords, jj, pyramid[0].shape[1], H1, W1, 32)
     esz = out.element_size()
     levels = [_level(fm, float(sc), out.data_ptr() + l * esz, stride, L)
               for l, (fm, sc) in enumerate(zip(pyramid, scales))]
-    _launch(fmap1, coords, ii, jj, radius, levels)
+    _launch(fmap1, coords, ii, jj, radius, levels, perm)
     return out
 
 
@@ -315,6 +339,9 @@ def backward(fmap1, fmap2, coords, ii, jj, corr_grad, radius):
         acc1 = torch.zeros((B * N1 * C * 9,), dtype=torch.float32, device=dev) if half else None
         acc2 = torch.zeros((B * N2 * H2 * W2 * C,), dtype=torch.float32, device=dev) if half else None
         s1, s2 = f1.stride(), f2.stride()
+        perm = None
+        if ORDER_EDGES and B == 1 and M >= 2048:
+            perm = edge_order(coords, jj, N2, H2, W2, 32 if max(H2, W2) > 64 else 8)
         with _lib.device_guard(fmap1):
             check(lib.dpvo_corr_backward_nhwc(
                 c_i32(dtype_code(fmap1)), ptr(f1), c_i64(s1[0]), c_i64(s1[1]),
@@ -322,7 +349,7 @@ def backward(fmap1, fmap2, coords, ii, jj, corr_grad, radius):
                 c_i32(N1), c_i32(N2), c_i32(H2), c_i32(W2),
                 ptr(coords), ptr(ii), ptr(jj), c_i32(B), c_i32(M),
                 ptr(corr_grad), c_i64(cg[0]), c_i64(cg[1]), c_i64(cg[2]), c_i64(cg[3]), c_i64(cg[4]), c_i64(cg[5]),
-                ptr(g1), ptr(g2), ptr(acc1), ptr(acc2), stream_of(fmap1)), "cuda_corr.backward")
+                ptr(g1), ptr(g2), ptr(acc1), ptr(acc2), ptr(perm), stream_of(fmap1)), "cuda_corr.backward")
         return [g1, g2.permute(0, 1, 4, 2, 3)]
     g1 = torch.zeros(fmap1.shape, dtype=fmap1.dtype, device=fmap1.device)
     g2 = torch.zeros(fmap2.shape, dtype=fmap2.dtype, device=fmap2.device)

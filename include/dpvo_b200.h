@@ -60,6 +60,20 @@ int dpvo_corr_forward(dpvo_dtype dtype,
                       const dpvo_corr_level* levels, int32_t nlev,
                       void* stream);
 
+/* Locality order for the lookup (csrc/corr_order.cu): counting sort of the B = 1 edge list by (target-frame slot vs[e],
+ * tile x tile pixel tile of the patch centre at level 1) so that the warps resident on an SM read the same part of the
+ * same frame.  perm: [M] int32 out; ws: dpvo_corr_order_workspace_bytes(...) bytes.  No host synchronisation. */
+int64_t dpvo_corr_order_workspace_bytes(int64_t M, int32_t N2, int32_t H1, int32_t W1, int32_t tile);
+int dpvo_corr_order(const float* coords, const int64_t* vs, int64_t M, int32_t N2, int32_t H1, int32_t W1,
+                    int32_t tile, int32_t* perm, void* ws, int64_t ws_bytes, void* stream);
+/* dpvo_corr_forward walked in the order `perm`; each edge's result is written at its own index (bit-identical output). */
+int dpvo_corr_forward_ordered(dpvo_dtype dtype,
+                              const void* fmap1, int64_t g_sb, int64_t g_sn, int64_t g_sc, int64_t g_sy, int64_t g_sx,
+                              int32_t N1, int32_t C, int32_t PH, int32_t PW,
+                              const float* coords, const int64_t* us, const int64_t* vs,
+                              int32_t B, int32_t M, int32_t radius,
+                              const dpvo_corr_level* levels, int32_t nlev, const int32_t* perm, void* stream);
+
 /* Name of the kernel the last dpvo_corr_forward call launched (static string; instrumentation for bench.py). */
 const char* dpvo_corr_last_kernel(void);
 
@@ -86,7 +100,9 @@ int dpvo_corr_backward(dpvo_dtype dtype,
  * forward lookup already reads; fmap2_grad_nhwc: contiguous [B][N2][H2][W2][128] (return it to autograd as
  * a permuted view); fmap1_grad: contiguous like fmap1.
  * F16: acc1 ([B*N1*1152]) and acc2 ([B*N2*H2*W2*128]) are ZEROED float32 scratch and both gradients are
- * written in full.  F32: acc1/acc2 are ignored, the gradients must be PRE-ZEROED and are accumulated in place. */
+ * written in full.  F32: acc1/acc2 are ignored, the gradients must be PRE-ZEROED and are accumulated in place.
+ * perm (optional): processing order from dpvo_corr_order — edges of one target frame / tile back to back keep the
+ * gradient lines they reduce into resident in L2 (the sums are order-independent up to fp32 rounding). */
 int dpvo_corr_backward_nhwc(
     dpvo_dtype dtype,
     const void* fmap1, int64_t g_sb, int64_t g_sn,
@@ -94,7 +110,8 @@ int dpvo_corr_backward_nhwc(
     int32_t N1, int32_t N2, int32_t H2, int32_t W2,
     const float* coords, const int64_t* us, const int64_t* vs, int32_t B, int32_t M,
     const void* corr_grad, int64_t cg_sb, int64_t cg_sm, int64_t cg_sx, int64_t cg_sy, int64_t cg_si, int64_t cg_sj,
-    void* fmap1_grad, void* fmap2_grad_nhwc, float* acc1, float* acc2, void* stream);
+    void* fmap1_grad, void* fmap2_grad_nhwc, float* acc1, float* acc2, const int32_t* perm /* optional, dpvo_corr_order */,
+    void* stream);
 
 /* Patch gather — replaces cuda_corr.patchify_forward (correlation_kernel.cu:17-48,289-308).
  * net: [B, C, H, W] strides n_*; coords: [B, M, 2] float32 contiguous;

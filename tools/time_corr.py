@@ -54,9 +54,26 @@ def main():
             ts.append(e0.elapsed_time(e1))
         return float(np.median(ts)), float(np.min(ts))
 
-    med, mn = timeit(lambda: pkg.altcorr.corr_pyramid(g, (f1, f2), c, us, vs, 3), a.iters)
-    print(json.dumps({"impl": "b200 fused 2-level", "edges": E, "ms_median": med, "ms_min": mn,
-                      "alg_bytes": nbytes, "alg_GBs": nbytes / med / 1e6, "bytes_per_edge": nbytes / E}))
+    cc = pkg.cuda_corr
+    outs = {}
+    for label, flag in (("b200 fused 2-level, append order", False), ("b200 fused 2-level, locality order (sort included)", True)):
+        cc.ORDER_EDGES = flag
+        outs[flag] = pkg.altcorr.corr_pyramid(g, (f1, f2), c, us, vs, 3)
+        med, mn = timeit(lambda: pkg.altcorr.corr_pyramid(g, (f1, f2), c, us, vs, 3), a.iters)
+        print(json.dumps({"impl": label, "edges": E, "ms_median": med, "ms_min": mn,
+                          "alg_bytes": nbytes, "alg_GBs": nbytes / med / 1e6, "bytes_per_edge": nbytes / E}))
+    print(json.dumps({"ordered_equals_unordered_bitwise": bool(torch.equal(outs[True], outs[False]))}))
+    med, mn = timeit(lambda: cc.edge_order(c, vs, f1.shape[1], 120, 160, 32), a.iters)
+    print(json.dumps({"impl": "edge_order alone (3 launches)", "ms_median": med, "ms_min": mn}))
+    for tile in (16, 32, 64):
+        perm = cc.edge_order(c, vs, f1.shape[1], 120, 160, tile)
+        real = cc.edge_order
+        cc.edge_order = lambda *a_, **k_: perm
+        cc.ORDER_EDGES = True
+        med, mn = timeit(lambda: pkg.altcorr.corr_pyramid(g, (f1, f2), c, us, vs, 3), a.iters)
+        cc.edge_order = real
+        print(json.dumps({"impl": f"lookup kernel alone, precomputed locality order, tile {tile}", "ms_median": med, "ms_min": mn,
+                          "alg_GBs": nbytes / med / 1e6}))
     if a.ref:
         from oracle.ref_ext import load_ref
         ref = load_ref("cuda_corr")

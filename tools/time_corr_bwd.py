@@ -40,8 +40,12 @@ def main():
                 ts.append(e0.elapsed_time(e1))
             return float(np.median(ts))
 
+        pkg.cuda_corr.ORDER_EDGES = False
+        ms_append = timeit(lambda: pkg.cuda_corr.backward(g, f, cc, us, vs, grad, 3))
+        pkg.cuda_corr.ORDER_EDGES = True
         row = {"op": "corr_backward", "level": lvl, "dtype": a.dtype, "edges": a.edges,
                "ms_b200": timeit(lambda: pkg.cuda_corr.backward(g, f, cc, us, vs, grad, 3)),
+               "ms_b200_append_order": ms_append,
                "ms_b200_forward": timeit(lambda: pkg.cuda_corr.forward(g, f, cc, us, vs, 3))}
         if a.ref:
             from oracle.ref_ext import load_ref
