@@ -156,9 +156,13 @@ def _level(fmap2, scale, out, out_edge_stride, out_elem_stride):
     return lv
 
 
-# Locality order (csrc/corr_order.cu): on for edge lists large enough to span several SMs' worth of warps.
-# DPVO_CORR_ORDER=0 turns it off (A/B measurements); the output is bit-identical either way.
-ORDER_EDGES = os.environ.get("DPVO_CORR_ORDER", "1") != "0"
+# Locality order (csrc/corr_order.cu).  Measured on B200 (profiles/r02_time_corr_locality_order.jsonl,
+# r02_time_corr_bwd_locality_order.jsonl): the BACKWARD gains 20 % at 18k edges including the sort (the fp32 gradient
+# lines it reduces into stay in L2), so it is on; the FORWARD lookup kernel gains 8 % (0.267 -> 0.246 ms at 45,312 edges)
+# which the 0.026 ms sort gives back — the lookup is bound by bytes in flight, not by where they come from — so it is
+# off unless a caller already has a permutation to pass.  The output is bit-identical either way.
+ORDER_FORWARD = os.environ.get("DPVO_CORR_ORDER_FWD", "0") != "0"
+ORDER_EDGES = os.environ.get("DPVO_CORR_ORDER", "1") != "0"      # backward
 ORDER_MIN_EDGES = 4096
 lib.dpvo_corr_order_workspace_bytes.restype = c_i64
 
@@ -205,7 +209,7 @@ def forward(fmap1, fmap2, coords, ii, jj, radius):
         fmap2 = _channels_last_view(fmap2)
         if not _dense_patch_blob(fmap1):
             fmap1 = fmap1.contiguous()
-        if ORDER_EDGES and B == 1 and M >= ORDER_MIN_EDGES:
+        if ORDER_FORWARD and B == 1 and M >= ORDER_MIN_EDGES:
             H2, W2 = fmap2.shape[3], fmap2.shape[4]
             perm = edge_order(coords, jj, fmap2.shape[1], H2, W2, 32 if max(H2, W2) > 64 else 8)
     lv = _level(fmap2, 1.0, out.data_ptr(), DO * DO * PH * PW, 1)
@@ -251,7 +255,7 @@ def pyramid_forward(fmap1, pyramid, scales, coords, ii, jj, radius, row_stride=N
         pyramid = [_channels_last_view(fm) for fm in pyramid]
         if not _dense_patch_blob(fmap1):
             fmap1 = fmap1.contiguous()
-        if ORDER_EDGES and B == 1 and M >= ORDER_MIN_EDGES and float(scales[0]) == 1.0:
+        if ORDER_FORWARD and B == 1 and M >= ORDER_MIN_EDGES and float(scales[0]) == 1.0:
             H1, W1 = pyramid[0].shape[3], pyramid[0].shape[4]
             perm = edge_order(coords, jj, pyramid[0].shape[1], H1, W1, 32)
     esz = out.element_size()

@@ -57,7 +57,7 @@ def main():
     cc = pkg.cuda_corr
     outs = {}
     for label, flag in (("b200 fused 2-level, append order", False), ("b200 fused 2-level, locality order (sort included)", True)):
-        cc.ORDER_EDGES = flag
+        cc.ORDER_FORWARD = flag
         outs[flag] = pkg.altcorr.corr_pyramid(g, (f1, f2), c, us, vs, 3)
         med, mn = timeit(lambda: pkg.altcorr.corr_pyramid(g, (f1, f2), c, us, vs, 3), a.iters)
         print(json.dumps({"impl": label, "edges": E, "ms_median": med, "ms_min": mn,
@@ -69,7 +69,7 @@ def main():
         perm = cc.edge_order(c, vs, f1.shape[1], 120, 160, tile)
         real = cc.edge_order
         cc.edge_order = lambda *a_, **k_: perm
-        cc.ORDER_EDGES = True
+        cc.ORDER_FORWARD = True
         med, mn = timeit(lambda: pkg.altcorr.corr_pyramid(g, (f1, f2), c, us, vs, 3), a.iters)
         cc.edge_order = real
         print(json.dumps({"impl": f"lookup kernel alone, precomputed locality order, tile {tile}", "ms_median": med, "ms_min": mn,
