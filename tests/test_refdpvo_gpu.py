@@ -31,9 +31,9 @@ FRAMES = 120
 POSE_FLOOR = 2e-4        # absolute, on scale-normalised poses (trajectory extent ~1) / unit quaternions
 
 
-def _run(backend, out, update="reference", frames=FRAMES):
+def _run(backend, out, update="reference", frames=FRAMES, pipeline="reference"):
     cmd = [sys.executable, os.path.join(ROOT, "tools", "refdpvo.py"), "--backend", backend, "--mode", "parity",
-           "--frames", str(frames), "--update", update, "--out", out]
+           "--frames", str(frames), "--update", update, "--pipeline", pipeline, "--out", out]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=1500)
     assert r.returncode == 0, r.stderr[-3000:]
     summary = json.loads(r.stdout.strip().splitlines()[-1])
@@ -102,4 +102,15 @@ def test_reference_dpvo_class_with_b200_update_operator(arms, tmp_path):
     # outputs differ from the torch module's at the 1e-2 level (bounded in tests/test_update_gpu.py), which the teacher's
     # ALPHA * tanh(.) passes into the BA targets -> a looser floor on the poses; the bookkeeping must still be bit-exact
     _compare(arms[0], ours, "dpvo.DPVO unmodified + dpvo_b200_update.Update vs reference extensions + torch Update",
+             ref2=arms[2], floor=5e-3)
+
+
+def test_b200_dpvo_class_matches_reference_class(arms, tmp_path):
+    """This repo's OWN `DPVO` class (deep-visual-odometry-slam_b200/dpvo.py: the reference's API and state machine on
+    the B200 operators and the device-resident buffer layout — channels-last rings, fixed-capacity device edge list,
+    fused reprojection / lookup / Update operator / BA / encoders) against the reference class on the reference
+    extensions, same sequence, seeds, weights and teacher: bit-identical ii / jj / kk at every frame, poses within the
+    same measured bar (looser floor: its encoders and Update operator are the fp16 kernels, see the test above)."""
+    ours = _run("dropin", str(tmp_path / "b200_pipeline.npz"), pipeline="b200")
+    _compare(arms[0], ours, "deep-visual-odometry-slam_b200.dpvo.DPVO vs reference dpvo.DPVO on reference extensions",
              ref2=arms[2], floor=5e-3)

@@ -313,7 +313,7 @@ def make_teacher(inner, slam, seq, alpha):
 
 # --------------------------------------------------------------------------- building a DPVO instance
 def build_slam(seed=1234, cfg=None, ht=480, wd=640, seq=None, alpha=0.25, teacher=True, update_impl="reference",
-               patchify_impl="reference", cpu_dryrun=False):
+               patchify_impl="reference", pipeline="reference", cpu_dryrun=False):
     """Unmodified reference DPVO (dpvo.py:22-112) with a seeded random-init VONet (no checkpoint in the image)."""
     import torch
     dpvo_mod = importlib.import_module("dpvo.dpvo")
@@ -321,7 +321,14 @@ def build_slam(seed=1234, cfg=None, ht=480, wd=640, seq=None, alpha=0.25, teache
     torch.manual_seed(seed)
     network = net_mod.VONet()
     cfg = cfg or make_cfg()
-    slam = dpvo_mod.DPVO(cfg, network, ht=ht, wd=wd, viz=False)
+    if pipeline == "b200":
+        # this repo's DPVO class (deep-visual-odometry-slam_b200/dpvo.py): same API and state machine on the B200
+        # operators and the device-resident buffer layout; the reference VONet only supplies the seeded weights
+        sys.path.insert(0, ROOT)
+        slam = importlib.import_module(PKG + ".dpvo").DPVO(cfg, network, ht=ht, wd=wd, viz=False)
+        update_impl = patchify_impl = "bound"
+    else:
+        slam = dpvo_mod.DPVO(cfg, network, ht=ht, wd=wd, viz=False)
     if update_impl == "b200":
         # the one-line binding of the Update operator (next row N1)
         import dpvo_b200_update
@@ -444,13 +451,18 @@ def instrument(slam):
                 c[1] += time.perf_counter() - t0
         return timed
 
-    dm = sys.modules["dpvo.dpvo"]
+    ours = type(slam).__module__.startswith(PKG)
+    dm = sys.modules[type(slam).__module__] if ours else sys.modules["dpvo.dpvo"]
     slam.update = wrap(slam.update, "update (whole)")
     slam.keyframe = wrap(slam.keyframe, "keyframe")
     slam.corr = wrap(slam.corr, "  corr x2 + stack")
     slam.reproject = wrap(slam.reproject, "  reproject (pops.transform)")
     slam.motion_probe = wrap(slam.motion_probe, "motion_probe")
-    slam.pg.edges_loop = wrap(slam.pg.edges_loop, "edges_loop")
+    if ours:
+        slam.edges_loop = wrap(slam.edges_loop, "edges_loop")
+        slam.normalize = wrap(slam.normalize, "  normalize")
+    else:
+        slam.pg.edges_loop = wrap(slam.pg.edges_loop, "edges_loop")
     slam.network.patchify.forward = wrap(slam.network.patchify.forward, "patchify (encoders + gathers)")
     slam.network.update.forward = wrap(slam.network.update.forward, "  Update operator (+teacher)")
     orig_ba = dm.fastba.BA
@@ -473,6 +485,8 @@ def main():
     ap.add_argument("--alpha", type=float, default=0.25)
     ap.add_argument("--update", default="reference", choices=["reference", "b200"])
     ap.add_argument("--patchify", default="reference", choices=["reference", "b200"])
+    ap.add_argument("--pipeline", default="reference", choices=["reference", "b200"],
+                    help="b200: this repo's DPVO class instead of the reference's (needs --backend dropin)")
     ap.add_argument("--no-teacher", action="store_true")
     ap.add_argument("--no-loop-closure", action="store_true")
     ap.add_argument("--patches", type=int, default=None)
@@ -497,11 +511,12 @@ def main():
     torch.set_grad_enabled(False)             # evaluate_tartan.py:46 runs DPVO under @torch.no_grad()
     try:
         slam = build_slam(seed=args.seed, cfg=make_cfg(**over), seq=seq, alpha=args.alpha, teacher=not args.no_teacher,
-                          update_impl=args.update, patchify_impl=args.patchify, cpu_dryrun=args.cpu_dryrun)
+                          update_impl=args.update, patchify_impl=args.patchify, pipeline=args.pipeline,
+                          cpu_dryrun=args.cpu_dryrun)
         if args.mode == "parity":
             res = run_parity(slam, seq, args.frames, dev=dev)
             import numpy as np
-            summary = dict(backend=args.backend, frames=args.frames, final_n=int(res["final_n"]),
+            summary = dict(backend=args.backend, pipeline=args.pipeline, frames=args.frames, final_n=int(res["final_n"]),
                            removed=int(res["removed"].sum()), gba=int(res["gba"].sum()),
                            loop_added=int(res["loop_added"].sum()), E_last=int(res["E"][-1]),
                            Einac_last=int(res["Einac"][-1]), modules=files)
@@ -515,7 +530,7 @@ def main():
             if acc is not None:
                 res["stages"] = {k: {"calls": c, "s": round(t, 3), "ms_per_call": round(1e3 * t / max(c, 1), 3)}
                                  for k, (c, t) in sorted(acc.items(), key=lambda kv: -kv[1][1])}
-            res.update(backend=args.backend, update=args.update, patchify=args.patchify, modules=files)
+            res.update(backend=args.backend, update=args.update, patchify=args.patchify, pipeline=args.pipeline, modules=files)
             if args.out:
                 with open(args.out, "w") as f:
                     json.dump(res, f)
