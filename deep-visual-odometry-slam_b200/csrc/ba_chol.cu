@@ -221,17 +221,26 @@ chol_trsm_kernel(float* __restrict__ A, int lda, int n, int p0, const float* __r
 }
 
 // trailing update: tile (ti, tj), tj <= ti, of rows/cols starting at q0 = p0 + nb.
+// mode 0: every tile; mode 1: the first tile column only (tj = 0: what the NEXT panel's factorisation needs);
+// mode 2: every tile with tj >= 1 (runs on the look-ahead stream under the next panel's diag + trsm).
 __global__ void __launch_bounds__(256)
-chol_syrk_kernel(float* __restrict__ A, int lda, int n, int p0, const int* __restrict__ meta) {
+chol_syrk_kernel(float* __restrict__ A, int lda, int n, int p0, const int* __restrict__ meta, int mode) {
   __shared__ float As[NB][NB + 1];
   __shared__ float Bs[NB][NB + 1];
   if (meta[1]) return;
   // linear tile index -> (ti, tj) with tj <= ti
-  const int t = blockIdx.x;
-  int ti = (int)((sqrtf(8.f * t + 1.f) - 1.f) * 0.5f);
-  while ((ti + 1) * (ti + 2) / 2 <= t) ++ti;
-  while (ti * (ti + 1) / 2 > t) --ti;
-  const int tj = t - ti * (ti + 1) / 2;
+  int ti, tj;
+  if (mode == 1) {
+    ti = blockIdx.x;
+    tj = 0;
+  } else {
+    const int t = blockIdx.x;
+    ti = (int)((sqrtf(8.f * t + 1.f) - 1.f) * 0.5f);
+    while ((ti + 1) * (ti + 2) / 2 <= t) ++ti;
+    while (ti * (ti + 1) / 2 > t) --ti;
+    tj = t - ti * (ti + 1) / 2;
+    if (mode == 2) { ++ti; ++tj; }
+  }
   const int nb = min(NB, n - p0);
   const int q0 = p0 + nb;
   const int ri = q0 + ti * NB, rj = q0 + tj * NB;
@@ -342,32 +351,95 @@ int64_t chol_scratch_floats(int n) { return 3 * (int64_t)n + 64 + (int64_t)((n +
     }                                                                                               \
   } while (0)
 
+// Look-ahead resources (one set per device): a HIGHEST-priority internal stream for the critical path and a small ring
+// of events.  Panel p's trailing update is split: its first tile column (all the NEXT panel needs) follows diag(p) /
+// trsm(p) on the critical-path stream; the bulk (thousands of short CTAs) runs on the caller's stream underneath
+// diag(p+1) / trsm(p+1), whose few CTAs win every SM slot that frees up because of the stream priority (the caller's
+// stream — torch's default — has the lowest priority there is, so the roles cannot be the other way round).
+struct CholLookahead {
+  cudaStream_t side = nullptr;
+  cudaEvent_t trsm_done[2] = {nullptr, nullptr};
+  cudaEvent_t rest_done[2] = {nullptr, nullptr};
+  cudaEvent_t fork = nullptr;
+  bool ok = false;
+};
+static CholLookahead* chol_lookahead() {
+  static CholLookahead per_dev[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  CholLookahead& L = per_dev[dev];
+  if (!L.ok) {
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);             // hi = most urgent (numerically smallest)
+    if (cudaStreamCreateWithPriority(&L.side, cudaStreamNonBlocking, hi) != cudaSuccess) return nullptr;
+    bool good = cudaEventCreateWithFlags(&L.fork, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; i < 2 && good; ++i)
+      good = cudaEventCreateWithFlags(&L.trsm_done[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&L.rest_done[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!good) return nullptr;
+    L.ok = true;
+  }
+  return &L;
+}
+
 int ba_chol_solve(const BADev& p, float* A, int lda, float* xbuf, cudaStream_t st) {
   const int n = p.n;
   int launches = 0;
   static const bool dbg = debug_env("DPVO_DEBUG_SYNC") != nullptr;
+  static const bool no_la = debug_env("DPVO_CHOL_NO_LOOKAHEAD") != nullptr;
   int p0 = -1;
   float* z = xbuf;
   float* acc = z + n;
   float* sol = acc + n;
   float* Linv = sol + n + (64 - (3 * n) % 64) % 64;     // 256-byte aligned panels
+  // look-ahead pays once the trailing update is big enough to hide a diag + trsm under it (>= 16 panels)
+  CholLookahead* la = (!dbg && !no_la && n >= 16 * NB) ? chol_lookahead() : nullptr;
+  bool rest_pending = false;
+  int slot = 0;
+  cudaStream_t crit = st;                          // diag / trsm / first trailing column
+  if (la) {
+    crit = la->side;
+    cudaEventRecord(la->fork, st);
+    cudaStreamWaitEvent(crit, la->fork, 0);
+  }
   for (p0 = 0; p0 < n; p0 += NB) {
     const int nb = n - p0 < NB ? n - p0 : NB;
     const int rows = n + 1 - p0 - nb;            // rows below the panel, incl. the y row
     const int T = (rows + NB - 1) / NB;
     float* Li = Linv + (int64_t)(p0 / NB) * NB * NB;
-    chol_diag_kernel<<<1, 256, 0, st>>>(A, lda, n, p0, Li, p.meta);
+    chol_diag_kernel<<<1, 256, 0, crit>>>(A, lda, n, p0, Li, p.meta);
     ++launches;
     CHOL_DBG("diag");
-    chol_trsm_kernel<<<T, 256, 0, st>>>(A, lda, n, p0, Li, p.meta);
+    chol_trsm_kernel<<<T, 256, 0, crit>>>(A, lda, n, p0, Li, p.meta);
     ++launches;
     CHOL_DBG("trsm");
     const int Tc = (n - p0 - nb + NB - 1) / NB;  // column tiles of the trailing matrix
     if (Tc > 0) {
-      chol_syrk_kernel<<<T * (T + 1) / 2, 256, 0, st>>>(A, lda, n, p0, p.meta);
-      ++launches;
-      CHOL_DBG("syrk");
+      if (!la) {
+        chol_syrk_kernel<<<T * (T + 1) / 2, 256, 0, st>>>(A, lda, n, p0, p.meta, 0);
+        ++launches;
+        CHOL_DBG("syrk");
+      } else {
+        cudaEventRecord(la->trsm_done[slot], crit);
+        // the previous panel's bulk update also wrote this panel's first trailing column: order the two writers
+        if (rest_pending) cudaStreamWaitEvent(crit, la->rest_done[slot ^ 1], 0);
+        chol_syrk_kernel<<<T, 256, 0, crit>>>(A, lda, n, p0, p.meta, 1);
+        ++launches;
+        rest_pending = false;
+        if (T > 1) {
+          cudaStreamWaitEvent(st, la->trsm_done[slot], 0);
+          chol_syrk_kernel<<<(T - 1) * T / 2, 256, 0, st>>>(A, lda, n, p0, p.meta, 2);
+          ++launches;
+          cudaEventRecord(la->rest_done[slot], st);
+          rest_pending = true;
+        }
+        slot ^= 1;
+      }
     }
+  }
+  if (la) {                                       // join: the critical-path stream's work is visible to the caller's stream
+    cudaEventRecord(la->fork, crit);
+    cudaStreamWaitEvent(st, la->fork, 0);
   }
   chol_init_x_kernel<<<(n + 255) / 256, 256, 0, st>>>(A, lda, n, z, acc, p.meta);
   ++launches;

@@ -130,6 +130,17 @@ class DPVO:
         self.pyramid = (self.fmap1_, self.fmap2_)
         self.viewer = None
         self._lmbda = torch.as_tensor([1e-4], device=dev)
+        # relative poses of removed frames (`pg.delta`, dpvo.py:274-277): rows of one device tensor, so that normalize()
+        # rescales all of them with one kernel instead of one per removed frame
+        self._delta_poses = torch.zeros(4096, 7, device=dev)
+        self._delta_n = 0
+
+    def _add_delta(self, t, t0, dP):
+        if self._delta_n == self._delta_poses.shape[0]:
+            self._delta_poses = torch.cat([self._delta_poses, torch.zeros_like(self._delta_poses)], 0)
+        self._delta_poses[self._delta_n] = dP.reshape(7)
+        self.pg.delta[t] = (t0, self._delta_n)
+        self._delta_n += 1
 
     def load_weights(self, network):
         """`network`: the reference's VONet (or any object with `.patchify` / `.update` modules carrying the reference
@@ -213,8 +224,7 @@ class DPVO:
         if m / 2 < cfg.KEYFRAME_THRESH:
             k = self.n - cfg.KEYFRAME_INDEX
             t0, t1 = pg.tstamps_[k - 1], pg.tstamps_[k]
-            dP = self._mul(pg.poses_[k:k + 1], self._inv(pg.poses_[k - 1:k]))
-            pg.delta[t1] = (t0, dP)
+            self._add_delta(t1, t0, self._mul(pg.poses_[k:k + 1], self._inv(pg.poses_[k - 1:k])))
             pg.edges.remove_frame(k)
             n = self.n
             pg.tstamps_[k:n - 1] = pg.tstamps_[k + 1:n]
@@ -269,10 +279,7 @@ class DPVO:
         s = pg.patches_[:n, :, 2].mean()
         pg.patches_[:n, :, 2] /= s
         pg.poses_[:n, :3] *= s
-        for t, (t0, dP) in pg.delta.items():
-            d = dP.clone()
-            d[:, :3] *= s
-            pg.delta[t] = (t0, d)
+        self._delta_poses[:self._delta_n, :3] *= s
         inv0 = self._inv(pg.poses_[0:1]).expand(n, 7)
         pg.poses_[:n] = self._mul(pg.poses_[:n], inv0)
         self._points()
@@ -358,7 +365,7 @@ class DPVO:
         self.counter += 1
         if n > 0 and not self.is_initialized:
             if float(self.motion_probe()) < 2.0:
-                pg.delta[self.counter - 1] = (self.counter - 2, torch.tensor([[0, 0, 0, 0, 0, 0, 1.0]], device=self.device))
+                self._add_delta(self.counter - 1, self.counter - 2, torch.tensor([0, 0, 0, 0, 0, 0, 1.0], device=self.device))
                 return
         self.n += 1
         self.m += M
@@ -385,8 +392,8 @@ class DPVO:
     def get_pose(self, t):
         if t in self.traj:
             return self.traj[t]
-        t0, dP = self.pg.delta[t]
-        self.traj[t] = self._mul(dP.cpu(), self.get_pose(t0))
+        t0, row = self.pg.delta[t]
+        self.traj[t] = self._mul(self._delta_host[row:row + 1], self.get_pose(t0))
         return self.traj[t]
 
     def terminate(self):
@@ -401,6 +408,7 @@ class DPVO:
         import sys
         sys.setrecursionlimit(max(sys.getrecursionlimit(), self.counter + 100))
         poses_h = self.pg.poses_[:self.n].cpu()
+        self._delta_host = self._delta_poses[:self._delta_n].cpu()
         self.traj = {int(self.pg.tstamps_[i]): poses_h[i:i + 1] for i in range(self.n)}
         poses = torch.cat([self.get_pose(t) for t in range(self.counter)], 0)
         poses = self._inv(poses).numpy()

@@ -167,11 +167,11 @@ class Patchifier(torch.nn.Module):
         return cls(BasicEncoder4.from_reference(module.fnet, 0.25), BasicEncoder4.from_reference(module.inet, 0.25),
                    module.patch_size)
 
-    def forward(self, images, patches_per_image=80, disps=None, centroid_sel_strat="RANDOM", return_color=False,
-                coords=None):
-        from . import altcorr
-        if centroid_sel_strat != "RANDOM":
-            raise NotImplementedError(f"Patch centroid selection not built: {centroid_sel_strat}")
+    use_graph = True        # replay the two encoders as one CUDA graph per image shape (≈30 launches -> 1)
+
+    def _encode(self, images):
+        """fnet and inet are independent and each layer fills a fraction of the GPU: inet runs beside fnet on a side
+        stream (two branches when captured)."""
         main = torch.cuda.current_stream(images.device)          # inet beside fnet on a side stream (independent nets)
         if getattr(self, "_side", None) is None:
             self._side = torch.cuda.Stream(images.device)
@@ -183,27 +183,76 @@ class Patchifier(torch.nn.Module):
             i.nhwc.record_stream(main)
             join.record(self._side)
         f = self.fnet(images)
-        self.fmap_nhwc = f.nhwc
-        self.fmap2_nhwc = avg_pool4(f.nhwc)
+        f2 = avg_pool4(f.nhwc)
         main.wait_event(join)
+        return f, i, f2
+
+    def _encode_graphed(self, images):
+        """One graph per (shape, device): the image is copied into the graph's input buffer, the encoders' outputs live
+        in the graph's buffers and are valid until the next call (DPVO copies them into its rings right away)."""
+        if not hasattr(self, "_graphs"):
+            self._graphs = {}
+        key = (tuple(images.shape), images.device.index)
+        ent = self._graphs.get(key)
+        if ent is None:
+            static = images.clone()
+            self._encode(static)                                  # warm-up outside the capture (lazy initialisations)
+            torch.cuda.synchronize(images.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                out = self._encode(static)
+            ent = self._graphs[key] = (g, static, out)
+        g, static, out = ent
+        static.copy_(images)
+        g.replay()
+        return out
+
+    def forward(self, images, patches_per_image=80, disps=None, centroid_sel_strat="RANDOM", return_color=False,
+                coords=None):
+        from . import altcorr
+        if centroid_sel_strat != "RANDOM":
+            raise NotImplementedError(f"Patch centroid selection not built: {centroid_sel_strat}")
+        if self.use_graph and not torch.cuda.is_current_stream_capturing():
+            f, i, f2 = self._encode_graphed(images)
+        else:
+            f, i, f2 = self._encode(images)
+        self.fmap_nhwc = f.nhwc
+        self.fmap2_nhwc = f2
         fmap, imap = f.nchw5, i.nchw5
         b, n, c, h, w = fmap.shape
         P = self.patch_size
         dev = images.device
+        integer = coords is None
         if coords is None:
             x = torch.randint(1, w - 1, size=[n, patches_per_image], device=dev)
             y = torch.randint(1, h - 1, size=[n, patches_per_image], device=dev)
             coords = torch.stack([x, y], dim=-1).float()
-        imap_p = altcorr.patchify(imap[0], coords, 0).view(b, -1, imap.shape[2], 1, 1)
-        gmap = altcorr.patchify(fmap[0], coords, P // 2).view(b, -1, c, P, P)
-        if disps is None:
-            disps = torch.ones(b, n, h, w, device=dev)
-        ys, xs = torch.meshgrid(torch.arange(h, device=dev, dtype=torch.float32),
-                                torch.arange(w, device=dev, dtype=torch.float32), indexing="ij")
-        grid = torch.stack([xs.expand(b, n, h, w), ys.expand(b, n, h, w), disps], dim=2)     # utils.py:39-50
-        patches = altcorr.patchify(grid[0], coords, P // 2).view(b, -1, 3, P, P)
+        if integer:
+            # integer centres (the reference's randint, net.py:113-115): the bilinear blend of altcorr.patchify has zero
+            # fractional weights, i.e. it IS the leading (2r+1)^2 window of the raw (2r+2)^2 gather — one launch per map
+            from . import cuda_corr
+
+            def gather(net, xy, r):
+                d = 2 * r + 1
+                return cuda_corr.patchify_forward(net, xy, r)[0][..., :d, :d]
+        else:
+            gather = altcorr.patchify
+        imap_p = gather(imap[0], coords, 0).reshape(b, -1, imap.shape[2], 1, 1)
+        gmap = gather(fmap[0], coords, P // 2).reshape(b, -1, c, P, P)
+        gkey = (b, n, h, w, dev.index)
+        grid = getattr(self, "_grid_cache", {}).get(gkey) if disps is None else None
+        if grid is None:
+            d = torch.ones(b, n, h, w, device=dev) if disps is None else disps
+            ys, xs = torch.meshgrid(torch.arange(h, device=dev, dtype=torch.float32),
+                                    torch.arange(w, device=dev, dtype=torch.float32), indexing="ij")
+            grid = torch.stack([xs.expand(b, n, h, w), ys.expand(b, n, h, w), d], dim=2)     # utils.py:39-50
+            if disps is None:                                    # inference: the unit-disparity grid never changes
+                if not hasattr(self, "_grid_cache"):
+                    self._grid_cache = {}
+                self._grid_cache[gkey] = grid
+        patches = gather(grid[0], coords, P // 2).reshape(b, -1, 3, P, P)
         index = torch.arange(n, device=dev).view(n, 1).repeat(1, coords.shape[1]).reshape(-1)
         if return_color:
-            clr = altcorr.patchify(images[0], 4 * (coords + 0.5), 0).view(b, -1, 3)
+            clr = gather(images[0], 4 * (coords + 0.5), 0).reshape(b, -1, 3)
             return fmap, gmap, imap_p, patches, index, clr
         return fmap, gmap, imap_p, patches, index

@@ -105,7 +105,8 @@ class Update(torch.nn.Module):
 
     # ------------------------------------------------------------------ pieces
     def _lin(self, name, A, **kw):
-        return update_ops.linear384(A, self.W[name], self.b[name], **kw)
+        # operands are produced / validated by forward(); the device is current and the stream fixed for the call
+        return update_ops.linear384_trusted(A, self.W[name], self.b[name], self._st, **kw)
 
     def _gather(self, x, index):
         out = torch.empty_like(x)
@@ -191,6 +192,7 @@ class Update(torch.nn.Module):
             ii = ii.contiguous(); jj = jj.contiguous(); kk = kk.contiguous()
             # the index-only work runs on a side stream underneath the correlation encoder
             main = torch.cuda.current_stream(net.device)
+            self._st = _lib.c_p(main.cuda_stream)
             if self._side is None:
                 self._side = torch.cuda.Stream(net.device)
                 self._fork, self._join = torch.cuda.Event(), torch.cuda.Event()

@@ -49,6 +49,26 @@ def _vec384(t, name):
     return t
 
 
+def _dp(t):
+    return 0 if t is None else t.data_ptr()
+
+
+def linear384_trusted(A, W, bias, stream, gate=None, res1=None, res2=None, idx=None, ln=None, act=0, head=None):
+    """linear384 for callers that have already validated their operands and made the device current (update.Update
+    issues 19 of these per call: the checks, the device guard and the stream lookup of the public entry cost more host
+    time than the launch)."""
+    M, K = A.shape
+    Y = torch.empty((M, DIM), dtype=torch.float16, device=A.device)
+    gamma, beta, eps = ln if ln is not None else (None, None, 0.0)
+    hw, ha = head if head is not None else (None, None)
+    p = _LinearParams(_dp(A), A.stride(0) if M > 1 else max(A.stride(0), K), _dp(W), W.stride(0), _dp(bias), _dp(gate),
+                      _dp(res1), _dp(res2), _dp(idx), _dp(gamma), _dp(beta), float(eps), int(act), _dp(Y), M, K, _dp(hw),
+                      _dp(ha))
+    if _lib.lib.dpvo_linear384_f16(ctypes.byref(p), stream):
+        _lib.check(1, "linear384")
+    return Y
+
+
 def linear384(A, W, bias=None, gate=None, res1=None, res2=None, idx=None, ln=None, act=0, out=None, head=None):
     """Y = act(LN((A W^T + bias) * gate + res1 + res2[idx])) as float16 [M, 384].
 
