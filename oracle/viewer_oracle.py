@@ -2,7 +2,7 @@
 
 numpy float32 restatement of DPViewer's two CUDA helpers (modules/DPViewer/dpviewer/viewer_cuda.cu):
   pose_to_matrix_kernel :221-262, iproj_kernel :56-164, backproject_and_filter's selection :199-213.
-PARITY UNPINNED: the reference kernels only exist as CUDA inside a torch + Pangolin/OpenGL extension that cannot be
+PARITY (round 1: unpinned; since round 2 pinned on the GPU box by oracle/_ref/dpviewer_cuda.so, see tests/test_viewer_gpu.py): the reference kernels only exist as CUDA inside a torch + Pangolin/OpenGL extension that cannot be
 built or run here (no GPU in this container, no graphics stack on the box), and the reference has no test or golden
 vector for them.  pose_to_matrix is cross-checked against the pinned lietorch oracle (inverse pose -> 4x4 matrix).
 """

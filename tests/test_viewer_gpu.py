@@ -1,5 +1,6 @@
 """GPU tests for the headless DPViewer helpers (N5) through the C ABI (dpvo_viewer_pose_to_matrix,
-dpvo_viewer_iproj) against oracle/viewer_oracle.py (numpy float32 restatement; parity UNPINNED — see its header).
+dpvo_viewer_iproj) against oracle/viewer_oracle.py (numpy float32 restatement) and, since round 2, against the reference's own
+viewer_cuda.cu compiled untouched into oracle/_ref/dpviewer_cuda.so (last test).
 Tolerances: pose_to_matrix 2e-6 absolute (unit quaternions, products of O(1) terms; the device contracts
 a*b+c into FMAs); iproj points 1e-5 relative; colours exact; the per-pixel counts exact wherever no comparison
 of the kernel sits within 1e-3 of its decision boundary (those pixels are skipped and must stay below 5 %)."""
