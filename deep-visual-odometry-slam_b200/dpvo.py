@@ -211,16 +211,29 @@ class DPVO:
         return torch.quantile(delta.norm(dim=-1).float(), 0.5)
 
     def motionmag(self, i, j):
+        """dpvo.py:240-246 for ONE direction (kept for callers that want it; keyframe() uses motionmag_pair)."""
         pg = self.pg
         k = torch.nonzero((pg.ii == i) & (pg.jj == j)).view(-1)
         flow, _ = pops.flow_mag(self.poses, self.patches, self.intrinsics, pg.ii[k], pg.jj[k], pg.kk[k], beta=0.5)
         return flow.mean()
 
+    def motionmag_pair(self, i, j):
+        """motionmag(i, j) + motionmag(j, i) without the two boolean-mask index synchronisations: the flow magnitude of
+        every live edge (one launch) and two masked means on the device; empty selections give NaN like the reference's
+        mean over an empty tensor (=> no keyframe removal)."""
+        pg = self.pg
+        flow, _ = pops.flow_mag(self.poses, self.patches, self.intrinsics, pg.ii, pg.jj, pg.kk, beta=0.5)
+        f = flow[0].mean(dim=(1, 2))
+        a = (pg.ii == i) & (pg.jj == j)
+        b = (pg.ii == j) & (pg.jj == i)
+        z = torch.zeros_like(f)                      # where(), not a product: unselected edges may hold inf / NaN
+        return torch.where(a, f, z).sum() / a.sum() + torch.where(b, f, z).sum() / b.sum()
+
     def keyframe(self):
         cfg, pg = self.cfg, self.pg
         i = self.n - cfg.KEYFRAME_INDEX - 1
         j = self.n - cfg.KEYFRAME_INDEX + 1
-        m = float((self.motionmag(i, j) + self.motionmag(j, i)).item())        # the decision is a host read (dpvo.py:268)
+        m = float(self.motionmag_pair(i, j).item())                            # the decision is a host read (dpvo.py:268)
         if m / 2 < cfg.KEYFRAME_THRESH:
             k = self.n - cfg.KEYFRAME_INDEX
             t0, t1 = pg.tstamps_[k - 1], pg.tstamps_[k]
