@@ -765,7 +765,8 @@ static int ba_forward_impl(int mode, float* poses, float* patches, const float* 
   p.P = P; p.t0 = t0; p.N = N; p.n = 6 * N; p.ppf = ppf;
 
   DPVO_REQUIRE(eff_impl || N <= 2048, "ba_forward: dense path supports at most 2048 free poses (use eff_impl)");
-  DPVO_REQUIRE(N <= 8192, "ba_forward: at most 8192 free poses");
+  // the dense float64 U and G accumulators are (6N)^2 each: 9.7 GB at the reference's BUFFER_SIZE = 4096 (config.py:6)
+  DPVO_REQUIRE(N <= 4096, "ba_forward: at most 4096 free poses (the dense Schur accumulators are (6N)^2 float64)");
   const int egrid = (int)(ceil_div64(n_edges, 256) < kNumSMs * 8 ? ceil_div64(n_edges, 256) : kNumSMs * 8);
   if (mode != 2) {
     cudaMemsetAsync(p.bitmap, 0, reinterpret_cast<char*>(p.meta) + 64 - reinterpret_cast<char*>(p.bitmap), st);
