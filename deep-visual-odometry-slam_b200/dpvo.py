@@ -52,6 +52,7 @@ class _Graph:
                                                 net_dim=DIM)
         self.E = 0            # live active edges (host copy, refreshed once per frame)
         self.E_inac = 0
+        self.min_ii = self.BIG  # smallest source frame among the live edges (host copy, same refresh)
 
     # ---- views of the live edges (host-known counts: no synchronisation)
     @property
@@ -86,10 +87,18 @@ class _Graph:
     @property
     def ix(self): return self.index_.view(-1)
 
+    BIG = 1 << 40
+
     def sync_counts(self):
-        """The one host read per frame: live counts of both lists."""
-        both = torch.cat([self.edges.active.count_, self.edges.inactive.count_]).cpu()
-        self.E, self.E_inac = int(both[0]), int(both[1])
+        """The one host read per frame: live counts of both lists and the smallest source frame of a live edge (what
+        `update()` needs for its "are there long-range edges" test, dpvo.py:348 — read here instead of with a second
+        synchronisation inside the next update)."""
+        a = self.edges.active
+        b = min(max(a.bound, 1), a.capacity)
+        live = torch.arange(b, device=a.ii_.device) < a.count_
+        mn = torch.where(live, a.ii_[:b], torch.full_like(a.ii_[:b], self.BIG)).min().view(1)
+        both = torch.cat([a.count_, self.edges.inactive.count_, mn]).cpu()
+        self.E, self.E_inac, self.min_ii = int(both[0]), int(both[1]), int(both[2])
         self.edges.active.bound, self.edges.inactive.bound = self.E, self.E_inac
         return self.E
 
@@ -283,8 +292,12 @@ class DPVO:
         return kk.flatten(), ej.flatten()
 
     def append_factors(self, ii, jj):
+        """Loop-closure edges (patchgraph.py:56-82): jj - source frame >= 30 and jj <= n - KEYFRAME_INDEX - 1, so every one
+        of them is a long-range edge in the sense of dpvo.py:348."""
         self.pg.edges.append_factors(ii, jj)
         self.pg.E += ii.numel()
+        if ii.numel():
+            self.pg.min_ii = min(self.pg.min_ii, self.n - self.cfg.KEYFRAME_INDEX - 1 - 30)
 
     def normalize(self):
         """patchgraph.py:84-96."""
@@ -330,7 +343,10 @@ class DPVO:
         act.target_[:E].copy_(target[0])
         act.weight_[:E].copy_(weight[0])
         try:
-            far = bool((pg.ii < self.n - cfg.REMOVAL_WINDOW - 1).any().item()) if cfg.LOOP_CLOSURE else False
+            # (pg.ii < n - REMOVAL_WINDOW - 1).any() of dpvo.py:348 from the host copy of min(ii): refreshed by the
+            # frame's one host read (keyframe -> sync_counts); edges appended since are either the new frame's
+            # (source frame >= n - PATCH_LIFETIME) or loop-closure edges (accounted for in append_factors)
+            far = bool(cfg.LOOP_CLOSURE) and pg.min_ii < self.n - cfg.REMOVAL_WINDOW - 1
             if far and not self.ran_global_ba[self.n]:
                 self._run_global_BA()
             else:
