@@ -21,7 +21,7 @@ lib = ctypes.CDLL(LIB_PATH)
 lib.dpvo_last_error.restype = ctypes.c_char_p
 lib.dpvo_abi_version.restype = ctypes.c_int
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 if lib.dpvo_abi_version() != ABI_VERSION:
     raise ImportError(f"libdpvo_b200.so ABI {lib.dpvo_abi_version()} != expected {ABI_VERSION}: rebuild")
 

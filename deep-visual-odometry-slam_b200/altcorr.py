@@ -75,8 +75,8 @@ def corr(fmap1, fmap2, coords, ii, jj, radius=1, dropout=1):
     return CorrLayer.apply(fmap1, fmap2, coords, ii, jj, radius, dropout)
 
 
-def corr_pyramid(fmap1, pyramid, coords, ii, jj, radius=3, scales=(1.0, 0.25), row_stride=None):
+def corr_pyramid(fmap1, pyramid, coords, ii, jj, radius=3, scales=(1.0, 0.25), row_stride=None, out=None):
     """Inference-only fused lookup over the 2-level pyramid: [B, M, 49*P*P*2] (a view of rows
     `row_stride` elements apart when given — see cuda_corr.pyramid_forward)."""
     return cuda_corr.pyramid_forward(fmap1, list(pyramid), list(scales), coords.float(), ii, jj, radius,
-                                     row_stride=row_stride)
+                                     row_stride=row_stride, out=out)

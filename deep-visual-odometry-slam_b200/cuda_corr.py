@@ -226,7 +226,7 @@ def _dense_patch_blob(fmap1):
     return span == C * PH * PW and s[1] % 8 == 0 and s[0] % 8 == 0 and fmap1.data_ptr() % 16 == 0
 
 
-def pyramid_forward(fmap1, pyramid, scales, coords, ii, jj, radius, row_stride=None):
+def pyramid_forward(fmap1, pyramid, scales, coords, ii, jj, radius, row_stride=None, out=None):
     """Fused multi-level lookup: returns [B, M, 49*P*P*L] with the level index fastest,
     i.e. torch.stack([corr_l ...], -1).view(B, M, -1) of the per-level results
     (dpvo.py:203-207, net.py:165-169).  One launch for two levels.  `row_stride` (elements, even,
@@ -247,7 +247,14 @@ def pyramid_forward(fmap1, pyramid, scales, coords, ii, jj, radius, row_stride=N
     stride = per * L if row_stride is None else int(row_stride)
     if stride < per * L or stride % 2:
         raise RuntimeError(f"pyramid_forward: row_stride must be even and >= {per * L}")
-    out = torch.empty((B, M, stride), dtype=fmap1.dtype, device=fmap1.device)[:, :, :per * L]
+    if out is not None:
+        # caller-owned buffer [B, >= M, stride] (a persistent one keeps the consumer's pointer signature stable)
+        if out.dim() != 3 or out.shape[0] != B or out.shape[1] < M or out.shape[2] != stride or out.dtype != fmap1.dtype \
+                or not out.is_contiguous() or out.device != fmap1.device:
+            raise RuntimeError(f"pyramid_forward: out must be a contiguous [{B}, >={M}, {stride}] tensor of the feature dtype")
+        out = out[:, :M, :per * L]
+    else:
+        out = torch.empty((B, M, stride), dtype=fmap1.dtype, device=fmap1.device)[:, :, :per * L]
     if B * M == 0:
         return out
     perm = None

@@ -143,6 +143,7 @@ class DPVO:
         # rescales all of them with one kernel instead of one per removed frame
         self._delta_poses = torch.zeros(4096, 7, device=dev)
         self._delta_n = 0
+        self._corr_buf = self._ctx_buf = None
 
     def _add_delta(self, t, t0, dP):
         if self._delta_n == self._delta_poses.shape[0]:
@@ -164,6 +165,9 @@ class DPVO:
             network.eval()
         if not isinstance(network.update, Update):
             network.update = Update.from_reference(network.update)
+        # The operator's operands live in persistent buffers here, so its opt-in CUDA-graph cache (update.Update.use_graphs)
+        # COULD be used; it is not: keyframe removal makes the edge count differ from frame to frame (measured on the
+        # 1,000-frame sequence: a new signature almost every frame, 146 -> 93 frames/s from the captures alone).
         if not isinstance(network.patchify, Patchifier):
             network.patchify = Patchifier.from_reference(network.patchify)
         self.device = network.update.device
@@ -201,7 +205,24 @@ class DPVO:
         ii, jj = indicies if indicies is not None else (self.pg.kk, self.pg.jj)
         ii1 = ii % (self.M * self.pmem)
         jj1 = jj % self.mem
-        return altcorr.corr_pyramid(self.gmap, self.pyramid, coords, ii1, jj1, 3, row_stride=896)
+        E = ii.numel()
+        out = None
+        if indicies is None:
+            # the live edge list's lookup lands in a persistent buffer: the Update operator then sees the same operand
+            # pointers frame after frame and replays its CUDA graph (update.Update._graph_lookup)
+            if self._corr_buf is None or self._corr_buf.shape[1] < E:
+                self._corr_buf = torch.empty((1, max(int(E * 1.25), 65536), 896), **self.kwargs)
+            out = self._corr_buf
+        return altcorr.corr_pyramid(self.gmap, self.pyramid, coords, ii1, jj1, 3, row_stride=896, out=out)
+
+    def _ctx_index(self):
+        """kk % (M * pmem) of dpvo.py:333 into a persistent buffer (stable pointer, see corr())."""
+        E = self.pg.E
+        if self._ctx_buf is None or self._ctx_buf.numel() < E:
+            self._ctx_buf = torch.empty(max(int(E * 1.25), 65536), dtype=torch.int64, device=self.device)
+        out = self._ctx_buf[:E]
+        torch.remainder(self.pg.kk, self.M * self.pmem, out=out)
+        return out
 
     def reproject(self, indicies=None):
         ii, jj, kk = indicies if indicies is not None else (self.pg.ii, self.pg.jj, self.pg.kk)
@@ -333,9 +354,10 @@ class DPVO:
         E = pg.E
         coords = self.reproject()
         corr = self.corr(coords)
-        ctx = (self.imap[0], pg.kk % (self.M * self.pmem))
+        ctx = (self.imap[0], self._ctx_index())
+        nf = (self.n + 64) // 64 * 64              # coarse bounds: the operator's graph signature changes every 64 frames
         net, (delta, weight, _) = self.network.update(pg.net, ctx, corr, None, pg.ii, pg.jj, pg.kk,
-                                                      n_frames=self.n + 1, n_patches=self.m + self.M)
+                                                      n_frames=nf, n_patches=nf * self.M)
         weight = weight.float()
         target = coords[..., self.P // 2, self.P // 2] + delta.float()
         act = pg.edges.active

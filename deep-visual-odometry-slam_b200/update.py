@@ -24,6 +24,10 @@ residual stream in float32 between its float16 GEMMs; the difference is bounded 
 tests/test_update_gpu.py against the float32 oracle next to the autocast graph's own error.
 CUDA only — there is no CPU fallback.
 """
+import collections
+import ctypes
+import os
+
 import torch
 
 from . import _lib, cuda_ba, update_ops
@@ -32,6 +36,20 @@ DIM = update_ops.DIM
 LN_EPS = 1e-3   # net.py:37,42,44,53
 _L = _lib.lib
 _L.dpvo_softagg_workspace_bytes.restype = _lib.c_i64
+
+class _UpdateWeights(ctypes.Structure):
+    """Mirror of dpvo_update_weights."""
+    _fields_ = [("W", ctypes.c_void_p * 19), ("ldw", ctypes.c_int64 * 19), ("bias", ctypes.c_void_p * 19),
+                ("ln_gamma", ctypes.c_void_p * 4), ("ln_beta", ctypes.c_void_p * 4), ("ln_eps", ctypes.c_float),
+                ("corr_features", ctypes.c_int32),
+                ("head_w", ctypes.c_void_p), ("head_bias_d", ctypes.c_void_p), ("head_bias_w", ctypes.c_void_p)]
+
+
+_L.dpvo_update_workspace_bytes.restype = _lib.c_i64
+_L.dpvo_update_workspace_bytes.argtypes = [ctypes.c_int64] * 3
+_L.dpvo_update_forward.restype = ctypes.c_int
+_L.dpvo_update_forward.argtypes = [ctypes.POINTER(_UpdateWeights)] + [ctypes.c_void_p] * 4 + [ctypes.c_int64] + \
+    [ctypes.c_void_p] * 3 + [ctypes.c_int64] * 3 + [ctypes.c_void_p] * 4 + [ctypes.c_int64, ctypes.c_void_p]
 
 _LINEAR = ("c1.0", "c1.2", "c2.0", "c2.2", "agg_kk.f", "agg_kk.g", "agg_kk.h", "agg_ij.f", "agg_ij.g", "agg_ij.h",
            "gru.1.gate.0", "gru.1.res.0", "gru.1.res.2", "gru.3.gate.0", "gru.3.res.0", "gru.3.res.2",
@@ -84,6 +102,26 @@ class Update(torch.nn.Module):
         self.head_w = torch.cat([self.head["d.1"][0], self.head["w.1"][0]], 0).contiguous()   # [4, 384]
         self.corr_features = self.W["corr.0"].shape[1]
         self._side = None
+        self._cw = self._c_weights()
+        self._ws = None
+
+
+    def _c_weights(self):
+        """dpvo_update_weights (include/dpvo_b200.h) over this instance's tensors, built once."""
+        w = _UpdateWeights()
+        for i, k in enumerate(_LINEAR):
+            w.W[i] = self.W[k].data_ptr()
+            w.ldw[i] = self.W[k].stride(0)
+            w.bias[i] = self.b[k].data_ptr()
+        for i, k in enumerate(_NORMS):
+            w.ln_gamma[i] = self.ln[k][0].data_ptr()
+            w.ln_beta[i] = self.ln[k][1].data_ptr()
+        w.ln_eps = LN_EPS
+        w.corr_features = self.corr_features
+        w.head_w = self.head_w.data_ptr()
+        w.head_bias_d = self.head["d.1"][1].data_ptr()
+        w.head_bias_w = self.head["w.1"][1].data_ptr()
+        return w
 
     # ------------------------------------------------------------------ construction helpers
     @classmethod
@@ -190,6 +228,98 @@ class Update(torch.nn.Module):
                 buf[:, :self.corr_features].copy_(corr)
                 corr = buf[:, :self.corr_features]
             ii = ii.contiguous(); jj = jj.contiguous(); kk = kk.contiguous()
+            if tidx is not None:
+                if tidx.dtype != torch.int64 or tidx.numel() != E:
+                    raise RuntimeError("Update: the context index must be int64 with one entry per edge")
+                tidx = tidx.contiguous()
+            if ii.dtype != torch.int64 or jj.dtype != torch.int64 or kk.dtype != torch.int64:
+                raise RuntimeError("Update: ii, jj, kk must be int64")
+            args = (net, table, tidx, corr, ii, jj, kk, int(n_frames), int(n_patches))
+            ent = self._graph_lookup(args) if self.use_graphs and E >= self.graph_min_edges else None
+            if ent is not None:
+                ent[0].replay()
+                return ent[1]
+            net, delta, weight = self._forward_impl(*args)
+        return net[None], (delta[None], weight[None], None)
+
+    # ------------------------------------------------------------------ CUDA-graph cache
+    # Issued eagerly the operator is host-bound: ~45 ctypes launches take 1.46 ms against 0.72 ms of GPU time at
+    # E = 45,312 (profiles/r02_time_update.json).  A caller that keeps its operands in persistent buffers (this repo's
+    # DPVO class: edge store, context index and correlation buffers) presents the same (pointers, E, bounds) frame
+    # after frame; the second time a signature is seen the operator is captured and from then on replayed.  Outputs
+    # live in the graph's buffers and are valid until the next call with the same signature.  OFF unless the caller opts
+    # in (`update.use_graphs = True`): it pays only for a caller whose edge list keeps its size for many consecutive
+    # calls (fixed-window replay, the 12 updates of initialisation / terminate); in DPVO's steady state keyframe
+    # removal changes the edge count almost every frame and every new signature costs a capture (measured: 146 -> 93
+    # frames/s on the 1,000-frame sequence), so this repo's DPVO class leaves it off.
+    use_graphs = False
+    graph_min_edges = 4096
+    graph_cache_size = 3
+
+    def _graph_lookup(self, args):
+        if torch.cuda.is_current_stream_capturing():
+            return None
+        net, table, tidx, corr, ii, jj, kk, n_frames, n_patches = args
+        key = (net.shape[0], net.data_ptr(), table.data_ptr(), table.shape[0], 0 if tidx is None else tidx.data_ptr(),
+               corr.data_ptr(), corr.stride(0), ii.data_ptr(), jj.data_ptr(), kk.data_ptr(), n_frames, n_patches,
+               net.device.index)
+        if not hasattr(self, "_graphs"):
+            self._graphs, self._seen = collections.OrderedDict(), {}
+        ent = self._graphs.get(key)
+        if ent is not None:
+            self._graphs.move_to_end(key)
+            return ent
+        n = self._seen.get(key, 0) + 1
+        if len(self._seen) > 256:
+            self._seen.clear()
+        self._seen[key] = n
+        if n < 2:
+            return None
+        while len(self._graphs) >= self.graph_cache_size:
+            self._graphs.popitem(last=False)
+        self._forward_impl(*args)                                   # warm-up outside the capture
+        torch.cuda.synchronize(net.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            o_net, o_delta, o_weight = self._forward_impl(*args)
+        ent = (g, (o_net[None], (o_delta[None], o_weight[None], None)), args)   # args kept alive: the graph reads them
+        self._graphs[key] = ent
+        return ent
+
+    # DPVO_UPDATE_PYTHON=1: issue the launches one ctypes call at a time (the round-1 path; A/B and debugging)
+    launch_by_launch = os.environ.get("DPVO_UPDATE_PYTHON", "0") == "1"
+
+    def _forward_impl(self, net, table, tidx, corr, ii, jj, kk, n_frames, n_patches):
+        """One C call (csrc/update_forward.cu): same launches, same order, same operands as _forward_python."""
+        if self.launch_by_launch:
+            return self._forward_python(net, table, tidx, corr, ii, jj, kk, n_frames, n_patches)
+        E = net.shape[0]
+        dev = net.device
+        nbytes = int(_L.dpvo_update_workspace_bytes(E, n_frames, n_patches))
+        if self._ws is None or self._ws.numel() < nbytes or self._ws.device != dev \
+                or torch.cuda.is_current_stream_capturing():
+            ws = torch.empty(int(nbytes * 1.25) + 4096, dtype=torch.uint8, device=dev)
+            if not torch.cuda.is_current_stream_capturing():
+                self._ws = ws
+        else:
+            ws = self._ws
+        out = torch.empty((E, DIM), dtype=torch.float16, device=dev)
+        delta = torch.empty((E, 2), dtype=torch.float32, device=dev)
+        weight = torch.empty((E, 2), dtype=torch.float32, device=dev)
+        st = torch.cuda.current_stream(dev)
+        rc = _L.dpvo_update_forward(ctypes.byref(self._cw), net.data_ptr(), table.data_ptr(),
+                                    0 if tidx is None else tidx.data_ptr(), corr.data_ptr(), corr.stride(0),
+                                    ii.data_ptr(), jj.data_ptr(), kk.data_ptr(), E, n_frames, n_patches,
+                                    out.data_ptr(), delta.data_ptr(), weight.data_ptr(), ws.data_ptr(), ws.numel(),
+                                    st.cuda_stream)
+        if rc:
+            _lib.check(rc, "update_forward")
+        ws.record_stream(st)
+        return out, delta, weight
+
+    def _forward_python(self, net, table, tidx, corr, ii, jj, kk, n_frames, n_patches):
+        E = net.shape[0]
+        if True:
             # the index-only work runs on a side stream underneath the correlation encoder
             main = torch.cuda.current_stream(net.device)
             self._st = _lib.c_p(main.cuda_stream)
@@ -226,4 +356,4 @@ class Update(torch.nn.Module):
             _lib.check(_L.dpvo_update_heads_finish(_lib.ptr(acc), _lib.ptr(self.head["d.1"][1]),
                                                    _lib.ptr(self.head["w.1"][1]), _lib.c_i64(E), _lib.ptr(delta),
                                                    _lib.ptr(weight), _lib.stream_of(net)), "update_heads_finish")
-        return net[None], (delta[None], weight[None], None)
+        return net, delta, weight

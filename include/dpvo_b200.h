@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define DPVO_B200_ABI_VERSION 4
+#define DPVO_B200_ABI_VERSION 5
 
 typedef enum { DPVO_F16 = 0, DPVO_F32 = 1, DPVO_F64 = 2 } dpvo_dtype;
 
@@ -267,6 +267,29 @@ int dpvo_update_heads_f16(const void* net, const float* wd, const float* bd, con
  * delta = acc[:, 0:2] + bd, weight = sigmoid(acc[:, 2:4] + bw). */
 int dpvo_update_heads_finish(const float* acc, const float* bd, const float* bw, int64_t n_edges,
                              float* delta, float* weight, void* stream);
+
+/* The whole operator (net.py:69-88) in one call: the same launches update.py would issue one ctypes call at a time
+ * (csrc/update_forward.cu), without the host time of ~45 Python round trips.  Layer order of W / ldw / bias:
+ *   c1.0 c1.2 c2.0 c2.2 agg_kk.f agg_kk.g agg_kk.h agg_ij.f agg_ij.g agg_ij.h gru.1.gate.0 gru.1.res.0 gru.1.res.2
+ *   gru.3.gate.0 gru.3.res.0 gru.3.res.2 corr.0 corr.2 corr.5          (reference state-dict names, net.py:23-66)
+ * LayerNorm order of ln_gamma / ln_beta: norm, gru.0, gru.2, corr.3.  W: fp16 [384, K] rows ldw apart (K = 384, corr.0:
+ * corr_features = 882); bias / gamma / beta: float32 [384]; head_w: float32 [4, 384] (d.1 rows then w.1 rows);
+ * head_bias_d / head_bias_w: float32 [2]. */
+typedef struct {
+  const void* W[19]; int64_t ldw[19]; const float* bias[19];
+  const float* ln_gamma[4]; const float* ln_beta[4]; float ln_eps;
+  int32_t corr_features;
+  const float* head_w; const float* head_bias_d; const float* head_bias_w;
+} dpvo_update_weights;
+/* net: fp16 [E,384]; table: fp16 [*,384] context rows, gathered with table_index [E] (NULL: row e); corr: fp16
+ * [E, corr_features] rows ld_corr elements apart (16-byte aligned rows); ii / jj / kk: int64 [E]; n_frames /
+ * n_patches: exclusive upper bounds of the frame / patch indices.  Outputs: net_out fp16 [E,384] (must not alias an
+ * input), delta / weight float32 [E,2].  workspace: dpvo_update_workspace_bytes(E, n_frames, n_patches). */
+int64_t dpvo_update_workspace_bytes(int64_t n_edges, int64_t n_frames, int64_t n_patches);
+int dpvo_update_forward(const dpvo_update_weights* w, const void* net, const void* table, const int64_t* table_index,
+                        const void* corr, int64_t ld_corr, const int64_t* ii, const int64_t* jj, const int64_t* kk,
+                        int64_t n_edges, int64_t n_frames, int64_t n_patches, void* net_out, float* delta, float* weight,
+                        void* workspace, int64_t workspace_bytes, void* stream);
 
 /* cuda_ba.solve_system (fastba/ba.cpp:99-180): one Gauss-Newton step of the classic loop-closure
  * pose graph over Sim(3).  J_Ginv_i / J_Ginv_j: float32 [r,7,7] blocks of edge x at poses ii[x] / jj[x]

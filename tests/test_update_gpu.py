@@ -225,3 +225,76 @@ def test_update_empty_edge_list():
     net, (delta, weight, _) = op(torch.zeros(1, 0, 384, device="cuda").half(), torch.zeros(1, 0, 384, device="cuda").half(),
                                  torch.zeros(1, 0, 882, device="cuda").half(), None, z, z, z)
     assert net.shape == (1, 0, 384) and delta.shape == (1, 0, 2) and weight.shape == (1, 0, 2)
+
+
+def test_update_graph_cache_replays():
+    """Opt-in CUDA-graph cache (update.Update.use_graphs): with the operands in persistent buffers the second call with
+    the same signature captures, later calls replay; results must equal the eager run (to the operator's own run-to-run
+    spread: its grouped sums and head dot products use float atomics), follow NEW contents of the same buffers, and a
+    different edge count must fall back to an eager run."""
+    pkg = load_pkg()
+    upd_mod = importlib.import_module(pkg.__name__ + ".update")
+    sd_np, d = _operator_case(pkg, 22, 32, seed_w=3, seed_x=4)
+    op = upd_mod.Update.from_state_dict({k: torch.from_numpy(v) for k, v in sd_np.items()}, device="cuda")
+    ii, jj, kk = (torch.from_numpy(d[k]).cuda() for k in ("ii", "jj", "kk"))
+    E = ii.numel()
+    assert E >= op.graph_min_edges
+    net = torch.from_numpy(d["net"]).cuda().half()[None].contiguous()
+    corr_buf = torch.zeros(1, E, 896, dtype=torch.float16, device="cuda")
+    corr_buf[:, :, :882] = torch.from_numpy(d["corr"]).cuda().half()
+    corr = corr_buf[:, :, :882]
+    imap = torch.from_numpy(d["imap"]).cuda().half()
+    tidx = (kk % imap.shape[0]).contiguous()
+    nf, npat = int(max(ii.max(), jj.max())) + 1, int(kk.max()) + 1
+    call = lambda: op(net, (imap, tidx), corr, None, ii, jj, kk, n_frames=nf, n_patches=npat)
+    clone = lambda o: (o[0].clone(), o[1][0].clone(), o[1][1].clone())
+    eager = clone(call())
+    op.use_graphs = True
+    first = clone(call())                       # first sighting: eager
+    assert not getattr(op, "_graphs", {})
+    second = clone(call())                      # second sighting: capture + replay
+    assert len(op._graphs) == 1
+    third = clone(call())                       # replay
+    same = lambda a, b: _rel(a.float(), b.float()) < 1e-3
+    for got in (first, second, third):
+        for a, b in zip(got, eager):
+            assert same(a, b)
+    # new contents in the same buffers are picked up by the replay
+    net.mul_(0.5)
+    corr_buf.mul_(-1.0)
+    replayed = clone(call())
+    op.use_graphs = False
+    want = clone(call())
+    for a, b in zip(replayed, want):
+        assert same(a, b)
+    assert not same(replayed[0], eager[0])
+    # a different edge count is a different signature: eager, cache untouched
+    op.use_graphs = True
+    sub = slice(0, E - 64)
+    out = op(net[:, sub].contiguous(), (imap, tidx[sub].contiguous()), corr_buf[:, sub, :882], None, ii[sub].contiguous(),
+             jj[sub].contiguous(), kk[sub].contiguous(), n_frames=nf, n_patches=npat)
+    assert out[0].shape[1] == E - 64 and len(op._graphs) == 1
+
+
+def test_update_one_call_path_matches_launch_by_launch_path():
+    """csrc/update_forward.cu (the whole operator behind one C call) against update.py's launch-by-launch path: same
+    kernels, same order, same operands -> equal to the operator's run-to-run spread (float atomics in the grouped sums)."""
+    pkg = load_pkg()
+    upd_mod = importlib.import_module(pkg.__name__ + ".update")
+    for n_frames, M, fused in ((22, 96, True), (5, 13, False), (14, 16, True)):
+        sd_np, d = _operator_case(pkg, n_frames, M, seed_w=5, seed_x=n_frames)
+        op = upd_mod.Update.from_state_dict({k: torch.from_numpy(v) for k, v in sd_np.items()}, device="cuda")
+        ii, jj, kk = (torch.from_numpy(d[k]).cuda() for k in ("ii", "jj", "kk"))
+        net = torch.from_numpy(d["net"]).cuda().half()[None]
+        corr = torch.from_numpy(d["corr"]).cuda().half()[None]
+        imap = torch.from_numpy(d["imap"]).cuda().half()
+        tidx = kk % imap.shape[0]
+        inp = (imap, tidx) if fused else imap[tidx][None]
+        assert not op.launch_by_launch
+        a = op(net, inp, corr, None, ii, jj, kk)
+        op.launch_by_launch = True
+        b = op(net, inp, corr, None, ii, jj, kk)
+        b2 = op(net, inp, corr, None, ii, jj, kk)
+        spread = max(_rel(b2[0].float(), b[0].float()), _rel(b2[1][0], b[1][0]), _rel(b2[1][1], b[1][1]))
+        for x, y in ((a[0], b[0]), (a[1][0], b[1][0]), (a[1][1], b[1][1])):
+            assert _rel(x.float(), y.float()) <= max(1e-4, 3 * spread), (n_frames, M, _rel(x.float(), y.float()), spread)
