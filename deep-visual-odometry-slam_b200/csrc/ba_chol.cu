@@ -22,6 +22,10 @@
 #include "ba_internal.cuh"
 #include <stdlib.h>
 
+#ifndef DPVO_CHOL_NOALLOC_MAX_N
+#define DPVO_CHOL_NOALLOC_MAX_N 768
+#endif
+
 namespace dpvo {
 
 constexpr int NB = 64;
@@ -505,4 +509,70 @@ extern "C" int dpvo_chol_solve(const float* S, const float* y, int32_t n, float*
   if (ba_chol_solve(p, A, lda, A + (int64_t)(n + 1) * lda, st)) return 1;
   cudaMemcpyAsync(info, p.meta + 1, sizeof(int), cudaMemcpyDeviceToDevice, st);
   return check_launch("chol_solve");
+}
+
+// ------------------------------------------------------------------ allocation-free variant
+// dpvo_chol_solve for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc): the workspace is a file-scope device array, so every GPU that loads the library holds
+// kNoAllocBytes (about 2.6 MB) until the process exits.  No counterpart in the reference.
+namespace dpvo {
+constexpr int kNoAllocMaxN = DPVO_CHOL_NOALLOC_MAX_N;      // 768 = 128 free poses; below the look-ahead threshold
+                                                           // (16 panels), so no internal stream / events either
+constexpr int64_t kNoAllocFloats =
+    64 /* meta */ + (int64_t)(kNoAllocMaxN + 1) * ((kNoAllocMaxN + 63) & ~63) /* A + y row */ +
+    3 * (int64_t)kNoAllocMaxN + 64 + (int64_t)((kNoAllocMaxN + NB - 1) / NB) * NB * NB /* chol_scratch_floats */ + 128;
+static_assert(kNoAllocMaxN < 16 * NB, "the static-scratch solve must stay below the look-ahead threshold (stream / event creation)");
+static __device__ __align__(256) float g_chol_noalloc_scratch[kNoAllocFloats];
+
+// In host code `g_chol_noalloc_scratch` is only a handle: the device address comes from cudaGetSymbolAddress,
+// once per device with that device current.
+static float* chol_noalloc_scratch() {
+  static float* per_dev[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    set_error("chol_solve_noalloc: no current device");
+    return nullptr;
+  }
+  float* ptr = __atomic_load_n(&per_dev[dev], __ATOMIC_ACQUIRE);
+  if (!ptr) {
+    const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_chol_noalloc_scratch);
+    if (e != cudaSuccess || !ptr) {
+      set_error("chol_solve_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return nullptr;
+    }
+    __atomic_store_n(&per_dev[dev], ptr, __ATOMIC_RELEASE);  // every thread resolves the same address: benign race
+  }
+  return ptr;
+}
+}  // namespace dpvo
+
+extern "C" int32_t dpvo_chol_solve_noalloc_max_n(void) { return dpvo::kNoAllocMaxN; }
+
+extern "C" int dpvo_chol_solve_noalloc(const float* S, const float* y, int32_t n, float* x, int32_t* info,
+                                       void* stream) {
+  using namespace dpvo;
+  DPVO_REQUIRE(n >= 0, "chol_solve_noalloc: negative size");
+  DPVO_REQUIRE(n <= kNoAllocMaxN,
+               "chol_solve_noalloc: n = %d exceeds the static scratch (max %d); use dpvo_chol_solve with a workspace",
+               n, kNoAllocMaxN);
+  if (n == 0) return 0;
+  DPVO_REQUIRE(S && y && x && info, "chol_solve_noalloc: null pointer");
+  float* base = chol_noalloc_scratch();
+  if (!base) return 1;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  BADev p;
+  memset(&p, 0, sizeof(p));
+  p.n = n; p.N = 0; p.dX = x;
+  p.meta = reinterpret_cast<int*>(base);          // 64 ints; meta[1] (failure flag) is cleared by the pack kernel
+  float* A = base + 64;
+  const int lda = chol_lda(n);
+  const int64_t tot = (int64_t)(n + 1) * n;
+  const int grid = (int)(ceil_div64(tot, 256) < kNumSMs * 8 ? ceil_div64(tot, 256) : kNumSMs * 8);
+  // everything the factorisation reads is rewritten per call: lower triangle + y row (pack), z / acc (init_x),
+  // inv(L11) per panel (diag); the rest of the array keeps the previous call's bytes and is never read
+  chol_pack_kernel<<<grid, 256, 0, st>>>(S, y, n, A, lda, p.meta);
+  note_launches(1);
+  if (ba_chol_solve(p, A, lda, A + (int64_t)(n + 1) * lda, st)) return 1;
+  cudaMemcpyAsync(info, p.meta + 1, sizeof(int), cudaMemcpyDeviceToDevice, st);
+  return check_launch("chol_solve_noalloc");
 }

@@ -201,6 +201,17 @@ int64_t dpvo_chol_workspace_bytes(int32_t n);
 int dpvo_chol_solve(const float* S, const float* y, int32_t n, float* x, int32_t* info,
                     void* workspace, int64_t workspace_bytes, void* stream);
 
+/* dpvo_chol_solve without a workspace argument and without any allocation (no cudaMalloc / cudaFree, no stream or
+ * event creation): for callers that cannot allocate — CUDA graph capture, serving loops, harnesses that forbid it.
+ * No counterpart in the reference.  The scratch is a file-scope
+ * device array of the library (about 2.6 MB, held by every GPU that loads the library until the process exits), so
+ * n <= dpvo_chol_solve_noalloc_max_n() (768 = 128 free poses); larger n returns 1 with a message in
+ * dpvo_last_error().  All calls on a device share that array: calls that overlap on the GPU (different streams
+ * without an ordering between them) race; calls on one stream, or ordered by events, are safe.  Same arguments,
+ * results and info semantics as dpvo_chol_solve otherwise. */
+int32_t dpvo_chol_solve_noalloc_max_n(void);
+int dpvo_chol_solve_noalloc(const float* S, const float* y, int32_t n, float* x, int32_t* info, void* stream);
+
 /* ---- Update operator (net.py:23-88, blocks.py:15-48): edge-MLP layers on the tensor cores -------
  * One nn.Linear(K, 384) over E edge rows with the row-local work that follows it in the reference
  * fused into the epilogue:
