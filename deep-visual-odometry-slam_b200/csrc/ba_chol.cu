@@ -30,191 +30,284 @@ namespace dpvo {
 
 constexpr int NB = 64;
 
-// Factor the nb x nb SPD block held in L (lower triangle, row-major, leading dimension NB+1) in place
-// and invert the factor into X (lower).  Blocked 4 x 16 inside the tile so that the serial chain is
-// short: each 16x16 diagonal block is factored AND inverted by one warp in registers (row l in lane l,
-// pivots / multipliers broadcast with shuffles: no barriers), the panel below is a product with that
-// inverse, the trailing update and the assembly of inv(L) from the block inverses use all 256 threads.
-// ~22 barriers instead of 64 + a 2,000-step serial substitution.  Returns false on a non-positive pivot.
-__device__ __forceinline__ bool chol_factor_invert(float (*L)[NB + 1], float (*X)[NB + 1], int nb) {
-  constexpr int SB = 16;
-  __shared__ float Tm[3][SB][SB + 1];
-  __shared__ int s_fail;
-  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  if (tid == 0) s_fail = 0;
-  for (int i = tid; i < NB * NB; i += 256) {
-    const int r = i / NB, c = i % NB;
-    X[r][c] = 0.f;
-    if (r >= nb || c > r) L[r][c] = (r == c) ? 1.f : 0.f;     // identity padding, clean upper triangle
+constexpr int LDT = 68;                    // shared-memory tile row stride (floats): rows stay 16-byte aligned for
+                                           // float4 reads along k, and 8 consecutive rows cover all 32 banks
+constexpr int TILE = NB * LDT;
+constexpr int kPanelSmemBytes = 4 * TILE * (int)sizeof(float);
+
+// acc[i][j] += sum_{k < 64} As[ty + 16 i][k] * Bs[tx + 16 j][k]   (both tiles row-major with stride LDT).
+// float4 along k: per 4 k-steps a thread issues 8 LDS.128 for 64 FMAs (scalar reads: 32 LDS for 64 FMAs, which made
+// the old 64^3 tile products shared-memory-issue bound); the 16 lanes that share ty read one address (broadcast).
+__device__ __forceinline__ void tile_mma(float (&acc)[4][4], const float* __restrict__ As, const float* __restrict__ Bs,
+                                         int ty, int tx) {
+#pragma unroll 2
+  for (int k = 0; k < NB; k += 4) {
+    float4 a[4], b[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      a[i] = *reinterpret_cast<const float4*>(As + (ty + 16 * i) * LDT + k);
+      b[i] = *reinterpret_cast<const float4*>(Bs + (tx + 16 * i) * LDT + k);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        acc[i][j] = fmaf(a[i].x, b[j].x, acc[i][j]);
+        acc[i][j] = fmaf(a[i].y, b[j].y, acc[i][j]);
+        acc[i][j] = fmaf(a[i].z, b[j].z, acc[i][j]);
+        acc[i][j] = fmaf(a[i].w, b[j].w, acc[i][j]);
+      }
+  }
+}
+
+// One warp factors the 32x32 SPD block at (o, o) of D in registers (lane l owns row l), right-looking so that the
+// serial chain per pivot is one shuffle, one reciprocal and two dependent FMAs: the column below pivot j is used
+// UNSCALED in the update,  A[l][k] -= (A[l][j] / d_j) * A[k][j],  and scaled to L[l][j] = A[l][j] * rsqrt(d_j) off the
+// critical path.  Writes L (lower, zero upper) back into D and 1 / L_jj into rinv; a[] (row l of L) and my_rs
+// (1 / L_ll) stay in registers for chol_invert32.  Returns false on a non-positive (or NaN) pivot.
+__device__ __forceinline__ bool chol_factor32(float* __restrict__ D, float* __restrict__ rinv, int o, int lane,
+                                              float (&a)[32], float& my_rs) {
+  constexpr int SB = 32;
+  constexpr unsigned FULL = 0xffffffffu;
+#pragma unroll
+  for (int k = 0; k < SB; ++k) a[k] = D[(o + lane) * LDT + o + k];
+  bool bad = false;
+  my_rs = 0.f;
+#pragma unroll
+  for (int j = 0; j < SB; ++j) {
+    const float d = __shfl_sync(FULL, a[j], j);
+    if (!(d > 0.f)) bad = true;
+    const float inv_d = __frcp_rn(d);
+    float rs = rsqrtf(d);
+    rs = rs * (1.5f - 0.5f * d * rs * rs);
+    const float t = a[j] * inv_d;
+#pragma unroll
+    for (int k = j + 1; k < SB; ++k) {
+      const float akj = __shfl_sync(FULL, a[j], k);        // A[k][j], still unscaled (independent of the reciprocal)
+      a[k] = fmaf(-t, akj, a[k]);          // lanes l < k compute don't-care values (masked at the store)
+    }
+    a[j] = (lane == j) ? d * rs : a[j] * rs;
+    if (lane == j) my_rs = rs;
+  }
+#pragma unroll
+  for (int k = 0; k < SB; ++k) D[(o + lane) * LDT + o + k] = (k <= lane) ? a[k] : 0.f;
+  rinv[o + lane] = my_rs;
+  return !__any_sync(FULL, bad);
+}
+
+// inv(L) of the block chol_factor32 left in registers: lane c solves L x = e_c forwards (right-looking);
+// L[i2][i] = a[i] of lane i2, 1 / L_ii = my_rs of lane i.  Writes the block (lower, zero upper) into X.
+__device__ __forceinline__ void chol_invert32(float* __restrict__ X, int o, int lane, const float (&a)[32], float my_rs) {
+  constexpr int SB = 32;
+  constexpr unsigned FULL = 0xffffffffu;
+  float x[SB];
+#pragma unroll
+  for (int i = 0; i < SB; ++i) x[i] = (i == lane) ? 1.f : 0.f;
+#pragma unroll
+  for (int i = 0; i < SB; ++i) {
+    x[i] *= __shfl_sync(FULL, my_rs, i);
+#pragma unroll
+    for (int i2 = i + 1; i2 < SB; ++i2) x[i2] = fmaf(-__shfl_sync(FULL, a[i], i2), x[i], x[i2]);
+  }
+#pragma unroll
+  for (int k = 0; k < SB; ++k) X[(o + k) * LDT + o + lane] = (k >= lane) ? x[k] : 0.f;
+}
+
+// Factor the 64x64 SPD tile D (lower triangle; identity-padded by the caller when the panel is narrower) in place
+// and build X = inv(L), by 256 threads: two 32x32 register factorisations on warp 0 (above), the 32x32 panel between
+// them by substitution on warp 1 WHILE warp 0 inverts the first block (from the registers it factored in), the trailing update and the off-diagonal block
+// of the inverse (X10 = -X11 L10 X00) on all warps.  7 barriers.  Returns false on a non-positive pivot.
+__device__ __forceinline__ bool chol_factor_invert64(float* __restrict__ D, float* __restrict__ X,
+                                                     float* __restrict__ rinv, int* __restrict__ s_fail) {
+  constexpr int H = 32;
+  const int tid = threadIdx.x, lane = tid & 31;
+  // the warp index through a shuffle: tells the compiler it is warp-uniform, so the shuffles inside the per-warp
+  // roles below are not each wrapped in a WARPSYNC / reconvergence sequence
+  const int wid = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  for (int i = tid; i < NB * NB; i += 256) X[(i >> 6) * LDT + (i & 63)] = 0.f;
+  if (tid == 0) *s_fail = 0;
+  __syncthreads();
+  float a[H], my_rs = 0.f;                 // warp 0: row of L00 / L11; warp 1: row of the panel
+  if (wid == 0) {
+    if (!chol_factor32(D, rinv, 0, lane, a, my_rs) && lane == 0) *s_fail = 1;
   }
   __syncthreads();
-#pragma unroll 1
-  for (int b = 0; b < NB / SB; ++b) {
-    const int o = b * SB;
-    if (wid == 0) {
-      // ---- 16x16 diagonal block: lane l < 16 owns row l
-      const int l = lane & 15;
-      float a[SB];
+  if (*s_fail) return false;
+  if (wid == 0) {
+    chol_invert32(X, 0, lane, a, my_rs);   // underneath the panel substitution of warp 1
+  } else if (wid == 1) {
+    // panel: row r = 32 + lane of L10 = A10 * L00^-T by forward substitution (right-looking, broadcast reads of L00)
 #pragma unroll
-      for (int k = 0; k < SB; ++k) a[k] = L[o + l][o + k];      // upper triangle is zero (kept so below)
-      bool bad = false;
+    for (int c = 0; c < H; ++c) a[c] = D[(H + lane) * LDT + c];
 #pragma unroll
-      for (int j = 0; j < SB; ++j) {
-        const float d = __shfl_sync(0xffffffffu, a[j], j);
-        if (!(d > 0.f)) bad = true;
-        float rs = rsqrtf(d);
-        rs = rs * (1.5f - 0.5f * d * rs * rs);
-        a[j] = (l == j) ? d * rs : a[j] * rs;                    // L[l][j] for l >= j
+    for (int c = 0; c < H; ++c) {
+      a[c] *= rinv[c];
 #pragma unroll
-        for (int k = j + 1; k < SB; ++k) {
-          const float lkj = __shfl_sync(0xffffffffu, a[j], k);   // L[k][j]
-          a[k] -= a[j] * lkj;      // unconditional: entries above the diagonal (l < k) become don't-care values
-                                  // (never read by another lane, masked at the store) and a[] stays in registers
-        }
-      }
-      // ---- inverse: lane c < 16 owns column c of Xd; L[i][k] comes from lane i
-      float x[SB];
-#pragma unroll
-      for (int i = 0; i < SB; ++i) {
-        float sacc = (i == l) ? 1.f : 0.f;
-#pragma unroll
-        for (int k = 0; k < i; ++k) sacc -= __shfl_sync(0xffffffffu, a[k], i) * x[k];
-        x[i] = sacc / __shfl_sync(0xffffffffu, a[i], i);
-      }
-      if (lane < SB) {
-#pragma unroll
-        for (int k = 0; k < SB; ++k) {                           // unconditional stores: selects, not branches,
-          L[o + l][o + k] = (k <= l) ? a[k] : 0.f;               // so the arrays stay in registers
-          X[o + k][o + l] = (k >= l) ? x[k] : 0.f;
-        }
-        if (bad) s_fail = 1;
-      }
+      for (int c2 = c + 1; c2 < H; ++c2) a[c2] = fmaf(-a[c], D[c2 * LDT + c], a[c2]);
     }
-    __syncthreads();
-    if (s_fail) return false;
-    const int below = NB - o - SB;           // rows under the diagonal block
-    if (below > 0) {
-      // ---- panel: L21 = A21 * Xd^T  (below x 16 outputs, <= 3 per thread)
-      float outv[3];
 #pragma unroll
-      for (int q = 0; q < 3; ++q) {
-        const int idx = tid + 256 * q;
-        float sacc = 0.f;
-        if (idx < below * SB) {
-          const int r = o + SB + idx / SB, c = idx % SB;
-          for (int k = 0; k <= c; ++k) sacc += L[r][o + k] * X[o + c][o + k];
+    for (int c = 0; c < H; ++c) D[(H + lane) * LDT + c] = a[c];
+  }
+  __syncthreads();
+  {
+    // trailing update D11 -= L10 L10^T: thread -> row r, 4 columns; blocks above the diagonal are skipped
+    const int r = tid >> 3, c0 = (tid & 7) * 4;
+    if (c0 <= r) {
+      float s[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int k = 0; k < H; k += 4) {
+        const float4 av = *reinterpret_cast<const float4*>(D + (H + r) * LDT + k);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float4 bv = *reinterpret_cast<const float4*>(D + (H + c0 + j) * LDT + k);
+          s[j] = fmaf(av.x, bv.x, s[j]); s[j] = fmaf(av.y, bv.y, s[j]);
+          s[j] = fmaf(av.z, bv.z, s[j]); s[j] = fmaf(av.w, bv.w, s[j]);
         }
-        outv[q] = sacc;
       }
-      __syncthreads();
 #pragma unroll
-      for (int q = 0; q < 3; ++q) {
-        const int idx = tid + 256 * q;
-        if (idx < below * SB) L[o + SB + idx / SB][o + idx % SB] = outv[q];
-      }
-      __syncthreads();
-      // ---- trailing update of the lower triangle: A22[r][c] -= L21[r][:] . L21[c][:]
-#pragma unroll 1
-      for (int idx = tid; idx < below * below; idx += 256) {
-        const int r = idx / below, c = idx - r * below;
-        if (c > r) continue;
-        float sacc = 0.f;
-#pragma unroll
-        for (int k = 0; k < SB; ++k) sacc += L[o + SB + r][o + k] * L[o + SB + c][o + k];
-        L[o + SB + r][o + SB + c] -= sacc;
-      }
-      __syncthreads();
+      for (int j = 0; j < 4; ++j) D[(H + r) * LDT + H + c0 + j] -= s[j];
     }
   }
-  // ---- inv(L): X_ij = -X_ii * sum_{k=j}^{i-1} L_ik X_kj for block distance 1, 2, 3
-#pragma unroll 1
-  for (int dist = 1; dist < NB / SB; ++dist) {
-    const int nblk = NB / SB - dist;
-    const int r = tid / SB, c = tid % SB;
-#pragma unroll 1
-    for (int q = 0; q < nblk; ++q) {         // block (i = q + dist, j = q): one output per thread
-      const int i = q + dist, j = q;
-      float sacc = 0.f;
-#pragma unroll 1
-      for (int k = j; k < i; ++k)
-#pragma unroll
-        for (int t = 0; t < SB; ++t) sacc += L[i * SB + r][k * SB + t] * X[k * SB + t][j * SB + c];
-      Tm[q][r][c] = sacc;
+  __syncthreads();
+  if (wid == 0) {
+    if (!chol_factor32(D, rinv, H, lane, a, my_rs) && lane == 0) *s_fail = 1;
+    chol_invert32(X, H, lane, a, my_rs);
+  } else {
+    // Y = L10 * X00 (32x32, X00 lower) into the X10 block, by warps 1..7
+    for (int idx = tid - 32; idx < 256; idx += 224) {
+      const int r = idx >> 3, c0 = (idx & 7) * 4;
+      float s[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 8
+      for (int k = 0; k < H; ++k) {
+        const float l = D[(H + r) * LDT + k];
+        const float4 xv = *reinterpret_cast<const float4*>(X + k * LDT + c0);
+        s[0] = fmaf(l, xv.x, s[0]); s[1] = fmaf(l, xv.y, s[1]); s[2] = fmaf(l, xv.z, s[2]); s[3] = fmaf(l, xv.w, s[3]);
+      }
+      *reinterpret_cast<float4*>(X + (H + r) * LDT + c0) = make_float4(s[0], s[1], s[2], s[3]);
     }
-    __syncthreads();
-#pragma unroll 1
-    for (int q = 0; q < nblk; ++q) {
-      const int i = q + dist, j = q;
-      float sacc = 0.f;
-#pragma unroll 4
-      for (int t = 0; t <= r; ++t) sacc += X[i * SB + r][i * SB + t] * Tm[q][t][c];
-      X[i * SB + r][j * SB + c] = -sacc;
-    }
-    __syncthreads();
   }
+  __syncthreads();
+  if (*s_fail) return false;
+  {
+    // X10 = -X11 * Y (X11 lower: k <= r)
+    const int r = tid >> 3, c0 = (tid & 7) * 4;
+    float s[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 8
+    for (int k = 0; k < H; ++k) {
+      const float xr = X[(H + r) * LDT + H + k];
+      const float4 yv = *reinterpret_cast<const float4*>(X + (H + k) * LDT + c0);
+      s[0] = fmaf(xr, yv.x, s[0]); s[1] = fmaf(xr, yv.y, s[1]); s[2] = fmaf(xr, yv.z, s[2]); s[3] = fmaf(xr, yv.w, s[3]);
+    }
+    __syncthreads();
+    *reinterpret_cast<float4*>(X + (H + r) * LDT + c0) = make_float4(-s[0], -s[1], -s[2], -s[3]);
+  }
+  __syncthreads();
   return true;
 }
 
-// write L11 (lower incl. diagonal) into A and inv(L11) into Linv (dense NB x NB, zero upper)
-__device__ __forceinline__ void chol_store_diag(float* __restrict__ A, int lda, int p0, int nb, float (*L)[NB + 1],
-                                                float (*X)[NB + 1], float* __restrict__ Linv) {
-  for (int i = threadIdx.x; i < NB * NB; i += 256) {
-    const int r = i / NB, c = i % NB;
-    if (r < nb && c <= r) A[(int64_t)(p0 + r) * lda + p0 + c] = L[r][c];
-    Linv[i] = X[r][c];
+// global (row-major, leading dimension lda, 64-float aligned columns) -> shared tile, 4 floats per thread and step
+//   mode 0: rectangular rows [row0, row0 + nrows) x cols [col0, col0 + ncols), zero elsewhere
+//   mode 1: lower triangle of the diagonal tile, identity where r >= nrows or c >= ncols (narrow last panel)
+__device__ __forceinline__ void chol_load_tile(float* __restrict__ T, const float* __restrict__ A, int lda, int row0,
+                                               int col0, int nrows, int ncols, int mode) {
+  for (int i = threadIdx.x; i < NB * (NB / 4); i += 256) {
+    const int r = i >> 4, c = (i & 15) * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < nrows) v = *reinterpret_cast<const float4*>(A + (int64_t)(row0 + r) * lda + col0 + c);
+    float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int cc = c + q;
+      if (mode == 0) {
+        if (cc >= ncols) e[q] = 0.f;
+      } else {
+        if (r >= nrows || cc >= ncols) e[q] = (r == cc) ? 1.f : 0.f;
+        else if (cc > r) e[q] = 0.f;
+      }
+    }
+    *reinterpret_cast<float4*>(T + r * LDT + c) = make_float4(e[0], e[1], e[2], e[3]);
   }
 }
 
-// diagonal block of panel p0: factor + invert (one CTA)
+// ONE launch per panel on the critical path.  CTA 0 owns the diagonal tile, CTA i >= 1 the i-th 64-row tile below it
+// (the last one includes the y row).  Every CTA
+//   1. applies the PREVIOUS panel's trailing update to what it needs of this panel's column — the diagonal tile and
+//      its own row tile:  D -= Lp_d Lp_d^T,  R -= Lp_r Lp_d^T  (the bulk update of the previous panel, which runs
+//      underneath this kernel, leaves this column alone),
+//   2. factors the diagonal tile and inverts the factor — redundantly in every CTA, so that there is no second
+//      launch and no dependency between "diag" and "trsm" (identical inputs and code: identical results),
+//   3. forms its rows of L21 = R inv(L11)^T as one 64^3 product and stores them.
+// CTA 0 stores L11 and inv(L11) (for the back substitution) instead of step 3.
 __global__ void __launch_bounds__(256)
-chol_diag_kernel(float* __restrict__ A, int lda, int n, int p0, float* __restrict__ Linv, int* __restrict__ meta) {
-  __shared__ float L[NB][NB + 1];
-  __shared__ float X[NB][NB + 1];
+chol_panel_kernel(float* __restrict__ A, int lda, int n, int p0, int has_prev, float* __restrict__ Linv,
+                  int* __restrict__ meta) {
+  extern __shared__ __align__(16) float chol_sm[];
+  float* Pd = chol_sm;               // previous panel's L, rows of the diagonal tile; later X = inv(L11)
+  float* Pr = chol_sm + TILE;        // previous panel's L, rows of this CTA's tile
+  float* D = chol_sm + 2 * TILE;
+  float* R = chol_sm + 3 * TILE;
+  __shared__ float rinv[NB];
+  __shared__ int s_fail;
   if (meta[1]) return;
-  const int nb = min(NB, n - p0);
-  for (int i = threadIdx.x; i < NB * NB; i += 256) {
-    const int r = i / NB, c = i % NB;
-    L[r][c] = (r < nb && c <= r) ? A[(int64_t)(p0 + r) * lda + p0 + c] : 0.f;
-  }
-  __syncthreads();
-  if (!chol_factor_invert(L, X, nb)) { if (threadIdx.x == 0) meta[1] = 1; return; }
-  chol_store_diag(A, lda, p0, nb, L, X, Linv);
-}
-
-// rows [p0+nb, n] (incl. the y row) in tiles of 64: L21 = A21 * inv(L11)^T
-__global__ void __launch_bounds__(256)
-chol_trsm_kernel(float* __restrict__ A, int lda, int n, int p0, const float* __restrict__ Linv,
-                 const int* __restrict__ meta) {
-  __shared__ float Xi[NB][NB + 1];   // inv(L11), lower
-  __shared__ float T[NB][NB + 1];    // A21 tile
-  if (meta[1]) return;
-  const int nb = min(NB, n - p0);
-  const int r0 = p0 + nb + blockIdx.x * NB;
-  const int nr = min(NB, n + 1 - r0);
   const int tid = threadIdx.x;
-  for (int i = tid; i < NB * NB; i += 256) {
-    const int r = i / NB, c = i % NB;
-    Xi[r][c] = Linv[i];
-    T[r][c] = (r < nr && c < nb) ? A[(int64_t)(r0 + r) * lda + p0 + c] : 0.f;
+  const int nb = min(NB, n - p0);
+  const bool diag_cta = blockIdx.x == 0;
+  const int r0 = p0 + nb + ((int)blockIdx.x - 1) * NB;
+  const int nr = diag_cta ? 0 : min(NB, n + 1 - r0);
+  chol_load_tile(D, A, lda, p0, p0, nb, nb, 1);
+  if (!diag_cta) chol_load_tile(R, A, lda, r0, p0, nr, nb, 0);
+  if (has_prev) {
+    chol_load_tile(Pd, A, lda, p0, p0 - NB, nb, NB, 0);
+    if (!diag_cta) chol_load_tile(Pr, A, lda, r0, p0 - NB, nr, NB, 0);
   }
   __syncthreads();
-  // out[r][c] = sum_{k <= c} T[r][k] * Xi[c][k];  thread: 4 rows x 4 cols
   const int tx = tid & 15, ty = tid >> 4;
+  if (has_prev) {
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    tile_mma(acc, Pd, Pd, ty, tx);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int r = ty + 16 * i, c = tx + 16 * j;
+        if (c <= r) D[r * LDT + c] -= acc[i][j];       // rows / columns >= nb of Pd are zero: the padding survives
+      }
+    if (!diag_cta) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+      tile_mma(acc, Pr, Pd, ty, tx);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) R[(ty + 16 * i) * LDT + tx + 16 * j] -= acc[i][j];
+    }
+    __syncthreads();                 // Pd is dead from here on: it becomes X
+  }
+  float* X = Pd;
+  if (!chol_factor_invert64(D, X, rinv, &s_fail)) {
+    if (tid == 0) meta[1] = 1;
+    return;
+  }
+  if (diag_cta) {
+    for (int i = tid; i < NB * NB; i += 256) {
+      const int r = i >> 6, c = i & 63;
+      if (r < nb && c <= r) A[(int64_t)(p0 + r) * lda + p0 + c] = D[r * LDT + c];
+      Linv[i] = X[r * LDT + c];
+    }
+    return;
+  }
   float acc[4][4];
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-#pragma unroll 8
-  for (int k = 0; k < NB; ++k) {
-    float av[4], bv[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) { av[i] = T[ty + 16 * i][k]; bv[i] = Xi[tx + 16 * i][k]; }
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) acc[i][j] += av[i] * bv[j];
-  }
+  tile_mma(acc, R, X, ty, tx);       // out[r][c] = sum_k R[r][k] X[c][k]  (X lower: terms with k > c are zero)
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -224,56 +317,35 @@ chol_trsm_kernel(float* __restrict__ A, int lda, int n, int p0, const float* __r
     }
 }
 
-// trailing update: tile (ti, tj), tj <= ti, of rows/cols starting at q0 = p0 + nb.
-// mode 0: every tile; mode 1: the first tile column only (tj = 0: what the NEXT panel's factorisation needs);
-// mode 2: every tile with tj >= 1 (runs on the look-ahead stream under the next panel's diag + trsm).
+// Bulk of panel p0's trailing update: tile (ti, tj), 1 <= tj <= ti, of the rows / columns starting at q0 = p0 + nb.
+// The first tile column (tj = 0) is the next panel's and is updated by that panel's chol_panel_kernel.
 __global__ void __launch_bounds__(256)
-chol_syrk_kernel(float* __restrict__ A, int lda, int n, int p0, const int* __restrict__ meta, int mode) {
-  __shared__ float As[NB][NB + 1];
-  __shared__ float Bs[NB][NB + 1];
+chol_syrk_kernel(float* __restrict__ A, int lda, int n, int p0, const int* __restrict__ meta) {
+  __shared__ __align__(16) float As[TILE];
+  __shared__ __align__(16) float Bs[TILE];
   if (meta[1]) return;
-  // linear tile index -> (ti, tj) with tj <= ti
-  int ti, tj;
-  if (mode == 1) {
-    ti = blockIdx.x;
-    tj = 0;
-  } else {
-    const int t = blockIdx.x;
-    ti = (int)((sqrtf(8.f * t + 1.f) - 1.f) * 0.5f);
-    while ((ti + 1) * (ti + 2) / 2 <= t) ++ti;
-    while (ti * (ti + 1) / 2 > t) --ti;
-    tj = t - ti * (ti + 1) / 2;
-    if (mode == 2) { ++ti; ++tj; }
-  }
+  const int t = blockIdx.x;
+  int ti = (int)((sqrtf(8.f * t + 1.f) - 1.f) * 0.5f);
+  while ((ti + 1) * (ti + 2) / 2 <= t) ++ti;
+  while (ti * (ti + 1) / 2 > t) --ti;
+  int tj = t - ti * (ti + 1) / 2;
+  ++ti; ++tj;
   const int nb = min(NB, n - p0);
   const int q0 = p0 + nb;
   const int ri = q0 + ti * NB, rj = q0 + tj * NB;
   const int nri = min(NB, n + 1 - ri);        // rows may include the y row
   const int nrj = min(NB, n - rj);            // columns never do
-  if (nrj <= 0) return;
-  const int tid = threadIdx.x;
-  for (int i = tid; i < NB * NB; i += 256) {
-    const int r = i / NB, c = i % NB;
-    As[r][c] = (r < nri && c < nb) ? A[(int64_t)(ri + r) * lda + p0 + c] : 0.f;
-    Bs[r][c] = (r < nrj && c < nb) ? A[(int64_t)(rj + r) * lda + p0 + c] : 0.f;
-  }
+  if (nrj <= 0 || nri <= 0) return;
+  chol_load_tile(As, A, lda, ri, p0, nri, nb, 0);
+  chol_load_tile(Bs, A, lda, rj, p0, nrj, nb, 0);
   __syncthreads();
-  const int tx = tid & 15, ty = tid >> 4;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   float acc[4][4];
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-#pragma unroll 8
-  for (int k = 0; k < NB; ++k) {
-    float av[4], bv[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) { av[i] = As[ty + 16 * i][k]; bv[i] = Bs[tx + 16 * i][k]; }
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) acc[i][j] += av[i] * bv[j];
-  }
+  tile_mma(acc, As, Bs, ty, tx);
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -396,50 +468,47 @@ int ba_chol_solve(const BADev& p, float* A, int lda, float* xbuf, cudaStream_t s
   float* acc = z + n;
   float* sol = acc + n;
   float* Linv = sol + n + (64 - (3 * n) % 64) % 64;     // 256-byte aligned panels
-  // look-ahead pays once the trailing update is big enough to hide a diag + trsm under it (>= 16 panels)
+  {
+    // per device and cheap: once per solve, not per panel
+    const cudaError_t e = cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanelSmemBytes);
+    if (e != cudaSuccess) {
+      set_error("ba_chol_solve: cannot reserve %d bytes of shared memory: %s", kPanelSmemBytes, cudaGetErrorString(e));
+      return 1;
+    }
+  }
+  // look-ahead pays once the trailing update is big enough to hide the next panel under it (>= 16 panels)
   CholLookahead* la = (!dbg && !no_la && n >= 16 * NB) ? chol_lookahead() : nullptr;
-  bool rest_pending = false;
-  int slot = 0;
-  cudaStream_t crit = st;                          // diag / trsm / first trailing column
+  cudaStream_t crit = st;                          // the panel kernels
   if (la) {
     crit = la->side;
     cudaEventRecord(la->fork, st);
     cudaStreamWaitEvent(crit, la->fork, 0);
   }
-  for (p0 = 0; p0 < n; p0 += NB) {
+  // panel(p) = previous panel's update of column p + factor + L21;  bulk(p) = trailing update of columns >= p + 2.
+  // bulk(q) writes column p for every q <= p - 2, so panel(p) waits for bulk(p - 2) and runs underneath bulk(p - 1);
+  // bulk(p) needs panel(p).  Without look-ahead everything is on one stream in that order.
+  int np = 0;
+  for (p0 = 0; p0 < n; p0 += NB, ++np) {
     const int nb = n - p0 < NB ? n - p0 : NB;
     const int rows = n + 1 - p0 - nb;            // rows below the panel, incl. the y row
     const int T = (rows + NB - 1) / NB;
     float* Li = Linv + (int64_t)(p0 / NB) * NB * NB;
-    chol_diag_kernel<<<1, 256, 0, crit>>>(A, lda, n, p0, Li, p.meta);
+    const int slot = np & 1;
+    if (la && np >= 2) cudaStreamWaitEvent(crit, la->rest_done[slot], 0);     // bulk(np - 2): same slot, recorded earlier
+    chol_panel_kernel<<<1 + T, 256, kPanelSmemBytes, crit>>>(A, lda, n, p0, p0 > 0 ? 1 : 0, Li, p.meta);
     ++launches;
-    CHOL_DBG("diag");
-    chol_trsm_kernel<<<T, 256, 0, crit>>>(A, lda, n, p0, Li, p.meta);
-    ++launches;
-    CHOL_DBG("trsm");
+    CHOL_DBG("panel");
     const int Tc = (n - p0 - nb + NB - 1) / NB;  // column tiles of the trailing matrix
-    if (Tc > 0) {
-      if (!la) {
-        chol_syrk_kernel<<<T * (T + 1) / 2, 256, 0, st>>>(A, lda, n, p0, p.meta, 0);
-        ++launches;
-        CHOL_DBG("syrk");
-      } else {
-        cudaEventRecord(la->trsm_done[slot], crit);
-        // the previous panel's bulk update also wrote this panel's first trailing column: order the two writers
-        if (rest_pending) cudaStreamWaitEvent(crit, la->rest_done[slot ^ 1], 0);
-        chol_syrk_kernel<<<T, 256, 0, crit>>>(A, lda, n, p0, p.meta, 1);
-        ++launches;
-        rest_pending = false;
-        if (T > 1) {
-          cudaStreamWaitEvent(st, la->trsm_done[slot], 0);
-          chol_syrk_kernel<<<(T - 1) * T / 2, 256, 0, st>>>(A, lda, n, p0, p.meta, 2);
-          ++launches;
-          cudaEventRecord(la->rest_done[slot], st);
-          rest_pending = true;
-        }
-        slot ^= 1;
-      }
+    if (la) {
+      cudaEventRecord(la->trsm_done[slot], crit);
+      cudaStreamWaitEvent(st, la->trsm_done[slot], 0);
     }
+    if (Tc > 1 && T > 1) {
+      chol_syrk_kernel<<<(T - 1) * T / 2, 256, 0, st>>>(A, lda, n, p0, p.meta);
+      ++launches;
+      CHOL_DBG("syrk");
+    }
+    if (la) cudaEventRecord(la->rest_done[slot], st);
   }
   if (la) {                                       // join: the critical-path stream's work is visible to the caller's stream
     cudaEventRecord(la->fork, crit);
