@@ -78,6 +78,9 @@ ba_prep_kernel(const __grid_constant__ BADev p) {
   }
 }
 
+constexpr int kKeyScanDirect = 8192;   // up to this many keys ba_prefix_kernel scans the histogram itself
+constexpr int kKeyScanBlock = 4096;    // keys per CTA of the blocked scan (1024 threads x 4)
+
 // One CTA: (1) exclusive popcount prefix over the bitmap words, list of set bits (kx), total M;
 // (2) exclusive scans of the key histogram: edge offsets `off` and warp-task offsets `toff`
 // (a task = up to 32 edges of one key).
@@ -130,13 +133,16 @@ ba_prefix_kernel(const __grid_constant__ BADev p) {
   }
   if (tid == 0) p.meta[0] = (int)(s_carry < p.Mmax ? s_carry : p.Mmax);
 
-  // ---- key histogram scans
+  // ---- key histogram scans.  Many keys (global BA: K = (N+1)^2 ~ 10^6): the histogram itself was reduced per
+  // 4096-key block by ba_keysum_kernel; only the block sums are scanned here, ba_keyscan_kernel finishes the job.
+  const bool blocked = p.K > kKeyScanDirect;
+  const int nscan = blocked ? (p.K + kKeyScanBlock - 1) / kKeyScanBlock : p.K;
   if (tid == 0) s_carry = 0;
   __syncthreads();
-  for (int base = 0; base < p.K; base += 1024) {
+  for (int base = 0; base < nscan; base += 1024) {
     const int k = base + tid;
-    const int c = (k < p.K) ? p.hist[k] : 0;
-    const int t = (c + 31) >> 5;
+    const int c = (k < nscan) ? (blocked ? p.ksum[2 * k] : p.hist[k]) : 0;
+    const int t = blocked ? ((k < nscan) ? p.ksum[2 * k + 1] : 0) : (c + 31) >> 5;
     int inc = c, inc2 = t;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -157,9 +163,14 @@ ba_prefix_kernel(const __grid_constant__ BADev p) {
       s_warp[lane] = x; s_warp2[lane] = y;
     }
     __syncthreads();
-    if (k < p.K) {
-      p.off[k] = s_carry + (wid ? s_warp[wid - 1] : 0) + inc - c;
-      p.toff[k] = s_carry2 + (wid ? s_warp2[wid - 1] : 0) + inc2 - t;
+    if (k < nscan) {
+      const int e0 = s_carry + (wid ? s_warp[wid - 1] : 0) + inc - c;
+      const int e1 = s_carry2 + (wid ? s_warp2[wid - 1] : 0) + inc2 - t;
+      if (blocked) { p.ksum[2 * k] = e0; p.ksum[2 * k + 1] = e1; }
+      else {
+        p.off[k] = e0; p.toff[k] = e1;
+        for (int i = 0; i < t; ++i) p.tkey[e1 + i] = k;     // task -> key, so the assembly does not search toff
+      }
     }
     __syncthreads();
     if (tid == 0) { s_carry += s_warp[31]; s_carry2 += s_warp2[31]; }
@@ -169,6 +180,77 @@ ba_prefix_kernel(const __grid_constant__ BADev p) {
     p.off[p.K] = s_carry;
     p.toff[p.K] = s_carry2;
     p.meta[2] = s_carry2;  // number of warp tasks
+  }
+}
+
+// Blocked form of the key scans (K > kKeyScanDirect): sums of (edge count, warp-task count) per block of 4096 keys ..
+__global__ void __launch_bounds__(1024)
+ba_keysum_kernel(const __grid_constant__ BADev p) {
+  __shared__ int s_a[32], s_b[32];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int k0 = blockIdx.x * kKeyScanBlock + tid * 4;
+  int a = 0, b = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = (k0 + i < p.K) ? p.hist[k0 + i] : 0;
+    a += c;
+    b += (c + 31) >> 5;
+  }
+  a = __reduce_add_sync(0xffffffffu, a);
+  b = __reduce_add_sync(0xffffffffu, b);
+  if (lane == 0) { s_a[wid] = a; s_b[wid] = b; }
+  __syncthreads();
+  if (wid == 0) {
+    a = __reduce_add_sync(0xffffffffu, s_a[lane]);
+    b = __reduce_add_sync(0xffffffffu, s_b[lane]);
+    if (lane == 0) { p.ksum[2 * blockIdx.x] = a; p.ksum[2 * blockIdx.x + 1] = b; }
+  }
+}
+
+// .. and, after ba_prefix_kernel turned the block sums into block offsets, the scan inside every block.
+__global__ void __launch_bounds__(1024)
+ba_keyscan_kernel(const __grid_constant__ BADev p) {
+  __shared__ int s_warp[32], s_warp2[32];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int k0 = blockIdx.x * kKeyScanBlock + tid * 4;
+  int c[4], t[4], a = 0, b = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    c[i] = (k0 + i < p.K) ? p.hist[k0 + i] : 0;
+    t[i] = (c[i] + 31) >> 5;
+    a += c[i];
+    b += t[i];
+  }
+  int inc = a, inc2 = b;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int x = __shfl_up_sync(0xffffffffu, inc, o);
+    const int y = __shfl_up_sync(0xffffffffu, inc2, o);
+    if (lane >= o) { inc += x; inc2 += y; }
+  }
+  if (lane == 31) { s_warp[wid] = inc; s_warp2[wid] = inc2; }
+  __syncthreads();
+  if (wid == 0) {
+    int x = s_warp[lane], y = s_warp2[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int x1 = __shfl_up_sync(0xffffffffu, x, o);
+      const int y1 = __shfl_up_sync(0xffffffffu, y, o);
+      if (lane >= o) { x += x1; y += y1; }
+    }
+    s_warp[lane] = x; s_warp2[lane] = y;
+  }
+  __syncthreads();
+  int e0 = p.ksum[2 * blockIdx.x] + (wid ? s_warp[wid - 1] : 0) + inc - a;
+  int e1 = p.ksum[2 * blockIdx.x + 1] + (wid ? s_warp2[wid - 1] : 0) + inc2 - b;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if (k0 + i < p.K) {
+      p.off[k0 + i] = e0; p.toff[k0 + i] = e1;
+      for (int q = 0; q < t[i]; ++q) p.tkey[e1 + q] = k0 + i;
+    }
+    e0 += c[i];
+    e1 += t[i];
   }
 }
 
@@ -232,13 +314,9 @@ ba_assemble_kernel(const __grid_constant__ BADev p) {
   const int lane = threadIdx.x & 31;
   const int task = blockIdx.x * kAsmWarps + (threadIdx.x >> 5);
   if (task >= p.meta[2]) return;
-  // segment of this task: last key s with toff[s] <= task (empty keys have toff[s] == toff[s+1])
-  int lo = 0, hi = p.K;  // invariant: toff[lo] <= task < toff[hi]
-  while (hi - lo > 1) {
-    const int mid = (lo + hi) >> 1;
-    if (p.toff[mid] <= task) lo = mid; else hi = mid;
-  }
-  const int key = lo;
+  // the task's pose-pair key: written next to the scan of the task offsets (a binary search over toff here was ~20
+  // dependent loads per warp at the 10^6 keys of a global BA)
+  const int key = p.tkey[task];
   const int chunk = task - p.toff[key];
   const int pos = p.off[key] + chunk * 32 + lane;
   const bool act = pos < p.off[key + 1];
@@ -292,8 +370,9 @@ ba_assemble_kernel(const __grid_constant__ BADev p) {
         for (int a = 0; a < 6; ++a) atomicAdd(&et[6 * jx + a], ej[a]);
       }
     } else {
-      // block-E path: the edge's two E entries (w.r.t. its source and target pose) stay per edge
-      float4* ee = reinterpret_cast<float4*>(p.Ee + (int64_t)p.perm[pos] * 12);
+      // block-E path: the edge's two E entries (w.r.t. its source and target pose) stay per edge, stored in the
+      // (source frame, slot) order the Schur kernel walks them in
+      float4* ee = reinterpret_cast<float4*>(p.Ee + (int64_t)p.finv[p.perm[pos]] * 12);
       ee[0] = make_float4(ei[0], ei[1], ei[2], ei[3]);
       ee[1] = make_float4(ei[4], ei[5], ej[0], ej[1]);
       ee[2] = make_float4(ej[2], ej[3], ej[4], ej[5]);
@@ -301,7 +380,7 @@ ba_assemble_kernel(const __grid_constant__ BADev p) {
     atomicAdd(&p.C[k], cc);
     atomicAdd(&p.u[k], uu);
   } else if (act && !p.Et) {
-    float4* ee = reinterpret_cast<float4*>(p.Ee + (int64_t)p.perm[pos] * 12);
+    float4* ee = reinterpret_cast<float4*>(p.Ee + (int64_t)p.finv[p.perm[pos]] * 12);
     ee[0] = ee[1] = ee[2] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   if (ix < 0 && jx < 0) return;  // both poses fixed: no pose blocks (warp-uniform)
@@ -668,6 +747,8 @@ int64_t ba_carve(BADev& p, char* base, int64_t E, int64_t npatches, int N, int e
   p.prefix = (int*)take(W * 4);
   p.off = (int*)take((K + 1) * 4);
   p.toff = (int*)take((K + 1) * 4);
+  p.tkey = (int*)take((E / 32 + K + 2) * 4);
+  p.ksum = (int*)take((2 * ((K + kKeyScanBlock - 1) / kKeyScanBlock) + 2) * 4);
   p.perm = (int*)take(E * 4);
   p.ekey = (int*)take(E * 4);
   p.kx = (int64_t*)take(Mmax * 8);
@@ -771,10 +852,13 @@ static int ba_forward_impl(int mode, float* poses, float* patches, const float* 
   if (mode != 2) {
     cudaMemsetAsync(p.bitmap, 0, reinterpret_cast<char*>(p.meta) + 64 - reinterpret_cast<char*>(p.bitmap), st);
     ba_prep_kernel<<<egrid, 256, 0, st>>>(p);
+    const int kblocks = p.K > kKeyScanDirect ? (p.K + kKeyScanBlock - 1) / kKeyScanBlock : 0;
+    if (kblocks) ba_keysum_kernel<<<kblocks, 1024, 0, st>>>(p);
     ba_prefix_kernel<<<1, 1024, 0, st>>>(p);
+    if (kblocks) ba_keyscan_kernel<<<kblocks, 1024, 0, st>>>(p);
     if (check_launch("ba_prefix")) return 1;
     ba_scatter_kernel<<<egrid, 256, 0, st>>>(p);
-    note_launches(3);
+    note_launches(kblocks ? 5 : 3);
   }
   if (eff_impl) {
     if (mode == 1) return check_launch("ba_prepare");

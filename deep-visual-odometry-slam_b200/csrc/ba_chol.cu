@@ -20,6 +20,7 @@
 // A non-positive pivot sets meta[1]; every later kernel returns early and dX is zeroed.
 #include "se3.cuh"
 #include "ba_internal.cuh"
+#include "sm100.cuh"
 #include <stdlib.h>
 
 #ifndef DPVO_CHOL_NOALLOC_MAX_N
@@ -355,6 +356,288 @@ chol_syrk_kernel(float* __restrict__ A, int lda, int n, int p0, const int* __res
     }
 }
 
+// The same bulk update as ONE persistent CTA per SM over 128x128 tiles, 8x8 outputs per thread (rows ty + 16 i,
+// columns tx + 16 j): per 4 k-steps a thread issues 16 LDS.128 for 256 FMAs (the 64x64 kernel: 8 for 64, LDS issue and
+// FMA issue neck and neck) and the L21 rows cross L2 -> SM half as often.  The next tile's rows arrive by cp.async in a
+// second buffer while this one is multiplied; the result leaves as fire-and-forget reductions (RED.ADD.F32 of -acc:
+// every element has exactly one writer per launch, so the sum is the same single rounding as load-subtract-store and
+// no thread waits for the old value).
+// Why persistent and why 136 KB of shared memory: the factorisation's critical path (chol_panel_kernel, on the
+// high-priority stream) runs UNDERNEATH this kernel and needs a free slot on <= 95 SMs the moment it is launched.  Two
+// buffers make a second bulk CTA impossible on an SM (2 x 136 KB > 227 KB) while one bulk CTA + one panel CTA always fit
+// (136 + 68 KB, 127 + 121 registers x 256 threads) — with short-lived 2-per-SM CTAs of this size the panel kernels
+// queued behind 10 us tiles and the look-ahead was lost.
+// Used while the trailing matrix has at least one 128-tile per SM (ba_chol_solve picks); tile (ti, tj), tj <= ti,
+// starts at row / column c0 + 128 ti / c0 + 128 tj with c0 = p0 + 128 (the 64 columns before c0 are the next panel's).
+constexpr int SB = 128;
+constexpr int kSyrkStage = 2 * SB * LDT;                      // floats: rows of the tile's row block + of its column block
+constexpr int kSyrk128SmemBytes = 2 * kSyrkStage * (int)sizeof(float);
+constexpr int kSyrk128MinTiles = kNumSMs;    // fewer 128-tiles than SMs: the 64x64 kernel spreads the work better
+
+__device__ __forceinline__ void cp_async16(float* dst_smem, const float* src, bool valid) {
+  const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(dst_smem));
+  const int sz = valid ? 16 : 0;             // 0 source bytes: the 16 destination bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+__device__ __forceinline__ uint32_t tf32_rna(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+
+__device__ __forceinline__ void syrk_tile_coords(int t, int& ti, int& tj) {
+  ti = (int)((sqrtf(8.f * t + 1.f) - 1.f) * 0.5f);
+  while ((ti + 1) * (ti + 2) / 2 <= t) ++ti;
+  while (ti * (ti + 1) / 2 > t) --ti;
+  tj = t - ti * (ti + 1) / 2;
+}
+
+// rows [row0, row0 + 128) x the panel's 64 columns -> T (stride LDT); rows past `nrows` are zero-filled
+__device__ __forceinline__ void syrk_issue_rows(float* __restrict__ T, const float* __restrict__ A, int lda, int row0,
+                                                int col0, int nrows) {
+#pragma unroll
+  for (int q = 0; q < SB * (NB / 4) / 256; ++q) {
+    const int i = threadIdx.x + q * 256;
+    const int r = i >> 4, c = (i & 15) * 4;
+    const bool ok = r < nrows;
+    cp_async16(T + r * LDT + c, A + (int64_t)(row0 + (ok ? r : 0)) * lda + col0 + c, ok);
+  }
+}
+
+// 0: split-TF32 tensor-core tiles (default); 1: fp32 FMA tiles (dpvo_chol_bulk_mode, A/B measurements and tests)
+static int g_chol_bulk_mode = 0;
+
+__global__ void __launch_bounds__(256, 2)   // <= 128 registers: a panel CTA (121) must fit beside this one
+chol_syrk128_kernel(float* __restrict__ A, int lda, int n, int p0, int ntiles, const int* __restrict__ meta) {
+  extern __shared__ __align__(16) float syrk_sm[];
+  if (meta[1]) return;
+  const int c0 = p0 + 2 * NB;                 // only full panels have a bulk update
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  int t = blockIdx.x;
+  if (t >= ntiles) return;
+  {
+    int ti, tj;
+    syrk_tile_coords(t, ti, tj);
+    const int ri = c0 + ti * SB, rj = c0 + tj * SB;
+    syrk_issue_rows(syrk_sm, A, lda, ri, p0, min(SB, n + 1 - ri));
+    if (ti != tj) syrk_issue_rows(syrk_sm + SB * LDT, A, lda, rj, p0, min(SB, n - rj));
+    cp_async_commit();
+  }
+  for (int it = 0; t < ntiles; t += gridDim.x, ++it) {
+    float* As = syrk_sm + (it & 1) * kSyrkStage;
+    int ti, tj;
+    syrk_tile_coords(t, ti, tj);
+    const int ri = c0 + ti * SB, rj = c0 + tj * SB;
+    const int nri = min(SB, n + 1 - ri);      // rows may include the y row
+    const int nrj = min(SB, n - rj);          // columns never do (<= 0: the tile holds nothing, e.g. the y row's own column)
+    const float* Bs = (ti == tj) ? As : As + SB * LDT;      // diagonal tile: the same rows on both sides
+    const int tn = t + gridDim.x;
+    if (tn < ntiles) {
+      float* An = syrk_sm + ((it + 1) & 1) * kSyrkStage;
+      int ni, nj;
+      syrk_tile_coords(tn, ni, nj);
+      const int rni = c0 + ni * SB, rnj = c0 + nj * SB;
+      syrk_issue_rows(An, A, lda, rni, p0, min(SB, n + 1 - rni));
+      if (ni != nj) syrk_issue_rows(An + SB * LDT, A, lda, rnj, p0, min(SB, n - rnj));
+      cp_async_commit();
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads();
+    if (nrj > 0) {
+      float acc[8][8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+#pragma unroll 1
+      for (int k = 0; k < NB; k += 4) {
+        float4 a[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a[i] = *reinterpret_cast<const float4*>(As + (ty + 16 * i) * LDT + k);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 b = *reinterpret_cast<const float4*>(Bs + (tx + 16 * j) * LDT + k);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            acc[i][j] = fmaf(a[i].x, b.x, acc[i][j]);
+            acc[i][j] = fmaf(a[i].y, b.y, acc[i][j]);
+            acc[i][j] = fmaf(a[i].z, b.z, acc[i][j]);
+            acc[i][j] = fmaf(a[i].w, b.w, acc[i][j]);
+          }
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int r = ty + 16 * i;
+        if (r >= nri) continue;
+        float* row = A + (int64_t)(ri + r) * lda + rj;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int c = tx + 16 * j;
+          if (c < nrj && (rj + c) <= (ri + r)) atomicAdd(&row[c], -acc[i][j]);   // result unused: RED.ADD.F32
+        }
+      }
+    }
+    __syncthreads();                          // this buffer is the target of the next iteration's prefetch
+  }
+}
+
+// ---- the same tiles on the 5th-generation tensor cores: split-TF32 ("3xTF32") with tcgen05.mma.
+// Every fp32 operand x is split into hi = tf32(x) and lo = tf32(x - hi) (x - hi is exact in fp32), and
+//   a b ~= a_lo b_hi + a_hi b_lo + a_hi b_hi      (the dropped a_lo b_lo term is 2^-22 relative)
+// is accumulated in fp32 in tensor memory, small terms first: 24 UMMA instructions (M128 x N128 x K8) per tile.
+// Measured against numpy float64 at n = 5,994: 5.8e-7 (split) vs 4.4e-7 (fp32 FMA) on the solve.
+// (mma.sync m16n8k8 TF32 was tried first: HMMA.1688.F32.TF32 retires one instruction per ~17 cycles per sub-partition
+//  on this part, so three products cost exactly what the FMA loop costs — the legacy path is no tensor core to speak of.)
+// Pipeline per persistent CTA (one per SM; 128 KB of shared memory keeps a second one out and a panel CTA in):
+//   TMA (128-byte swizzle, zero fill past the last row) brings the 128 x 64 fp32 row blocks of tile t  ->  all threads
+//   split them IN PLACE (hi) and into a second buffer (lo) — element-wise, so the swizzle never matters  ->  one
+//   thread issues the 24 MMAs and commits  ->  as soon as they have read shared memory the TMA of tile t + 1 starts
+//   underneath the epilogue: TMEM -> registers (a thread owns a row, 2 x 32 columns) -> red.global.add.v4.f32.
+constexpr int kUmmaAtomBytes = SB * 128;                   // 128 rows x 32 fp32: one K-atom of an operand (16 KB)
+constexpr int kUmmaOperandBytes = 2 * kUmmaAtomBytes;      // K = 64: two atoms
+constexpr int kSyrkUmmaSmemBytes = 4 * kUmmaOperandBytes + 1024;   // A hi, B hi, A lo, B lo + alignment slack
+constexpr uint32_t kSyrkTmemCols = 128;
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+__global__ void __launch_bounds__(256, 1)
+chol_syrk128_umma_kernel(const __grid_constant__ CUtensorMap tmA, float* __restrict__ A, int lda, int n, int p0,
+                         int ntiles, const int* __restrict__ meta) {
+  using namespace sm100;
+  extern __shared__ uint8_t umma_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(umma_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* a_hi = smem;
+  uint8_t* b_hi = smem + kUmmaOperandBytes;
+  uint8_t* a_lo = smem + 2 * kUmmaOperandBytes;
+  uint8_t* b_lo = smem + 3 * kUmmaOperandBytes;
+  __shared__ uint64_t full, mma_done;
+  __shared__ uint32_t tmem_base_s;
+  if (meta[1]) return;
+  if ((int)blockIdx.x >= ntiles) return;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int c0 = p0 + 2 * NB;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmA);
+      mbar_init(&full, 1);
+      mbar_init(&mma_done, 1);
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc(&tmem_base_s, kSyrkTmemCols);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  auto issue_loads = [&](int t) {              // one thread
+    int ti, tj;
+    syrk_tile_coords(t, ti, tj);
+    const int ri = c0 + ti * SB, rj = c0 + tj * SB;
+    mbar_arrive_expect_tx(&full, (ti == tj ? 1 : 2) * kUmmaOperandBytes);
+    tma_load_2d(a_hi, &tmA, &full, p0, ri);
+    tma_load_2d(a_hi + kUmmaAtomBytes, &tmA, &full, p0 + 32, ri);
+    if (ti != tj) {
+      tma_load_2d(b_hi, &tmA, &full, p0, rj);
+      tma_load_2d(b_hi + kUmmaAtomBytes, &tmA, &full, p0 + 32, rj);
+    }
+  };
+  if (tid == 0) issue_loads(blockIdx.x);
+
+  int it = 0;
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
+    int ti, tj;
+    syrk_tile_coords(t, ti, tj);
+    const int ri = c0 + ti * SB, rj = c0 + tj * SB;
+    const int nri = min(SB, n + 1 - ri);
+    const int nrj = min(SB, n - rj);
+    const bool diag = ti == tj;
+    mbar_wait(&full, it & 1);
+    // hi / lo split, 16 bytes per thread and step (A and, off the diagonal, B are contiguous)
+    {
+      const int nvec = (diag ? 1 : 2) * kUmmaOperandBytes / 16;
+      float4* hi = reinterpret_cast<float4*>(a_hi);
+      float4* lo = reinterpret_cast<float4*>(a_lo);
+      for (int q = tid; q < nvec; q += 256) {
+        const float4 x = hi[q];
+        float4 h, l;
+        h.x = __uint_as_float(tf32_rna(x.x)); l.x = __uint_as_float(tf32_rna(x.x - h.x));
+        h.y = __uint_as_float(tf32_rna(x.y)); l.y = __uint_as_float(tf32_rna(x.y - h.y));
+        h.z = __uint_as_float(tf32_rna(x.z)); l.z = __uint_as_float(tf32_rna(x.z - h.z));
+        h.w = __uint_as_float(tf32_rna(x.w)); l.w = __uint_as_float(tf32_rna(x.w - h.w));
+        hi[q] = h;
+        lo[q] = l;
+      }
+    }
+    fence_proxy_async_smem();                 // generic-proxy writes -> visible to the tensor core's operand reads
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      constexpr uint32_t idesc = instr_desc_tf32(SB, SB);
+      const uint32_t ah = smem_u32(a_hi), al = smem_u32(a_lo);
+      const uint32_t bh = diag ? ah : smem_u32(b_hi), bl = diag ? al : smem_u32(b_lo);
+      uint32_t accf = 0;
+#pragma unroll
+      for (int prod = 0; prod < 3; ++prod) {
+        const uint32_t pa = prod == 0 ? al : ah;
+        const uint32_t pb = prod == 1 ? bl : bh;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          const uint32_t off = (ks >> 2) * kUmmaAtomBytes + (ks & 3) * 32;
+          mma_tf32_ss(tmem_base, smem_desc_sw128(pa + off), smem_desc_sw128(pb + off), idesc, accf);
+          accf = 1;
+        }
+      }
+      mma_commit(&mma_done);
+    }
+    mbar_wait(&mma_done, it & 1);
+    tc_fence_after();
+    if (tid == 0 && t + (int)gridDim.x < ntiles) issue_loads(t + gridDim.x);   // operands have been read
+    // epilogue: warp w reads TMEM lanes 32 (w % 4) .., columns 64 (w / 4) ..; thread = one row, 2 x 32 columns
+    {
+      const int q = warp & 3, hcol = (warp >> 2) * 64;
+      const int r = q * 32 + lane;
+      float* row = A + (int64_t)(ri + (r < nri ? r : 0)) * lda + rj;
+      const bool fast = !diag && nrj == SB;
+#pragma unroll 1
+      for (int c = 0; c < 2; ++c) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + hcol + c * 32, v);
+        tmem_ld_wait();
+        const int cb = hcol + c * 32;
+        if (r < nri) {
+          if (fast) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              red_add_v4(row + cb + j, -__uint_as_float(v[j]), -__uint_as_float(v[j + 1]), -__uint_as_float(v[j + 2]),
+                         -__uint_as_float(v[j + 3]));
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int col = cb + j;
+              if (col < nrj && (rj + col) <= (ri + r)) atomicAdd(&row[col], -__uint_as_float(v[j]));
+            }
+          }
+        }
+      }
+    }
+    tc_fence_before();
+    __syncthreads();                          // tensor memory drained before the next tile's MMAs overwrite it
+  }
+  if (warp == 0) tmem_dealloc(tmem_base, kSyrkTmemCols);
+}
+
 // Back substitution, panel p0: x_p = inv(L11)^T (z_p - acc_p); CTA 0 stores it, CTA q+1 folds it into
 // acc for column tile q (< p):  acc_q += L[p rows, q cols]^T x_p.
 __global__ void __launch_bounds__(256)
@@ -476,6 +759,23 @@ int ba_chol_solve(const BADev& p, float* A, int lda, float* xbuf, cudaStream_t s
       return 1;
     }
   }
+  CUtensorMap tmA;
+  bool have_map = false;
+  {
+    const int rows0 = n + 1 - NB, t128 = (rows0 - NB + SB - 1) / SB;      // the first panel's bulk region
+    if (n >= 16 * NB && t128 * (t128 + 1) / 2 >= kSyrk128MinTiles) {
+      cudaError_t e = cudaFuncSetAttribute(chol_syrk128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128SmemBytes);
+      if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(chol_syrk128_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrkUmmaSmemBytes);
+      if (e != cudaSuccess) {
+        set_error("ba_chol_solve: cannot reserve shared memory for the bulk update: %s", cudaGetErrorString(e));
+        return 1;
+      }
+      // fp32 matrix as a [n + 1][lda] tensor, boxes of 32 columns x 128 rows (rows past n + 1 read as zero)
+      have_map = sm100::make_tensor_map_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, A, (uint64_t)lda, (uint64_t)n + 1,
+                                           (uint64_t)lda, 32, SB);
+    }
+  }
   // look-ahead pays once the trailing update is big enough to hide the next panel under it (>= 16 panels)
   CholLookahead* la = (!dbg && !no_la && n >= 16 * NB) ? chol_lookahead() : nullptr;
   cudaStream_t crit = st;                          // the panel kernels
@@ -504,7 +804,17 @@ int ba_chol_solve(const BADev& p, float* A, int lda, float* xbuf, cudaStream_t s
       cudaStreamWaitEvent(st, la->trsm_done[slot], 0);
     }
     if (Tc > 1 && T > 1) {
-      chol_syrk_kernel<<<(T - 1) * T / 2, 256, 0, st>>>(A, lda, n, p0, p.meta);
+      const int T128 = (rows - NB + SB - 1) / SB;          // 128-row tiles of the bulk region (rows >= p0 + nb + 64)
+      const int nt128 = T128 * (T128 + 1) / 2;
+      if (nb == NB && nt128 >= kSyrk128MinTiles)
+      {
+        if (g_chol_bulk_mode == 0 && have_map)
+          chol_syrk128_umma_kernel<<<kNumSMs, 256, kSyrkUmmaSmemBytes, st>>>(tmA, A, lda, n, p0, nt128, p.meta);
+        else
+          chol_syrk128_kernel<<<kNumSMs, 256, kSyrk128SmemBytes, st>>>(A, lda, n, p0, nt128, p.meta);
+      }
+      else
+        chol_syrk_kernel<<<(T - 1) * T / 2, 256, 0, st>>>(A, lda, n, p0, p.meta);
       ++launches;
       CHOL_DBG("syrk");
     }
@@ -546,6 +856,12 @@ chol_pack_kernel(const float* __restrict__ S, const float* __restrict__ y, int n
   }
 }
 }  // namespace dpvo
+
+extern "C" int dpvo_chol_bulk_mode(int32_t mode) {
+  DPVO_REQUIRE(mode == 0 || mode == 1, "chol_bulk_mode: 0 (split-TF32 tensor-core tiles) or 1 (fp32 FMA tiles)");
+  dpvo::g_chol_bulk_mode = mode;
+  return 0;
+}
 
 extern "C" int64_t dpvo_chol_workspace_bytes(int32_t n) {
   if (n < 0) n = 0;

@@ -17,6 +17,8 @@ struct BADev {
   // edge grouping by pose-pair key (counting sort): hist[K], cursor[K], off[K+1], toff[K+1], perm[E], ekey[E]
   int K;
   int *hist, *cursor, *off, *toff, *perm, *ekey;
+  int* tkey;         // [E / 32 + K + 1] key of every warp task (a task = up to 32 edges of one key)
+  int* ksum;         // [2 * ceil(K / 4096)] (edges, warp tasks) per block of keys: blocked scan of a large histogram
   // normal equations (dense path)
   // U, v, G, g are float64 accumulators: S = B - E Q E^T cancels most of B, so the sums over
   // ~10^3-10^4 edge / patch terms are kept exact to fp32 rounding and S, y are rounded once.
@@ -24,9 +26,11 @@ struct BADev {
   float *C, *u, *Et, *dX, *Sg;
   // block-E path (global BA): E is kept as two 6-vectors per edge (entries w.r.t. the edge's
   // source and target pose), edges are grouped by source frame for the Schur product
-  float* Ee;         // [E][12]  (ei[6], ej[6]); zero for masked edges
+  float* Ee;         // [E][12]  (ei[6], ej[6]) in sorted order (below); zero for masked edges
   float* w;          // [Mmax]   E^T dX accumulator
-  int *fhist, *foff, *fcursor, *fperm;   // counting sort of the edges by source frame (nframes keys)
+  // counting sort of the edges by (source frame, slot of the patch in its frame): nframes * ppf keys + 1 for ignored
+  // edges; fperm[pos] = edge, finv[edge] = pos, ejx[pos] = target pose - t0 or -1, fscan = scan scratch
+  int *fhist, *foff, *fcursor, *fperm, *finv, *ejx, *fscan;
 };
 
 struct EdgeTerms {

@@ -35,7 +35,7 @@ __device__ __forceinline__ int block_exclusive_scan(int val, int* s_warp, int& t
   return res;
 }
 
-__global__ void __launch_bounds__(kScanThreads)
+static __global__ void __launch_bounds__(kScanThreads)
 scan_reduce_kernel(const int* __restrict__ in, int64_t n, int* __restrict__ block_sums) {
   __shared__ int s_warp[32];
   const int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanItems;
@@ -49,7 +49,7 @@ scan_reduce_kernel(const int* __restrict__ in, int64_t n, int* __restrict__ bloc
 }
 
 // single CTA: in-place exclusive scan of block_sums[nb]; writes grand total to *total_out (may be null)
-__global__ void __launch_bounds__(kScanThreads)
+static __global__ void __launch_bounds__(kScanThreads)
 scan_sums_kernel(int* __restrict__ block_sums, int nb, int* __restrict__ total_out) {
   __shared__ int s_warp[32];
   __shared__ int s_carry;
@@ -68,7 +68,7 @@ scan_sums_kernel(int* __restrict__ block_sums, int nb, int* __restrict__ total_o
   if (threadIdx.x == 0 && total_out) *total_out = s_carry;
 }
 
-__global__ void __launch_bounds__(kScanThreads)
+static __global__ void __launch_bounds__(kScanThreads)
 scan_apply_kernel(const int* __restrict__ in, int* __restrict__ out, int64_t n, const int* __restrict__ block_sums) {
   __shared__ int s_warp[32];
   const int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanItems;

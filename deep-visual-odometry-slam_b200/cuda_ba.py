@@ -163,6 +163,12 @@ def cholesky_solve(S, y):
     return x, info
 
 
+def chol_bulk_mode(mode):
+    """0: split-TF32 tensor-core tiles in the blocked Cholesky's bulk trailing update (default), 1: fp32 FMA tiles
+    (include/dpvo_b200.h: dpvo_chol_bulk_mode).  Process-wide; for A/B measurements and the accuracy test."""
+    check(lib.dpvo_chol_bulk_mode(c_i32(int(mode))), "cuda_ba.chol_bulk_mode")
+
+
 def solve_system(J_Ginv_i, J_Ginv_j, ii, jj, res, ep, lm, freen, n_poses=None, refinements=2, return_info=False):
     """cuda_ba.solve_system (fastba/ba.cpp:120-180; caller loop_closure/optim_utils.py:229): one damped
     Gauss-Newton step of the Sim(3) pose graph, on the device.  Returns [delta [n,7]] like the reference

@@ -212,6 +212,13 @@ int dpvo_chol_solve(const float* S, const float* y, int32_t n, float* x, int32_t
 int32_t dpvo_chol_solve_noalloc_max_n(void);
 int dpvo_chol_solve_noalloc(const float* S, const float* y, int32_t n, float* x, int32_t* info, void* stream);
 
+/* Arithmetic of the blocked Cholesky's bulk trailing update (the 128x128 tiles used while the trailing matrix has at
+ * least one tile per SM, i.e. global bundle adjustment; smaller systems never reach it): 0 (default) = split-TF32 on
+ * the tensor cores (each fp32 operand as hi + lo TF32 halves, three mma products per term, fp32 accumulation — fp32
+ * results to ~2^-21 per product), 1 = fp32 FMA.  Process-wide switch for A/B measurements and the accuracy test;
+ * where the reference calls cuSOLVER potrf (ba_cuda.cu:547) there is no such choice. */
+int dpvo_chol_bulk_mode(int32_t mode);
+
 /* ---- Update operator (net.py:23-88, blocks.py:15-48): edge-MLP layers on the tensor cores -------
  * One nn.Linear(K, 384) over E edge rows with the row-local work that follows it in the reference
  * fused into the epilogue:

@@ -12,7 +12,10 @@ from trace_global_ba import kernel_profile, time_call
 
 def main():
     pkg = importlib.import_module("deep-visual-odometry-slam_b200")
-    sizes = [int(a) for a in sys.argv[1:]] or [384, 1000, 2310, 4890, 5994]
+    args = [a for a in sys.argv[1:] if not a.startswith("--")]
+    mode = 1 if "--fp32" in sys.argv else 0          # bulk trailing update: 0 split-TF32 tensor cores, 1 fp32 FMA
+    pkg.cuda_ba.chol_bulk_mode(mode)
+    sizes = [int(a) for a in args] or [384, 1000, 2310, 4890, 5994]
     rows = []
     for n in sizes:
         g = torch.Generator(device="cuda").manual_seed(n)
@@ -24,7 +27,7 @@ def main():
         want = torch.linalg.solve(S.double(), y.double())
         err = float((x.double() - want).norm() / want.norm())
         ms, reps = time_call(lambda: pkg.cuda_ba.cholesky_solve(S, y))
-        row = {"n": n, "info": int(info.item()), "rel_err_vs_float64": err, "ms": ms, "reps_ms": reps}
+        row = {"n": n, "bulk": "fp32" if mode else "split_tf32", "info": int(info.item()), "rel_err_vs_float64": err, "ms": ms, "reps_ms": reps}
         if n == sizes[-1]:
             row.update(kernel_profile(lambda: pkg.cuda_ba.cholesky_solve(S, y)))
         rows.append(row)

@@ -132,16 +132,19 @@ def main():
 
         def call():
             pkg.fastba.BA(P0.clone(), Z0.clone(), *rest, t0, t1, M, 2, True)
-    ms, reps = time_call(call)
-    prof = kernel_profile(call)
     occ = occupancy(ii.long(), jj.long(), kk.long(), int(t1))
-    tag = what + (("_" + a.tag) if a.tag else "")
-    row = {"what": what, "tag": a.tag, "t0": int(t0), "t1": int(t1), "free_poses": int(t1 - t0), "system": 6 * int(t1 - t0),
-           "edges": int(kk.numel()), "ms_per_call": ms, "reps_ms": reps,
-           "occupied_frame_pairs": float(occ[t0:, t0:].mean()), **prof}
-    with open(os.path.join(ROOT, "gpurun_out", f"gba_trace_{tag}.json"), "w") as f:
-        json.dump(row, f, indent=1)
-    print(json.dumps(row), flush=True)
+    # the blocked Cholesky's bulk update in both arithmetics (include/dpvo_b200.h: dpvo_chol_bulk_mode)
+    for mode, name in ((1, "fp32"), (0, "split_tf32")):
+        pkg.cuda_ba.chol_bulk_mode(mode)
+        ms, reps = time_call(call)
+        prof = kernel_profile(call)
+        tag = what + "_" + name + (("_" + a.tag) if a.tag else "")
+        row = {"what": what, "tag": a.tag, "chol_bulk": name, "t0": int(t0), "t1": int(t1), "free_poses": int(t1 - t0),
+               "system": 6 * int(t1 - t0), "edges": int(kk.numel()), "ms_per_call": ms, "reps_ms": reps,
+               "occupied_frame_pairs": float(occ[t0:, t0:].mean()), **prof}
+        with open(os.path.join(ROOT, "gpurun_out", f"gba_trace_{tag}.json"), "w") as f:
+            json.dump(row, f, indent=1)
+        print(json.dumps(row), flush=True)
 
 
 if __name__ == "__main__":
