@@ -115,9 +115,14 @@ __device__ __forceinline__ void chol_invert32(float* __restrict__ X, int o, int 
 }
 
 // Factor the 64x64 SPD tile D (lower triangle; identity-padded by the caller when the panel is narrower) in place
-// and build X = inv(L), by 256 threads: two 32x32 register factorisations on warp 0 (above), the 32x32 panel between
-// them by substitution on warp 1 WHILE warp 0 inverts the first block (from the registers it factored in), the trailing update and the off-diagonal block
-// of the inverse (X10 = -X11 L10 X00) on all warps.  7 barriers.  Returns false on a non-positive pivot.
+// and build X = inv(L), by 256 threads: the two 32x32 diagonal blocks are factored and inverted by warp 0 in registers
+// (above), the 32x32 panel between them by substitution on warp 1 WHILE warp 0 inverts the first block, the trailing
+// update and the off-diagonal block of the inverse (X10 = -X11 L10 X00) on all warps.  Returns false on a non-positive
+// pivot.
+// The two diagonal blocks go through ONE copy of the factor / invert code (a two-trip loop that is not unrolled):
+// those ~2,400 straight-line instructions are executed by a single warp and ncu shows them waiting for instruction
+// fetch 3 cycles out of 4 the first time through (and the second block's copy, when the code was inlined twice, taking
+// several times longer than the first); on the second trip they come from the instruction cache.
 __device__ __forceinline__ bool chol_factor_invert64(float* __restrict__ D, float* __restrict__ X,
                                                      float* __restrict__ rinv, int* __restrict__ s_fail) {
   constexpr int H = 32;
@@ -128,67 +133,70 @@ __device__ __forceinline__ bool chol_factor_invert64(float* __restrict__ D, floa
   for (int i = tid; i < NB * NB; i += 256) X[(i >> 6) * LDT + (i & 63)] = 0.f;
   if (tid == 0) *s_fail = 0;
   __syncthreads();
-  float a[H], my_rs = 0.f;                 // warp 0: row of L00 / L11; warp 1: row of the panel
-  if (wid == 0) {
-    if (!chol_factor32(D, rinv, 0, lane, a, my_rs) && lane == 0) *s_fail = 1;
-  }
-  __syncthreads();
-  if (*s_fail) return false;
-  if (wid == 0) {
-    chol_invert32(X, 0, lane, a, my_rs);   // underneath the panel substitution of warp 1
-  } else if (wid == 1) {
-    // panel: row r = 32 + lane of L10 = A10 * L00^-T by forward substitution (right-looking, broadcast reads of L00)
+#pragma unroll 1
+  for (int blk = 0; blk < 2; ++blk) {
+    const int o = blk * H;
+    if (wid == 0) {
+      float a[H], my_rs = 0.f;
+      if (!chol_factor32(D, rinv, o, lane, a, my_rs) && lane == 0) *s_fail = 1;
+      __threadfence_block();
+      asm volatile("bar.arrive 1, 64;" ::: "memory");      // L_oo and rinv are in shared memory: warp 1 may go on
+      chol_invert32(X, o, lane, a, my_rs);
+    } else {
+      if (wid == 1) asm volatile("bar.sync 1, 64;" ::: "memory");
+      if (blk == 0) {
+        if (wid == 1 && !*s_fail) {
+          // panel: row r = 32 + lane of L10 = A10 * L00^-T by forward substitution (right-looking, broadcast reads of L00)
+          float a[H];
 #pragma unroll
-    for (int c = 0; c < H; ++c) a[c] = D[(H + lane) * LDT + c];
+          for (int c = 0; c < H; ++c) a[c] = D[(H + lane) * LDT + c];
 #pragma unroll
-    for (int c = 0; c < H; ++c) {
-      a[c] *= rinv[c];
+          for (int c = 0; c < H; ++c) {
+            a[c] *= rinv[c];
 #pragma unroll
-      for (int c2 = c + 1; c2 < H; ++c2) a[c2] = fmaf(-a[c], D[c2 * LDT + c], a[c2]);
-    }
+            for (int c2 = c + 1; c2 < H; ++c2) a[c2] = fmaf(-a[c], D[c2 * LDT + c], a[c2]);
+          }
 #pragma unroll
-    for (int c = 0; c < H; ++c) D[(H + lane) * LDT + c] = a[c];
-  }
-  __syncthreads();
-  {
-    // trailing update D11 -= L10 L10^T: thread -> row r, 4 columns; blocks above the diagonal are skipped
-    const int r = tid >> 3, c0 = (tid & 7) * 4;
-    if (c0 <= r) {
-      float s[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-      for (int k = 0; k < H; k += 4) {
-        const float4 av = *reinterpret_cast<const float4*>(D + (H + r) * LDT + k);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float4 bv = *reinterpret_cast<const float4*>(D + (H + c0 + j) * LDT + k);
-          s[j] = fmaf(av.x, bv.x, s[j]); s[j] = fmaf(av.y, bv.y, s[j]);
-          s[j] = fmaf(av.z, bv.z, s[j]); s[j] = fmaf(av.w, bv.w, s[j]);
+          for (int c = 0; c < H; ++c) D[(H + lane) * LDT + c] = a[c];
+        }
+      } else {
+        // Y = L10 * X00 (32x32, X00 lower) into the X10 block, by warps 1..7 underneath the second block's factorisation
+        for (int idx = tid - 32; idx < 256; idx += 224) {
+          const int r = idx >> 3, c0 = (idx & 7) * 4;
+          float s[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 8
+          for (int k = 0; k < H; ++k) {
+            const float l = D[(H + r) * LDT + k];
+            const float4 xv = *reinterpret_cast<const float4*>(X + k * LDT + c0);
+            s[0] = fmaf(l, xv.x, s[0]); s[1] = fmaf(l, xv.y, s[1]); s[2] = fmaf(l, xv.z, s[2]); s[3] = fmaf(l, xv.w, s[3]);
+          }
+          *reinterpret_cast<float4*>(X + (H + r) * LDT + c0) = make_float4(s[0], s[1], s[2], s[3]);
         }
       }
+    }
+    __syncthreads();
+    if (*s_fail) return false;
+    if (blk == 0) {
+      // trailing update D11 -= L10 L10^T: thread -> row r, 4 columns; blocks above the diagonal are skipped
+      const int r = tid >> 3, c0 = (tid & 7) * 4;
+      if (c0 <= r) {
+        float s[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int j = 0; j < 4; ++j) D[(H + r) * LDT + H + c0 + j] -= s[j];
-    }
-  }
-  __syncthreads();
-  if (wid == 0) {
-    if (!chol_factor32(D, rinv, H, lane, a, my_rs) && lane == 0) *s_fail = 1;
-    chol_invert32(X, H, lane, a, my_rs);
-  } else {
-    // Y = L10 * X00 (32x32, X00 lower) into the X10 block, by warps 1..7
-    for (int idx = tid - 32; idx < 256; idx += 224) {
-      const int r = idx >> 3, c0 = (idx & 7) * 4;
-      float s[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 8
-      for (int k = 0; k < H; ++k) {
-        const float l = D[(H + r) * LDT + k];
-        const float4 xv = *reinterpret_cast<const float4*>(X + k * LDT + c0);
-        s[0] = fmaf(l, xv.x, s[0]); s[1] = fmaf(l, xv.y, s[1]); s[2] = fmaf(l, xv.z, s[2]); s[3] = fmaf(l, xv.w, s[3]);
+        for (int k = 0; k < H; k += 4) {
+          const float4 av = *reinterpret_cast<const float4*>(D + (H + r) * LDT + k);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4 bv = *reinterpret_cast<const float4*>(D + (H + c0 + j) * LDT + k);
+            s[j] = fmaf(av.x, bv.x, s[j]); s[j] = fmaf(av.y, bv.y, s[j]);
+            s[j] = fmaf(av.z, bv.z, s[j]); s[j] = fmaf(av.w, bv.w, s[j]);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) D[(H + r) * LDT + H + c0 + j] -= s[j];
       }
-      *reinterpret_cast<float4*>(X + (H + r) * LDT + c0) = make_float4(s[0], s[1], s[2], s[3]);
+      __syncthreads();
     }
   }
-  __syncthreads();
-  if (*s_fail) return false;
   {
     // X10 = -X11 * Y (X11 lower: k <= r)
     const int r = tid >> 3, c0 = (tid & 7) * 4;

@@ -1,11 +1,10 @@
 #!/bin/bash
-# ncu --set full of the global BA's Schur kernel (late in the 1,000-frame sequence) and of the blocked Cholesky's kernels
+# ncu --set full of the blocked Cholesky's kernels with WARM caches (--cache-control none: the panel kernel's one-warp
+# sections are instruction-fetch bound when every replay starts cold, which is not how they run in the factorisation)
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:eff_schur_kernel --launch-skip 620 --launch-count 1 \
-  -f -o gpurun_out/r02_eff_schur python tools/trace_global_ba.py --sequence 1000 > gpurun_out/ncu_eff_schur.log 2>&1
-echo "ncu eff_schur rc=$?"; tail -n 3 gpurun_out/ncu_eff_schur.log | cut -c1-300
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:"chol_syrk128_kernel|chol_panel_kernel" --launch-skip 8 --launch-count 4 \
-  -f -o gpurun_out/r02_chol python tools/time_chol.py 5994 > gpurun_out/ncu_chol.log 2>&1
+timeout 300 python tools/time_chol.py 1000 2>&1 | cut -c1-1200
+timeout 600 ncu --set full --clock-control none --cache-control none --import-source on -k regex:"chol_syrk128_umma_kernel|chol_panel_kernel" --launch-skip 40 --launch-count 4 \
+  -f -o gpurun_out/r02_chol_warm python tools/time_chol.py 5994 > gpurun_out/ncu_chol.log 2>&1
 echo "ncu chol rc=$?"; tail -n 3 gpurun_out/ncu_chol.log | cut -c1-300
 ls -la gpurun_out/*.ncu-rep
