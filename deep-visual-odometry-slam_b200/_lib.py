@@ -9,7 +9,8 @@ import os
 import torch
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libdpvo_b200.so")
+# DPVO_B200_LIB: a differently built copy of the library (development: tools/build_prof.sh)
+LIB_PATH = os.environ.get("DPVO_B200_LIB") or os.path.join(_PKG, "libdpvo_b200.so")
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(

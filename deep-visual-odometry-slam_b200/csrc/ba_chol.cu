@@ -36,6 +36,28 @@ constexpr int LDT = 68;                    // shared-memory tile row stride (flo
 constexpr int TILE = NB * LDT;
 constexpr int kPanelSmemBytes = 4 * TILE * (int)sizeof(float);
 
+// Stage clocks of chol_panel_kernel (development builds with -DDPVO_CHOL_PROFILE only: tools/build_prof.sh): thread 0
+// of CTA 1 adds the cycles between consecutive marks to g_chol_prof[mark]; [31] counts launches.
+#ifdef DPVO_CHOL_PROFILE
+__device__ long long g_chol_prof[32];
+#define CHOL_MARK(i)                                                                         \
+  do {                                                                                       \
+    if (threadIdx.x == 0 && blockIdx.x == 1) {                                               \
+      const long long now_ = clock64();                                                      \
+      atomicAdd(reinterpret_cast<unsigned long long*>(&g_chol_prof[i]), (unsigned long long)(now_ - chol_t_)); \
+      chol_t_ = now_;                                                                        \
+    }                                                                                        \
+  } while (0)
+#define CHOL_MARK_DECL long long chol_t_ = clock64()
+#define CHOL_MARK_ARG , long long& chol_t_
+#define CHOL_MARK_PASS , chol_t_
+#else
+#define CHOL_MARK(i) do {} while (0)
+#define CHOL_MARK_DECL do {} while (0)
+#define CHOL_MARK_ARG
+#define CHOL_MARK_PASS
+#endif
+
 // acc[i][j] += sum_{k < 64} As[ty + 16 i][k] * Bs[tx + 16 j][k]   (both tiles row-major with stride LDT).
 // float4 along k: per 4 k-steps a thread issues 8 LDS.128 for 64 FMAs (scalar reads: 32 LDS for 64 FMAs, which made
 // the old 64^3 tile products shared-memory-issue bound); the 16 lanes that share ty read one address (broadcast).
@@ -78,10 +100,11 @@ __device__ __forceinline__ bool chol_factor32(float* __restrict__ D, float* __re
   for (int j = 0; j < SB; ++j) {
     const float d = __shfl_sync(FULL, a[j], j);
     if (!(d > 0.f)) bad = true;
-    const float inv_d = __frcp_rn(d);
+    // 1 / d as the square of the refined rsqrt: __frcp_rn's slow-path branch kept the 31 - j shuffles below from being
+    // issued underneath the reciprocal (stage clocks: 194 cycles per pivot, most of it that serialisation)
     float rs = rsqrtf(d);
     rs = rs * (1.5f - 0.5f * d * rs * rs);
-    const float t = a[j] * inv_d;
+    const float t = a[j] * (rs * rs);
 #pragma unroll
     for (int k = j + 1; k < SB; ++k) {
       const float akj = __shfl_sync(FULL, a[j], k);        // A[k][j], still unscaled (independent of the reciprocal)
@@ -124,7 +147,7 @@ __device__ __forceinline__ void chol_invert32(float* __restrict__ X, int o, int 
 // fetch 3 cycles out of 4 the first time through (and the second block's copy, when the code was inlined twice, taking
 // several times longer than the first); on the second trip they come from the instruction cache.
 __device__ __forceinline__ bool chol_factor_invert64(float* __restrict__ D, float* __restrict__ X,
-                                                     float* __restrict__ rinv, int* __restrict__ s_fail) {
+                                                     float* __restrict__ rinv, int* __restrict__ s_fail CHOL_MARK_ARG) {
   constexpr int H = 32;
   const int tid = threadIdx.x, lane = tid & 31;
   // the warp index through a shuffle: tells the compiler it is warp-uniform, so the shuffles inside the per-warp
@@ -138,10 +161,13 @@ __device__ __forceinline__ bool chol_factor_invert64(float* __restrict__ D, floa
     const int o = blk * H;
     if (wid == 0) {
       float a[H], my_rs = 0.f;
+      CHOL_MARK(3);                                         // barrier / trailing update since the last mark
       if (!chol_factor32(D, rinv, o, lane, a, my_rs) && lane == 0) *s_fail = 1;
+      CHOL_MARK(4 + 4 * blk);                               // factor32
       __threadfence_block();
       asm volatile("bar.arrive 1, 64;" ::: "memory");      // L_oo and rinv are in shared memory: warp 1 may go on
       chol_invert32(X, o, lane, a, my_rs);
+      CHOL_MARK(5 + 4 * blk);                               // invert32
     } else {
       if (wid == 1) asm volatile("bar.sync 1, 64;" ::: "memory");
       if (blk == 0) {
@@ -175,6 +201,7 @@ __device__ __forceinline__ bool chol_factor_invert64(float* __restrict__ D, floa
       }
     }
     __syncthreads();
+    CHOL_MARK(6 + 4 * blk);                                 // waiting for the other warps of this trip
     if (*s_fail) return false;
     if (blk == 0) {
       // trailing update D11 -= L10 L10^T: thread -> row r, 4 columns; blocks above the diagonal are skipped
@@ -212,6 +239,42 @@ __device__ __forceinline__ bool chol_factor_invert64(float* __restrict__ D, floa
   }
   __syncthreads();
   return true;
+}
+
+__device__ __forceinline__ void cp_async16(float* dst_smem, const float* src, bool valid) {
+  const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(dst_smem));
+  const int sz = valid ? 16 : 0;             // 0 source bytes: the 16 destination bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+// Full-width tiles (64 valid columns) by cp.async: all of a CTA's tile loads are in flight together and nothing waits
+// in registers (stage clocks: the load-process-store loops below cost 8-10k cycles per launch, four L2 round trips
+// back to back).  Rows past `nrows` are zero-filled.
+__device__ __forceinline__ void chol_issue_tile(float* __restrict__ T, const float* __restrict__ A, int lda, int row0,
+                                                int col0, int nrows) {
+#pragma unroll
+  for (int q = 0; q < NB * (NB / 4) / 256; ++q) {
+    const int i = threadIdx.x + q * 256;
+    const int r = i >> 4, c = (i & 15) * 4;
+    const bool ok = r < nrows;
+    cp_async16(T + r * LDT + c, A + (int64_t)(row0 + (ok ? r : 0)) * lda + col0 + c, ok);
+  }
+}
+// strict upper triangle of a freshly loaded diagonal tile -> 0 (the workspace above the diagonal is never written)
+__device__ __forceinline__ void chol_zero_upper(float* __restrict__ T) {
+  for (int i = threadIdx.x; i < NB * (NB / 4); i += 256) {
+    const int r = i >> 4, c = (i & 15) * 4;
+    if (c + 3 <= r) continue;
+    float4 v = *reinterpret_cast<float4*>(T + r * LDT + c);
+    if (c + 0 > r) v.x = 0.f;
+    if (c + 1 > r) v.y = 0.f;
+    if (c + 2 > r) v.z = 0.f;
+    if (c + 3 > r) v.w = 0.f;
+    *reinterpret_cast<float4*>(T + r * LDT + c) = v;
+  }
 }
 
 // global (row-major, leading dimension lda, 64-float aligned columns) -> shared tile, 4 floats per thread and step
@@ -263,13 +326,28 @@ chol_panel_kernel(float* __restrict__ A, int lda, int n, int p0, int has_prev, f
   const bool diag_cta = blockIdx.x == 0;
   const int r0 = p0 + nb + ((int)blockIdx.x - 1) * NB;
   const int nr = diag_cta ? 0 : min(NB, n + 1 - r0);
-  chol_load_tile(D, A, lda, p0, p0, nb, nb, 1);
-  if (!diag_cta) chol_load_tile(R, A, lda, r0, p0, nr, nb, 0);
-  if (has_prev) {
-    chol_load_tile(Pd, A, lda, p0, p0 - NB, nb, NB, 0);
-    if (!diag_cta) chol_load_tile(Pr, A, lda, r0, p0 - NB, nr, NB, 0);
+  CHOL_MARK_DECL;
+  if (nb == NB) {                    // every panel but a ragged last one
+    chol_issue_tile(D, A, lda, p0, p0, NB);
+    if (!diag_cta) chol_issue_tile(R, A, lda, r0, p0, nr);
+    if (has_prev) {
+      chol_issue_tile(Pd, A, lda, p0, p0 - NB, NB);
+      if (!diag_cta) chol_issue_tile(Pr, A, lda, r0, p0 - NB, nr);
+    }
+    cp_async_commit();
+    cp_async_wait<0>();
+    __syncthreads();
+    chol_zero_upper(D);
+  } else {
+    chol_load_tile(D, A, lda, p0, p0, nb, nb, 1);
+    if (!diag_cta) chol_load_tile(R, A, lda, r0, p0, nr, nb, 0);
+    if (has_prev) {
+      chol_load_tile(Pd, A, lda, p0, p0 - NB, nb, NB, 0);
+      if (!diag_cta) chol_load_tile(Pr, A, lda, r0, p0 - NB, nr, NB, 0);
+    }
   }
   __syncthreads();
+  CHOL_MARK(1);                       // tile loads
   const int tx = tid & 15, ty = tid >> 4;
   if (has_prev) {
     float acc[4][4];
@@ -299,7 +377,8 @@ chol_panel_kernel(float* __restrict__ A, int lda, int n, int p0, int has_prev, f
     __syncthreads();                 // Pd is dead from here on: it becomes X
   }
   float* X = Pd;
-  if (!chol_factor_invert64(D, X, rinv, &s_fail)) {
+  CHOL_MARK(2);                       // previous panel's update of this column (two 64^3 products)
+  if (!chol_factor_invert64(D, X, rinv, &s_fail CHOL_MARK_PASS)) {
     if (tid == 0) meta[1] = 1;
     return;
   }
@@ -316,6 +395,7 @@ chol_panel_kernel(float* __restrict__ A, int lda, int n, int p0, int has_prev, f
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  CHOL_MARK(12);                      // X10 = -X11 Y and its barriers
   tile_mma(acc, R, X, ty, tx);       // out[r][c] = sum_k R[r][k] X[c][k]  (X lower: terms with k > c are zero)
 #pragma unroll
   for (int i = 0; i < 4; ++i)
@@ -324,6 +404,10 @@ chol_panel_kernel(float* __restrict__ A, int lda, int n, int p0, int has_prev, f
       const int r = ty + 16 * i, c = tx + 16 * j;
       if (r < nr && c < nb) A[(int64_t)(r0 + r) * lda + p0 + c] = acc[i][j];
     }
+  CHOL_MARK(13);                      // L21 product + store
+#ifdef DPVO_CHOL_PROFILE
+  if (threadIdx.x == 0 && blockIdx.x == 1) atomicAdd(reinterpret_cast<unsigned long long*>(&g_chol_prof[31]), 1ull);
+#endif
 }
 
 // Bulk of panel p0's trailing update: tile (ti, tj), 1 <= tj <= ti, of the rows / columns starting at q0 = p0 + nb.
@@ -381,15 +465,6 @@ constexpr int SB = 128;
 constexpr int kSyrkStage = 2 * SB * LDT;                      // floats: rows of the tile's row block + of its column block
 constexpr int kSyrk128SmemBytes = 2 * kSyrkStage * (int)sizeof(float);
 constexpr int kSyrk128MinTiles = kNumSMs;    // fewer 128-tiles than SMs: the 64x64 kernel spreads the work better
-
-__device__ __forceinline__ void cp_async16(float* dst_smem, const float* src, bool valid) {
-  const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(dst_smem));
-  const int sz = valid ? 16 : 0;             // 0 source bytes: the 16 destination bytes are zero-filled
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(src), "r"(sz) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
 
 __device__ __forceinline__ uint32_t tf32_rna(float x) {
   uint32_t r;
@@ -864,6 +939,18 @@ chol_pack_kernel(const float* __restrict__ S, const float* __restrict__ y, int n
   }
 }
 }  // namespace dpvo
+
+#ifdef DPVO_CHOL_PROFILE
+extern "C" int dpvo_chol_profile_read(long long* out32, int reset) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out32, dpvo::g_chol_prof, sizeof(long long) * 32);
+  if (reset) {
+    long long z[32] = {};
+    cudaMemcpyToSymbol(dpvo::g_chol_prof, z, sizeof(z));
+  }
+  return 0;
+}
+#endif
 
 extern "C" int dpvo_chol_bulk_mode(int32_t mode) {
   DPVO_REQUIRE(mode == 0 || mode == 1, "chol_bulk_mode: 0 (split-TF32 tensor-core tiles) or 1 (fp32 FMA tiles)");
