@@ -61,77 +61,100 @@ __device__ long long g_chol_prof[32];
 // acc[i][j] += sum_{k < 64} As[ty + 16 i][k] * Bs[tx + 16 j][k]   (both tiles row-major with stride LDT).
 // float4 along k: per 4 k-steps a thread issues 8 LDS.128 for 64 FMAs (scalar reads: 32 LDS for 64 FMAs, which made
 // the old 64^3 tile products shared-memory-issue bound); the 16 lanes that share ty read one address (broadcast).
+// Output block (i, j) is the 16x16 block (i, j) of the tile, k block kb its 16 columns 16 kb ..:
+//   SKIP = 1: only blocks on or below the diagonal are wanted (symmetric update of a diagonal tile): j > i skipped
+//   SKIP = 2: Bs is lower triangular (Bs[c][k] = 0 for k > c): products with kb > j skipped
+template <int SKIP>
 __device__ __forceinline__ void tile_mma(float (&acc)[4][4], const float* __restrict__ As, const float* __restrict__ Bs,
                                          int ty, int tx) {
-#pragma unroll 2
-  for (int k = 0; k < NB; k += 4) {
-    float4 a[4], b[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      a[i] = *reinterpret_cast<const float4*>(As + (ty + 16 * i) * LDT + k);
-      b[i] = *reinterpret_cast<const float4*>(Bs + (tx + 16 * i) * LDT + k);
-    }
+  for (int kb = 0; kb < 4; ++kb) {
+#pragma unroll 1
+    for (int k = 16 * kb; k < 16 * kb + 16; k += 4) {
+      float4 a[4], b[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        acc[i][j] = fmaf(a[i].x, b[j].x, acc[i][j]);
-        acc[i][j] = fmaf(a[i].y, b[j].y, acc[i][j]);
-        acc[i][j] = fmaf(a[i].z, b[j].z, acc[i][j]);
-        acc[i][j] = fmaf(a[i].w, b[j].w, acc[i][j]);
+      for (int i = 0; i < 4; ++i) {
+        a[i] = *reinterpret_cast<const float4*>(As + (ty + 16 * i) * LDT + k);
+        if (SKIP != 2 || i >= kb) b[i] = *reinterpret_cast<const float4*>(Bs + (tx + 16 * i) * LDT + k);
       }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (SKIP == 1 && j > i) continue;
+          if (SKIP == 2 && j < kb) continue;
+          acc[i][j] = fmaf(a[i].x, b[j].x, acc[i][j]);
+          acc[i][j] = fmaf(a[i].y, b[j].y, acc[i][j]);
+          acc[i][j] = fmaf(a[i].z, b[j].z, acc[i][j]);
+          acc[i][j] = fmaf(a[i].w, b[j].w, acc[i][j]);
+        }
+    }
   }
 }
 
-// One warp factors the 32x32 SPD block at (o, o) of D in registers (lane l owns row l), right-looking so that the
-// serial chain per pivot is one shuffle, one reciprocal and two dependent FMAs: the column below pivot j is used
-// UNSCALED in the update,  A[l][k] -= (A[l][j] / d_j) * A[k][j],  and scaled to L[l][j] = A[l][j] * rsqrt(d_j) off the
-// critical path.  Writes L (lower, zero upper) back into D and 1 / L_jj into rinv; a[] (row l of L) and my_rs
-// (1 / L_ll) stay in registers for chol_invert32.  Returns false on a non-positive (or NaN) pivot.
+// One warp factors the 32x32 SPD block at (o, o) of D in registers (lane l owns row l), right-looking: the column below
+// pivot j is used UNSCALED in the update,  A[l][k] -= (A[l][j] / d_j) * A[k][j],  and scaled to L[l][j] = A[l][j] *
+// rsqrt(d_j) off the critical path.  Column j travels between the lanes through shared memory: every lane parks its
+// A[l][j] in a 32-float buffer (double-buffered by pivot parity, one __syncwarp per pivot) and reads the pivot and the
+// A[k][j], k > j, back as broadcast LDS.128 — 145 vector loads per block where one shuffle per (j, k) pair took 528
+// (stage clocks: 153 cycles per pivot with shuffles, shuffle-issue bound).  The scaled columns go to Lt[j][l] =
+// L[l][j] for chol_invert32 / the panel substitution, 1 / L_jj to rinv; L (lower, zero upper) is written back into D.
+// Returns false on a non-positive (or NaN) pivot.
 __device__ __forceinline__ bool chol_factor32(float* __restrict__ D, float* __restrict__ rinv, int o, int lane,
-                                              float (&a)[32], float& my_rs) {
+                                              float* __restrict__ Lt, float* __restrict__ ucol) {
   constexpr int SB = 32;
   constexpr unsigned FULL = 0xffffffffu;
+  float a[SB];
 #pragma unroll
   for (int k = 0; k < SB; ++k) a[k] = D[(o + lane) * LDT + o + k];
   bool bad = false;
-  my_rs = 0.f;
 #pragma unroll
   for (int j = 0; j < SB; ++j) {
-    const float d = __shfl_sync(FULL, a[j], j);
+    float* uc = ucol + (j & 1) * SB;
+    uc[lane] = a[j];
+    __syncwarp();
+    const float d = uc[j];
     if (!(d > 0.f)) bad = true;
-    // 1 / d as the square of the refined rsqrt: __frcp_rn's slow-path branch kept the 31 - j shuffles below from being
-    // issued underneath the reciprocal (stage clocks: 194 cycles per pivot, most of it that serialisation)
+    // 1 / d as the square of the refined rsqrt (no slow-path branch in the pivot chain)
     float rs = rsqrtf(d);
     rs = rs * (1.5f - 0.5f * d * rs * rs);
     const float t = a[j] * (rs * rs);
 #pragma unroll
-    for (int k = j + 1; k < SB; ++k) {
-      const float akj = __shfl_sync(FULL, a[j], k);        // A[k][j], still unscaled (independent of the reciprocal)
-      a[k] = fmaf(-t, akj, a[k]);          // lanes l < k compute don't-care values (masked at the store)
+    for (int g = (j + 1) / 4; g < SB / 4; ++g) {
+      const float4 u = *reinterpret_cast<const float4*>(uc + 4 * g);
+      if (4 * g + 0 > j) a[4 * g + 0] = fmaf(-t, u.x, a[4 * g + 0]);   // lanes l < k compute don't-care values
+      if (4 * g + 1 > j) a[4 * g + 1] = fmaf(-t, u.y, a[4 * g + 1]);
+      if (4 * g + 2 > j) a[4 * g + 2] = fmaf(-t, u.z, a[4 * g + 2]);
+      if (4 * g + 3 > j) a[4 * g + 3] = fmaf(-t, u.w, a[4 * g + 3]);
     }
-    a[j] = (lane == j) ? d * rs : a[j] * rs;
-    if (lane == j) my_rs = rs;
+    Lt[j * SB + lane] = (lane > j) ? a[j] * rs : ((lane == j) ? d * rs : 0.f);
+    if (lane == 0) rinv[o + j] = rs;
   }
+  __syncwarp();
 #pragma unroll
-  for (int k = 0; k < SB; ++k) D[(o + lane) * LDT + o + k] = (k <= lane) ? a[k] : 0.f;
-  rinv[o + lane] = my_rs;
+  for (int k = 0; k < SB; ++k) D[(o + lane) * LDT + o + k] = Lt[k * SB + lane];
   return !__any_sync(FULL, bad);
 }
 
-// inv(L) of the block chol_factor32 left in registers: lane c solves L x = e_c forwards (right-looking);
-// L[i2][i] = a[i] of lane i2, 1 / L_ii = my_rs of lane i.  Writes the block (lower, zero upper) into X.
-__device__ __forceinline__ void chol_invert32(float* __restrict__ X, int o, int lane, const float (&a)[32], float my_rs) {
+// inv(L) of the block chol_factor32 left in Lt / rinv: lane c solves L x = e_c forwards (right-looking); column i of
+// L is row i of Lt, read as broadcast LDS.128.  Writes the block (lower, zero upper) into X.
+__device__ __forceinline__ void chol_invert32(float* __restrict__ X, int o, int lane, const float* __restrict__ Lt,
+                                              const float* __restrict__ rinv) {
   constexpr int SB = 32;
-  constexpr unsigned FULL = 0xffffffffu;
   float x[SB];
 #pragma unroll
   for (int i = 0; i < SB; ++i) x[i] = (i == lane) ? 1.f : 0.f;
 #pragma unroll
   for (int i = 0; i < SB; ++i) {
-    x[i] *= __shfl_sync(FULL, my_rs, i);
+    x[i] *= rinv[o + i];
 #pragma unroll
-    for (int i2 = i + 1; i2 < SB; ++i2) x[i2] = fmaf(-__shfl_sync(FULL, a[i], i2), x[i], x[i2]);
+    for (int g = (i + 1) / 4; g < SB / 4; ++g) {
+      const float4 l = *reinterpret_cast<const float4*>(Lt + i * SB + 4 * g);
+      if (4 * g + 0 > i) x[4 * g + 0] = fmaf(-l.x, x[i], x[4 * g + 0]);
+      if (4 * g + 1 > i) x[4 * g + 1] = fmaf(-l.y, x[i], x[4 * g + 1]);
+      if (4 * g + 2 > i) x[4 * g + 2] = fmaf(-l.z, x[i], x[4 * g + 2]);
+      if (4 * g + 3 > i) x[4 * g + 3] = fmaf(-l.w, x[i], x[4 * g + 3]);
+    }
   }
 #pragma unroll
   for (int k = 0; k < SB; ++k) X[(o + k) * LDT + o + lane] = (k >= lane) ? x[k] : 0.f;
@@ -147,7 +170,8 @@ __device__ __forceinline__ void chol_invert32(float* __restrict__ X, int o, int 
 // fetch 3 cycles out of 4 the first time through (and the second block's copy, when the code was inlined twice, taking
 // several times longer than the first); on the second trip they come from the instruction cache.
 __device__ __forceinline__ bool chol_factor_invert64(float* __restrict__ D, float* __restrict__ X,
-                                                     float* __restrict__ rinv, int* __restrict__ s_fail CHOL_MARK_ARG) {
+                                                     float* __restrict__ rinv, int* __restrict__ s_fail,
+                                                     float* __restrict__ Lt, float* __restrict__ ucol CHOL_MARK_ARG) {
   constexpr int H = 32;
   const int tid = threadIdx.x, lane = tid & 31;
   // the warp index through a shuffle: tells the compiler it is warp-uniform, so the shuffles inside the per-warp
@@ -160,19 +184,19 @@ __device__ __forceinline__ bool chol_factor_invert64(float* __restrict__ D, floa
   for (int blk = 0; blk < 2; ++blk) {
     const int o = blk * H;
     if (wid == 0) {
-      float a[H], my_rs = 0.f;
       CHOL_MARK(3);                                         // barrier / trailing update since the last mark
-      if (!chol_factor32(D, rinv, o, lane, a, my_rs) && lane == 0) *s_fail = 1;
+      if (!chol_factor32(D, rinv, o, lane, Lt, ucol) && lane == 0) *s_fail = 1;
       CHOL_MARK(4 + 4 * blk);                               // factor32
       __threadfence_block();
-      asm volatile("bar.arrive 1, 64;" ::: "memory");      // L_oo and rinv are in shared memory: warp 1 may go on
-      chol_invert32(X, o, lane, a, my_rs);
+      asm volatile("bar.arrive 1, 64;" ::: "memory");      // L_oo, Lt and rinv are in shared memory: warp 1 may go on
+      chol_invert32(X, o, lane, Lt, rinv);
       CHOL_MARK(5 + 4 * blk);                               // invert32
     } else {
       if (wid == 1) asm volatile("bar.sync 1, 64;" ::: "memory");
       if (blk == 0) {
         if (wid == 1 && !*s_fail) {
-          // panel: row r = 32 + lane of L10 = A10 * L00^-T by forward substitution (right-looking, broadcast reads of L00)
+          // panel: row r = 32 + lane of L10 = A10 * L00^-T by forward substitution (right-looking; column c of L00 is
+          // row c of Lt: broadcast LDS.128)
           float a[H];
 #pragma unroll
           for (int c = 0; c < H; ++c) a[c] = D[(H + lane) * LDT + c];
@@ -180,7 +204,13 @@ __device__ __forceinline__ bool chol_factor_invert64(float* __restrict__ D, floa
           for (int c = 0; c < H; ++c) {
             a[c] *= rinv[c];
 #pragma unroll
-            for (int c2 = c + 1; c2 < H; ++c2) a[c2] = fmaf(-a[c], D[c2 * LDT + c], a[c2]);
+            for (int g = (c + 1) / 4; g < H / 4; ++g) {
+              const float4 l = *reinterpret_cast<const float4*>(Lt + c * H + 4 * g);
+              if (4 * g + 0 > c) a[4 * g + 0] = fmaf(-a[c], l.x, a[4 * g + 0]);
+              if (4 * g + 1 > c) a[4 * g + 1] = fmaf(-a[c], l.y, a[4 * g + 1]);
+              if (4 * g + 2 > c) a[4 * g + 2] = fmaf(-a[c], l.z, a[4 * g + 2]);
+              if (4 * g + 3 > c) a[4 * g + 3] = fmaf(-a[c], l.w, a[4 * g + 3]);
+            }
           }
 #pragma unroll
           for (int c = 0; c < H; ++c) D[(H + lane) * LDT + c] = a[c];
@@ -320,6 +350,8 @@ chol_panel_kernel(float* __restrict__ A, int lda, int n, int p0, int has_prev, f
   float* R = chol_sm + 3 * TILE;
   __shared__ float rinv[NB];
   __shared__ int s_fail;
+  __shared__ __align__(16) float Lt[32 * 32];   // columns of the 32x32 block being factored, as rows
+  __shared__ __align__(16) float ucol[2 * 32];  // the current pivot's unscaled column, double-buffered
   if (meta[1]) return;
   const int tid = threadIdx.x;
   const int nb = min(NB, n - p0);
@@ -355,7 +387,7 @@ chol_panel_kernel(float* __restrict__ A, int lda, int n, int p0, int has_prev, f
     for (int i = 0; i < 4; ++i)
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-    tile_mma(acc, Pd, Pd, ty, tx);
+    tile_mma<1>(acc, Pd, Pd, ty, tx);
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -368,7 +400,7 @@ chol_panel_kernel(float* __restrict__ A, int lda, int n, int p0, int has_prev, f
       for (int i = 0; i < 4; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-      tile_mma(acc, Pr, Pd, ty, tx);
+      tile_mma<0>(acc, Pr, Pd, ty, tx);
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -378,7 +410,7 @@ chol_panel_kernel(float* __restrict__ A, int lda, int n, int p0, int has_prev, f
   }
   float* X = Pd;
   CHOL_MARK(2);                       // previous panel's update of this column (two 64^3 products)
-  if (!chol_factor_invert64(D, X, rinv, &s_fail CHOL_MARK_PASS)) {
+  if (!chol_factor_invert64(D, X, rinv, &s_fail, Lt, ucol CHOL_MARK_PASS)) {
     if (tid == 0) meta[1] = 1;
     return;
   }
@@ -396,7 +428,7 @@ chol_panel_kernel(float* __restrict__ A, int lda, int n, int p0, int has_prev, f
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
   CHOL_MARK(12);                      // X10 = -X11 Y and its barriers
-  tile_mma(acc, R, X, ty, tx);       // out[r][c] = sum_k R[r][k] X[c][k]  (X lower: terms with k > c are zero)
+  tile_mma<2>(acc, R, X, ty, tx);    // out[r][c] = sum_k R[r][k] X[c][k]  (X lower: terms with k > c are zero)
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -438,7 +470,7 @@ chol_syrk_kernel(float* __restrict__ A, int lda, int n, int p0, const int* __res
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-  tile_mma(acc, As, Bs, ty, tx);
+  tile_mma<0>(acc, As, Bs, ty, tx);
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
