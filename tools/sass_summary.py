@@ -31,7 +31,7 @@ def main():
             out[name] = collections.Counter()
             out[name]["instructions"] = 0
             continue
-        if name and re.search(r"/\*[0-9a-f]{4}\*/", line):
+        if name and re.search(r"/\*[0-9a-f]{4,}\*/", line):
             out[name]["instructions"] += 1
             for key, pat in PAT:
                 if re.search(pat, line):
