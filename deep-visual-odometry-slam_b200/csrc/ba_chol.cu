@@ -6,16 +6,15 @@
 //
 // A is (n+1) x lda row-major in global memory: rows 0..n-1 hold the lower triangle of
 // S = B - E Q E^T (+ damping), row n holds y^T, so the forward substitution L z = y is part of
-// the factorisation (row n of L is z^T).  Panels of 64 columns, three launches per panel:
-//   diag   one CTA factors the 64x64 diagonal block AND inverts the factor (blocked 4 x 16 inside the
-//          tile, 16x16 blocks in one warp's registers with shuffles: ~22 barriers, not 64 + a serial solve)
-//   trsm   one CTA per 64-row tile below the panel: L21 = A21 * inv(L11)^T as a 64x64x64 product
-//          (inv(L11) was left behind by the CTA that factored the diagonal block), no sequential loop
-//   syrk   one CTA per 64x64 lower tile of the trailing matrix: A22 -= L21 L21^T (fp32 SIMT; the
-//          update is K=64 deep per panel — not worth a tensor-core pipeline at these sizes).
-// Back substitution L^T x = z from the bottom, ONE launch per panel: every CTA forms
-// x_p = inv(L11)^T (z_p - acc_p) (a 64x64 mat-vec), CTA q then adds L[p, q]^T x_p to acc_q for its
-// 64-column tile q < p (each acc segment has exactly one writer per launch: no atomics).
+// the factorisation (row n of L is z^T).  Panels of 64 columns:
+//   panel  ONE launch per panel on the critical path (chol_panel_kernel): every CTA applies the previous panel's
+//          update to the column it needs, factors the 64x64 diagonal block AND inverts the factor (redundantly, in
+//          registers / shared memory), and forms its 64 rows of L21 = A21 * inv(L11)^T as a 64^3 product
+//   bulk   trailing update A22 -= L21 L21^T of everything right of the next panel, on the caller's stream underneath
+//          the next panel (look-ahead): 128x128 tiles on the tensor cores as split-TF32 tcgen05.mma
+//          (chol_syrk128_umma_kernel) while there is a tile per SM, 64x64 fp32 tiles (chol_syrk_kernel) below that;
+//          chol_syrk128_kernel is the fp32 form of the big tiles (dpvo_chol_bulk_mode)
+// Back substitution L^T x = z from the bottom, four panels per launch (chol_bs_kernel).
 // Finally dX -> global and the SE3 retraction (ba_cuda.cu:178-206).
 // A non-positive pivot sets meta[1]; every later kernel returns early and dX is zeroed.
 #include "se3.cuh"
@@ -753,34 +752,96 @@ chol_syrk128_umma_kernel(const __grid_constant__ CUtensorMap tmA, float* __restr
   if (warp == 0) tmem_dealloc(tmem_base, kSyrkTmemCols);
 }
 
-// Back substitution, panel p0: x_p = inv(L11)^T (z_p - acc_p); CTA 0 stores it, CTA q+1 folds it into
-// acc for column tile q (< p):  acc_q += L[p rows, q cols]^T x_p.
+// Back substitution L^T x = z, FOUR panels per launch (the launches are a serial chain: 94 of them at 6N = 5,994 took
+// 0.65 ms of a 4.1 ms solve).  Panels pl..ph, from ph down: every CTA redundantly forms
+//   x_p = inv(L_pp)^T (z_p - acc_p - sum_{p' in (p, ph]} L[p', p]^T x_p')
+// from shared-memory copies of the group's inv(L_pp) and of its (up to six) coupling tiles (cp.async, all in flight
+// together), then CTA 0 stores the x_p and CTA q+1 folds sum_p L[p rows, q cols]^T x_p into acc_q for its 64-column
+// tile q < pl (each acc segment has exactly one writer per launch: no atomics).
+constexpr int BSG = 4;
+constexpr int kBsSmemBytes = (BSG + BSG * (BSG - 1) / 2) * NB * NB * (int)sizeof(float);   // 160 KB
+
 __global__ void __launch_bounds__(256)
-chol_bs_kernel(const float* __restrict__ A, int lda, int n, int p0, const float* __restrict__ Linv,
+chol_bs_kernel(const float* __restrict__ A, int lda, int n, int pl, int ph, const float* __restrict__ Linv,
                const float* __restrict__ z, float* __restrict__ acc, float* __restrict__ sol,
                const int* __restrict__ meta) {
+  extern __shared__ __align__(16) float bs_sm[];
+  __shared__ float xs[BSG][NB];
   __shared__ float rhs[NB];
-  __shared__ float xs[NB];
   __shared__ float part[4][NB];
   if (meta[1]) return;
-  const int nb = min(NB, n - p0);
   const int tid = threadIdx.x;
-  if (tid < NB) rhs[tid] = (tid < nb) ? z[p0 + tid] - acc[p0 + tid] : 0.f;
-  __syncthreads();
-  if (tid < NB) {
-    float s = 0.f;
-    for (int k = tid; k < nb; ++k) s += Linv[k * NB + tid] * rhs[k];
-    xs[tid] = s;
+  const int G = ph - pl + 1;
+  float* sLinv = bs_sm;                              // [G][64][64]
+  float* sL = bs_sm + BSG * NB * NB;                 // [pair(b, a), a < b][64 rows of panel pl + b][64 columns of panel pl + a]
+  for (int g = 0; g < G; ++g) {
+    const float* src = Linv + (int64_t)(pl + g) * NB * NB;
+    for (int i = tid; i < NB * NB / 4; i += 256) cp_async16(sLinv + g * NB * NB + 4 * i, src + 4 * i, true);
   }
+  for (int b = 1; b < G; ++b) {
+    const int nbb = min(NB, n - (pl + b) * NB);      // valid rows of panel pl + b
+    for (int a = 0; a < b; ++a) {
+      float* dst = sL + (b * (b - 1) / 2 + a) * NB * NB;
+      for (int i = tid; i < NB * NB / 4; i += 256) {
+        const int r = i >> 4, c = (i & 15) * 4;
+        const bool ok = r < nbb;
+        cp_async16(dst + r * NB + c, A + (int64_t)((pl + b) * NB + (ok ? r : 0)) * lda + (pl + a) * NB + c, ok);
+      }
+    }
+  }
+  cp_async_commit();
+  cp_async_wait<0>();
   __syncthreads();
+  const int c = tid & 63, rg = tid >> 6;
+  for (int g = G - 1; g >= 0; --g) {
+    const int p0 = (pl + g) * NB;
+    float s = 0.f;
+    for (int b = g + 1; b < G; ++b) {
+      const float* t = sL + (b * (b - 1) / 2 + g) * NB * NB;
+#pragma unroll 4
+      for (int r = rg; r < NB; r += 4) s = fmaf(t[r * NB + c], xs[b][r], s);
+    }
+    part[rg][c] = s;
+    __syncthreads();
+    if (tid < NB) {
+      const int i = p0 + tid;
+      rhs[tid] = (i < n) ? z[i] - acc[i] - (part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid]) : 0.f;
+    }
+    __syncthreads();
+    {
+      // x[c] = sum_{k >= c} inv(L)[k][c] rhs[k], four partial sums per column
+      const float* li = sLinv + g * NB * NB;
+      float v = 0.f;
+      for (int k = c + rg; k < NB; k += 4) v = fmaf(li[k * NB + c], rhs[k], v);
+      __syncthreads();                               // part[] of the coupling sums has been consumed
+      part[rg][c] = v;
+    }
+    __syncthreads();
+    if (tid < NB) xs[g][tid] = part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid];
+    __syncthreads();
+  }
   if (blockIdx.x == 0) {
-    if (tid < nb) sol[p0 + tid] = xs[tid];
+    for (int i = tid; i < G * NB; i += 256) {
+      const int g = i >> 6, k = i & 63;
+      if ((pl + g) * NB + k < n) sol[(pl + g) * NB + k] = xs[g][k];
+    }
     return;
   }
   const int c0 = (blockIdx.x - 1) * NB;
-  const int c = tid & 63, rg = tid >> 6;
   float s = 0.f;
-  for (int r = rg; r < nb; r += 4) s += A[(int64_t)(p0 + r) * lda + c0 + c] * xs[r];
+  for (int g = 0; g < G; ++g) {
+    const int p0 = (pl + g) * NB;
+    const int nb = min(NB, n - p0);
+    // 16 independent loads in flight per thread (a rolled load-FMA loop exposed one L2 round trip per row)
+    float v[NB / 4];
+#pragma unroll
+    for (int i = 0; i < NB / 4; ++i) {
+      const int r = rg + 4 * i;
+      v[i] = (r < nb) ? __ldg(A + (int64_t)(p0 + r) * lda + c0 + c) : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < NB / 4; ++i) s = fmaf(v[i], xs[g][rg + 4 * i], s);
+  }
   part[rg][c] = s;
   __syncthreads();
   if (tid < NB) acc[c0 + tid] += part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid];
@@ -868,7 +929,8 @@ int ba_chol_solve(const BADev& p, float* A, int lda, float* xbuf, cudaStream_t s
   float* Linv = sol + n + (64 - (3 * n) % 64) % 64;     // 256-byte aligned panels
   {
     // per device and cheap: once per solve, not per panel
-    const cudaError_t e = cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanelSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanelSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(chol_bs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBsSmemBytes);
     if (e != cudaSuccess) {
       set_error("ba_chol_solve: cannot reserve %d bytes of shared memory: %s", kPanelSmemBytes, cudaGetErrorString(e));
       return 1;
@@ -942,11 +1004,13 @@ int ba_chol_solve(const BADev& p, float* A, int lda, float* xbuf, cudaStream_t s
   chol_init_x_kernel<<<(n + 255) / 256, 256, 0, st>>>(A, lda, n, z, acc, p.meta);
   ++launches;
   CHOL_DBG("init_x");
-  const int last = ((n - 1) / NB) * NB;
-  for (p0 = last; p0 >= 0; p0 -= NB) {
-    chol_bs_kernel<<<1 + p0 / NB, 256, 0, st>>>(A, lda, n, p0, Linv + (int64_t)(p0 / NB) * NB * NB, z, acc, sol, p.meta);
+  for (int ph = (n - 1) / NB; ph >= 0;) {
+    const int pl = ph - BSG + 1 > 0 ? ph - BSG + 1 : 0;
+    p0 = pl * NB;
+    chol_bs_kernel<<<1 + pl, 256, kBsSmemBytes, st>>>(A, lda, n, pl, ph, Linv, z, acc, sol, p.meta);
     ++launches;
     CHOL_DBG("bs");
+    ph = pl - 1;
   }
   const int m = n > p.N ? n : p.N;
   chol_finish_kernel<<<(m + 255) / 256, 256, 0, st>>>(p, sol);
