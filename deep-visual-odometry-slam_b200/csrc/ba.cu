@@ -309,11 +309,20 @@ __device__ __forceinline__ void reduce_scatter_step(float (&v)[96], bool hi, int
 
 constexpr int kAsmWarps = 4;
 
+// The task count lives on the device (meta[2]); its host-side bound E / 32 + K is ~10^6 for a global BA (K = (N+1)^2
+// pose-pair keys, nearly all of them empty), so the grid is capped and the warps stride over the tasks: 250,000 CTAs
+// that only read the count and exit cost more than the assembly itself.
+__device__ __forceinline__ void ba_assemble_task(const BADev& p, int task, int lane);
+
 __global__ void __launch_bounds__(kAsmWarps * 32)
 ba_assemble_kernel(const __grid_constant__ BADev p) {
   const int lane = threadIdx.x & 31;
-  const int task = blockIdx.x * kAsmWarps + (threadIdx.x >> 5);
-  if (task >= p.meta[2]) return;
+  const int ntasks = p.meta[2];
+  for (int task = blockIdx.x * kAsmWarps + (threadIdx.x >> 5); task < ntasks; task += gridDim.x * kAsmWarps)
+    ba_assemble_task(p, task, lane);
+}
+
+__device__ __forceinline__ void ba_assemble_task(const BADev& p, int task, int lane) {
   // the task's pose-pair key: written next to the scan of the task offsets (a binary search over toff here was ~20
   // dependent loads per warp at the 10^6 keys of a global BA)
   const int key = p.tkey[task];
@@ -776,7 +785,8 @@ int64_t ba_carve(BADev& p, char* base, int64_t E, int64_t npatches, int N, int e
 
 void ba_launch_assemble(const BADev& p, cudaStream_t st) {
   const int64_t max_tasks = p.E / 32 + p.K + 1;
-  const int agrid = (int)ceil_div64(max_tasks, kAsmWarps);
+  const int64_t cap = (int64_t)kNumSMs * 32;       // 148 x 32 CTAs of 4 warps: several waves of resident CTAs
+  const int agrid = (int)(ceil_div64(max_tasks, kAsmWarps) < cap ? ceil_div64(max_tasks, kAsmWarps) : cap);
   ba_assemble_kernel<<<agrid, kAsmWarps * 32, 0, st>>>(p);
   note_launches(1);
 }
