@@ -179,9 +179,11 @@ def test_ba_wide_window_and_structure_only():
     assert _rel(got[1][:, 2], want[1][:, 2]) < STATE_TOL
 
 
-def test_ba_masked_and_degenerate_edges():
+@pytest.mark.parametrize("eff", [False, True])
+def test_ba_masked_and_degenerate_edges(eff):
     """Edges behind the camera / far out of bounds / zero weight contribute nothing; duplicate
-    (loop-closure style) edges and self edges are handled."""
+    (loop-closure style) edges are summed — on the dense path and on the block-E path, whose shared-memory fill gives
+    every (patch, target pose) entry one writer and must let two edges with the same target take turns."""
     pkg = load_pkg(); synth = load_pkg("synth")
     d = synth.ba_inputs(14, seed=3, M=24)
     rng = np.random.default_rng(0)
@@ -193,9 +195,9 @@ def test_ba_masked_and_degenerate_edges():
         d[k] = np.concatenate([d[k], d[k][dup]])
     d["target"] = np.concatenate([d["target"], d["target"][dup] + 0.3])
     d["weight"] = np.concatenate([d["weight"], d["weight"][dup]])
-    got = _run_ours(pkg, d, 4, 14)
+    got = _run_ours(pkg, d, 4, 14, eff=eff)
     want = _run_oracle(d, 4, 14)
-    _assert_parity(d, 4, 14, got, want, tag="masked_and_degenerate_edges")
+    _assert_parity(d, 4, 14, got, want, eff=eff, tag="masked_and_degenerate_edges" + ("_eff" if eff else ""))
 
 
 def _with_loop_edges(synth, n_frames, M, seed, hub=None, n_pairs=12):
