@@ -614,6 +614,15 @@ chol_syrk128_kernel(float* __restrict__ A, int lda, int n, int p0, int ntiles, c
 //   split them IN PLACE (hi) and into a second buffer (lo) — element-wise, so the swizzle never matters  ->  one
 //   thread issues the 24 MMAs and commits  ->  as soon as they have read shared memory the TMA of tile t + 1 starts
 //   underneath the epilogue: TMEM -> registers (a thread owns a row, 2 x 32 columns) -> red.global.add.v4.f32.
+// Per tile (stage clocks of a development build): split 1.8k cycles, MMAs 1.8k, epilogue 5.0k + 0.9k at its barrier,
+// of 10.4k.  The epilogue runs at the L2's reduction rate (~13 bytes per clock per SM with every SM reducing):
+// coalescing the reductions through shared memory (8 lanes per 128-byte row segment) changed nothing, a prefetched
+// load - subtract - store of the thread's row was slower (7.9k cycles), and a warp-specialised version (control warp
+// for TMA / MMA, two accumulators, epilogue of tile t - 1 underneath the MMAs of tile t) took the same time per
+// launch.  Tiles are assigned with a stride of gridDim: giving a CTA a contiguous run of tiles (to keep the row
+// block's operand resident) made the solve irreproducible — about one solve in ten off by 1e-2 at 6N = 4,890, with
+// or without the reuse, cause not found — so it is not done; tests/test_ba_gpu.py checks that both arithmetics
+// repeat bit for bit.
 constexpr int kUmmaAtomBytes = SB * 128;                   // 128 rows x 32 fp32: one K-atom of an operand (16 KB)
 constexpr int kUmmaOperandBytes = 2 * kUmmaAtomBytes;      // K = 64: two atoms
 constexpr int kSyrkUmmaSmemBytes = 4 * kUmmaOperandBytes + 1024;   // A hi, B hi, A lo, B lo + alignment slack

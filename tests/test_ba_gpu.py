@@ -428,7 +428,7 @@ def test_blocked_cholesky_solve(n):
     assert int(info2.item()) == 1 and float(x2.abs().max()) == 0.0
 
 
-@pytest.mark.parametrize("n", [2309, 3000])
+@pytest.mark.parametrize("n", [2309, 3000, 4890])
 def test_blocked_cholesky_bulk_update_both_arithmetics(n):
     """Systems large enough for the 128x128 bulk trailing update (>= one tile per SM: n > ~2,240; global bundle
     adjustment sizes): split-TF32 tensor-core tiles (default) and fp32 FMA tiles (dpvo_chol_bulk_mode) against numpy
@@ -451,6 +451,16 @@ def test_blocked_cholesky_bulk_update_both_arithmetics(n):
     e_fp32, e_tf32 = _rel(got[1], want), _rel(got[0], want)
     _log({"case": f"blocked_cholesky_n{n}", "fp32_bulk_to_float64": e_fp32, "split_tf32_bulk_to_float64": e_tf32,
           "between": _rel(got[0], got[1])})
+    # every matrix element has one writer per launch: both arithmetics must repeat bit for bit (a hand-rolled
+    # producer / consumer pipeline that does not is racing)
+    try:
+        for mode in (1, 0):
+            pkg.cuda_ba.chol_bulk_mode(mode)
+            for _ in range(4):
+                x, _info = pkg.cuda_ba.cholesky_solve(_dev(S), _dev(y))
+                assert np.array_equal(x.cpu().numpy(), got[mode]), f"bulk mode {mode} does not repeat"
+    finally:
+        pkg.cuda_ba.chol_bulk_mode(0)
     assert e_fp32 < 2e-5 and e_tf32 < 2e-5, (e_fp32, e_tf32)
     assert e_tf32 < 4 * e_fp32 + 1e-6, (e_fp32, e_tf32)          # the split loses at most a couple of bits
     with pytest.raises(RuntimeError):
