@@ -15,6 +15,12 @@
 //          (chol_syrk128_umma_kernel) while there is a tile per SM, 64x64 fp32 tiles (chol_syrk_kernel) below that;
 //          chol_syrk128_kernel is the fp32 form of the big tiles (dpvo_chol_bulk_mode)
 // Back substitution L^T x = z from the bottom, four panels per launch (chol_bs_kernel).
+// Structure of S is NOT used.  Measured: a bitmap of the non-zero 64x64 tiles (one warp per tile), its symbolic
+// elimination (one CTA) and early exits in the panel / trailing-update kernels.  In time order the factor of a
+// 1,000-keyframe system with 193 loop-closure pairs fills 85 % of its tiles (24 % before elimination), 74 % at 1,500
+// keyframes: 21.2 -> 13.9 ms at 1,500 keyframes, nothing at 1,000, and the 1,000-frame sequence (S 45 % occupied, the
+// factor dense) paid 0.3 - 0.7 ms per call for the bookkeeping on its critical path.  A fill-reducing order (loop
+// closure targets last) is the prerequisite for this to pay; not built.
 // Finally dX -> global and the SE3 retraction (ba_cuda.cu:178-206).
 // A non-positive pivot sets meta[1]; every later kernel returns early and dX is zeroed.
 #include "se3.cuh"

@@ -467,6 +467,42 @@ def test_blocked_cholesky_bulk_update_both_arithmetics(n):
         pkg.cuda_ba.chol_bulk_mode(2)
 
 
+@pytest.mark.parametrize("n,loops", [(2400, 6), (3001, 0), (3001, 40)])
+def test_blocked_cholesky_band_plus_loop_closures(n, loops):
+    """A reduced camera system shaped like a long trajectory's: a block band (half-width 150) plus a few loop-closure
+    blocks far from the diagonal.  Most 64x64 tiles of the factor are structurally zero and the solver skips them
+    (tile bitmap + symbolic elimination in csrc/ba_chol.cu); the result must still be the dense float64 solve's."""
+    pkg = load_pkg()
+    rng = np.random.default_rng(n + loops)
+    S = np.zeros((n, n), np.float64)
+    bw = 150
+    for i0 in range(0, n, 6):
+        j0 = max(0, i0 - bw)
+        rows = min(6, n - i0)
+        S[i0:i0 + rows, j0:i0 + rows] += rng.standard_normal((rows, i0 - j0 + rows)) * 0.05
+    for _ in range(loops):
+        a, b = sorted(int(v) for v in rng.integers(0, n // 6, 2))
+        if b - a > 60:
+            S[6 * b:6 * b + 6, 6 * a:6 * a + 6] += rng.standard_normal((6, 6)) * 0.05
+    S = np.tril(S); S = S + S.T
+    S += np.diag(np.abs(S).sum(1) + 1.0)                 # strictly diagonally dominant: SPD
+    S32 = S.astype(np.float32)
+    y = rng.standard_normal(n).astype(np.float32)
+    want = np.linalg.solve(S32.astype(np.float64), y.astype(np.float64))
+    got = {}
+    try:
+        for mode in (1, 0):
+            pkg.cuda_ba.chol_bulk_mode(mode)
+            x, info = pkg.cuda_ba.cholesky_solve(_dev(S32), _dev(y))
+            assert int(info.item()) == 0
+            got[mode] = x.cpu().numpy()
+            x2, _ = pkg.cuda_ba.cholesky_solve(_dev(S32), _dev(y))
+            assert np.array_equal(x2.cpu().numpy(), got[mode])
+    finally:
+        pkg.cuda_ba.chol_bulk_mode(0)
+    assert _rel(got[0], want) < 2e-5 and _rel(got[1], want) < 2e-5, (_rel(got[0], want), _rel(got[1], want))
+
+
 @pytest.mark.parametrize("eff", [False, True])
 def test_ba_prepare_then_forward_matches_single_call(eff):
     """dpvo_ba_prepare on a side stream + dpvo_ba_forward_prepared on the main stream (what the frame graph
