@@ -272,13 +272,31 @@ def make_teacher(inner, slam, seq, alpha):
             super().__init__()
             self.inner = inner
             self.gt = None
+            self._conj = None
+            self._pin, self._pin_i = None, 0
+
+        def _tstamps(self, n_hi, dev):
+            """time stamps of the window on the device WITHOUT a device synchronisation: a pageable host-to-device copy
+            (torch.as_tensor(numpy, device=cuda)) waits for everything queued before it, i.e. it stalled the tracker in
+            the middle of every update; here the stamps go through a small ring of pinned buffers."""
+            ts = slam.pg.tstamps_[:n_hi + 1]
+            if dev.type != "cuda":
+                return torch.as_tensor(ts.copy(), device=dev)
+            if self._pin is None:
+                cap = len(slam.pg.tstamps_)
+                self._pin = [torch.empty(cap, dtype=torch.from_numpy(ts[:1]).dtype).pin_memory() for _ in range(8)]
+            buf = self._pin[self._pin_i % len(self._pin)]
+            self._pin_i += 1
+            buf[:len(ts)].copy_(torch.from_numpy(ts))
+            return buf[:len(ts)].to(dev, non_blocking=True)
 
         def gt_centres(self, ii, jj, kk):
             dev = ii.device
             if self.gt is None or self.gt.device != dev:
                 self.gt = torch.as_tensor(seq.gt, dtype=torch.float64, device=dev)
+                self._conj = torch.tensor([-1.0, -1.0, -1.0, 1.0], dtype=torch.float64, device=dev)
             n_hi = int(slam.n) + 1
-            ts = torch.as_tensor(slam.pg.tstamps_[:n_hi + 1].copy(), device=dev)
+            ts = self._tstamps(n_hi, dev)
             G = self.gt[ts]                                            # [n+2, 7]
             P = slam.pg.patches_.view(-1, 3, 3, 3)[kk]                # [E,3,3,3]
             x = P[:, 0, 1, 1].double()
@@ -288,7 +306,7 @@ def make_teacher(inner, slam, seq, alpha):
             d = seq.depth(x, y, ts[ii].double())
             Xi = torch.stack([(x - K[:, 2]) / K[:, 0], (y - K[:, 3]) / K[:, 1], torch.ones_like(x)], -1) / d[:, None]
             Gi, Gj = G[ii], G[jj]
-            qi_inv = Gi[:, 3:] * torch.tensor([-1.0, -1.0, -1.0, 1.0], dtype=torch.float64, device=dev)
+            qi_inv = Gi[:, 3:] * self._conj
             Xw = _qrot(qi_inv, Xi - Gi[:, :3])
             Xj = _qrot(Gj[:, 3:], Xw) + Gj[:, :3]
             z = Xj[:, 2]
