@@ -131,6 +131,66 @@ flow_mag_kernel(const TransformArgs a, float beta, float* __restrict__ flow, uns
   }
 }
 
+// motionmag(i, j) + motionmag(j, i) (dpvo.py:240-246, 266-268): the keyframe test reads the mean flow magnitude of the
+// edges i -> j and of the edges j -> i.  One CTA scans the live edge list, evaluates flow_mag only on the matching
+// edges (about two frames' worth of patches) and reduces in a fixed order (no atomics: the decision must repeat bit for bit); an empty selection gives
+// 0 / 0 = NaN like torch's mean over an empty tensor (=> the comparison is false, no keyframe is removed).
+__global__ void __launch_bounds__(1024)
+motionmag_pair_kernel(const TransformArgs a, float beta, int64_t fa, int64_t fb, float* __restrict__ out) {
+  const int PP = a.P * a.P;
+  float s[2] = {0.f, 0.f}, c[2] = {0.f, 0.f};
+  for (int64_t e = threadIdx.x; e < a.E; e += blockDim.x) {
+    const int64_t fi = a.ii[e], fj = a.jj[e];
+    int dir;
+    if (fi == fa && fj == fb) dir = 0;
+    else if (fi == fb && fj == fa) dir = 1;
+    else continue;
+    const int64_t kf = a.kk[e];
+    float m = 0.f;
+    if (fi >= 0 && fi < a.nframes && fj >= 0 && fj < a.nframes && kf >= 0 && kf < a.npatches) {
+      const SE3<float> G0 = relative_pose(a.poses + fi * 7, a.poses + fi * 7, false);
+      const SE3<float> G1 = relative_pose(a.poses + fi * 7, a.poses + fj * 7, false);
+      const SE3<float> G2 = relative_pose(a.poses + fi * 7, a.poses + fj * 7, true);
+      const float* Ki = a.intr + fi * 4;
+      const float* Kj = a.intr + fj * 4;
+      const float* pt = a.patches + kf * 3 * PP;
+      for (int i = 0; i < PP; ++i) {
+        const float X0[4] = {(pt[i] - Ki[2]) / Ki[0], (pt[PP + i] - Ki[3]) / Ki[1], 1.0f, pt[2 * PP + i]};
+        float A0[4], A1[4], A2[4];
+        G0.act4(X0, A0); G1.act4(X0, A1); G2.act4(X0, A2);
+        const float d0 = 1.0f / fmaxf(A0[2], 0.1f), d1 = 1.0f / fmaxf(A1[2], 0.1f), d2 = 1.0f / fmaxf(A2[2], 0.1f);
+        const float x0 = Ki[0] * (d0 * A0[0]) + Ki[2], y0 = Ki[1] * (d0 * A0[1]) + Ki[3];
+        const float x1 = Kj[0] * (d1 * A1[0]) + Kj[2], y1 = Kj[1] * (d1 * A1[1]) + Kj[3];
+        const float x2 = Kj[0] * (d2 * A2[0]) + Kj[2], y2 = Kj[1] * (d2 * A2[1]) + Kj[3];
+        const float f1 = sqrtf((x1 - x0) * (x1 - x0) + (y1 - y0) * (y1 - y0));
+        const float f2 = sqrtf((x2 - x0) * (x2 - x0) + (y2 - y0) * (y2 - y0));
+        m += beta * f1 + (1.0f - beta) * f2;
+      }
+      m /= (float)PP;
+    }
+    s[dir] += m;
+    c[dir] += 1.f;
+  }
+  __shared__ float red[32][4];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float v[4] = {s[0], c[0], s[1], c[1]};
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+    for (int o = 16; o > 0; o >>= 1) v[q] += __shfl_xor_sync(0xffffffffu, v[q], o);
+  if (lane == 0)
+    for (int q = 0; q < 4; ++q) red[warp][q] = v[q];
+  __syncthreads();
+  if (warp == 0) {
+    const int nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      v[q] = lane < nw ? red[lane][q] : 0.f;
+      for (int o = 16; o > 0; o >>= 1) v[q] += __shfl_xor_sync(0xffffffffu, v[q], o);
+    }
+    if (lane == 0) out[0] = v[0] / v[1] + v[2] / v[3];
+  }
+}
+
 // point_cloud (projective_ops.py:111-113): G_ix^-1 * iproj(patch n, intrinsics[ix[n]])
 __global__ void __launch_bounds__(128)
 point_cloud_kernel(const float* __restrict__ poses, const float* __restrict__ patches, const float* __restrict__ intr,
@@ -190,6 +250,19 @@ extern "C" int dpvo_flow_mag(const float* poses, const float* patches, const flo
   flow_mag_kernel<<<grid_for(n_edges), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a, beta, flow, valid);
   note_launches(1);
   return check_launch("flow_mag");
+}
+
+extern "C" int dpvo_motionmag_pair(const float* poses, const float* patches, const float* intrinsics,
+                                  const int64_t* ii, const int64_t* jj, const int64_t* kk,
+                                  int64_t n_edges, int64_t n_frames, int64_t n_patches, int32_t P, float beta,
+                                  int64_t frame_a, int64_t frame_b, float* out, void* stream) {
+  DPVO_REQUIRE(n_edges >= 0 && n_frames > 0 && n_patches > 0 && P > 0 && P <= 8, "motionmag_pair: bad sizes");
+  DPVO_REQUIRE(poses && patches && intrinsics && out && (n_edges == 0 || (ii && jj && kk)), "motionmag_pair: null pointer");
+  TransformArgs a{poses, patches, intrinsics, ii, jj, kk, n_edges, n_frames, n_patches, P, 0, 0,
+                  nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  motionmag_pair_kernel<<<1, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a, beta, frame_a, frame_b, out);
+  note_launches(1);
+  return check_launch("motionmag_pair");
 }
 
 extern "C" int dpvo_point_cloud(const float* poses, const float* patches, const float* intrinsics, const int64_t* ix,

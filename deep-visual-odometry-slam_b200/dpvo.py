@@ -248,16 +248,11 @@ class DPVO:
         return flow.mean()
 
     def motionmag_pair(self, i, j):
-        """motionmag(i, j) + motionmag(j, i) without the two boolean-mask index synchronisations: the flow magnitude of
-        every live edge (one launch) and two masked means on the device; empty selections give NaN like the reference's
-        mean over an empty tensor (=> no keyframe removal)."""
+        """motionmag(i, j) + motionmag(j, i) without the two boolean-mask index synchronisations: ONE launch over the
+        live edge list (`pops.motionmag_pair`: flow magnitude of the matching edges, the two means reduced in a fixed
+        order); empty selections give NaN like the reference's mean over an empty tensor (=> no keyframe removal)."""
         pg = self.pg
-        flow, _ = pops.flow_mag(self.poses, self.patches, self.intrinsics, pg.ii, pg.jj, pg.kk, beta=0.5)
-        f = flow[0].mean(dim=(1, 2))
-        a = (pg.ii == i) & (pg.jj == j)
-        b = (pg.ii == j) & (pg.jj == i)
-        z = torch.zeros_like(f)                      # where(), not a product: unselected edges may hold inf / NaN
-        return torch.where(a, f, z).sum() / a.sum() + torch.where(b, f, z).sum() / b.sum()
+        return pops.motionmag_pair(self.poses, self.patches, self.intrinsics, pg.ii, pg.jj, pg.kk, i, j, beta=0.5)
 
     def keyframe(self):
         cfg, pg = self.cfg, self.pg

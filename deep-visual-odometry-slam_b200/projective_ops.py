@@ -73,6 +73,19 @@ def flow_mag(poses, patches, intrinsics, ii, jj, kk, beta=0.3):
     return flow, val
 
 
+def motionmag_pair(poses, patches, intrinsics, ii, jj, kk, i, j, beta=0.5, out=None):
+    """`DPVO.motionmag(i, j) + DPVO.motionmag(j, i)` (dpvo.py:240-246, 266-268) as a 0-d device tensor: one launch over
+    the live edge list, fixed reduction order, NaN when a direction has no edge.  `out`: optional [1] float32 buffer."""
+    poses, patches, intrinsics, ii, jj, kk = _prep(poses, patches, intrinsics, ii, jj, kk)
+    if out is None:
+        out = torch.empty(1, dtype=torch.float32, device=poses.device)
+    check(lib.dpvo_motionmag_pair(ptr(poses), ptr(patches), ptr(intrinsics), ptr(ii), ptr(jj), ptr(kk),
+                                  c_i64(ii.numel()), c_i64(poses.shape[1]), c_i64(patches.shape[1]),
+                                  c_i32(patches.shape[-1]), c_f32(float(beta)), c_i64(int(i)), c_i64(int(j)), ptr(out),
+                                  stream_of(poses)), "projective_ops.motionmag_pair")
+    return out[0]
+
+
 def point_cloud(poses, patches, intrinsics, ix):
     poses, patches, intrinsics, ix = _prep(poses, patches, intrinsics, ix)
     n, P = patches.shape[1], patches.shape[-1]

@@ -350,6 +350,15 @@ int dpvo_flow_mag(const float* poses, const float* patches, const float* intrins
                   int64_t n_edges, int64_t n_frames, int64_t n_patches, int32_t P, float beta,
                   float* flow, uint8_t* valid, void* stream);
 
+/* DPVO.motionmag(a, b) + DPVO.motionmag(b, a) (dpvo/dpvo.py:240-246 as called by keyframe(), :266-268): out[0] =
+ * mean of flow_mag over the edges a -> b plus the mean over the edges b -> a, in one launch over the live edge list
+ * (the reference selects each direction with a boolean mask, i.e. two device synchronisations, and runs flow_mag twice).
+ * Fixed reduction order; an empty direction gives NaN like torch's mean of an empty tensor. */
+int dpvo_motionmag_pair(const float* poses, const float* patches, const float* intrinsics,
+                        const int64_t* ii, const int64_t* jj, const int64_t* kk,
+                        int64_t n_edges, int64_t n_frames, int64_t n_patches, int32_t P, float beta,
+                        int64_t frame_a, int64_t frame_b, float* out, void* stream);
+
 /* projective_ops.point_cloud (:111-113): points [n,P,P,4] = G_{ix[n]}^-1 * iproj(patches[n], intrinsics[ix[n]]). */
 int dpvo_point_cloud(const float* poses, const float* patches, const float* intrinsics, const int64_t* ix,
                      int64_t n, int64_t n_frames, int32_t P, float* points, void* stream);

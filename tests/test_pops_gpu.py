@@ -64,6 +64,46 @@ def test_flow_mag_and_point_cloud_match_reference_cpu_golden():
     assert pts.shape == g["points"].shape and _rel(pts, g["points"]) < TOL
 
 
+def test_motionmag_pair_matches_two_masked_flow_mag_means():
+    """DPVO.keyframe's motionmag(i, j) + motionmag(j, i) (dpvo.py:240-246, 266-268) in one launch: against the reference
+    formulation (boolean-mask selection, flow_mag of the selected edges, mean) built from pops.flow_mag — itself pinned
+    to the reference's projective_ops.py above — and against the float64 oracle.  1e-6 relative (fp32 sums of ~100
+    terms in another order); NaN for an empty direction; bit-identical on repetition (it drives a decision)."""
+    pops = load_pkg("projective_ops"); synth = load_pkg("synth")
+    d = synth.ba_inputs(40, seed=4)
+    a = (_dev(d["poses"])[None], _dev(d["patches"])[None], _dev(d["intrinsics"])[None],
+         _dev(d["ii"]), _dev(d["jj"]), _dev(d["kk"]))
+    ii, jj, kk = a[3], a[4], a[5]
+    pairs = torch.stack([ii, jj], 1).unique(dim=0).cpu().numpy()
+    both = [(int(i), int(j)) for i, j in pairs if i < j and ((pairs[:, 0] == j) & (pairs[:, 1] == i)).any()]
+    assert len(both) >= 3
+    for i, j in both[:2] + both[-2:]:
+        want = 0.0
+        want64 = 0.0
+        for x, y in ((i, j), (j, i)):
+            k = torch.nonzero((ii == x) & (jj == y)).view(-1)
+            f, _ = pops.flow_mag(a[0], a[1], a[2], ii[k], jj[k], kk[k], beta=0.5)
+            want += float(f.double().mean())
+            kc = k.cpu().numpy()
+            f64, _ = po.flow_mag(d["poses"], d["patches"], d["intrinsics"], d["ii"][kc], d["jj"][kc], d["kk"][kc], beta=0.5)
+            want64 += float(np.mean(f64))
+        got = pops.motionmag_pair(*a, i, j, beta=0.5)
+        assert got.dim() == 0 and abs(float(got) - want) <= 1e-6 * abs(want)
+        assert abs(float(got) - want64) <= 2e-4 * abs(want64)      # flow_mag's own bar against float64 (above)
+        assert torch.equal(got, pops.motionmag_pair(*a, i, j, beta=0.5))
+        assert float(pops.motionmag_pair(*a, j, i, beta=0.5)) == float(got)
+    # one direction only / no edge at all: NaN like torch's mean of an empty selection; empty edge list too
+    only = [(int(i), int(j)) for i, j in pairs if not ((pairs[:, 0] == j) & (pairs[:, 1] == i)).any()]
+    if only:
+        assert np.isnan(float(pops.motionmag_pair(*a, *only[0], beta=0.5)))
+    assert np.isnan(float(pops.motionmag_pair(*a, 10 ** 6, 3, beta=0.5)))
+    e = torch.zeros(0, dtype=torch.int64, device="cuda")
+    assert np.isnan(float(pops.motionmag_pair(a[0], a[1], a[2], e, e, e, 0, 1)))
+    out = torch.zeros(1, device="cuda")
+    r = pops.motionmag_pair(*a, *both[0], out=out)
+    assert r.data_ptr() == out.data_ptr() and float(out[0]) == float(r)
+
+
 def test_transform_full_size_vs_oracle_and_lietorch_composition():
     """45,312-edge DPVO graph: against float64, and against Inv/Mul/Act4 of this repo's lietorch
     kernels composed like projective_ops.py:57-68."""

@@ -1,0 +1,7 @@
+#!/bin/bash
+# after the host-side trims: new unit tests, sequence parity, fps with / without loop closure, host profile
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_pops_gpu.py tests/test_teacher_gpu.py -x -q > gpurun_out/host2_unit.log 2>&1; echo "unit rc=$?"; tail -n 15 gpurun_out/host2_unit.log
+bash tools/gpu_r2_seq2.sh
+bash tools/gpu_r2_hostprof.sh

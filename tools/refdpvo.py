@@ -253,6 +253,27 @@ def _rot_to_quat(R):
 
 
 # --------------------------------------------------------------------------- teacher
+def _load_teacher_lib():
+    """tools/libteacher.so (tools/teacher_kernel.cu, built by __graft_entry__.build()): the teacher in one launch.
+    REFDPVO_TORCH_TEACHER=1 keeps the torch formulation (tests compare the two)."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libteacher.so")
+    if os.environ.get("REFDPVO_TORCH_TEACHER") == "1" or not os.path.exists(path):
+        return None
+    import ctypes
+    lib = ctypes.CDLL(path)
+    lib.teacher_targets.restype = ctypes.c_int
+    return lib
+
+
+_TEACHER_LIB = _load_teacher_lib()
+
+
+def _teacher_kind(args):
+    if args.no_teacher:
+        return "none"
+    return "one-launch kernel (tools/teacher_kernel.cu)" if (_TEACHER_LIB is not None and not args.cpu_dryrun) else "torch ops"
+
+
 def _qrot(q, v):
     """rotate v [.,3] by unit quaternion q [.,4] (x y z w)"""
     import torch
@@ -292,7 +313,7 @@ def make_teacher(inner, slam, seq, alpha):
 
         def gt_centres(self, ii, jj, kk):
             dev = ii.device
-            if self.gt is None or self.gt.device != dev:
+            if self.gt is None or self.gt.device != dev or self._conj is None:
                 self.gt = torch.as_tensor(seq.gt, dtype=torch.float64, device=dev)
                 self._conj = torch.tensor([-1.0, -1.0, -1.0, 1.0], dtype=torch.float64, device=dev)
             n_hi = int(slam.n) + 1
@@ -316,9 +337,39 @@ def make_teacher(inner, slam, seq, alpha):
             v = Kj[:, 1] * Xj[:, 1] / zc + Kj[:, 3]
             return torch.stack([u, v], -1).float()[None], ok[None, :, None]
 
+        def fused(self, delta, weight, coords, ii, jj, kk):
+            """the same targets from ONE launch (tools/teacher_kernel.cu, float64 like gt_centres) — ~70 torch kernels
+            per update otherwise, which is harness time on the host-bound arm"""
+            dev = ii.device
+            if self.gt is None or self.gt.device != dev:
+                self.gt = torch.as_tensor(seq.gt, dtype=torch.float64, device=dev).contiguous()
+            ts = self._tstamps(int(slam.n) + 1, dev)
+            pt, K = slam.pg.patches_, slam.pg.intrinsics_
+            E = ii.numel()
+            if not (pt.is_contiguous() and K.is_contiguous() and coords.is_contiguous() and pt.dtype == torch.float32
+                    and K.dtype == torch.float32 and coords.dtype == torch.float32 and tuple(coords.shape[2:]) == (2, 3, 3)
+                    and tuple(pt.shape[-3:]) == (3, 3, 3) and ii.is_contiguous() and jj.is_contiguous() and kk.is_contiguous()):
+                raise RuntimeError("teacher kernel: unexpected buffer layout")
+            d32 = delta.float().contiguous().view(-1, 2)
+            w32 = weight.float().contiguous().view(-1, 2)
+            d = torch.empty((1, E, 2), dtype=torch.float32, device=dev)
+            w = torch.empty((1, E, 2), dtype=torch.float32, device=dev)
+            import ctypes as C
+            p = lambda t: C.c_void_p(t.data_ptr())
+            rc = _TEACHER_LIB.teacher_targets(
+                p(self.gt), C.c_int64(self.gt.shape[0]), p(ts), C.c_int64(ts.numel()), p(pt), C.c_int64(pt.numel() // 27),
+                p(K), p(ii), p(jj), p(kk), C.c_int64(E), p(coords), C.c_int64(18), C.c_int64(9), C.c_int64(4),
+                p(d32), p(w32), C.c_float(alpha), p(d), p(w), C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+            if rc != 0:
+                raise RuntimeError(f"teacher kernel launch failed: CUDA error {rc}")
+            return d, w
+
         def forward(self, net, inp, corr, flow, ii, jj, kk, **kw):
             net, (delta, weight, _) = self.inner(net, inp, corr, flow, ii, jj, kk, **kw)
             coords = slam._last_coords                                  # [1,E,2,P,P]
+            if _TEACHER_LIB is not None and ii.is_cuda:
+                d, w = self.fused(delta, weight, coords, ii, jj, kk)
+                return net, (d, w, None)
             c = coords[:, :, :, 1, 1]
             gt, ok = self.gt_centres(ii, jj, kk)
             d = (gt - c) + alpha * torch.tanh(delta.float())
@@ -537,7 +588,7 @@ def main():
             summary = dict(backend=args.backend, pipeline=args.pipeline, frames=args.frames, final_n=int(res["final_n"]),
                            removed=int(res["removed"].sum()), gba=int(res["gba"].sum()),
                            loop_added=int(res["loop_added"].sum()), E_last=int(res["E"][-1]),
-                           Einac_last=int(res["Einac"][-1]), modules=files)
+                           Einac_last=int(res["Einac"][-1]), modules=files, teacher=_teacher_kind(args))
             if args.out:
                 np.savez_compressed(args.out, **res)
             print(json.dumps(summary), flush=True)
@@ -548,7 +599,8 @@ def main():
             if acc is not None:
                 res["stages"] = {k: {"calls": c, "s": round(t, 3), "ms_per_call": round(1e3 * t / max(c, 1), 3)}
                                  for k, (c, t) in sorted(acc.items(), key=lambda kv: -kv[1][1])}
-            res.update(backend=args.backend, update=args.update, patchify=args.patchify, pipeline=args.pipeline, modules=files)
+            res.update(backend=args.backend, update=args.update, patchify=args.patchify, pipeline=args.pipeline, modules=files,
+                       teacher=_teacher_kind(args))
             if args.out:
                 with open(args.out, "w") as f:
                     json.dump(res, f)

@@ -10,11 +10,36 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 
+def host_profile(slam, hf, intr, a, frames):
+    """where the HOST time of a frame goes (the tracker is host-bound): cProfile over the same frames, unsynchronised"""
+    import cProfile, io, pstats
+    pr = cProfile.Profile()
+    t0 = time.perf_counter()
+    pr.enable()
+    for t in range(a.start, frames):
+        slam(t, hf[t].cuda(non_blocking=True), intr)
+    pr.disable()
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    out = {}
+    for key in ("tottime", "cumulative"):
+        buf = io.StringIO()
+        pstats.Stats(pr, stream=buf).strip_dirs().sort_stats(key).print_stats(45)
+        out[key] = buf.getvalue()
+    tag = "nolc" if a.no_loop_closure else "lc"
+    with open(os.path.join(ROOT, "gpurun_out", f"seq_host_profile_{tag}.txt"), "w") as f:
+        f.write(f"frames {a.count} from {a.start}; wall {1e3 * wall / a.count:.3f} ms per frame under cProfile\n")
+        for key, v in out.items():
+            f.write(f"==== sorted by {key}\n{v}\n")
+    print(f"host profile: {1e3 * wall / a.count:.3f} ms per frame under cProfile")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--start", type=int, default=500)
     ap.add_argument("--count", type=int, default=60)
     ap.add_argument("--no-loop-closure", action="store_true")
+    ap.add_argument("--host", action="store_true", help="cProfile of the host side instead of the CUPTI trace")
     a = ap.parse_args()
     import refdpvo
     from torch.profiler import profile, ProfilerActivity
@@ -29,6 +54,8 @@ def main():
     for t in range(a.start):
         slam(t, hf[t].cuda(non_blocking=True), intr)
     torch.cuda.synchronize()
+    if a.host:
+        return host_profile(slam, hf, intr, a, frames)
     t0 = time.perf_counter()
     with profile(activities=[ProfilerActivity.CUDA]) as prof:
         for t in range(a.start, frames):
