@@ -11,6 +11,8 @@
 // depth clamp d = 1 / max(Z, 0.1) (projective_ops.py:43), validity Z > 0.2, Jacobians at the centre
 // pixel with d = 1/Z only where |Z| > 0.2 (:76-77), Ji = -Adj(Gij)^T Jj (:103), Jz = Jp Gij[:, 3].
 // Output layout [E, P, P, 2|3] like the reference (DPVO.reproject permutes it afterwards).
+#include <cooperative_groups.h>
+
 #include "lie.cuh"
 
 namespace dpvo {
@@ -132,14 +134,19 @@ flow_mag_kernel(const TransformArgs a, float beta, float* __restrict__ flow, uns
 }
 
 // motionmag(i, j) + motionmag(j, i) (dpvo.py:240-246, 266-268): the keyframe test reads the mean flow magnitude of the
-// edges i -> j and of the edges j -> i.  One CTA scans the live edge list, evaluates flow_mag only on the matching
-// edges (about two frames' worth of patches) and reduces in a fixed order (no atomics: the decision must repeat bit for bit); an empty selection gives
-// 0 / 0 = NaN like torch's mean over an empty tensor (=> the comparison is false, no keyframe is removed).
-__global__ void __launch_bounds__(1024)
+// edges i -> j and of the edges j -> i.  ONE cluster of 8 CTAs scans the live edge list (a single CTA took 34 us for
+// 45k edges, right in front of the frame's host read), evaluates flow_mag only on the matching edges (about two frames'
+// worth of patches) and reduces in a fixed order — warp shuffles, then shared memory, then CTA 0 reads the other CTAs'
+// partial sums through distributed shared memory: no atomics, no scratch, the decision repeats bit for bit.  An empty
+// selection gives 0 / 0 = NaN like torch's mean over an empty tensor (=> the comparison is false, nothing is removed).
+constexpr int kMotionCluster = 8;
+__global__ void __cluster_dims__(kMotionCluster, 1, 1) __launch_bounds__(1024)
 motionmag_pair_kernel(const TransformArgs a, float beta, int64_t fa, int64_t fb, float* __restrict__ out) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
   const int PP = a.P * a.P;
   float s[2] = {0.f, 0.f}, c[2] = {0.f, 0.f};
-  for (int64_t e = threadIdx.x; e < a.E; e += blockDim.x) {
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < a.E; e += (int64_t)gridDim.x * blockDim.x) {
     const int64_t fi = a.ii[e], fj = a.jj[e];
     int dir;
     if (fi == fa && fj == fb) dir = 0;
@@ -172,6 +179,7 @@ motionmag_pair_kernel(const TransformArgs a, float beta, int64_t fa, int64_t fb,
     c[dir] += 1.f;
   }
   __shared__ float red[32][4];
+  __shared__ float part[4];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float v[4] = {s[0], c[0], s[1], c[1]};
 #pragma unroll
@@ -187,8 +195,19 @@ motionmag_pair_kernel(const TransformArgs a, float beta, int64_t fa, int64_t fb,
       v[q] = lane < nw ? red[lane][q] : 0.f;
       for (int o = 16; o > 0; o >>= 1) v[q] += __shfl_xor_sync(0xffffffffu, v[q], o);
     }
-    if (lane == 0) out[0] = v[0] / v[1] + v[2] / v[3];
+    if (lane == 0)
+      for (int q = 0; q < 4; ++q) part[q] = v[q];
   }
+  cluster.sync();
+  if (cluster.block_rank() == 0 && threadIdx.x == 0) {
+    float t[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int r = 0; r < kMotionCluster; ++r) {
+      const float* pr = cluster.map_shared_rank(part, r);
+      for (int q = 0; q < 4; ++q) t[q] += pr[q];
+    }
+    out[0] = t[0] / t[1] + t[2] / t[3];
+  }
+  cluster.sync();                       // the other CTAs' shared memory stays alive until CTA 0 has read it
 }
 
 // point_cloud (projective_ops.py:111-113): G_ix^-1 * iproj(patch n, intrinsics[ix[n]])
@@ -260,7 +279,7 @@ extern "C" int dpvo_motionmag_pair(const float* poses, const float* patches, con
   DPVO_REQUIRE(poses && patches && intrinsics && out && (n_edges == 0 || (ii && jj && kk)), "motionmag_pair: null pointer");
   TransformArgs a{poses, patches, intrinsics, ii, jj, kk, n_edges, n_frames, n_patches, P, 0, 0,
                   nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  motionmag_pair_kernel<<<1, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a, beta, frame_a, frame_b, out);
+  motionmag_pair_kernel<<<kMotionCluster, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a, beta, frame_a, frame_b, out);
   note_launches(1);
   return check_launch("motionmag_pair");
 }

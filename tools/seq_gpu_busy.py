@@ -39,6 +39,7 @@ def main():
     ap.add_argument("--start", type=int, default=500)
     ap.add_argument("--count", type=int, default=60)
     ap.add_argument("--no-loop-closure", action="store_true")
+    ap.add_argument("--top", type=int, default=14)
     ap.add_argument("--host", action="store_true", help="cProfile of the host side instead of the CUPTI trace")
     a = ap.parse_args()
     import refdpvo
@@ -77,9 +78,10 @@ def main():
     span = ivs[-1][1] - ivs[0][0]
     agg = {}
     for e in evs:
-        name = e.name.split("(")[0].split("<")[0].replace("dpvo::", "")[-44:]
+        name = e.name.replace("(anonymous namespace)::", "").replace("<unnamed>::", "")
+        name = name.split("(")[0].split("<")[0].replace("void ", "").replace("dpvo::", "").replace("at::native::", "")[-44:]
         c = agg.setdefault(name, [0, 0.0]); c[0] += 1; c[1] += e.time_range.end - e.time_range.start
-    top = sorted(agg.items(), key=lambda kv: -kv[1][1])[:14]
+    top = sorted(agg.items(), key=lambda kv: -kv[1][1])[:a.top]
     row = {"frames": a.count, "start": a.start, "loop_closure": not a.no_loop_closure,
            "wall_ms_per_frame_under_profiler": 1e3 * wall / a.count, "gpu_span_ms_per_frame": span / 1e3 / a.count,
            "gpu_busy_ms_per_frame": busy / 1e3 / a.count, "gpu_busy_fraction": busy / span,
