@@ -133,7 +133,7 @@ flow_mag_kernel(const TransformArgs a, float beta, float* __restrict__ flow, uns
   }
 }
 
-// motionmag(i, j) + motionmag(j, i) (dpvo.py:240-246, 266-268): the keyframe test reads the mean flow magnitude of the
+// motionmag(i, j) + motionmag(j, i) (dpvo.py:257-264, 266-272): the keyframe test reads the mean flow magnitude of the
 // edges i -> j and of the edges j -> i.  ONE cluster of 8 CTAs scans the live edge list (a single CTA took 34 us for
 // 45k edges, right in front of the frame's host read), evaluates flow_mag only on the matching edges (about two frames'
 // worth of patches) and reduces in a fixed order — warp shuffles, then shared memory, then CTA 0 reads the other CTAs'

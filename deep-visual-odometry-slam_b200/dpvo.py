@@ -241,7 +241,7 @@ class DPVO:
         return torch.quantile(delta.norm(dim=-1).float(), 0.5)
 
     def motionmag(self, i, j):
-        """dpvo.py:240-246 for ONE direction (kept for callers that want it; keyframe() uses motionmag_pair)."""
+        """dpvo.py:257-264 for ONE direction (kept for callers that want it; keyframe() uses motionmag_pair)."""
         pg = self.pg
         k = torch.nonzero((pg.ii == i) & (pg.jj == j)).view(-1)
         flow, _ = pops.flow_mag(self.poses, self.patches, self.intrinsics, pg.ii[k], pg.jj[k], pg.kk[k], beta=0.5)

@@ -424,7 +424,7 @@ class FullFrame(ImageFrontHotPath, UpdateIteration):
         self.steady_edges = e.active.count()
         e.inactive.count()
         e.check_info()
-        # motionmag(i, j) + motionmag(j, i) edge subsets of the fixed window (dpvo.py:241-246,266-268)
+        # motionmag(i, j) + motionmag(j, i) edge subsets of the fixed window (dpvo.py:257-264, 266-272)
         hi, hj = self.host["d"]["ii"], self.host["d"]["jj"]
         i, j = n - self.KEYFRAME_INDEX - 1, n - self.KEYFRAME_INDEX + 1
         sel = np.nonzero(((hi == i) & (hj == j)) | ((hi == j) & (hj == i)))[0]

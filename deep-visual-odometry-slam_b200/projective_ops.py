@@ -74,7 +74,7 @@ def flow_mag(poses, patches, intrinsics, ii, jj, kk, beta=0.3):
 
 
 def motionmag_pair(poses, patches, intrinsics, ii, jj, kk, i, j, beta=0.5, out=None):
-    """`DPVO.motionmag(i, j) + DPVO.motionmag(j, i)` (dpvo.py:240-246, 266-268) as a 0-d device tensor: one launch over
+    """`DPVO.motionmag(i, j) + DPVO.motionmag(j, i)` (dpvo.py:257-264, 266-272) as a 0-d device tensor: one launch over
     the live edge list, fixed reduction order, NaN when a direction has no edge.  `out`: optional [1] float32 buffer."""
     poses, patches, intrinsics, ii, jj, kk = _prep(poses, patches, intrinsics, ii, jj, kk)
     if out is None:

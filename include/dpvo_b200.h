@@ -350,7 +350,7 @@ int dpvo_flow_mag(const float* poses, const float* patches, const float* intrins
                   int64_t n_edges, int64_t n_frames, int64_t n_patches, int32_t P, float beta,
                   float* flow, uint8_t* valid, void* stream);
 
-/* DPVO.motionmag(a, b) + DPVO.motionmag(b, a) (dpvo/dpvo.py:240-246 as called by keyframe(), :266-268): out[0] =
+/* DPVO.motionmag(a, b) + DPVO.motionmag(b, a) (dpvo/dpvo.py:257-264 as called by keyframe(), :266-272): out[0] =
  * mean of flow_mag over the edges a -> b plus the mean over the edges b -> a, in one launch over the live edge list
  * (the reference selects each direction with a boolean mask, i.e. two device synchronisations, and runs flow_mag twice).
  * Fixed reduction order; an empty direction gives NaN like torch's mean of an empty tensor. */

@@ -65,7 +65,7 @@ def test_flow_mag_and_point_cloud_match_reference_cpu_golden():
 
 
 def test_motionmag_pair_matches_two_masked_flow_mag_means():
-    """DPVO.keyframe's motionmag(i, j) + motionmag(j, i) (dpvo.py:240-246, 266-268) in one launch: against the reference
+    """DPVO.keyframe's motionmag(i, j) + motionmag(j, i) (dpvo.py:257-264, 266-272) in one launch: against the reference
     formulation (boolean-mask selection, flow_mag of the selected edges, mean) built from pops.flow_mag — itself pinned
     to the reference's projective_ops.py above — and against the float64 oracle.  1e-6 relative (fp32 sums of ~100
     terms in another order); NaN for an empty direction; bit-identical on repetition (it drives a decision)."""
