@@ -362,16 +362,30 @@ def sequence_leg(frames, timeout_s=900):
             "dropin_update_patchify": ["--backend", "dropin", "--update", "b200", "--patchify", "b200"],
             "b200_dpvo_class": ["--backend", "dropin", "--pipeline", "b200"]}
     res = {}
+    # the host-bound arm is repeated: on the pool's shared 16-vCPU boxes one and the same command read 170 - 235
+    # frames/s in consecutive runs (tools/gpu_r2_seqvar.sh); the median run is reported, every run is listed.  The
+    # other arms are GPU-bound (the reference: 80 s per run) and run once.
+    repeats = {"b200_dpvo_class": 3}
     for name, extra in arms.items():
         cmd = [sys.executable, tool, "--mode", "fps", "--frames", str(frames)] + extra
-        t0 = time.perf_counter()
-        try:
-            r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout_s)
-            j = json.loads(r.stdout.strip().splitlines()[-1]) if r.returncode == 0 else {"error": r.stderr[-400:]}
-        except Exception as ex:
-            j = {"error": str(ex)[:300]}
-        j["process_wall_s"] = round(time.perf_counter() - t0, 1)
-        j.pop("modules", None)
+        runs = []
+        for _ in range(repeats.get(name, 1)):
+            t0 = time.perf_counter()
+            try:
+                r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout_s)
+                j = json.loads(r.stdout.strip().splitlines()[-1]) if r.returncode == 0 else {"error": r.stderr[-400:]}
+            except Exception as ex:
+                j = {"error": str(ex)[:300]}
+            j["process_wall_s"] = round(time.perf_counter() - t0, 1)
+            j.pop("modules", None)
+            runs.append(j)
+            if "fps" not in j:
+                break
+        good = sorted((x for x in runs if "fps" in x), key=lambda x: x["fps"])
+        j = dict(good[len(good) // 2]) if good and len(good) == len(runs) else dict(runs[-1])
+        if len(runs) > 1:
+            j["fps_runs"] = [round(x["fps"], 1) for x in runs if "fps" in x]
+            j["reported"] = "median of the runs"
         res[name] = j
     out = {"what": "synthetic 480x640 sequence, default config incl. LOOP_CLOSURE, teacher-forced flow, image H2D every "
                    "frame, terminate() included; wall clock.  reference_cuda_ext / dropin / dropin_update_patchify run the "
