@@ -39,7 +39,7 @@ constexpr int NB = 64;
 constexpr int LDT = 68;                    // shared-memory tile row stride (floats): rows stay 16-byte aligned for
                                            // float4 reads along k, and 8 consecutive rows cover all 32 banks
 constexpr int TILE = NB * LDT;
-constexpr int kPanelSmemBytes = 4 * TILE * (int)sizeof(float);
+constexpr int kPanelSmemBytes = 5 * TILE * (int)sizeof(float);   // Pd, Pr, D, R, X: 85 KB (+ 129 KB of a bulk CTA fit one SM)
 
 // Stage clocks of chol_panel_kernel (development builds with -DDPVO_CHOL_PROFILE only: tools/build_prof.sh): thread 0
 // of CTA 1 adds the cycles between consecutive marks to g_chol_prof[mark]; [31] counts launches.
@@ -95,6 +95,43 @@ __device__ __forceinline__ void tile_mma(float (&acc)[4][4], const float* __rest
         }
     }
   }
+}
+
+// Rows [32 h, 32 h + 32) of  R -= Pr Pd^T  (64 columns, K = 64) by 128 threads (t = 0..127): the previous panel's update
+// of a row tile, done by warps 4..7 of chol_panel_kernel UNDERNEATH the factorisation of the diagonal tile (warps 0 / 1),
+// one half per trip of chol_factor_invert64.  Same k order per output as tile_mma<0>.
+__device__ __forceinline__ void chol_r_update_half(float* __restrict__ R, const float* __restrict__ Pr,
+                                                   const float* __restrict__ Pd, int h, int t) {
+  const int ty = t >> 4, tx = t & 15;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  const float* Ar = Pr + (32 * h + ty) * LDT;
+  const float* Br = Pd + tx * LDT;
+#pragma unroll 1
+  for (int k = 0; k < NB; k += 4) {
+    float4 a[4], b[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      a[i] = *reinterpret_cast<const float4*>(Ar + 8 * i * LDT + k);
+      b[i] = *reinterpret_cast<const float4*>(Br + 16 * i * LDT + k);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        acc[i][j] = fmaf(a[i].x, b[j].x, acc[i][j]);
+        acc[i][j] = fmaf(a[i].y, b[j].y, acc[i][j]);
+        acc[i][j] = fmaf(a[i].z, b[j].z, acc[i][j]);
+        acc[i][j] = fmaf(a[i].w, b[j].w, acc[i][j]);
+      }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) R[(32 * h + ty + 8 * i) * LDT + tx + 16 * j] -= acc[i][j];
 }
 
 // One warp factors the 32x32 SPD block at (o, o) of D in registers (lane l owns row l), right-looking: the column below
@@ -174,9 +211,13 @@ __device__ __forceinline__ void chol_invert32(float* __restrict__ X, int o, int 
 // those ~2,400 straight-line instructions are executed by a single warp and ncu shows them waiting for instruction
 // fetch 3 cycles out of 4 the first time through (and the second block's copy, when the code was inlined twice, taking
 // several times longer than the first); on the second trip they come from the instruction cache.
+// R / Pr / Pd (Pr may be null): the row tile's pending update R -= Pr Pd^T, worked off by warps 4..7 while they would
+// otherwise wait for warp 0 (above).
 __device__ __forceinline__ bool chol_factor_invert64(float* __restrict__ D, float* __restrict__ X,
                                                      float* __restrict__ rinv, int* __restrict__ s_fail,
-                                                     float* __restrict__ Lt, float* __restrict__ ucol CHOL_MARK_ARG) {
+                                                     float* __restrict__ Lt, float* __restrict__ ucol,
+                                                     float* __restrict__ R, const float* __restrict__ Pr,
+                                                     const float* __restrict__ Pd CHOL_MARK_ARG) {
   constexpr int H = 32;
   const int tid = threadIdx.x, lane = tid & 31;
   // the warp index through a shuffle: tells the compiler it is warp-uniform, so the shuffles inside the per-warp
@@ -220,6 +261,7 @@ __device__ __forceinline__ bool chol_factor_invert64(float* __restrict__ D, floa
 #pragma unroll
           for (int c = 0; c < H; ++c) D[(H + lane) * LDT + c] = a[c];
         }
+        if (Pr && wid >= 4) chol_r_update_half(R, Pr, Pd, 0, tid - 128);
       } else {
         // Y = L10 * X00 (32x32, X00 lower) into the X10 block, by warps 1..7 underneath the second block's factorisation
         for (int idx = tid - 32; idx < 256; idx += 224) {
@@ -233,6 +275,7 @@ __device__ __forceinline__ bool chol_factor_invert64(float* __restrict__ D, floa
           }
           *reinterpret_cast<float4*>(X + (H + r) * LDT + c0) = make_float4(s[0], s[1], s[2], s[3]);
         }
+        if (Pr && wid >= 4) chol_r_update_half(R, Pr, Pd, 1, tid - 128);
       }
     }
     __syncthreads();
@@ -340,7 +383,8 @@ __device__ __forceinline__ void chol_load_tile(float* __restrict__ T, const floa
 // (the last one includes the y row).  Every CTA
 //   1. applies the PREVIOUS panel's trailing update to what it needs of this panel's column — the diagonal tile and
 //      its own row tile:  D -= Lp_d Lp_d^T,  R -= Lp_r Lp_d^T  (the bulk update of the previous panel, which runs
-//      underneath this kernel, leaves this column alone),
+//      underneath this kernel, leaves this column alone); only the diagonal tile's update is on the critical path,
+//      the row tile's is done by warps 4..7 underneath step 2 (two warps' work, the other six used to wait),
 //   2. factors the diagonal tile and inverts the factor — redundantly in every CTA, so that there is no second
 //      launch and no dependency between "diag" and "trsm" (identical inputs and code: identical results),
 //   3. forms its rows of L21 = R inv(L11)^T as one 64^3 product and stores them.
@@ -349,10 +393,11 @@ __global__ void __launch_bounds__(256)
 chol_panel_kernel(float* __restrict__ A, int lda, int n, int p0, int has_prev, float* __restrict__ Linv,
                   int* __restrict__ meta) {
   extern __shared__ __align__(16) float chol_sm[];
-  float* Pd = chol_sm;               // previous panel's L, rows of the diagonal tile; later X = inv(L11)
+  float* Pd = chol_sm;               // previous panel's L, rows of the diagonal tile
   float* Pr = chol_sm + TILE;        // previous panel's L, rows of this CTA's tile
   float* D = chol_sm + 2 * TILE;
   float* R = chol_sm + 3 * TILE;
+  float* X = chol_sm + 4 * TILE;     // inv(L11)
   __shared__ float rinv[NB];
   __shared__ int s_fail;
   __shared__ __align__(16) float Lt[32 * 32];   // columns of the 32x32 block being factored, as rows
@@ -400,22 +445,12 @@ chol_panel_kernel(float* __restrict__ A, int lda, int n, int p0, int has_prev, f
         const int r = ty + 16 * i, c = tx + 16 * j;
         if (c <= r) D[r * LDT + c] -= acc[i][j];       // rows / columns >= nb of Pd are zero: the padding survives
       }
-    if (!diag_cta) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-      tile_mma<0>(acc, Pr, Pd, ty, tx);
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) R[(ty + 16 * i) * LDT + tx + 16 * j] -= acc[i][j];
-    }
-    __syncthreads();                 // Pd is dead from here on: it becomes X
+    __syncthreads();
   }
-  float* X = Pd;
-  CHOL_MARK(2);                       // previous panel's update of this column (two 64^3 products)
-  if (!chol_factor_invert64(D, X, rinv, &s_fail, Lt, ucol CHOL_MARK_PASS)) {
+  CHOL_MARK(2);                       // previous panel's update of the diagonal tile (the row tile's follows below)
+  // R -= Pr Pd^T is not needed before the L21 product: warps 4..7 do it underneath the factorisation
+  const bool pending_r = has_prev && !diag_cta;
+  if (!chol_factor_invert64(D, X, rinv, &s_fail, Lt, ucol, R, pending_r ? Pr : nullptr, Pd CHOL_MARK_PASS)) {
     if (tid == 0) meta[1] = 1;
     return;
   }
