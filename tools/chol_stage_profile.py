@@ -8,7 +8,7 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-NAMES = {1: "tile loads", 2: "previous panel's update (2 x 64^3)", 3: "barrier + trailing update before a factor32",
+NAMES = {1: "tile loads", 2: "previous panel's update of the diagonal tile (the row tile's runs under the factorisation)", 3: "barrier + trailing update before a factor32",
          4: "factor32 #1", 5: "invert32 #1", 6: "trip-1 barrier wait", 8: "factor32 #2", 9: "invert32 #2",
          10: "trip-2 barrier wait", 12: "X10 = -X11 Y", 13: "L21 product + store"}
 
