@@ -139,73 +139,146 @@ flow_mag_kernel(const TransformArgs a, float beta, float* __restrict__ flow, uns
 // worth of patches) and reduces in a fixed order — warp shuffles, then shared memory, then CTA 0 reads the other CTAs'
 // partial sums through distributed shared memory: no atomics, no scratch, the decision repeats bit for bit.  An empty
 // selection gives 0 / 0 = NaN like torch's mean over an empty tensor (=> the comparison is false, nothing is removed).
+//
+// With a KeyframePlan the same pass also COUNTS what keyframe() will do to the edge list under both outcomes of that
+// test (dpvo.py:272-310), so the host learns the decision and the edge counts that follow from it in ONE read and issues
+// the edits without reading their result back:
+//   outcome A (no removal):   edges moved to the inactive list by the window rule at n            -> out[1], min ii -> out[2]
+//   outcome B (frame k goes): edges touching k dropped -> out[3]; of the rest, renumbered (ii, jj > k shift down, kk by
+//                             M), those moved by the window rule at n - 1 -> out[4], min ii of the survivors -> out[5]
+// (the rules are edges_mask_keyframe / edges_renumber / edges_mask_window of csrc/edges.cu, evaluated without editing).
 constexpr int kMotionCluster = 8;
+constexpr int kPlanNone = 0x7fffffff;      // "no live edge" for the two minima
+struct KeyframePlan {
+  const int64_t* ix; int64_t n_ix;        // patch -> source frame table
+  int64_t k, n, M, removal_window, optimization_window;
+  int loop_closure;
+};
+
+__device__ __forceinline__ float edge_flow_mean(const TransformArgs& a, int64_t fi, int64_t fj, int64_t kf, float beta) {
+  const int PP = a.P * a.P;
+  if (!(fi >= 0 && fi < a.nframes && fj >= 0 && fj < a.nframes && kf >= 0 && kf < a.npatches)) return 0.f;
+  const SE3<float> G0 = relative_pose(a.poses + fi * 7, a.poses + fi * 7, false);
+  const SE3<float> G1 = relative_pose(a.poses + fi * 7, a.poses + fj * 7, false);
+  const SE3<float> G2 = relative_pose(a.poses + fi * 7, a.poses + fj * 7, true);
+  const float* Ki = a.intr + fi * 4;
+  const float* Kj = a.intr + fj * 4;
+  const float* pt = a.patches + kf * 3 * PP;
+  float m = 0.f;
+  for (int i = 0; i < PP; ++i) {
+    const float X0[4] = {(pt[i] - Ki[2]) / Ki[0], (pt[PP + i] - Ki[3]) / Ki[1], 1.0f, pt[2 * PP + i]};
+    float A0[4], A1[4], A2[4];
+    G0.act4(X0, A0); G1.act4(X0, A1); G2.act4(X0, A2);
+    const float d0 = 1.0f / fmaxf(A0[2], 0.1f), d1 = 1.0f / fmaxf(A1[2], 0.1f), d2 = 1.0f / fmaxf(A2[2], 0.1f);
+    const float x0 = Ki[0] * (d0 * A0[0]) + Ki[2], y0 = Ki[1] * (d0 * A0[1]) + Ki[3];
+    const float x1 = Kj[0] * (d1 * A1[0]) + Kj[2], y1 = Kj[1] * (d1 * A1[1]) + Kj[3];
+    const float x2 = Kj[0] * (d2 * A2[0]) + Kj[2], y2 = Kj[1] * (d2 * A2[1]) + Kj[3];
+    const float f1 = sqrtf((x1 - x0) * (x1 - x0) + (y1 - y0) * (y1 - y0));
+    const float f2 = sqrtf((x2 - x0) * (x2 - x0) + (y2 - y0) * (y2 - y0));
+    m += beta * f1 + (1.0f - beta) * f2;
+  }
+  return m / (float)PP;
+}
+
+// window rule of keyframe() (dpvo.py:304-309) for an edge (i, j) whose patch belongs to frame src, at frame count n
+__device__ __forceinline__ bool window_rule(const KeyframePlan& q, int64_t src, int64_t i, int64_t j, int64_t n) {
+  bool rem = src < n - q.removal_window;
+  if (q.loop_closure) rem = rem && !((j - i > 30) && (j > n - q.optimization_window));
+  return rem;
+}
+
+template <bool PLAN>
 __global__ void __cluster_dims__(kMotionCluster, 1, 1) __launch_bounds__(1024)
-motionmag_pair_kernel(const TransformArgs a, float beta, int64_t fa, int64_t fb, float* __restrict__ out) {
+motionmag_pair_kernel(const TransformArgs a, float beta, int64_t fa, int64_t fb, const KeyframePlan q,
+                      float* __restrict__ out) {
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
-  const int PP = a.P * a.P;
   float s[2] = {0.f, 0.f}, c[2] = {0.f, 0.f};
+  int cnt[3] = {0, 0, 0};                  // moved (A), dropped (B), moved (B)
+  int mn[2] = {kPlanNone, kPlanNone};      // min ii of the survivors (A), (B)
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < a.E; e += (int64_t)gridDim.x * blockDim.x) {
     const int64_t fi = a.ii[e], fj = a.jj[e];
-    int dir;
-    if (fi == fa && fj == fb) dir = 0;
-    else if (fi == fb && fj == fa) dir = 1;
-    else continue;
+    const int dir = (fi == fa && fj == fb) ? 0 : ((fi == fb && fj == fa) ? 1 : -1);
+    if (!PLAN && dir < 0) continue;
     const int64_t kf = a.kk[e];
-    float m = 0.f;
-    if (fi >= 0 && fi < a.nframes && fj >= 0 && fj < a.nframes && kf >= 0 && kf < a.npatches) {
-      const SE3<float> G0 = relative_pose(a.poses + fi * 7, a.poses + fi * 7, false);
-      const SE3<float> G1 = relative_pose(a.poses + fi * 7, a.poses + fj * 7, false);
-      const SE3<float> G2 = relative_pose(a.poses + fi * 7, a.poses + fj * 7, true);
-      const float* Ki = a.intr + fi * 4;
-      const float* Kj = a.intr + fj * 4;
-      const float* pt = a.patches + kf * 3 * PP;
-      for (int i = 0; i < PP; ++i) {
-        const float X0[4] = {(pt[i] - Ki[2]) / Ki[0], (pt[PP + i] - Ki[3]) / Ki[1], 1.0f, pt[2 * PP + i]};
-        float A0[4], A1[4], A2[4];
-        G0.act4(X0, A0); G1.act4(X0, A1); G2.act4(X0, A2);
-        const float d0 = 1.0f / fmaxf(A0[2], 0.1f), d1 = 1.0f / fmaxf(A1[2], 0.1f), d2 = 1.0f / fmaxf(A2[2], 0.1f);
-        const float x0 = Ki[0] * (d0 * A0[0]) + Ki[2], y0 = Ki[1] * (d0 * A0[1]) + Ki[3];
-        const float x1 = Kj[0] * (d1 * A1[0]) + Kj[2], y1 = Kj[1] * (d1 * A1[1]) + Kj[3];
-        const float x2 = Kj[0] * (d2 * A2[0]) + Kj[2], y2 = Kj[1] * (d2 * A2[1]) + Kj[3];
-        const float f1 = sqrtf((x1 - x0) * (x1 - x0) + (y1 - y0) * (y1 - y0));
-        const float f2 = sqrtf((x2 - x0) * (x2 - x0) + (y2 - y0) * (y2 - y0));
-        m += beta * f1 + (1.0f - beta) * f2;
-      }
-      m /= (float)PP;
+    if (dir >= 0) {
+      s[dir] += edge_flow_mean(a, fi, fj, kf, beta);
+      c[dir] += 1.f;
     }
-    s[dir] += m;
-    c[dir] += 1.f;
+    if (PLAN) {
+      const int64_t src = (kf >= 0 && kf < q.n_ix) ? q.ix[kf] : 0;
+      if (window_rule(q, src, fi, fj, q.n)) ++cnt[0];
+      else mn[0] = min(mn[0], (int)fi);
+      if (fi == q.k || fj == q.k) {
+        ++cnt[1];
+      } else {
+        const int64_t i2 = fi - (fi > q.k ? 1 : 0), j2 = fj - (fj > q.k ? 1 : 0);
+        const int64_t k2 = kf - (fi > q.k ? q.M : 0);
+        const int64_t src2 = (k2 >= 0 && k2 < q.n_ix) ? q.ix[k2] : 0;
+        if (window_rule(q, src2, i2, j2, q.n - 1)) ++cnt[2];
+        else mn[1] = min(mn[1], (int)i2);
+      }
+    }
   }
   __shared__ float red[32][4];
+  __shared__ int redi[32][5];
   __shared__ float part[4];
+  __shared__ int parti[5];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float v[4] = {s[0], c[0], s[1], c[1]};
+  int w[5] = {cnt[0], cnt[1], cnt[2], mn[0], mn[1]};
 #pragma unroll
-  for (int q = 0; q < 4; ++q)
-    for (int o = 16; o > 0; o >>= 1) v[q] += __shfl_xor_sync(0xffffffffu, v[q], o);
-  if (lane == 0)
-    for (int q = 0; q < 4; ++q) red[warp][q] = v[q];
+  for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) v[t] += __shfl_xor_sync(0xffffffffu, v[t], o);
+    if (PLAN) {
+#pragma unroll
+      for (int t = 0; t < 3; ++t) w[t] += __shfl_xor_sync(0xffffffffu, w[t], o);
+#pragma unroll
+      for (int t = 3; t < 5; ++t) w[t] = min(w[t], __shfl_xor_sync(0xffffffffu, w[t], o));
+    }
+  }
+  if (lane == 0) {
+    for (int t = 0; t < 4; ++t) red[warp][t] = v[t];
+    for (int t = 0; t < 5; ++t) redi[warp][t] = w[t];
+  }
   __syncthreads();
   if (warp == 0) {
     const int nw = (blockDim.x + 31) >> 5;
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      v[q] = lane < nw ? red[lane][q] : 0.f;
-      for (int o = 16; o > 0; o >>= 1) v[q] += __shfl_xor_sync(0xffffffffu, v[q], o);
+    for (int t = 0; t < 4; ++t) v[t] = lane < nw ? red[lane][t] : 0.f;
+#pragma unroll
+    for (int t = 0; t < 5; ++t) w[t] = lane < nw ? redi[lane][t] : (t < 3 ? 0 : kPlanNone);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int t = 0; t < 4; ++t) v[t] += __shfl_xor_sync(0xffffffffu, v[t], o);
+#pragma unroll
+      for (int t = 0; t < 3; ++t) w[t] += __shfl_xor_sync(0xffffffffu, w[t], o);
+#pragma unroll
+      for (int t = 3; t < 5; ++t) w[t] = min(w[t], __shfl_xor_sync(0xffffffffu, w[t], o));
     }
-    if (lane == 0)
-      for (int q = 0; q < 4; ++q) part[q] = v[q];
+    if (lane == 0) {
+      for (int t = 0; t < 4; ++t) part[t] = v[t];
+      for (int t = 0; t < 5; ++t) parti[t] = w[t];
+    }
   }
   cluster.sync();
   if (cluster.block_rank() == 0 && threadIdx.x == 0) {
-    float t[4] = {0.f, 0.f, 0.f, 0.f};
+    float t4[4] = {0.f, 0.f, 0.f, 0.f};
+    int t5[5] = {0, 0, 0, kPlanNone, kPlanNone};
     for (int r = 0; r < kMotionCluster; ++r) {
       const float* pr = cluster.map_shared_rank(part, r);
-      for (int q = 0; q < 4; ++q) t[q] += pr[q];
+      const int* pi = cluster.map_shared_rank(parti, r);
+      for (int t = 0; t < 4; ++t) t4[t] += pr[t];
+      for (int t = 0; t < 3; ++t) t5[t] += pi[t];
+      for (int t = 3; t < 5; ++t) t5[t] = min(t5[t], pi[t]);
     }
-    out[0] = t[0] / t[1] + t[2] / t[3];
+    out[0] = t4[0] / t4[1] + t4[2] / t4[3];
+    if (PLAN) {
+      int* oi = reinterpret_cast<int*>(out);
+      oi[1] = t5[0]; oi[2] = t5[3]; oi[3] = t5[1]; oi[4] = t5[2]; oi[5] = t5[4];
+    }
   }
   cluster.sync();                       // the other CTAs' shared memory stays alive until CTA 0 has read it
 }
@@ -279,9 +352,28 @@ extern "C" int dpvo_motionmag_pair(const float* poses, const float* patches, con
   DPVO_REQUIRE(poses && patches && intrinsics && out && (n_edges == 0 || (ii && jj && kk)), "motionmag_pair: null pointer");
   TransformArgs a{poses, patches, intrinsics, ii, jj, kk, n_edges, n_frames, n_patches, P, 0, 0,
                   nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  motionmag_pair_kernel<<<kMotionCluster, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a, beta, frame_a, frame_b, out);
+  motionmag_pair_kernel<false><<<kMotionCluster, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a, beta, frame_a, frame_b,
+                                                                                                    KeyframePlan{}, out);
   note_launches(1);
   return check_launch("motionmag_pair");
+}
+
+extern "C" int dpvo_keyframe_plan(const float* poses, const float* patches, const float* intrinsics,
+                                  const int64_t* ii, const int64_t* jj, const int64_t* kk, const int64_t* ix,
+                                  int64_t n_edges, int64_t n_frames, int64_t n_patches, int32_t P, float beta,
+                                  int64_t frame_a, int64_t frame_b, int64_t k, int64_t n, int64_t patches_per_frame,
+                                  int64_t removal_window, int32_t loop_closure, int64_t optimization_window,
+                                  int32_t* out, void* stream) {
+  DPVO_REQUIRE(n_edges >= 0 && n_edges < (int64_t(1) << 31) && n_frames > 0 && n_patches > 0 && P > 0 && P <= 8 &&
+               patches_per_frame > 0, "keyframe_plan: bad sizes");
+  DPVO_REQUIRE(poses && patches && intrinsics && ix && out && (n_edges == 0 || (ii && jj && kk)), "keyframe_plan: null pointer");
+  TransformArgs a{poses, patches, intrinsics, ii, jj, kk, n_edges, n_frames, n_patches, P, 0, 0,
+                  nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  const KeyframePlan q{ix, n_patches, k, n, patches_per_frame, removal_window, optimization_window, loop_closure ? 1 : 0};
+  motionmag_pair_kernel<true><<<kMotionCluster, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      a, beta, frame_a, frame_b, q, reinterpret_cast<float*>(out));
+  note_launches(1);
+  return check_launch("keyframe_plan");
 }
 
 extern "C" int dpvo_point_cloud(const float* poses, const float* patches, const float* intrinsics, const int64_t* ix,

@@ -139,6 +139,8 @@ class DPVO:
         self.pyramid = (self.fmap1_, self.fmap2_)
         self.viewer = None
         self._lmbda = torch.as_tensor([1e-4], device=dev)
+        self._plan_out = torch.zeros(8, dtype=torch.int32, device=dev)      # keyframe(): decision + edge counts, one read
+        self.verify_plan = False                                            # tests: compare the plan with the device counts
         # relative poses of removed frames (`pg.delta`, dpvo.py:274-277): rows of one device tensor, so that normalize()
         # rescales all of them with one kernel instead of one per removed frame
         self._delta_poses = torch.zeros(4096, 7, device=dev)
@@ -255,12 +257,21 @@ class DPVO:
         return pops.motionmag_pair(self.poses, self.patches, self.intrinsics, pg.ii, pg.jj, pg.kk, i, j, beta=0.5)
 
     def keyframe(self):
+        """dpvo.py:266-310.  ONE host read per frame: `pops.keyframe_plan` returns the motion magnitude the reference
+        reads at :270-272 together with the edge counts / smallest source frame that follow from either outcome (a dry
+        run of the removal rules in the same pass over the edge list), so the edits below are issued without reading
+        their result back.  `self.verify_plan = True` re-reads the device counts afterwards and compares (tests)."""
         cfg, pg = self.cfg, self.pg
         i = self.n - cfg.KEYFRAME_INDEX - 1
         j = self.n - cfg.KEYFRAME_INDEX + 1
-        m = float(self.motionmag_pair(i, j).item())                            # the decision is a host read (dpvo.py:268)
+        k = self.n - cfg.KEYFRAME_INDEX
+        plan = pops.keyframe_plan(self.poses, self.patches, self.intrinsics, pg.ii, pg.jj, pg.kk, self.ix, i, j, k, self.n,
+                                  self.M, cfg.REMOVAL_WINDOW, bool(cfg.LOOP_CLOSURE), cfg.OPTIMIZATION_WINDOW, beta=0.5,
+                                  out=self._plan_out)
+        h = plan.cpu()                                                           # the decision is a host read (dpvo.py:270)
+        m = float(h[:1].view(torch.float32)[0])
+        moved_a, min_a, dropped_b, moved_b, min_b = (int(v) for v in h[1:6].tolist())
         if m / 2 < cfg.KEYFRAME_THRESH:
-            k = self.n - cfg.KEYFRAME_INDEX
             t0, t1 = pg.tstamps_[k - 1], pg.tstamps_[k]
             self._add_delta(t1, t0, self._mul(pg.poses_[k:k + 1], self._inv(pg.poses_[k - 1:k])))
             pg.edges.remove_frame(k)
@@ -272,9 +283,19 @@ class DPVO:
             shift(self._fmap1[0], k, n, mod=self.mem); shift(self._fmap2[0], k, n, mod=self.mem)
             self.n -= 1
             self.m -= self.M
+            pg.edges.active.bound = pg.E - dropped_b
+            E, moved, mn = pg.E - dropped_b - moved_b, moved_b, min_b
+        else:
+            E, moved, mn = pg.E - moved_a, moved_a, min_a
         pg.edges.remove_old(self.n, cfg.REMOVAL_WINDOW, loop_closure=bool(cfg.LOOP_CLOSURE),
                             optimization_window=cfg.OPTIMIZATION_WINDOW)
-        pg.sync_counts()
+        planned = (E, pg.E_inac + moved, pg.BIG if mn == pops.PLAN_NONE else mn)
+        if self.verify_plan:
+            pg.sync_counts()
+            if (pg.E, pg.E_inac, pg.min_ii) != planned:
+                raise RuntimeError(f"keyframe plan {planned} != device counts {(pg.E, pg.E_inac, pg.min_ii)}")
+        pg.E, pg.E_inac, pg.min_ii = planned
+        pg.edges.active.bound, pg.edges.inactive.bound = pg.E, pg.E_inac
 
     def edges_loop(self):
         """patchgraph.py:56-82."""

@@ -359,6 +359,24 @@ int dpvo_motionmag_pair(const float* poses, const float* patches, const float* i
                         int64_t n_edges, int64_t n_frames, int64_t n_patches, int32_t P, float beta,
                         int64_t frame_a, int64_t frame_b, float* out, void* stream);
 
+/* dpvo_motionmag_pair plus a dry run of what DPVO.keyframe() (dpvo/dpvo.py:266-310) does to the edge list under both
+ * outcomes of its test, in the same pass over the live edges, so that the caller learns the decision AND the edge
+ * counts that follow from it in one host read and can issue the edits (dpvo_edges_mask_keyframe / _remove / _renumber /
+ * _mask_window) without reading their result back.  out: 8 x 32-bit words —
+ *   [0] float  motionmag(a, b) + motionmag(b, a)  (NaN when a direction has no edge)
+ *   [1] int32  no removal: edges the window rule (:304-309) moves to the inactive list at frame count n
+ *   [2] int32  no removal: smallest source frame among the edges that stay (0x7fffffff if none)
+ *   [3] int32  frame k removed: edges touching k (dropped, :280-281)
+ *   [4] int32  frame k removed: of the others, renumbered (:283-285), those the window rule moves at frame count n - 1
+ *   [5] int32  frame k removed: smallest (renumbered) source frame among the edges that stay (0x7fffffff if none)
+ * ix: patch -> source frame table [n_patches] (DPVO.ix).  n_edges: exact live count. */
+int dpvo_keyframe_plan(const float* poses, const float* patches, const float* intrinsics,
+                       const int64_t* ii, const int64_t* jj, const int64_t* kk, const int64_t* ix,
+                       int64_t n_edges, int64_t n_frames, int64_t n_patches, int32_t P, float beta,
+                       int64_t frame_a, int64_t frame_b, int64_t k, int64_t n, int64_t patches_per_frame,
+                       int64_t removal_window, int32_t loop_closure, int64_t optimization_window,
+                       int32_t* out, void* stream);
+
 /* projective_ops.point_cloud (:111-113): points [n,P,P,4] = G_{ix[n]}^-1 * iproj(patches[n], intrinsics[ix[n]]). */
 int dpvo_point_cloud(const float* poses, const float* patches, const float* intrinsics, const int64_t* ix,
                      int64_t n, int64_t n_frames, int32_t P, float* points, void* stream);

@@ -104,6 +104,57 @@ def test_motionmag_pair_matches_two_masked_flow_mag_means():
     assert r.data_ptr() == out.data_ptr() and float(out[0]) == float(r)
 
 
+@pytest.mark.parametrize("loop_closure", [False, True])
+def test_keyframe_plan_counts_match_the_reference_rules(loop_closure):
+    """`keyframe_plan` = motionmag_pair + a dry run of keyframe()'s edge edits (dpvo.py:272-310) under both outcomes:
+    the counts / minima must equal the reference's boolean-mask formulation on a random edge list that exercises every
+    rule (edges touching the removed frame, renumbering, the removal window, the loop-closure exemption).  Integers:
+    exact; word 0 is bit-identical to motionmag_pair."""
+    pops = load_pkg("projective_ops"); synth = load_pkg("synth")
+    d = synth.ba_inputs(48, seed=9)
+    M = int(d["M"])
+    poses, patches, intr = _dev(d["poses"])[None], _dev(d["patches"])[None], _dev(d["intrinsics"])[None]
+    N = poses.shape[1]
+    assert patches.shape[1] == N * M
+    ix = torch.arange(N, device="cuda").repeat_interleave(M)
+    g = torch.Generator().manual_seed(5)
+    E = 30000
+    ii = torch.randint(0, 48, (E,), generator=g)
+    jj = torch.randint(0, 48, (E,), generator=g)
+    kk = ii * M + torch.randint(0, M, (E,), generator=g)
+    ii, jj, kk = ii.cuda(), jj.cuda(), kk.cuda()
+    n, k, RW, OW = 48, 44, 22, 12
+    i, j = k - 1, k + 1
+    out = pops.keyframe_plan(poses, patches, intr, ii, jj, kk, ix, i, j, k, n, M, RW, loop_closure, OW, beta=0.5)
+    h = out.cpu()
+    assert h.dtype == torch.int32 and h.numel() == 8
+    mm = pops.motionmag_pair(poses, patches, intr, ii, jj, kk, i, j, beta=0.5)
+    assert h[:1].view(torch.float32)[0].item() == float(mm) and np.isfinite(float(mm))
+
+    def rule(src, a, b, nn):
+        rem = src < nn - RW
+        if loop_closure:
+            rem = rem & ~(((b - a) > 30) & (b > nn - OW))
+        return rem
+
+    rem_a = rule(ix[kk], ii, jj, n)
+    assert int(h[1]) == int(rem_a.sum()) and int(h[2]) == int(ii[~rem_a].min())
+    drop = (ii == k) | (jj == k)
+    i2 = ii - (ii > k).long(); j2 = jj - (jj > k).long(); k2 = kk - M * (ii > k).long()
+    rem_b = rule(ix[k2], i2, j2, n - 1) & ~drop
+    keep_b = ~drop & ~rem_b
+    assert int(h[3]) == int(drop.sum()) and int(h[4]) == int(rem_b.sum()) and int(h[5]) == int(i2[keep_b].min())
+    assert 0 < int(h[1]) < E and 0 < int(h[3]) < E and 0 < int(h[4]) < E
+    if loop_closure:                                                             # the exemption is exercised
+        assert int(((ix[kk] < n - RW) & ((jj - ii) > 30) & (jj > n - OW)).sum()) > 0
+    # nothing left alive: the minima read "none"
+    e0 = torch.zeros(0, dtype=torch.int64, device="cuda")
+    h0 = pops.keyframe_plan(poses, patches, intr, e0, e0, e0, ix, i, j, k, n, M, RW, loop_closure, OW).cpu()
+    assert h0[1:6].tolist() == [0, pops.PLAN_NONE, 0, 0, pops.PLAN_NONE] and np.isnan(h0[:1].view(torch.float32)[0].item())
+    # repeatable (it drives a decision and the host's edge counts)
+    assert torch.equal(out[:6], pops.keyframe_plan(poses, patches, intr, ii, jj, kk, ix, i, j, k, n, M, RW, loop_closure, OW)[:6])
+
+
 def test_transform_full_size_vs_oracle_and_lietorch_composition():
     """45,312-edge DPVO graph: against float64, and against Inv/Mul/Act4 of this repo's lietorch
     kernels composed like projective_ops.py:57-68."""

@@ -583,6 +583,8 @@ def main():
                           update_impl=args.update, patchify_impl=args.patchify, pipeline=args.pipeline,
                           cpu_dryrun=args.cpu_dryrun)
         if args.mode == "parity":
+            if hasattr(slam, "verify_plan"):
+                slam.verify_plan = True        # this repo's class: every keyframe() compares its one-read plan with the device counts
             res = run_parity(slam, seq, args.frames, dev=dev)
             import numpy as np
             summary = dict(backend=args.backend, pipeline=args.pipeline, frames=args.frames, final_n=int(res["final_n"]),
