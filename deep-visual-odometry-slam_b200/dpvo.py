@@ -320,9 +320,15 @@ class DPVO:
         if fi.numel() == 0:
             return torch.empty(2, 0, dtype=torch.long, device=dev)
         es, cnt = patchgraph.reduce_edges(flow_mag[mask], fi, fjj, max_num_edges=1000, nms=1, n_frames=self.n + 1)
-        es = es[:int(cnt.item())]
+        # the selection count is a host read (optim_utils.py returns host arrays); the smallest selected source frame
+        # rides along, so that the host's copy of min(ii) stays exact and __run_global_BA needs no read of its own
+        rows = torch.arange(es.shape[0], device=dev) < cnt
+        lo = torch.where(rows, es[:, 0], torch.full_like(es[:, 0], pg.BIG)).min().view(1)
+        c, lo = (int(v) for v in torch.cat([cnt.view(1), lo]).tolist())
+        es = es[:c]
         if es.shape[0] == 0:
             return torch.empty(2, 0, dtype=torch.long, device=dev)
+        self._lc_min_src = lo
         ei = es[:, 0:1].repeat(1, M)
         ej = es[:, 1:2].repeat(1, M)
         kk = ei * M + torch.arange(M, device=dev)
@@ -334,7 +340,7 @@ class DPVO:
         self.pg.edges.append_factors(ii, jj)
         self.pg.E += ii.numel()
         if ii.numel():
-            self.pg.min_ii = min(self.pg.min_ii, self.n - self.cfg.KEYFRAME_INDEX - 1 - 30)
+            self.pg.min_ii = min(self.pg.min_ii, self._lc_min_src)          # exact: read with the selection count
 
     def normalize(self):
         """patchgraph.py:84-96."""
@@ -360,7 +366,9 @@ class DPVO:
         full_jj = torch.cat((pg.jj_inac, pg.jj))
         full_kk = torch.cat((pg.kk_inac, pg.kk))
         self.normalize()
-        t0 = int(pg.ii.min().item())
+        t0 = pg.min_ii                   # = pg.ii.min() (dpvo.py:318): kept exact on the host by keyframe() and the appends
+        if self.verify_plan and t0 != int(pg.ii.min().item()):
+            raise RuntimeError(f"host copy of min(ii) {t0} != device {int(pg.ii.min().item())}")
         fastba.BA(self.poses, self.patches, self.intrinsics, full_target, full_weight, self._lmbda, full_ii, full_jj, full_kk,
                   t0, self.n, M=self.M, iterations=2, eff_impl=True)
         self.ran_global_ba[self.n] = True
@@ -445,7 +453,10 @@ class DPVO:
         r = cfg.PATCH_LIFETIME
         pg.edges.edges_forw(self.n, r)
         pg.edges.edges_back(self.n, r)
-        pg.E += M * (max(self.n - 1, 0) - max(self.n - r, 0)) + M * (self.n - max(self.n - r, 0))
+        added = M * (max(self.n - 1, 0) - max(self.n - r, 0)) + M * (self.n - max(self.n - r, 0))
+        pg.E += added
+        if added:
+            pg.min_ii = min(pg.min_ii, max(self.n - r, 0))                    # sources of the new edges: frames >= n - r
         pg.edges.active.bound = pg.E
         if self.n == 8 and not self.is_initialized:
             self.is_initialized = True
