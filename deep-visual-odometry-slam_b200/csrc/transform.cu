@@ -153,6 +153,7 @@ struct KeyframePlan {
   const int64_t* ix; int64_t n_ix;        // patch -> source frame table
   int64_t k, n, M, removal_window, optimization_window;
   int loop_closure;
+  const int64_t* live_count; const int32_t* info;    // optional: the edge store's device count / error flag, echoed
 };
 
 __device__ __forceinline__ float edge_flow_mean(const TransformArgs& a, int64_t fi, int64_t fj, int64_t kf, float beta) {
@@ -278,6 +279,8 @@ motionmag_pair_kernel(const TransformArgs a, float beta, int64_t fa, int64_t fb,
     if (PLAN) {
       int* oi = reinterpret_cast<int*>(out);
       oi[1] = t5[0]; oi[2] = t5[3]; oi[3] = t5[1]; oi[4] = t5[2]; oi[5] = t5[4];
+      oi[6] = q.live_count ? (int)min(*q.live_count, (int64_t)kPlanNone) : 0;
+      oi[7] = q.info ? *q.info : 0;
     }
   }
   cluster.sync();                       // the other CTAs' shared memory stays alive until CTA 0 has read it
@@ -363,13 +366,14 @@ extern "C" int dpvo_keyframe_plan(const float* poses, const float* patches, cons
                                   int64_t n_edges, int64_t n_frames, int64_t n_patches, int32_t P, float beta,
                                   int64_t frame_a, int64_t frame_b, int64_t k, int64_t n, int64_t patches_per_frame,
                                   int64_t removal_window, int32_t loop_closure, int64_t optimization_window,
-                                  int32_t* out, void* stream) {
+                                  const int64_t* live_count, const int32_t* info, int32_t* out, void* stream) {
   DPVO_REQUIRE(n_edges >= 0 && n_edges < (int64_t(1) << 31) && n_frames > 0 && n_patches > 0 && P > 0 && P <= 8 &&
                patches_per_frame > 0, "keyframe_plan: bad sizes");
   DPVO_REQUIRE(poses && patches && intrinsics && ix && out && (n_edges == 0 || (ii && jj && kk)), "keyframe_plan: null pointer");
   TransformArgs a{poses, patches, intrinsics, ii, jj, kk, n_edges, n_frames, n_patches, P, 0, 0,
                   nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  const KeyframePlan q{ix, n_patches, k, n, patches_per_frame, removal_window, optimization_window, loop_closure ? 1 : 0};
+  const KeyframePlan q{ix, n_patches, k, n, patches_per_frame, removal_window, optimization_window, loop_closure ? 1 : 0,
+                       live_count, info};
   motionmag_pair_kernel<true><<<kMotionCluster, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       a, beta, frame_a, frame_b, q, reinterpret_cast<float*>(out));
   note_launches(1);

@@ -267,10 +267,14 @@ class DPVO:
         k = self.n - cfg.KEYFRAME_INDEX
         plan = pops.keyframe_plan(self.poses, self.patches, self.intrinsics, pg.ii, pg.jj, pg.kk, self.ix, i, j, k, self.n,
                                   self.M, cfg.REMOVAL_WINDOW, bool(cfg.LOOP_CLOSURE), cfg.OPTIMIZATION_WINDOW, beta=0.5,
-                                  out=self._plan_out)
+                                  out=self._plan_out, live_count=pg.edges.active.count_, info=pg.edges.info)
         h = plan.cpu()                                                           # the decision is a host read (dpvo.py:270)
         m = float(h[:1].view(torch.float32)[0])
-        moved_a, min_a, dropped_b, moved_b, min_b = (int(v) for v in h[1:6].tolist())
+        moved_a, min_a, dropped_b, moved_b, min_b, dev_count, info = (int(v) for v in h[1:8].tolist())
+        if info != 0 or dev_count != pg.E:
+            # the host mirrors the edge counts instead of reading them back: fail loudly if the mirror is not true
+            raise RuntimeError(f"patch graph out of sync: device holds {dev_count} live edges, host expects {pg.E}; "
+                               f"edge-kernel flag {info} (1 = a capacity was exceeded, 2 = patch index outside ix)")
         if m / 2 < cfg.KEYFRAME_THRESH:
             t0, t1 = pg.tstamps_[k - 1], pg.tstamps_[k]
             self._add_delta(t1, t0, self._mul(pg.poses_[k:k + 1], self._inv(pg.poses_[k - 1:k])))

@@ -90,21 +90,26 @@ PLAN_NONE = 0x7FFFFFFF
 
 
 def keyframe_plan(poses, patches, intrinsics, ii, jj, kk, ix, i, j, k, n, M, removal_window, loop_closure,
-                  optimization_window, beta=0.5, out=None):
+                  optimization_window, beta=0.5, out=None, live_count=None, info=None):
     """`motionmag_pair` plus a dry run of keyframe()'s edge edits under both outcomes of the test (dpvo.py:266-310):
     int32 [8] device tensor, word 0 = the float32 bits of the motion magnitude, words 1..5 = (moved, min ii) without
-    removal and (dropped, moved, min ii) with frame k removed — see include/dpvo_b200.h `dpvo_keyframe_plan`."""
+    removal and (dropped, moved, min ii) with frame k removed; words 6 / 7 echo the edge store's device count (int64 [1]
+    `live_count`) and error flag (int32 [1] `info`) when given — see include/dpvo_b200.h `dpvo_keyframe_plan`."""
     poses, patches, intrinsics, ii, jj, kk, ix = _prep(poses, patches, intrinsics, ii, jj, kk, ix)
     if ix.numel() != patches.shape[1]:
         raise RuntimeError("projective_ops.keyframe_plan: ix must have one entry per patch")
+    if live_count is not None and (live_count.dtype != torch.int64 or not live_count.is_cuda):
+        raise RuntimeError("projective_ops.keyframe_plan: live_count must be a CUDA int64 tensor")
+    if info is not None and (info.dtype != torch.int32 or not info.is_cuda):
+        raise RuntimeError("projective_ops.keyframe_plan: info must be a CUDA int32 tensor")
     if out is None:
-        out = torch.zeros(8, dtype=torch.int32, device=poses.device)      # words 6, 7 are not written
+        out = torch.zeros(8, dtype=torch.int32, device=poses.device)
     check(lib.dpvo_keyframe_plan(ptr(poses), ptr(patches), ptr(intrinsics), ptr(ii), ptr(jj), ptr(kk), ptr(ix),
                                  c_i64(ii.numel()), c_i64(poses.shape[1]), c_i64(patches.shape[1]),
                                  c_i32(patches.shape[-1]), c_f32(float(beta)), c_i64(int(i)), c_i64(int(j)),
                                  c_i64(int(k)), c_i64(int(n)), c_i64(int(M)), c_i64(int(removal_window)),
-                                 c_i32(1 if loop_closure else 0), c_i64(int(optimization_window)), ptr(out),
-                                 stream_of(poses)), "projective_ops.keyframe_plan")
+                                 c_i32(1 if loop_closure else 0), c_i64(int(optimization_window)), ptr(live_count),
+                                 ptr(info), ptr(out), stream_of(poses)), "projective_ops.keyframe_plan")
     return out
 
 

@@ -369,13 +369,16 @@ int dpvo_motionmag_pair(const float* poses, const float* patches, const float* i
  *   [3] int32  frame k removed: edges touching k (dropped, :280-281)
  *   [4] int32  frame k removed: of the others, renumbered (:283-285), those the window rule moves at frame count n - 1
  *   [5] int32  frame k removed: smallest (renumbered) source frame among the edges that stay (0x7fffffff if none)
+ *   [6] int32  *live_count (the edge store's device count, dpvo_edge_store.count) or 0 when live_count is NULL
+ *   [7] int32  *info (the edge kernels' error flag) or 0 when info is NULL
+ * so a caller that mirrors the count on the host sees in the same read whether the mirror is still true.
  * ix: patch -> source frame table [n_patches] (DPVO.ix).  n_edges: exact live count. */
 int dpvo_keyframe_plan(const float* poses, const float* patches, const float* intrinsics,
                        const int64_t* ii, const int64_t* jj, const int64_t* kk, const int64_t* ix,
                        int64_t n_edges, int64_t n_frames, int64_t n_patches, int32_t P, float beta,
                        int64_t frame_a, int64_t frame_b, int64_t k, int64_t n, int64_t patches_per_frame,
                        int64_t removal_window, int32_t loop_closure, int64_t optimization_window,
-                       int32_t* out, void* stream);
+                       const int64_t* live_count, const int32_t* info, int32_t* out, void* stream);
 
 /* projective_ops.point_cloud (:111-113): points [n,P,P,4] = G_{ix[n]}^-1 * iproj(patches[n], intrinsics[ix[n]]). */
 int dpvo_point_cloud(const float* poses, const float* patches, const float* intrinsics, const int64_t* ix,

@@ -147,6 +147,12 @@ def test_keyframe_plan_counts_match_the_reference_rules(loop_closure):
     assert 0 < int(h[1]) < E and 0 < int(h[3]) < E and 0 < int(h[4]) < E
     if loop_closure:                                                             # the exemption is exercised
         assert int(((ix[kk] < n - RW) & ((jj - ii) > 30) & (jj > n - OW)).sum()) > 0
+    # words 6 / 7 echo the edge store's device count and error flag when the caller passes them
+    assert h[6:8].tolist() == [0, 0]
+    lc_t = torch.tensor([E], dtype=torch.int64, device="cuda"); inf_t = torch.tensor([2], dtype=torch.int32, device="cuda")
+    h2 = pops.keyframe_plan(poses, patches, intr, ii, jj, kk, ix, i, j, k, n, M, RW, loop_closure, OW, live_count=lc_t,
+                            info=inf_t).cpu()
+    assert h2[6:8].tolist() == [E, 2] and torch.equal(h2[:6], h[:6])
     # nothing left alive: the minima read "none"
     e0 = torch.zeros(0, dtype=torch.int64, device="cuda")
     h0 = pops.keyframe_plan(poses, patches, intr, e0, e0, e0, ix, i, j, k, n, M, RW, loop_closure, OW).cpu()
