@@ -190,3 +190,15 @@ def test_viewer_helpers_validation_without_gpu():
     rc = lib.dpvo_viewer_iproj(ctypes.c_int32(3), ctypes.c_int32(2), ctypes.c_float(1.0), null, null, null, null,
                                ctypes.c_int32(4), ctypes.c_int32(4), null, null, null, null)
     assert rc != 0 and b"index" in lib.dpvo_last_error()
+
+
+def test_harness_teacher_library_exports_its_entry_point():
+    """tools/libteacher.so (tools/teacher_kernel.cu, built by __graft_entry__.build()) is HARNESS code — the sequence
+    measurements' ground-truth teacher in one launch, used by every arm — and tools/refdpvo.py falls back to its torch
+    formulation when the library is absent; when it is there it must export what the harness binds."""
+    import ctypes
+    path = os.path.join(ROOT, "tools", "libteacher.so")
+    if not os.path.exists(path):
+        pytest.skip("tools/libteacher.so not built (python -c 'import __graft_entry__ as g; g.build()')")
+    lib = ctypes.CDLL(path)
+    assert hasattr(lib, "teacher_targets")
