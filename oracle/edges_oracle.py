@@ -78,6 +78,36 @@ class Edges:
         self.remove_factors(to_remove, store=True)
 
 
+def keyframe_plan_counts(ix, M, ii, jj, kk, k, n, removal_window, loop_closure=False, optimization_window=0):
+    """What DPVO.keyframe() (dpvo.py:272-310) does to the edge list under BOTH outcomes of its test, as a formula
+    evaluated directly on the list (this is what the product's one-read `dpvo_keyframe_plan` must return; the test
+    suite checks it against the methods above, which are pinned to the reference's own run):
+      no removal:       moved_a  = edges the window rule (:304-309) moves to the inactive list at frame count n,
+                        min_a    = smallest source frame that stays (None if nothing stays)
+      frame k removed:  dropped_b = edges touching k (:280-281); the others are renumbered (:283-285) and
+                        moved_b  = those the window rule moves at frame count n - 1,  min_b as above.
+    Returns (moved_a, min_a, dropped_b, moved_b, min_b)."""
+    ix = np.asarray(ix, dtype=np.int64)
+    ii, jj, kk = (np.asarray(x, dtype=np.int64) for x in (ii, jj, kk))
+
+    def rule(src, a, b, nn):
+        rem = src < nn - removal_window
+        if loop_closure:
+            rem = rem & ~(((b - a) > 30) & (b > (nn - optimization_window)))
+        return rem
+
+    rem_a = rule(ix[kk], ii, jj, n)
+    min_a = int(ii[~rem_a].min()) if (~rem_a).any() else None
+    drop = (ii == k) | (jj == k)
+    i2, j2, k2 = ii[~drop].copy(), jj[~drop].copy(), kk[~drop].copy()
+    k2[i2 > k] -= M
+    i2[i2 > k] -= 1
+    j2[j2 > k] -= 1
+    rem_b = rule(ix[k2], i2, j2, n - 1)
+    min_b = int(i2[~rem_b].min()) if (~rem_b).any() else None
+    return int(rem_a.sum()), min_a, int(drop.sum()), int(rem_b.sum()), min_b
+
+
 def frames_shift(buf, k, n, mod=None):
     """dpvo.py:287-297: for i in range(k, n-1): buf[i % mod] = buf[(i+1) % mod] (in place, in order)."""
     mod = buf.shape[0] if mod is None else mod

@@ -361,6 +361,55 @@ def test_edges_oracle_vs_reference(name, seed, lc):
     assert edges_replay.replay(_OracleEdges(m, seed), name, seed, lc) == 14
 
 
+class _PlanCheckingEdges(_OracleEdges):
+    """The replayed oracle, with `edges_oracle.keyframe_plan_counts` evaluated BEFORE every keyframe() edit and compared
+    with what the (reference-pinned) edits then do: the plan's counts for the outcome that is taken must be exact."""
+
+    def __init__(self, m, seed):
+        super().__init__(m, seed)
+        self.pending, self.checked = None, [0, 0]
+
+    def _plan(self, k, n, lc, ow):
+        c = self.m.CFG
+        return self.eo.keyframe_plan_counts(self.e.ix, self.e.M, self.e.ii, self.e.jj, self.e.kk, k, n,
+                                            c["REMOVAL_WINDOW"], lc, ow)
+
+    def remove_frame(self, k):
+        n = k + self.m.CFG["KEYFRAME_INDEX"]
+        # the loop-closure flag is not known here: both plans are kept, remove_old picks the one that applies
+        self.pending = (k, n, self.e.ii.size)
+        self.before = (self.e.ii.copy(), self.e.jj.copy(), self.e.kk.copy())
+        super().remove_frame(k)
+
+    def remove_old(self, n, window, lc, ow):
+        if self.pending is not None:
+            k, n0, size0 = self.pending
+            assert n0 - 1 == n
+            ii, jj, kk = self.before
+            _, _, dropped, moved, mn = self.eo.keyframe_plan_counts(self.e.ix, self.e.M, ii, jj, kk, k, n0, window, lc, ow)
+            assert size0 - self.e.ii.size == dropped
+            self.pending = None
+            self.checked[1] += 1
+        else:
+            moved, mn, _, _, _ = self._plan(n - self.m.CFG["KEYFRAME_INDEX"], n, lc, ow)
+            self.checked[0] += 1
+        size, inac = self.e.ii.size, self.e.ii_inac.size
+        super().remove_old(n, window, lc, ow)
+        assert size - self.e.ii.size == moved and self.e.ii_inac.size - inac == moved
+        assert (int(self.e.ii.min()) if self.e.ii.size else None) == mn
+
+
+@pytest.mark.parametrize("name,seed,lc", [("plain", 0, False), ("loop", 1, True)])
+def test_keyframe_plan_oracle_vs_reference_sequence(name, seed, lc):
+    """`edges_oracle.keyframe_plan_counts` (the expected output of the product's one-read keyframe plan) on the scripted
+    sequence whose every state is the reference's own (tests/golden/ref_cpu_edges.npz): both outcomes occur."""
+    import edges_replay
+    m = edges_replay.golden_module()
+    impl = _PlanCheckingEdges(m, seed)
+    edges_replay.replay(impl, name, seed, lc)
+    assert impl.checked[0] > 0 and impl.checked[1] > 0, impl.checked
+
+
 def test_reduce_edges_oracle_vs_reference():
     import edges_replay
     from oracle import edges_oracle as eo

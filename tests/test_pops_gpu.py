@@ -145,6 +145,11 @@ def test_keyframe_plan_counts_match_the_reference_rules(loop_closure):
     keep_b = ~drop & ~rem_b
     assert int(h[3]) == int(drop.sum()) and int(h[4]) == int(rem_b.sum()) and int(h[5]) == int(i2[keep_b].min())
     assert 0 < int(h[1]) < E and 0 < int(h[3]) < E and 0 < int(h[4]) < E
+    # ... and the oracle's restatement, pinned on CPU to the reference-run sequence (tests/test_oracle_cpu.py)
+    from oracle import edges_oracle as eo
+    want = eo.keyframe_plan_counts(ix.cpu().numpy(), M, ii.cpu().numpy(), jj.cpu().numpy(), kk.cpu().numpy(), k, n, RW,
+                                   loop_closure, OW)
+    assert [int(v) for v in h[1:6]] == [pops.PLAN_NONE if v is None else v for v in want]
     if loop_closure:                                                             # the exemption is exercised
         assert int(((ix[kk] < n - RW) & ((jj - ii) > 30) & (jj > n - OW)).sum()) > 0
     # words 6 / 7 echo the edge store's device count and error flag when the caller passes them
